@@ -1,0 +1,82 @@
+// Internal declarations shared by the kernels and the C ABI (not installed).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include "../../include/splat_cuda.h"
+
+#define SPLAT_MAX_SORT_PASSES 8
+#define SORT_TILE_KEYS 4096          // keys per onesweep tile (256 threads x 16)
+#define SCAN_TILE_ITEMS 1024         // splats per scan/duplicate tile (256 threads x 4)
+
+// Per-frame uniforms: role of the reference's Uniforms buffer
+// (shaders/gaussian_splat_tile.metal:16-21, src/instanced_splat_renderer.mm:456-469),
+// passed as a kernel argument so several frames can be in flight on one stream.
+struct FrameUniforms {
+    float V[16], P[16], VP[16];
+    float W, H;
+    int w, h, tiles_x, tiles_y, row_begin, row_end;
+    int mode, order, K, sh_degree;
+    float cam[3];
+    unsigned int n;
+};
+
+// Device control block, zeroed by one memsetAsync at the start of every frame.
+struct FrameCtl {
+    unsigned long long total_pairs;   // D (exact even when it exceeds capacity)
+    unsigned int overflow;
+    unsigned int scan_ticket;
+    unsigned int sort_ticket[SPLAT_MAX_SORT_PASSES];
+    unsigned int pad[6];
+    unsigned int hist[SPLAT_MAX_SORT_PASSES][256];
+};
+
+// SoA planes written once by splat_upload (AoS SplatInstance -> SoA).
+struct ScenePlanes {
+    const float4* rot;        // w x y z
+    const float4* pos_sx;     // position.xyz, scale.x
+    const float4* syz_op_rg;  // scale.y, scale.z, opacity, bits(half2(r, g))
+    const uint16_t* b;        // half(b)
+    const float* sh;          // [n][45] or nullptr
+};
+
+struct SortPlan {
+    int n_pass;
+    int shift[SPLAT_MAX_SORT_PASSES];
+};
+
+// Epoch-tagged 64-bit lookback word: [63:34] epoch, [33:32] flag, [31:0] value.
+// Stale words from earlier launches never match the current epoch, so the
+// status arrays are never cleared.
+#define LB_FLAG_AGG 1ull
+#define LB_FLAG_INC 2ull
+__device__ __forceinline__ unsigned long long lb_pack(unsigned int epoch, unsigned long long flag, unsigned int v) {
+    return ((unsigned long long)epoch << 34) | (flag << 32) | v;
+}
+__device__ __forceinline__ unsigned long long lb_load(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void lb_store(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// Launchers (each enqueues on `s` and returns).
+void launch_upload_soa(const float* aos_dev, unsigned int n, float4* rot, float4* pos_sx, float4* syz_op_rg,
+                       uint16_t* b, cudaStream_t s);
+void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record* rec, unsigned int* touched,
+                       cudaStream_t s);
+void launch_scan_duplicate(const FrameUniforms& U, const splat_record* rec, const unsigned int* touched,
+                           unsigned int* offsets, unsigned long long* keys, unsigned int* vals,
+                           unsigned long long capacity, FrameCtl* ctl, unsigned long long* scan_status,
+                           unsigned int epoch, SortPlan plan, int sm_count, cudaStream_t s);
+// Sorts n = *d_n (device) pairs; result buffer index (0 = in, 1 = alt) is n_pass & 1.
+void launch_radix_sort(unsigned long long* keys, unsigned int* vals, unsigned long long* keys_alt,
+                       unsigned int* vals_alt, const unsigned long long* d_n, unsigned long long capacity,
+                       FrameCtl* ctl, bool hist_ready, unsigned long long* sort_status, unsigned int epoch_base,
+                       SortPlan plan, int sm_count, cudaStream_t s);
+void launch_tile_ranges(const unsigned long long* keys_sorted, const unsigned long long* d_n,
+                        unsigned long long capacity, uint2* ranges, int sm_count, cudaStream_t s);
+void launch_blend(const FrameUniforms& U, const splat_record* rec, const unsigned int* vals_sorted,
+                  const uint2* ranges, void* fb_half4, cudaStream_t s);

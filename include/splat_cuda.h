@@ -1,0 +1,142 @@
+/* libsplat_cuda — C ABI of the B200 splat rasteriser (sm_100a).
+ *
+ * This is the drop-in boundary for the reference's splat hot path. Where the
+ * reference binds Metal buffers/textures and encodes passes
+ * (src/instanced_splat_renderer.mm:399-422 upload, :424-528 render,
+ * :491-494,507-509 binding table), a host binds these entry points instead.
+ * Plain pointers and sizes only; no C++/torch types. All functions return 0 on
+ * success or a negative SPLAT_ERR_* code; splat_last_error_string() explains.
+ * File:line citations are relative to the reference repository root.
+ */
+#ifndef SPLAT_CUDA_H
+#define SPLAT_CUDA_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPLAT_TILE 16
+
+enum { SPLAT_OK = 0, SPLAT_ERR_ARG = -1, SPLAT_ERR_CUDA = -2, SPLAT_ERR_OVERFLOW = -3, SPLAT_ERR_STATE = -4 };
+
+/* Renderer mode: which reference shader's per-pixel rule is applied. */
+enum {
+    SPLAT_MODE_TILE    = 0, /* shaders/gaussian_splat_tile.metal:178-267  (K = 32; 24 per gaussian_splat_types.h:10) */
+    SPLAT_MODE_LAYER50 = 1  /* shaders/gaussian_splat_50layer.metal:149-223 (K = 50) */
+};
+/* Depth order of the per-pixel sort. */
+enum {
+    SPLAT_ORDER_NEAR_FIRST = 0, /* ascending zFront: what the shader comments intend    */
+    SPLAT_ORDER_REFERENCE  = 1  /* descending zFront: what the shader code literally does
+                                   (gaussian_splat_tile.metal:244, 50layer.metal:201)  */
+};
+enum { SPLAT_FLAG_TIMING = 1 /* record per-stage CUDA events (adds event overhead) */ };
+
+/* Mirrors src/instanced_splat_renderer.h:6-11 (56 bytes, no padding). */
+typedef struct {
+    float rotation[4]; /* w x y z */
+    float scale[3];
+    float position[3];
+    float color[4];    /* r g b opacity */
+} SplatInstancePOD;
+
+/* Mirrors shaders/gaussian_splat_types.h:13-17 / gaussian_splat_tile.metal:160-164:
+ * the author's 10-byte fragment node (5 halfs). Kept for layout parity; per-pixel
+ * lists never leave the chip in this implementation. */
+typedef struct { uint16_t depth, color[3], alpha; } SplatFragmentPOD;
+
+typedef struct {
+    int32_t mode;           /* SPLAT_MODE_*                                             */
+    int32_t max_fragments;  /* K: 1..64 (reference values 24 / 32 / 50); 0 = mode default */
+    int32_t order;          /* SPLAT_ORDER_*                                            */
+    int32_t sh_degree;      /* 0 = reference parity (src/ply_loader.cpp:9-20); 1..3 extension */
+    int32_t tile_row_begin; /* band of tile rows rendered on this device: [begin, end)  */
+    int32_t tile_row_end;   /* <= 0: all rows                                           */
+    int32_t flags;          /* SPLAT_FLAG_*                                             */
+    int32_t reserved;
+} splat_opts;
+
+/* 48-byte per-splat record produced by the preprocess kernel (debug fetch). */
+typedef struct {
+    float cx, cy, ux, uy, vx, vy, opacity;
+    uint32_t rg, bd;
+    float z_front;
+    uint32_t rect_lo, rect_hi;
+} splat_record;
+
+typedef struct {
+    uint32_t n_splats, n_visible_unused;
+    uint64_t n_pairs;       /* D of the last completed frame                            */
+    uint64_t pair_capacity;
+    uint32_t overflow;      /* 1 if D exceeded capacity (frame truncated; see splat_frame_status) */
+    uint32_t sort_passes;
+} splat_status;
+
+typedef struct splat_ctx splat_ctx;
+
+/* Replaces MTLCreateSystemDefaultDevice + pipeline creation
+ * (src/metal_renderer.mm:42-53, src/instanced_splat_renderer.mm:40-222). */
+int splat_create(int device, splat_ctx** out);
+int splat_destroy(splat_ctx* ctx);
+
+/* Replaces newBufferWithBytes(_instances) (src/instanced_splat_renderer.mm:410-419).
+ * aos_host: n SplatInstancePOD records in host memory; converted to SoA planes on the device. */
+int splat_upload(splat_ctx* ctx, const void* aos_host, uint32_t n);
+/* Extension: f_rest coefficients parsed by src/ply_loader.cpp:76-81,125-127. */
+int splat_upload_sh(splat_ctx* ctx, const float* sh_rest45_host, uint32_t n, int degree);
+
+/* Replaces InstancedSplatRenderer::render (src/instanced_splat_renderer.mm:424-528).
+ * stream: cudaStream_t (role of the MTLCommandBuffer); fb_half4_dev: device pointer to
+ * w*h half4 (role of the drawable). Enqueues and returns without synchronising, exactly as
+ * the reference only encodes. view/proj: column-major float[16] (simd_float4x4). */
+int splat_render(splat_ctx* ctx, void* stream, void* fb_half4_dev,
+                 const float* view16, const float* proj16, int w, int h, const splat_opts* opts);
+/* Same, end to end with HOST buffers: uniforms from host, framebuffer copied back to
+ * fb_half4_host (pinned or pageable), synchronises, and transparently re-renders if the
+ * pair buffers overflowed. */
+int splat_render_host(splat_ctx* ctx, void* fb_half4_host,
+                      const float* view16, const float* proj16, int w, int h, const splat_opts* opts);
+/* Camera-batch: n_views frames, fb_dev[i] device pointers, view/proj 16 floats each. */
+int splat_render_batch(splat_ctx* ctx, void* stream, void* const* fb_half4_dev,
+                       const float* views16, const float* projs16, int n_views, int w, int h,
+                       const splat_opts* opts);
+
+/* After the stream has been synchronised: D, capacity and overflow of the last frame.
+ * If overflow is set the buffers have been grown; render the frame again. */
+int splat_frame_status(splat_ctx* ctx, splat_status* out);
+
+/* Intermediate stages of the last frame, for bit-exact tests. Synchronises the device.
+ * *bytes: in = capacity of host_dst, out = bytes written (or needed if host_dst is NULL). */
+enum {
+    SPLAT_FETCH_RECORDS = 0,     /* splat_record[n]  (culled entries zeroed)  */
+    SPLAT_FETCH_TILES_TOUCHED,   /* uint32[n]                                 */
+    SPLAT_FETCH_OFFSETS,         /* uint32[n] exclusive scan                  */
+    SPLAT_FETCH_KEYS_UNSORTED,   /* uint64[D]  (re-derived: runs duplication again) */
+    SPLAT_FETCH_VALS_UNSORTED,   /* uint32[D]                                 */
+    SPLAT_FETCH_KEYS_SORTED,     /* uint64[D]                                 */
+    SPLAT_FETCH_VALS_SORTED,     /* uint32[D]                                 */
+    SPLAT_FETCH_TILE_RANGES      /* uint32[T][2]                              */
+};
+int splat_debug_fetch(splat_ctx* ctx, int what, void* host_dst, size_t* bytes);
+
+/* ms of the last frame rendered with SPLAT_FLAG_TIMING:
+ * [0] preprocess [1] scan+duplicate [2] sort [3] ranges [4] blend [5] total. Synchronises. */
+int splat_stage_times(splat_ctx* ctx, float ms[8]);
+
+/* Stand-alone stable LSD radix sort of (uint64 key, uint32 value) pairs on device
+ * buffers (the "sort HBM GB/s" metric). Sorts bits [begin_bit, end_bit) in 8-bit
+ * digits; *_alt are scratch of the same size. On return *result_in_alt tells which
+ * buffer pair holds the sorted data. Enqueues on stream. */
+int splat_sort_pairs_u64_u32(splat_ctx* ctx, void* stream, uint64_t* keys, uint32_t* vals,
+                             uint64_t* keys_alt, uint32_t* vals_alt, uint64_t n,
+                             int begin_bit, int end_bit, int* result_in_alt);
+
+const char* splat_last_error_string(void);
+int splat_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
