@@ -1,0 +1,159 @@
+"""ctypes binding of libsplat_cuda.so (include/splat_cuda.h).
+
+The library is the product; this file only marshals pointers.  There is no CPU
+fallback: if the CUDA library is missing or fails, every call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsplat_cuda.so")
+
+MODE_TILE, MODE_LAYER50 = 0, 1
+ORDER_NEAR_FIRST, ORDER_REFERENCE = 0, 1
+FLAG_TIMING, FLAG_KEEP_UNSORTED = 1, 2
+(FETCH_RECORDS, FETCH_TILES_TOUCHED, FETCH_OFFSETS, FETCH_KEYS_UNSORTED, FETCH_VALS_UNSORTED,
+ FETCH_KEYS_SORTED, FETCH_VALS_SORTED, FETCH_TILE_RANGES) = range(8)
+
+RECORD_DTYPE = np.dtype([
+    ("cx", "<f4"), ("cy", "<f4"), ("ux", "<f4"), ("uy", "<f4"), ("vx", "<f4"), ("vy", "<f4"),
+    ("opacity", "<f4"), ("rg", "<u4"), ("bd", "<u4"), ("z_front", "<f4"),
+    ("rect_lo", "<u4"), ("rect_hi", "<u4")])
+
+EXPORTS = [
+    "splat_create", "splat_destroy", "splat_upload", "splat_upload_sh", "splat_render",
+    "splat_render_host", "splat_render_batch", "splat_frame_status", "splat_debug_fetch",
+    "splat_stage_times", "splat_sort_pairs_u64_u32", "splat_last_error_string", "splat_version",
+]
+
+
+class SplatOpts(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in (
+        "mode", "max_fragments", "order", "sh_degree", "tile_row_begin", "tile_row_end", "flags", "reserved")]
+
+
+class SplatStatus(C.Structure):
+    _fields_ = [("n_splats", C.c_uint32), ("n_visible_unused", C.c_uint32), ("n_pairs", C.c_uint64),
+                ("pair_capacity", C.c_uint64), ("overflow", C.c_uint32), ("sort_passes", C.c_uint32)]
+
+
+class SplatError(RuntimeError):
+    pass
+
+
+_LIB = None
+
+
+def lib():
+    """Load libsplat_cuda.so (fails loudly if it has not been built)."""
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise SplatError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                             "(there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        vp = C.c_void_p
+        L.splat_create.argtypes = [C.c_int, C.POINTER(vp)]
+        L.splat_destroy.argtypes = [vp]
+        L.splat_upload.argtypes = [vp, vp, C.c_uint32]
+        L.splat_upload_sh.argtypes = [vp, vp, C.c_uint32, C.c_int]
+        L.splat_render.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.POINTER(SplatOpts)]
+        L.splat_render_host.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.POINTER(SplatOpts)]
+        L.splat_render_batch.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.POINTER(SplatOpts)]
+        L.splat_frame_status.argtypes = [vp, C.POINTER(SplatStatus)]
+        L.splat_debug_fetch.argtypes = [vp, C.c_int, vp, C.POINTER(C.c_size_t)]
+        L.splat_stage_times.argtypes = [vp, C.POINTER(C.c_float)]
+        L.splat_sort_pairs_u64_u32.argtypes = [vp, vp, vp, vp, vp, vp, C.c_uint64, C.c_int, C.c_int,
+                                               C.POINTER(C.c_int)]
+        L.splat_last_error_string.restype = C.c_char_p
+        L.splat_version.restype = C.c_int
+        _LIB = L
+    return _LIB
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise SplatError(f"{what} failed ({rc}): {lib().splat_last_error_string().decode()}")
+
+
+def make_opts(mode=MODE_TILE, max_fragments=0, order=ORDER_NEAR_FIRST, sh_degree=0,
+              tile_row_begin=0, tile_row_end=0, flags=0):
+    return SplatOpts(mode, max_fragments, order, sh_degree, tile_row_begin, tile_row_end, flags, 0)
+
+
+_FETCH_DTYPE = {FETCH_RECORDS: RECORD_DTYPE, FETCH_TILES_TOUCHED: np.uint32, FETCH_OFFSETS: np.uint32,
+                FETCH_KEYS_UNSORTED: np.uint64, FETCH_VALS_UNSORTED: np.uint32, FETCH_KEYS_SORTED: np.uint64,
+                FETCH_VALS_SORTED: np.uint32, FETCH_TILE_RANGES: np.uint32}
+
+
+class Context:
+    """One splat_ctx = one CUDA device."""
+
+    def __init__(self, device: int = 0):
+        self._h = C.c_void_p()
+        _check(lib().splat_create(device, C.byref(self._h)), "splat_create")
+        self.device = device
+        self.n = 0
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib().splat_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def upload(self, instances: np.ndarray):
+        a = np.ascontiguousarray(instances, np.float32).reshape(-1, 14)
+        _check(lib().splat_upload(self._h, a.ctypes.data, a.shape[0]), "splat_upload")
+        self.n = a.shape[0]
+
+    def upload_sh(self, sh_rest: np.ndarray, degree: int):
+        a = np.ascontiguousarray(sh_rest, np.float32).reshape(-1, 45)
+        _check(lib().splat_upload_sh(self._h, a.ctypes.data, a.shape[0], degree), "splat_upload_sh")
+
+    def render(self, stream_ptr: int, fb_dev_ptr: int, view, proj, w: int, h: int, opts: SplatOpts | None = None):
+        v = np.ascontiguousarray(view, np.float32); p = np.ascontiguousarray(proj, np.float32)
+        _check(lib().splat_render(self._h, stream_ptr, fb_dev_ptr, v.ctypes.data, p.ctypes.data, w, h,
+                                  C.byref(opts) if opts is not None else None), "splat_render")
+
+    def render_host(self, fb_host_ptr: int, view, proj, w: int, h: int, opts: SplatOpts | None = None):
+        v = np.ascontiguousarray(view, np.float32); p = np.ascontiguousarray(proj, np.float32)
+        _check(lib().splat_render_host(self._h, fb_host_ptr, v.ctypes.data, p.ctypes.data, w, h,
+                                       C.byref(opts) if opts is not None else None), "splat_render_host")
+
+    def render_batch(self, stream_ptr: int, fb_dev_ptrs, views, projs, w: int, h: int, opts=None):
+        n = len(fb_dev_ptrs)
+        arr = (C.c_void_p * n)(*fb_dev_ptrs)
+        v = np.ascontiguousarray(views, np.float32).reshape(n, 16)
+        p = np.ascontiguousarray(projs, np.float32).reshape(n, 16)
+        _check(lib().splat_render_batch(self._h, stream_ptr, arr, v.ctypes.data, p.ctypes.data, n, w, h,
+                                        C.byref(opts) if opts is not None else None), "splat_render_batch")
+
+    def status(self) -> SplatStatus:
+        s = SplatStatus()
+        _check(lib().splat_frame_status(self._h, C.byref(s)), "splat_frame_status")
+        return s
+
+    def fetch(self, what: int) -> np.ndarray:
+        nbytes = C.c_size_t(0)
+        _check(lib().splat_debug_fetch(self._h, what, None, C.byref(nbytes)), "splat_debug_fetch")
+        dt = np.dtype(_FETCH_DTYPE[what])
+        out = np.zeros(nbytes.value // dt.itemsize, dt)
+        if nbytes.value:
+            _check(lib().splat_debug_fetch(self._h, what, out.ctypes.data, C.byref(nbytes)), "splat_debug_fetch")
+        return out.reshape(-1, 2) if what == FETCH_TILE_RANGES else out
+
+    def stage_times(self):
+        ms = (C.c_float * 8)()
+        _check(lib().splat_stage_times(self._h, ms), "splat_stage_times")
+        return dict(zip(("preprocess", "scan_duplicate", "sort", "ranges", "blend", "total"), list(ms)[:6]))
+
+    def sort_pairs(self, stream_ptr, keys_ptr, vals_ptr, keys_alt_ptr, vals_alt_ptr, n, begin_bit=0, end_bit=64):
+        res = C.c_int(0)
+        _check(lib().splat_sort_pairs_u64_u32(self._h, stream_ptr, keys_ptr, vals_ptr, keys_alt_ptr, vals_alt_ptr,
+                                              n, begin_bit, end_bit, C.byref(res)), "splat_sort_pairs_u64_u32")
+        return res.value

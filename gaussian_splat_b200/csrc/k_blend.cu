@@ -1,0 +1,179 @@
+// K4 tile ranges and K5 per-16x16-tile blend.
+// K5 folds the reference's fragment stage and per-pixel sort+composite into one kernel:
+//   TILE    fragment_main + tile_sort_composite   shaders/gaussian_splat_tile.metal:178-267
+//   LAYER50 fragment_accumulate + compute_sort_composite
+//                                                 shaders/gaussian_splat_50layer.metal:149-223
+// Per-pixel fragment lists never touch HBM (the reference keeps 504 B/pixel there and
+// clears it every frame, src/instanced_splat_renderer.mm:256-262,475-477).
+#include "splat_math.cuh"
+
+// ------------------------------------------------------------------ K4
+// ranges[t] = [lower_bound(t << 32), lower_bound((t+1) << 32)); empty tiles -> (0,0).
+__device__ __forceinline__ unsigned int key_lower_bound(const unsigned long long* __restrict__ keys, unsigned int n,
+                                                        unsigned long long x) {
+    unsigned int lo = 0, hi = n;
+    while (lo < hi) { const unsigned int mid = lo + ((hi - lo) >> 1); if (__ldg(keys + mid) < x) lo = mid + 1; else hi = mid; }
+    return lo;
+}
+
+__global__ void __launch_bounds__(128) tile_ranges_kernel(const unsigned long long* __restrict__ keys,
+                                                          const FrameCtl* __restrict__ ctl, unsigned int n_tiles,
+                                                          uint2* __restrict__ ranges)
+{
+    const unsigned int t = blockIdx.x * 128u + threadIdx.x;
+    if (t >= n_tiles) return;
+    if (ctl->overflow) { ranges[t] = make_uint2(0, 0); return; }
+    const unsigned int n = ctl->n_sort;
+    const unsigned int b = key_lower_bound(keys, n, (unsigned long long)t << 32);
+    const unsigned int e = key_lower_bound(keys, n, (unsigned long long)(t + 1) << 32);
+    ranges[t] = b < e ? make_uint2(b, e) : make_uint2(0, 0);
+}
+
+void launch_tile_ranges(const unsigned long long* keys_sorted, const FrameCtl* ctl, unsigned int n_tiles,
+                        uint2* ranges, cudaStream_t s)
+{
+    tile_ranges_kernel<<<(n_tiles + 127) / 128, 128, 0, s>>>(keys_sorted, ctl, n_tiles, ranges);
+}
+
+// ------------------------------------------------------------------ K5
+#define BLEND_THREADS 256
+#define BLEND_BATCH 256
+
+__device__ __forceinline__ unsigned short hbits(__half h) { return __half_as_ushort(h); }
+
+// Thread -> pixel mapping: a warp covers an 8x4 pixel block (better splat coherence than 16x2).
+__device__ __forceinline__ void pixel_of_thread(int& lx, int& ly) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    lx = (warp & 1) * 8 + (lane & 7);
+    ly = (warp >> 1) * 4 + (lane >> 3);
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
+    const __grid_constant__ FrameUniforms U, const splat_record* __restrict__ rec,
+    const unsigned int* __restrict__ vals, const uint2* __restrict__ ranges, const FrameCtl* __restrict__ ctl,
+    uint2* __restrict__ fb)
+{
+    __shared__ float4 s_a[BLEND_BATCH];      // cx cy ux uy
+    __shared__ float4 s_b[BLEND_BATCH];      // vx vy opacity rg
+    __shared__ unsigned int s_c[BLEND_BATCH];// bd
+    extern __shared__ unsigned int s_list[]; // LAYER50: [K][256] key|vis, [K][256] rg, [K][256] b (as u32)
+
+    const int tx = blockIdx.x, ty = U.row_begin + blockIdx.y;
+    const unsigned int tile = (unsigned int)(ty * U.tiles_x + tx);
+    int lx, ly; pixel_of_thread(lx, ly);
+    const int pi = tx * 16 + lx, pj = ty * 16 + ly;
+    const bool inside = pi < U.w && pj < U.h;
+    const float pxc = (float)pi + 0.5f, pyc = (float)pj + 0.5f;
+    const uint2 range = ctl->overflow ? make_uint2(0, 0) : ranges[tile];
+    const int K = U.K;
+    const unsigned int tid = threadIdx.x;
+
+    __half aR = __ushort_as_half(0), aG = aR, aB = aR;
+    const __half h_one = __ushort_as_half(0x3C00);
+    __half acc = (MODE == SPLAT_MODE_LAYER50) ? h_one : __ushort_as_half(0);
+    int cnt = 0;
+    bool done = !inside;
+
+    for (unsigned int b0 = range.x; b0 < range.y; b0 += BLEND_BATCH) {
+        const unsigned int nb = min((unsigned int)BLEND_BATCH, range.y - b0);
+        if (tid < nb) {
+            const unsigned int si = __ldg(vals + b0 + tid);
+            const float4* r = reinterpret_cast<const float4*>(rec + si);
+            s_a[tid] = __ldg(r);
+            s_b[tid] = __ldg(r + 1);
+            s_c[tid] = __float_as_uint(__ldg(reinterpret_cast<const float*>(r + 2)));
+        }
+        __syncthreads();
+        if (!done) {
+            for (unsigned int e = 0; e < nb; ++e) {
+                const float4 A = s_a[e];
+                const float dx = pxc - A.x, dy = pyc - A.y;
+                const float4 B = s_b[e];
+                const float u = fmaf(dx, A.z, dy * A.w);
+                const float v = fmaf(dx, B.x, dy * B.y);
+                const float q = fmaf(u, u, v * v);
+                if (!(fabsf(u) <= 3.0f && fabsf(v) <= 3.0f && q <= 9.2103404f)) continue;
+                const float alpha = exp_neg_half(q) * B.z;
+                const unsigned int rg = __float_as_uint(B.w), bd = s_c[e];
+                const __half cr = __ushort_as_half((unsigned short)(rg & 0xFFFFu));
+                const __half cg = __ushort_as_half((unsigned short)(rg >> 16));
+                const __half cb = __ushort_as_half((unsigned short)(bd & 0xFFFFu));
+                if (MODE == SPLAT_MODE_TILE) {
+                    // gaussian_splat_tile.metal:252-264, each half op rounded separately (D7)
+                    const __half ah = __float2half_rn(alpha);
+                    const __half src = __hmul_rn(ah, __hsub_rn(h_one, acc));
+                    aR = __hadd_rn(aR, __hmul_rn(cr, src));
+                    aG = __hadd_rn(aG, __hmul_rn(cg, src));
+                    aB = __hadd_rn(aB, __hmul_rn(cb, src));
+                    acc = __hadd_rn(acc, src);
+                    ++cnt;
+                    if (__hge(acc, __ushort_as_half(0x3BEB)) || cnt >= K) { done = true; break; }
+                } else {
+                    // gaussian_splat_50layer.metal:170-176: first K arrivals (instance order) kept
+                    const unsigned int h = bd >> 16;
+                    const unsigned int dk = U.order == SPLAT_ORDER_REFERENCE ? (0xFFFFu - h) : h;
+                    const unsigned int vis = hbits(__float2half_rn(1.0f - alpha));
+                    s_list[(0 * K + cnt) * BLEND_THREADS + tid] = (dk << 16) | vis;
+                    s_list[(1 * K + cnt) * BLEND_THREADS + tid] = rg;
+                    s_list[(2 * K + cnt) * BLEND_THREADS + tid] = bd & 0xFFFFu;
+                    if (++cnt >= K) { done = true; break; }
+                }
+            }
+        }
+        if (__syncthreads_and(done)) break;
+    }
+
+    if (!inside) return;
+    uint2 out;
+    if (MODE == SPLAT_MODE_TILE) {
+        out.x = (unsigned int)hbits(aR) | ((unsigned int)hbits(aG) << 16);
+        out.y = (unsigned int)hbits(aB) | ((unsigned int)hbits(acc) << 16);
+    } else if (cnt == 0) {
+        out = make_uint2(0, 0);
+    } else {
+        // gaussian_splat_50layer.metal:198-220. The stable descending insertion sort equals an
+        // ascending order on (depth key, arrival slot); walk it by repeated selection so an
+        // early exit (accumVis < 0.01h) skips the rest of the sort.
+        unsigned int last = 0;      // (dk << 8 | slot) + 1 of the previous pick
+        for (int step = 0; step < cnt; ++step) {
+            unsigned int best = 0xFFFFFFFFu;
+            for (int s = 0; s < cnt; ++s) {
+                const unsigned int kk = ((s_list[(0 * K + s) * BLEND_THREADS + tid] >> 16) << 8 | (unsigned int)s) + 1u;
+                if (kk > last && kk < best) best = kk;
+            }
+            last = best;
+            const int s = (int)((best - 1u) & 0xFFu);
+            const unsigned int w0 = s_list[(0 * K + s) * BLEND_THREADS + tid];
+            const unsigned int rg = s_list[(1 * K + s) * BLEND_THREADS + tid];
+            const unsigned int bb = s_list[(2 * K + s) * BLEND_THREADS + tid];
+            aR = __hadd_rn(aR, __hmul_rn(__ushort_as_half((unsigned short)(rg & 0xFFFFu)), acc));
+            aG = __hadd_rn(aG, __hmul_rn(__ushort_as_half((unsigned short)(rg >> 16)), acc));
+            aB = __hadd_rn(aB, __hmul_rn(__ushort_as_half((unsigned short)bb), acc));
+            acc = __hmul_rn(acc, __ushort_as_half((unsigned short)(w0 & 0xFFFFu)));
+            if (__hlt(acc, __ushort_as_half(0x211F))) break;
+        }
+        out.x = (unsigned int)hbits(aR) | ((unsigned int)hbits(aG) << 16);
+        out.y = (unsigned int)hbits(aB) | ((unsigned int)hbits(__hsub_rn(h_one, acc)) << 16);
+    }
+    fb[(size_t)pj * U.w + pi] = out;
+}
+
+int blend_layer_smem_bytes(int K) { return 3 * K * BLEND_THREADS * 4; }
+
+void launch_blend(const FrameUniforms& U, const splat_record* rec, const unsigned int* vals_sorted,
+                  const uint2* ranges, const FrameCtl* ctl, void* fb_half4, cudaStream_t s)
+{
+    const int rows = U.row_end - U.row_begin;
+    if (rows <= 0 || U.tiles_x <= 0) return;
+    const dim3 grid(U.tiles_x, rows);
+    if (U.mode == SPLAT_MODE_LAYER50) {
+        const int smem = blend_layer_smem_bytes(U.K);
+        cudaFuncSetAttribute(blend_kernel<SPLAT_MODE_LAYER50>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        blend_kernel<SPLAT_MODE_LAYER50><<<grid, BLEND_THREADS, smem, s>>>(U, rec, vals_sorted, ranges, ctl,
+                                                                          reinterpret_cast<uint2*>(fb_half4));
+    } else {
+        blend_kernel<SPLAT_MODE_TILE><<<grid, BLEND_THREADS, 0, s>>>(U, rec, vals_sorted, ranges, ctl,
+                                                                     reinterpret_cast<uint2*>(fb_half4));
+    }
+}

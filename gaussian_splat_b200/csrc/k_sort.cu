@@ -1,0 +1,187 @@
+// K3: stable LSD "onesweep" radix sort of (uint64 key, uint32 value) pairs, 8-bit digits.
+// One kernel per digit pass; each pass reads and writes every pair exactly once
+// (24 B per pair). Per-warp digit ranks come from __match_any_sync, tile prefixes from an
+// epoch-tagged decoupled lookback per digit. Replaces the per-pixel insertion sorts of
+// shaders/gaussian_splat_tile.metal:240-249 / gaussian_splat_50layer.metal:198-206 with
+// one global (tile | depth) sort.
+#include "splat_internal.cuh"
+
+#define SORT_WARPS (SORT_THREADS / 32)
+
+__global__ void __launch_bounds__(256) sort_histogram_kernel(const unsigned long long* __restrict__ keys,
+                                                             unsigned long long n, FrameCtl* ctl,
+                                                             const __grid_constant__ SortPlan plan)
+{
+    __shared__ unsigned int h[SPLAT_MAX_SORT_PASSES][256];
+    for (int p = 0; p < SPLAT_MAX_SORT_PASSES; ++p) h[p][threadIdx.x] = 0;
+    __syncthreads();
+    const unsigned long long stride = (unsigned long long)gridDim.x * 256ull;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * 256ull + threadIdx.x; i < n; i += stride) {
+        const unsigned long long k = __ldg(keys + i);
+        for (int p = 0; p < plan.n_pass; ++p) atomicAdd(&h[p][(unsigned int)(k >> plan.shift[p]) & plan.mask[p]], 1u);
+    }
+    __syncthreads();
+    for (int p = 0; p < plan.n_pass; ++p) {
+        const unsigned int v = h[p][threadIdx.x];
+        if (v) atomicAdd(&ctl->hist[p][threadIdx.x], v);
+    }
+}
+
+void launch_sort_histogram(const unsigned long long* keys, unsigned long long n, FrameCtl* ctl, SortPlan plan,
+                           int sm_count, cudaStream_t s)
+{
+    if (n == 0) return;
+    unsigned long long blocks = (n + 256ull * 16 - 1) / (256ull * 16);
+    if (blocks > (unsigned long long)sm_count * 8) blocks = (unsigned long long)sm_count * 8;
+    sort_histogram_kernel<<<(unsigned int)blocks, 256, 0, s>>>(keys, n, ctl, plan);
+}
+
+// Exclusive scan of one value per thread over a 256-thread block. s_w: SORT_WARPS words.
+__device__ __forceinline__ unsigned int block_excl_scan_256(unsigned int v, unsigned int* s_w, unsigned int& total) {
+    const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned int incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { unsigned int t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+    __syncthreads();            // protect s_w reuse
+    if (lane == 31) s_w[warp] = incl;
+    __syncthreads();
+    unsigned int base = 0; total = 0;
+#pragma unroll
+    for (int k = 0; k < SORT_WARPS; ++k) { const unsigned int t = s_w[k]; if (k < (int)warp) base += t; total += t; }
+    return base + incl - v;
+}
+
+__global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_pass_kernel(
+    const unsigned long long* __restrict__ keys_in, const unsigned int* __restrict__ vals_in,
+    unsigned long long* __restrict__ keys_out, unsigned int* __restrict__ vals_out,
+    FrameCtl* ctl, unsigned long long* status, unsigned int epoch, int pass, int shift, unsigned int mask)
+{
+    __shared__ unsigned long long s_keys[SORT_TILE_KEYS];          // reused for values
+    __shared__ unsigned int s_wh[SORT_WARPS][256];
+    __shared__ unsigned int s_gexcl[256], s_off[256], s_w[SORT_WARPS];
+    __shared__ unsigned int s_tile;
+    unsigned int* s_vals = reinterpret_cast<unsigned int*>(s_keys);
+
+    if (ctl->overflow) return;
+    const unsigned int n = ctl->n_sort;
+    const unsigned int n_tiles = (n + SORT_TILE_KEYS - 1) / SORT_TILE_KEYS;
+    const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned int lt_mask = (1u << lane) - 1u;
+
+    {   // bucket bases from the global digit histogram of this pass
+        unsigned int tot;
+        s_gexcl[tid] = block_excl_scan_256(ctl->hist[pass][tid], s_w, tot);
+    }
+
+    while (true) {
+        __syncthreads();
+        if (tid == 0) s_tile = atomicAdd(&ctl->sort_ticket[pass], 1u);
+        __syncthreads();
+        const unsigned int tile = s_tile;
+        if (tile >= n_tiles) break;
+        const unsigned int tbase = tile * SORT_TILE_KEYS;
+        const unsigned int tcount = min((unsigned int)SORT_TILE_KEYS, n - tbase);
+
+        // ---- load (warp-striped: order (warp, item, lane) == memory order)
+        unsigned long long key[SORT_ITEMS];
+        unsigned int val[SORT_ITEMS];
+        const unsigned int wofs = warp * (32 * SORT_ITEMS) + lane;
+#pragma unroll
+        for (int i = 0; i < SORT_ITEMS; ++i) {
+            const unsigned int li = wofs + i * 32;
+            key[i] = li < tcount ? keys_in[tbase + li] : ~0ull;
+        }
+#pragma unroll
+        for (int i = 0; i < SORT_ITEMS; ++i) {
+            const unsigned int li = wofs + i * 32;
+            val[i] = li < tcount ? vals_in[tbase + li] : 0u;
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) s_wh[warp][lane + k * 32] = 0;
+        __syncwarp();
+
+        // ---- per-warp ranks
+        unsigned int rank[SORT_ITEMS];
+#pragma unroll
+        for (int i = 0; i < SORT_ITEMS; ++i) {
+            const unsigned int d = (unsigned int)(key[i] >> shift) & mask;
+            const unsigned int peers = __match_any_sync(0xFFFFFFFFu, d);
+            const int leader = __ffs(peers) - 1;
+            unsigned int old = 0;
+            if ((int)lane == leader) { old = s_wh[warp][d]; s_wh[warp][d] = old + __popc(peers); }
+            old = __shfl_sync(0xFFFFFFFFu, old, leader);
+            rank[i] = old + __popc(peers & lt_mask);
+            __syncwarp();
+        }
+        __syncthreads();
+
+        // ---- digit column: totals over warps, tile-local exclusive scan, lookback
+        unsigned int cnt = 0;
+#pragma unroll
+        for (int w = 0; w < SORT_WARPS; ++w) cnt += s_wh[w][tid];
+        const unsigned int valid_cnt = cnt - (tid == mask ? (SORT_TILE_KEYS - tcount) : 0u);
+        unsigned long long* st = status + (size_t)tile * 256 + tid;
+        lb_store(st, lb_pack(epoch, tile == 0 ? LB_FLAG_INC : LB_FLAG_AGG, valid_cnt));
+        unsigned int tot;
+        const unsigned int lexcl = block_excl_scan_256(cnt, s_w, tot);
+        {
+            unsigned int run = lexcl;
+#pragma unroll
+            for (int w = 0; w < SORT_WARPS; ++w) { const unsigned int t = s_wh[w][tid]; s_wh[w][tid] = run; run += t; }
+        }
+        unsigned int prefix = 0;
+        for (int look = (int)tile - 1; look >= 0; --look) {
+            const unsigned long long* p = status + (size_t)look * 256 + tid;
+            unsigned long long wd;
+            do { wd = lb_load(p); } while ((unsigned int)(wd >> 34) != epoch || ((wd >> 32) & 3ull) == 0);
+            prefix += (unsigned int)wd;
+            if (((wd >> 32) & 3ull) == LB_FLAG_INC) break;
+        }
+        if (tile != 0) lb_store(st, lb_pack(epoch, LB_FLAG_INC, prefix + valid_cnt));
+        s_off[tid] = s_gexcl[tid] + prefix - lexcl;
+        __syncthreads();
+
+        // ---- keys: registers -> shared (tile-sorted) -> global (coalesced per digit run)
+#pragma unroll
+        for (int i = 0; i < SORT_ITEMS; ++i) {
+            const unsigned int d = (unsigned int)(key[i] >> shift) & mask;
+            rank[i] += s_wh[warp][d];
+            s_keys[rank[i]] = key[i];
+        }
+        __syncthreads();
+        unsigned int goff[SORT_ITEMS];
+#pragma unroll
+        for (int i = 0; i < SORT_ITEMS; ++i) {
+            const unsigned int j = tid + i * SORT_THREADS;
+            if (j < tcount) {
+                const unsigned long long k = s_keys[j];
+                goff[i] = s_off[(unsigned int)(k >> shift) & mask] + j;
+                keys_out[goff[i]] = k;
+            }
+        }
+        __syncthreads();
+        // ---- values through the same shared buffer
+#pragma unroll
+        for (int i = 0; i < SORT_ITEMS; ++i) s_vals[rank[i]] = val[i];
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < SORT_ITEMS; ++i) {
+            const unsigned int j = tid + i * SORT_THREADS;
+            if (j < tcount) vals_out[goff[i]] = s_vals[j];
+        }
+    }
+}
+
+void launch_radix_sort(unsigned long long* keys, unsigned int* vals, unsigned long long* keys_alt,
+                       unsigned int* vals_alt, FrameCtl* ctl, unsigned long long* sort_status,
+                       unsigned int epoch_base, SortPlan plan, int grid, cudaStream_t s)
+{
+    unsigned long long* ki = keys; unsigned int* vi = vals;
+    unsigned long long* ko = keys_alt; unsigned int* vo = vals_alt;
+    for (int p = 0; p < plan.n_pass; ++p) {
+        onesweep_pass_kernel<<<grid, SORT_THREADS, 0, s>>>(ki, vi, ko, vo, ctl, sort_status, epoch_base + p, p,
+                                                           plan.shift[p], plan.mask[p]);
+        unsigned long long* tk = ki; ki = ko; ko = tk;
+        unsigned int* tv = vi; vi = vo; vo = tv;
+    }
+}

@@ -1,0 +1,442 @@
+// libsplat_cuda C ABI (include/splat_cuda.h). Host side of the hot path: owns all device
+// scratch, builds the per-frame uniforms (src/instanced_splat_renderer.mm:453-469) and
+// enqueues K1..K5 on the caller's stream without synchronising, as the reference's
+// render() only encodes (src/instanced_splat_renderer.mm:424-528).
+#include "splat_internal.cuh"
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+static thread_local std::string g_err;
+
+#define CK(call)                                                                          \
+    do {                                                                                  \
+        cudaError_t e_ = (call);                                                          \
+        if (e_ != cudaSuccess) {                                                          \
+            g_err = std::string(#call) + ": " + cudaGetErrorString(e_);                   \
+            return SPLAT_ERR_CUDA;                                                        \
+        }                                                                                 \
+    } while (0)
+#define ARG_FAIL(msg) do { g_err = (msg); return SPLAT_ERR_ARG; } while (0)
+
+__global__ void set_n_sort_kernel(FrameCtl* ctl, unsigned int n) { ctl->n_sort = n; ctl->total_pairs = n; }
+
+struct splat_ctx {
+    int device = 0, sm_count = 148;
+    uint32_t n = 0; size_t n_pad = 0;
+    float4 *rot = nullptr, *pos_sx = nullptr, *syz = nullptr; uint16_t* bq = nullptr; float* sh = nullptr;
+    int sh_degree = 0;
+    splat_record* rec = nullptr; uint32_t *touched = nullptr, *offsets = nullptr;
+    unsigned long long* keys[2] = {nullptr, nullptr}; uint32_t* vals[2] = {nullptr, nullptr};
+    unsigned long long capacity = 0;
+    unsigned long long* dbg_keys = nullptr; uint32_t* dbg_vals = nullptr; unsigned long long dbg_cap = 0;
+    FrameCtl* ctl = nullptr; FrameCtl* ctl_host = nullptr;
+    unsigned long long *scan_status = nullptr, *sort_status = nullptr; size_t sort_status_tiles = 0;
+    uint2* ranges = nullptr; uint32_t ranges_cap = 0;
+    uint32_t frame_no = 0;
+    FrameUniforms lastU{}; SortPlan lastPlan{}; int sorted_buf = 0; bool have_frame = false, kept_unsorted = false;
+    cudaEvent_t ev[6] = {}; bool timed = false;
+    cudaStream_t own_stream = nullptr; void* fb_scratch = nullptr; size_t fb_scratch_bytes = 0;
+};
+
+static void mat4_mul_host(const float* a, const float* b, float* o) {
+    // simd_mul(a, b), k = 0..3 left to right (column-major)
+    float t[16];
+    for (int j = 0; j < 4; ++j)
+        for (int r = 0; r < 4; ++r) {
+            volatile float acc = a[0 * 4 + r] * b[j * 4 + 0];
+            volatile float m1 = a[1 * 4 + r] * b[j * 4 + 1]; acc = acc + m1;
+            volatile float m2 = a[2 * 4 + r] * b[j * 4 + 2]; acc = acc + m2;
+            volatile float m3 = a[3 * 4 + r] * b[j * 4 + 3]; acc = acc + m3;
+            t[j * 4 + r] = acc;
+        }
+    std::memcpy(o, t, 64);
+}
+
+static int free_pairs(splat_ctx* c) {
+    for (int k = 0; k < 2; ++k) { cudaFree(c->keys[k]); cudaFree(c->vals[k]); c->keys[k] = nullptr; c->vals[k] = nullptr; }
+    cudaFree(c->sort_status); c->sort_status = nullptr; c->sort_status_tiles = 0;
+    c->capacity = 0;
+    return 0;
+}
+
+static int ensure_sort_status(splat_ctx* c, unsigned long long n_keys) {
+    const size_t tiles = (size_t)((n_keys + SORT_TILE_KEYS - 1) / SORT_TILE_KEYS) + 1;
+    if (tiles <= c->sort_status_tiles) return 0;
+    CK(cudaDeviceSynchronize());
+    cudaFree(c->sort_status); c->sort_status = nullptr;
+    CK(cudaMalloc(&c->sort_status, tiles * 256 * 8));
+    CK(cudaMemset(c->sort_status, 0, tiles * 256 * 8));
+    c->sort_status_tiles = tiles;
+    return 0;
+}
+
+static int ensure_pairs(splat_ctx* c, unsigned long long cap) {
+    if (cap <= c->capacity) return 0;
+    if (cap >= 0xFFFF0000ull) ARG_FAIL("pair capacity would exceed 2^32");
+    CK(cudaDeviceSynchronize());
+    free_pairs(c);
+    cap = (cap + SORT_TILE_KEYS - 1) / SORT_TILE_KEYS * SORT_TILE_KEYS;
+    for (int k = 0; k < 2; ++k) {
+        CK(cudaMalloc(&c->keys[k], cap * 8));
+        CK(cudaMalloc(&c->vals[k], cap * 4));
+        CK(cudaMemset(c->vals[k], 0, cap * 4));   // stale slots must stay valid splat indices
+        CK(cudaMemset(c->keys[k], 0, cap * 8));
+    }
+    c->capacity = cap;
+    return ensure_sort_status(c, cap);
+}
+
+extern "C" {
+
+const char* splat_last_error_string(void) { return g_err.c_str(); }
+int splat_version(void) { return 100; }
+
+int splat_create(int device, splat_ctx** out) {
+    if (!out) ARG_FAIL("splat_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    CK(cudaGetDeviceCount(&count));
+    if (device < 0 || device >= count) ARG_FAIL("splat_create: no such CUDA device");
+    CK(cudaSetDevice(device));
+    splat_ctx* c = new splat_ctx();
+    c->device = device;
+    CK(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
+    CK(cudaMalloc(&c->ctl, sizeof(FrameCtl)));
+    CK(cudaMemset(c->ctl, 0, sizeof(FrameCtl)));
+    CK(cudaMallocHost(&c->ctl_host, sizeof(FrameCtl)));
+    std::memset(c->ctl_host, 0, sizeof(FrameCtl));
+    for (int k = 0; k < 6; ++k) CK(cudaEventCreate(&c->ev[k]));
+    CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+    *out = c;
+    return SPLAT_OK;
+}
+
+static void free_scene(splat_ctx* c) {
+    cudaFree(c->rot); cudaFree(c->pos_sx); cudaFree(c->syz); cudaFree(c->bq); cudaFree(c->sh);
+    cudaFree(c->rec); cudaFree(c->touched); cudaFree(c->offsets); cudaFree(c->scan_status);
+    c->rot = c->pos_sx = c->syz = nullptr; c->bq = nullptr; c->sh = nullptr; c->rec = nullptr;
+    c->touched = c->offsets = nullptr; c->scan_status = nullptr; c->n = 0; c->n_pad = 0; c->sh_degree = 0;
+}
+
+int splat_destroy(splat_ctx* c) {
+    if (!c) return SPLAT_OK;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    free_scene(c); free_pairs(c);
+    cudaFree(c->dbg_keys); cudaFree(c->dbg_vals); cudaFree(c->ranges); cudaFree(c->ctl); cudaFree(c->fb_scratch);
+    cudaFreeHost(c->ctl_host);
+    for (int k = 0; k < 6; ++k) if (c->ev[k]) cudaEventDestroy(c->ev[k]);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+    return SPLAT_OK;
+}
+
+int splat_upload(splat_ctx* c, const void* aos_host, uint32_t n) {
+    if (!c) ARG_FAIL("splat_upload: ctx is NULL");
+    if (n && !aos_host) ARG_FAIL("splat_upload: aos_host is NULL");
+    CK(cudaSetDevice(c->device));
+    CK(cudaDeviceSynchronize());
+    free_scene(c);
+    c->have_frame = false;
+    if (n == 0) return SPLAT_OK;
+    const size_t n_pad = ((size_t)n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS * SCAN_TILE_ITEMS;
+    CK(cudaMalloc(&c->rot, n_pad * 16)); CK(cudaMalloc(&c->pos_sx, n_pad * 16)); CK(cudaMalloc(&c->syz, n_pad * 16));
+    CK(cudaMalloc(&c->bq, n_pad * 2));
+    CK(cudaMalloc(&c->rec, n_pad * sizeof(splat_record)));
+    CK(cudaMalloc(&c->touched, n_pad * 4)); CK(cudaMalloc(&c->offsets, n_pad * 4));
+    CK(cudaMemset(c->touched, 0, n_pad * 4));
+    CK(cudaMemset(c->rec, 0, n_pad * sizeof(splat_record)));
+    const size_t scan_tiles = n_pad / SCAN_TILE_ITEMS + 1;
+    CK(cudaMalloc(&c->scan_status, scan_tiles * 8));
+    CK(cudaMemset(c->scan_status, 0, scan_tiles * 8));
+    float* aos_dev = nullptr;
+    CK(cudaMalloc(&aos_dev, (size_t)n * 56));
+    CK(cudaMemcpy(aos_dev, aos_host, (size_t)n * 56, cudaMemcpyHostToDevice));
+    launch_upload_soa(aos_dev, n, c->rot, c->pos_sx, c->syz, c->bq, 0);
+    CK(cudaGetLastError());
+    CK(cudaDeviceSynchronize());
+    cudaFree(aos_dev);
+    c->n = n; c->n_pad = n_pad;
+    // vals hold splat indices; stale ones from a larger scene must not survive
+    for (int k = 0; k < 2; ++k) if (c->vals[k]) CK(cudaMemset(c->vals[k], 0, c->capacity * 4));
+    unsigned long long want = (unsigned long long)n * 12ull;
+    if (want < (1ull << 20)) want = 1ull << 20;
+    if (want > 0xC0000000ull) want = 0xC0000000ull;
+    return ensure_pairs(c, want);
+}
+
+int splat_upload_sh(splat_ctx* c, const float* sh_host, uint32_t n, int degree) {
+    if (!c) ARG_FAIL("splat_upload_sh: ctx is NULL");
+    if (degree < 0 || degree > 3) ARG_FAIL("splat_upload_sh: degree must be 0..3");
+    if (n != c->n) ARG_FAIL("splat_upload_sh: n differs from splat_upload");
+    CK(cudaSetDevice(c->device));
+    CK(cudaDeviceSynchronize());
+    cudaFree(c->sh); c->sh = nullptr; c->sh_degree = 0;
+    if (degree == 0 || n == 0) return SPLAT_OK;
+    if (!sh_host) ARG_FAIL("splat_upload_sh: sh_rest45_host is NULL");
+    CK(cudaMalloc(&c->sh, (size_t)n * 45 * 4));
+    CK(cudaMemcpy(c->sh, sh_host, (size_t)n * 45 * 4, cudaMemcpyHostToDevice));
+    c->sh_degree = degree;
+    return SPLAT_OK;
+}
+
+}  // extern "C"
+
+// --------------------------------------------------------------------- frames
+static int tile_bits(unsigned int T) { int b = 0; while ((1ull << b) < T) ++b; return b; }
+
+static int build_frame(splat_ctx* c, const float* view, const float* proj, int w, int h, const splat_opts* o,
+                       FrameUniforms& U, SortPlan& plan) {
+    if (!view || !proj) ARG_FAIL("splat_render: view/proj is NULL");
+    if (w <= 0 || h <= 0 || w > 65536 || h > 65536) ARG_FAIL("splat_render: bad viewport");
+    splat_opts d{}; if (o) d = *o;
+    if (d.mode != SPLAT_MODE_TILE && d.mode != SPLAT_MODE_LAYER50) ARG_FAIL("splat_render: bad mode");
+    if (d.order != SPLAT_ORDER_NEAR_FIRST && d.order != SPLAT_ORDER_REFERENCE) ARG_FAIL("splat_render: bad order");
+    int K = d.max_fragments;
+    if (K == 0) K = d.mode == SPLAT_MODE_LAYER50 ? 50 : 32;
+    if (K < 1 || K > 64) ARG_FAIL("splat_render: max_fragments must be 1..64");
+    if (d.sh_degree < 0 || d.sh_degree > 3) ARG_FAIL("splat_render: sh_degree must be 0..3");
+    if (d.sh_degree > c->sh_degree) ARG_FAIL("splat_render: sh_degree exceeds uploaded SH data");
+    std::memcpy(U.V, view, 64); std::memcpy(U.P, proj, 64);
+    mat4_mul_host(proj, view, U.VP);                    // src/instanced_splat_renderer.mm:453
+    U.w = w; U.h = h; U.W = (float)w; U.H = (float)h;
+    U.tiles_x = (w + SPLAT_TILE - 1) / SPLAT_TILE; U.tiles_y = (h + SPLAT_TILE - 1) / SPLAT_TILE;
+    U.row_begin = 0; U.row_end = U.tiles_y;
+    if (d.tile_row_end > 0) {
+        if (d.tile_row_begin < 0 || d.tile_row_begin > d.tile_row_end) ARG_FAIL("splat_render: bad tile row band");
+        U.row_begin = d.tile_row_begin; U.row_end = d.tile_row_end < U.tiles_y ? d.tile_row_end : U.tiles_y;
+        if (U.row_begin > U.row_end) U.row_begin = U.row_end;
+    }
+    U.mode = d.mode; U.order = d.order; U.K = K; U.sh_degree = d.sh_degree;
+    U.cam[0] = U.cam[1] = U.cam[2] = 0.0f;
+    U.n = c->n;
+    const unsigned int T = (unsigned int)(U.tiles_x * U.tiles_y);
+    const int tb = tile_bits(T);
+    if (tb > 16) ARG_FAIL("splat_render: more than 65536 tiles");
+    plan = SortPlan{};
+    int p = 0;
+    if (d.mode == SPLAT_MODE_TILE) {       // 15 significant half-depth bits (sign bit is 0)
+        plan.shift[p] = 0; plan.mask[p++] = 0xFF;
+        plan.shift[p] = 8; plan.mask[p++] = 0xFF;
+    }                                       // LAYER50: pairs are emitted in instance order and the sort is stable
+    if (tb > 0) { plan.shift[p] = 32; plan.mask[p++] = tb >= 8 ? 0xFFu : ((1u << tb) - 1u); }
+    if (tb > 8) { plan.shift[p] = 40; plan.mask[p++] = (1u << (tb - 8)) - 1u; }
+    plan.n_pass = p;
+    return SPLAT_OK;
+}
+
+static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUniforms& U, const SortPlan& plan, int flags) {
+    const unsigned int T = (unsigned int)(U.tiles_x * U.tiles_y);
+    if (T > c->ranges_cap) {
+        CK(cudaDeviceSynchronize());
+        cudaFree(c->ranges); c->ranges = nullptr;
+        CK(cudaMalloc(&c->ranges, (size_t)T * 8));
+        c->ranges_cap = T;
+    }
+    const bool timed = (flags & SPLAT_FLAG_TIMING) != 0;
+    const bool keep = (flags & SPLAT_FLAG_KEEP_UNSORTED) != 0;
+    if (keep && c->dbg_cap < c->capacity) {
+        CK(cudaDeviceSynchronize());
+        cudaFree(c->dbg_keys); cudaFree(c->dbg_vals); c->dbg_keys = nullptr; c->dbg_vals = nullptr;
+        CK(cudaMalloc(&c->dbg_keys, c->capacity * 8)); CK(cudaMalloc(&c->dbg_vals, c->capacity * 4));
+        c->dbg_cap = c->capacity;
+    }
+    c->frame_no = c->frame_no + 1;
+    if (c->frame_no >= (1u << 25)) c->frame_no = 1;
+    const unsigned int epoch = c->frame_no * 16u;       // < 2^30; +0 scan, +1.. sort passes
+    if (timed) CK(cudaEventRecord(c->ev[0], s));
+    CK(cudaMemsetAsync(c->ctl, 0, sizeof(FrameCtl), s));
+    if (c->n) {
+        ScenePlanes sp{c->rot, c->pos_sx, c->syz, c->bq, c->sh};
+        launch_preprocess(sp, U, c->rec, c->touched, s);
+        if (timed) CK(cudaEventRecord(c->ev[1], s));
+        launch_scan_duplicate(U, c->rec, c->touched, c->offsets, c->keys[0], c->vals[0], c->capacity, c->ctl,
+                              c->scan_status, epoch, plan, s);
+        if (keep) {
+            CK(cudaMemcpyAsync(c->dbg_keys, c->keys[0], c->capacity * 8, cudaMemcpyDeviceToDevice, s));
+            CK(cudaMemcpyAsync(c->dbg_vals, c->vals[0], c->capacity * 4, cudaMemcpyDeviceToDevice, s));
+        }
+        if (timed) CK(cudaEventRecord(c->ev[2], s));
+        launch_radix_sort(c->keys[0], c->vals[0], c->keys[1], c->vals[1], c->ctl, c->sort_status, epoch + 1, plan,
+                          c->sm_count * 2, s);
+    } else if (timed) { CK(cudaEventRecord(c->ev[1], s)); CK(cudaEventRecord(c->ev[2], s)); }
+    if (timed) CK(cudaEventRecord(c->ev[3], s));
+    const int sb = plan.n_pass & 1;
+    launch_tile_ranges(c->keys[sb], c->ctl, T, c->ranges, s);
+    if (timed) CK(cudaEventRecord(c->ev[4], s));
+    launch_blend(U, c->rec, c->vals[sb], c->ranges, c->ctl, fb, s);
+    if (timed) CK(cudaEventRecord(c->ev[5], s));
+    CK(cudaGetLastError());
+    c->lastU = U; c->lastPlan = plan; c->sorted_buf = sb; c->have_frame = true; c->timed = timed; c->kept_unsorted = keep;
+    return SPLAT_OK;
+}
+
+extern "C" {
+
+int splat_render(splat_ctx* c, void* stream, void* fb, const float* view, const float* proj, int w, int h,
+                 const splat_opts* o) {
+    if (!c) ARG_FAIL("splat_render: ctx is NULL");
+    if (!fb) ARG_FAIL("splat_render: framebuffer is NULL");
+    CK(cudaSetDevice(c->device));
+    FrameUniforms U; SortPlan plan;
+    int rc = build_frame(c, view, proj, w, h, o, U, plan);
+    if (rc) return rc;
+    if (c->capacity == 0) { rc = ensure_pairs(c, 1ull << 20); if (rc) return rc; }
+    return enqueue_frame(c, (cudaStream_t)stream, fb, U, plan, o ? o->flags : 0);
+}
+
+int splat_render_batch(splat_ctx* c, void* stream, void* const* fbs, const float* views, const float* projs,
+                       int n_views, int w, int h, const splat_opts* o) {
+    if (!c) ARG_FAIL("splat_render_batch: ctx is NULL");
+    if (n_views < 0 || (n_views && (!fbs || !views || !projs))) ARG_FAIL("splat_render_batch: bad arguments");
+    for (int v = 0; v < n_views; ++v) {
+        const int rc = splat_render(c, stream, fbs[v], views + 16 * v, projs + 16 * v, w, h, o);
+        if (rc) return rc;
+    }
+    return SPLAT_OK;
+}
+
+int splat_frame_status(splat_ctx* c, splat_status* out) {
+    if (!c || !out) ARG_FAIL("splat_frame_status: NULL argument");
+    CK(cudaSetDevice(c->device));
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(c->ctl_host, c->ctl, 64, cudaMemcpyDeviceToHost));
+    std::memset(out, 0, sizeof(*out));
+    out->n_splats = c->n;
+    out->n_pairs = c->ctl_host->total_pairs;
+    out->pair_capacity = c->capacity;
+    out->overflow = c->ctl_host->overflow;
+    out->sort_passes = (uint32_t)c->lastPlan.n_pass;
+    if (out->overflow) {
+        unsigned long long want = out->n_pairs + out->n_pairs / 4 + SORT_TILE_KEYS;
+        const int rc = ensure_pairs(c, want);
+        if (rc) return rc;
+    }
+    return SPLAT_OK;
+}
+
+int splat_render_host(splat_ctx* c, void* fb_host, const float* view, const float* proj, int w, int h,
+                      const splat_opts* o) {
+    if (!c) ARG_FAIL("splat_render_host: ctx is NULL");
+    if (!fb_host) ARG_FAIL("splat_render_host: framebuffer is NULL");
+    CK(cudaSetDevice(c->device));
+    FrameUniforms U; SortPlan plan;
+    int rc = build_frame(c, view, proj, w, h, o, U, plan);
+    if (rc) return rc;
+    const size_t bytes = (size_t)w * h * 8;
+    if (bytes > c->fb_scratch_bytes) {
+        CK(cudaDeviceSynchronize());
+        cudaFree(c->fb_scratch); c->fb_scratch = nullptr;
+        CK(cudaMalloc(&c->fb_scratch, bytes));
+        c->fb_scratch_bytes = bytes;
+    }
+    if (c->capacity == 0) { rc = ensure_pairs(c, 1ull << 20); if (rc) return rc; }
+    // rows outside the band are not rendered: only the band is copied back
+    const size_t row0 = (size_t)U.row_begin * SPLAT_TILE, row1 = (size_t)U.row_end * SPLAT_TILE < (size_t)h ? (size_t)U.row_end * SPLAT_TILE : (size_t)h;
+    for (int attempt = 0; attempt < 4; ++attempt) {
+        rc = enqueue_frame(c, c->own_stream, c->fb_scratch, U, plan, o ? o->flags : 0);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(c->ctl_host, c->ctl, 64, cudaMemcpyDeviceToHost, c->own_stream));
+        if (row1 > row0)
+            CK(cudaMemcpyAsync((char*)fb_host + row0 * w * 8, (char*)c->fb_scratch + row0 * w * 8, (row1 - row0) * w * 8,
+                               cudaMemcpyDeviceToHost, c->own_stream));
+        CK(cudaStreamSynchronize(c->own_stream));
+        if (!c->ctl_host->overflow) return SPLAT_OK;
+        const unsigned long long D = c->ctl_host->total_pairs;
+        rc = ensure_pairs(c, D + D / 4 + SORT_TILE_KEYS);
+        if (rc) return rc;
+    }
+    g_err = "splat_render_host: pair buffers still overflow after regrowth";
+    return SPLAT_ERR_OVERFLOW;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------ debug / timing / sort
+extern "C" {
+
+int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
+    if (!c || !bytes) ARG_FAIL("splat_debug_fetch: NULL argument");
+    if (!c->have_frame) { g_err = "splat_debug_fetch: no frame rendered"; return SPLAT_ERR_STATE; }
+    CK(cudaSetDevice(c->device));
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(c->ctl_host, c->ctl, 64, cudaMemcpyDeviceToHost));
+    if (c->ctl_host->overflow) { g_err = "splat_debug_fetch: last frame overflowed the pair buffers"; return SPLAT_ERR_OVERFLOW; }
+    const size_t D = (size_t)c->ctl_host->n_sort;
+    const size_t T = (size_t)c->lastU.tiles_x * c->lastU.tiles_y;
+    const void* src = nullptr; size_t need = 0;
+    switch (what) {
+        case SPLAT_FETCH_RECORDS:       src = c->rec;      need = (size_t)c->n * sizeof(splat_record); break;
+        case SPLAT_FETCH_TILES_TOUCHED: src = c->touched;  need = (size_t)c->n * 4; break;
+        case SPLAT_FETCH_OFFSETS:       src = c->offsets;  need = (size_t)c->n * 4; break;
+        case SPLAT_FETCH_KEYS_UNSORTED: src = c->dbg_keys; need = D * 8; break;
+        case SPLAT_FETCH_VALS_UNSORTED: src = c->dbg_vals; need = D * 4; break;
+        case SPLAT_FETCH_KEYS_SORTED:   src = c->keys[c->sorted_buf]; need = D * 8; break;
+        case SPLAT_FETCH_VALS_SORTED:   src = c->vals[c->sorted_buf]; need = D * 4; break;
+        case SPLAT_FETCH_TILE_RANGES:   src = c->ranges;   need = T * 8; break;
+        default: ARG_FAIL("splat_debug_fetch: unknown item");
+    }
+    if ((what == SPLAT_FETCH_KEYS_UNSORTED || what == SPLAT_FETCH_VALS_UNSORTED) && !c->kept_unsorted) {
+        g_err = "splat_debug_fetch: frame was not rendered with SPLAT_FLAG_KEEP_UNSORTED"; return SPLAT_ERR_STATE;
+    }
+    if (!dst) { *bytes = need; return SPLAT_OK; }
+    if (*bytes < need) { *bytes = need; ARG_FAIL("splat_debug_fetch: destination too small"); }
+    if (need) CK(cudaMemcpy(dst, src, need, cudaMemcpyDeviceToHost));
+    if (what == SPLAT_FETCH_RECORDS && c->n) {
+        // culled splats have no record written: present them zeroed
+        uint32_t* t = new uint32_t[c->n];
+        cudaError_t e = cudaMemcpy(t, c->touched, (size_t)c->n * 4, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) {
+            splat_record* r = (splat_record*)dst;
+            for (uint32_t i = 0; i < c->n; ++i) if (!t[i]) std::memset(r + i, 0, sizeof(splat_record));
+        }
+        delete[] t;
+        CK(e);
+    }
+    *bytes = need;
+    return SPLAT_OK;
+}
+
+int splat_stage_times(splat_ctx* c, float ms[8]) {
+    if (!c || !ms) ARG_FAIL("splat_stage_times: NULL argument");
+    if (!c->have_frame || !c->timed) { g_err = "splat_stage_times: last frame had no SPLAT_FLAG_TIMING"; return SPLAT_ERR_STATE; }
+    CK(cudaSetDevice(c->device));
+    CK(cudaEventSynchronize(c->ev[5]));
+    for (int k = 0; k < 8; ++k) ms[k] = 0.0f;
+    for (int k = 0; k < 5; ++k) CK(cudaEventElapsedTime(&ms[k], c->ev[k], c->ev[k + 1]));
+    CK(cudaEventElapsedTime(&ms[5], c->ev[0], c->ev[5]));
+    return SPLAT_OK;
+}
+
+int splat_sort_pairs_u64_u32(splat_ctx* c, void* stream, uint64_t* keys, uint32_t* vals, uint64_t* keys_alt,
+                             uint32_t* vals_alt, uint64_t n, int begin_bit, int end_bit, int* result_in_alt) {
+    if (!c) ARG_FAIL("splat_sort_pairs: ctx is NULL");
+    if (n && (!keys || !vals || !keys_alt || !vals_alt)) ARG_FAIL("splat_sort_pairs: NULL buffer");
+    if (begin_bit < 0 || end_bit > 64 || begin_bit > end_bit) ARG_FAIL("splat_sort_pairs: bad bit range");
+    if (n >= 0xFFFF0000ull) ARG_FAIL("splat_sort_pairs: n must be below 2^32");
+    CK(cudaSetDevice(c->device));
+    SortPlan plan{};
+    for (int b = begin_bit; b < end_bit; b += 8) {
+        const int bits = end_bit - b < 8 ? end_bit - b : 8;
+        plan.shift[plan.n_pass] = b; plan.mask[plan.n_pass] = (1u << bits) - 1u; ++plan.n_pass;
+    }
+    if (result_in_alt) *result_in_alt = plan.n_pass & 1;
+    if (n == 0 || plan.n_pass == 0) return SPLAT_OK;
+    int rc = ensure_sort_status(c, n);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    c->frame_no = c->frame_no + 1;
+    if (c->frame_no >= (1u << 25)) c->frame_no = 1;
+    CK(cudaMemsetAsync(c->ctl, 0, sizeof(FrameCtl), s));
+    set_n_sort_kernel<<<1, 1, 0, s>>>(c->ctl, (unsigned int)n);
+    launch_sort_histogram((const unsigned long long*)keys, n, c->ctl, plan, c->sm_count, s);
+    launch_radix_sort((unsigned long long*)keys, vals, (unsigned long long*)keys_alt, vals_alt, c->ctl, c->sort_status,
+                      c->frame_no * 16u + 1, plan, c->sm_count * 2, s);
+    CK(cudaGetLastError());
+    c->have_frame = false;
+    return SPLAT_OK;
+}
+
+}  // extern "C"

@@ -6,8 +6,13 @@
 #include "../../include/splat_cuda.h"
 
 #define SPLAT_MAX_SORT_PASSES 8
-#define SORT_TILE_KEYS 4096          // keys per onesweep tile (256 threads x 16)
-#define SCAN_TILE_ITEMS 1024         // splats per scan/duplicate tile (256 threads x 4)
+#define SORT_THREADS 256
+#define SORT_ITEMS 16
+#define SORT_TILE_KEYS (SORT_THREADS * SORT_ITEMS)   // keys per onesweep tile
+#define SCAN_THREADS 256
+#define SCAN_ITEMS 4
+#define SCAN_TILE_ITEMS (SCAN_THREADS * SCAN_ITEMS)  // splats per scan/duplicate tile
+#define FRAME_MAX_PASSES 4                           // frame keys: <= 2 depth + <= 2 tile digits
 
 // Per-frame uniforms: role of the reference's Uniforms buffer
 // (shaders/gaussian_splat_tile.metal:16-21, src/instanced_splat_renderer.mm:456-469),
@@ -27,7 +32,8 @@ struct FrameCtl {
     unsigned int overflow;
     unsigned int scan_ticket;
     unsigned int sort_ticket[SPLAT_MAX_SORT_PASSES];
-    unsigned int pad[6];
+    unsigned int n_sort;              // min(D, capacity), written by the scan kernel's last tile
+    unsigned int pad[5];
     unsigned int hist[SPLAT_MAX_SORT_PASSES][256];
 };
 
@@ -35,14 +41,15 @@ struct FrameCtl {
 struct ScenePlanes {
     const float4* rot;        // w x y z
     const float4* pos_sx;     // position.xyz, scale.x
-    const float4* syz_op_rg;  // scale.y, scale.z, opacity, bits(half2(r, g))
+    const float4* syz_op_rg;  // scale.y, scale.z, opacity, bits(half r | half g << 16)
     const uint16_t* b;        // half(b)
     const float* sh;          // [n][45] or nullptr
 };
 
 struct SortPlan {
     int n_pass;
-    int shift[SPLAT_MAX_SORT_PASSES];
+    int shift[SPLAT_MAX_SORT_PASSES];   // digit = (key >> shift) & mask
+    unsigned int mask[SPLAT_MAX_SORT_PASSES];  // (1 << bits) - 1, bits <= 8
 };
 
 // Epoch-tagged 64-bit lookback word: [63:34] epoch, [33:32] flag, [31:0] value.
@@ -70,13 +77,18 @@ void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_reco
 void launch_scan_duplicate(const FrameUniforms& U, const splat_record* rec, const unsigned int* touched,
                            unsigned int* offsets, unsigned long long* keys, unsigned int* vals,
                            unsigned long long capacity, FrameCtl* ctl, unsigned long long* scan_status,
-                           unsigned int epoch, SortPlan plan, int sm_count, cudaStream_t s);
-// Sorts n = *d_n (device) pairs; result buffer index (0 = in, 1 = alt) is n_pass & 1.
+                           unsigned int epoch, SortPlan plan, cudaStream_t s);
+// Per-pass digit histograms of keys[0..n) into ctl->hist (stand-alone sort only; frames get
+// them from the duplication kernel).
+void launch_sort_histogram(const unsigned long long* keys, unsigned long long n, FrameCtl* ctl, SortPlan plan,
+                           int sm_count, cudaStream_t s);
+// Sorts n pairs, n read from ctl->n_sort on the device. Result lands in (keys, vals) when
+// plan.n_pass is even, in (keys_alt, vals_alt) when odd. Uses epochs epoch_base .. +n_pass-1.
 void launch_radix_sort(unsigned long long* keys, unsigned int* vals, unsigned long long* keys_alt,
-                       unsigned int* vals_alt, const unsigned long long* d_n, unsigned long long capacity,
-                       FrameCtl* ctl, bool hist_ready, unsigned long long* sort_status, unsigned int epoch_base,
-                       SortPlan plan, int sm_count, cudaStream_t s);
-void launch_tile_ranges(const unsigned long long* keys_sorted, const unsigned long long* d_n,
-                        unsigned long long capacity, uint2* ranges, int sm_count, cudaStream_t s);
+                       unsigned int* vals_alt, FrameCtl* ctl, unsigned long long* sort_status,
+                       unsigned int epoch_base, SortPlan plan, int grid, cudaStream_t s);
+void launch_tile_ranges(const unsigned long long* keys_sorted, const FrameCtl* ctl, unsigned int n_tiles,
+                        uint2* ranges, cudaStream_t s);
 void launch_blend(const FrameUniforms& U, const splat_record* rec, const unsigned int* vals_sorted,
-                  const uint2* ranges, void* fb_half4, cudaStream_t s);
+                  const uint2* ranges, const FrameCtl* ctl, void* fb_half4, cudaStream_t s);
+int blend_layer_smem_bytes(int K);

@@ -1,0 +1,154 @@
+// Pinned per-splat / per-fragment arithmetic.
+// Compiled with -fmad=false: every + - * / sqrt below is one correctly rounded
+// IEEE fp32 operation in the written order; fmaf() appears only where written.
+// Follows shaders/gaussian_splat_tile.metal:40-157 (vertex_main and helpers),
+// evaluated once per splat instead of once per quad corner.
+#pragma once
+#include "splat_internal.cuh"
+
+// exp(-0.5*q), q in [0, ~9.3]: Cody-Waite reduction + degree-6 Horner, explicit fmaf.
+__device__ __forceinline__ float exp_neg_half(float q) {
+    const float x = -0.5f * q;
+    const float t = x * 1.44269502162933349609375f;
+    const float n = rintf(t);
+    float r = fmaf(n, -0.693145751953125f, x);
+    r = fmaf(n, -1.428606765330187045037746429443359375e-06f, r);
+    float p = 1.0f / 720.0f;
+    p = fmaf(p, r, 1.0f / 120.0f);
+    p = fmaf(p, r, 1.0f / 24.0f);
+    p = fmaf(p, r, 1.0f / 6.0f);
+    p = fmaf(p, r, 0.5f);
+    p = fmaf(p, r, 1.0f);
+    p = fmaf(p, r, 1.0f);
+    const int e = (int)n + 127;
+    return p * __int_as_float(e << 23);
+}
+
+__device__ __forceinline__ void mat4_point(const float* M, float x, float y, float z, float out[4]) {
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+        out[r] = ((M[0 * 4 + r] * x + M[1 * 4 + r] * y) + M[2 * 4 + r] * z) + M[3 * 4 + r];
+}
+
+// One splat -> 48-byte record. Returns tiles touched (0 = culled; rec untouched).
+__device__ __forceinline__ unsigned int preprocess_one(
+    float qw, float qx, float qy, float qz, float s0, float s1, float s2,
+    float px, float py, float pz, unsigned int rg_half2, unsigned int b_half, float opacity,
+    const FrameUniforms& U, splat_record& rec)
+{
+    // gaussian_splat_tile.metal:94-105
+    float vp[4];
+    mat4_point(U.V, px, py, pz, vp);
+    const float zFront = -vp[2];
+    if (!(zFront >= 1e-4f)) return 0;
+
+    // :40-49 quaternionToMatrix (normalize = v / sqrt(dot))
+    const float qlen = sqrtf(((qw * qw + qx * qx) + qy * qy) + qz * qz);
+    const float w = qw / qlen, x = qx / qlen, y = qy / qlen, z = qz / qlen;
+    float R[3][3];
+    R[0][0] = 1.0f - 2.0f * (y * y + z * z); R[1][0] = 2.0f * (x * y + w * z); R[2][0] = 2.0f * (x * z - w * y);
+    R[0][1] = 2.0f * (x * y - w * z); R[1][1] = 1.0f - 2.0f * (x * x + z * z); R[2][1] = 2.0f * (y * z + w * x);
+    R[0][2] = 2.0f * (x * z + w * y); R[1][2] = 2.0f * (y * z - w * x); R[2][2] = 1.0f - 2.0f * (x * x + y * y);
+
+    // :51-60 M = R*S ; Sigma = M*M^T
+    const float sc[3] = {s0, s1, s2};
+    float M[3][3], Sg[3][3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) M[r][c] = R[r][c] * sc[c];
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) Sg[r][c] = (M[r][0] * M[c][0] + M[r][1] * M[c][1]) + M[r][2] * M[c][2];
+
+    // :109-115 viewCov = (viewRot*Sigma)*viewRot^T ; Wm[r][c] = V[c][r]
+    float Wm[3][3], T[3][3], C[3][3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) Wm[r][c] = U.V[c * 4 + r];
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) T[r][c] = (Wm[r][0] * Sg[0][c] + Wm[r][1] * Sg[1][c]) + Wm[r][2] * Sg[2][c];
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) C[r][c] = (T[r][0] * Wm[c][0] + T[r][1] * Wm[c][1]) + T[r][2] * Wm[c][2];
+
+    // :117-123 Jacobian rows (literal sign kept)
+    const float focalX = U.P[0] * (U.W * 0.5f);
+    const float focalY = U.P[5] * (U.H * 0.5f);
+    const float invZ = 1.0f / zFront;
+    const float invZ2 = invZ * invZ;
+    const float j00 = focalX * invZ, j02 = -((focalX * vp[0]) * invZ2);
+    const float j11 = focalY * invZ, j12 = -((focalY * vp[1]) * invZ2);
+
+    // :125-131 (exact-zero terms dropped)
+    const float t0 = C[0][0] * j00 + C[0][2] * j02;
+    const float t2 = C[2][0] * j00 + C[2][2] * j02;
+    float a = j00 * t0 + j02 * t2;
+    const float u0 = C[0][1] * j11 + C[0][2] * j12;
+    const float u1 = C[1][1] * j11 + C[1][2] * j12;
+    const float u2 = C[2][1] * j11 + C[2][2] * j12;
+    const float b = j00 * u0 + j02 * u2;
+    float c = j11 * u1 + j12 * u2;
+    a = a + 1e-4f;
+    c = c + 1e-4f;
+
+    // :62-83 eigenSym2x2, :136-140
+    const float tr = a + c;
+    const float det = a * c - b * b;
+    const float disc = fmaxf(0.0f, (0.25f * tr) * tr - det);
+    const float s = sqrtf(disc);
+    float l1 = 0.5f * tr + s;
+    float l2 = 0.5f * tr - s;
+    float e1x, e1y;
+    if (fabsf(b) > 1e-8f) {
+        const float ex = l1 - c, ey = b;
+        const float el = sqrtf(ex * ex + ey * ey);
+        e1x = ex / el; e1y = ey / el;
+    } else if (a >= c) { e1x = 1.0f; e1y = 0.0f; }
+    else { e1x = 0.0f; e1y = 1.0f; }
+    l1 = fmaxf(l1, 0.0f);
+    l2 = fmaxf(l2, 0.0f);
+    if (!(l1 > 0.0f && l2 > 0.0f)) return 0;
+    const float sd1 = sqrtf(l1), sd2 = sqrtf(l2);
+    const float r1 = 3.0f * sd1, r2 = 3.0f * sd2;
+    const float is1 = 1.0f / sd1, is2 = 1.0f / sd2;
+
+    // :145-152 clip / NDC ; Metal clip volume 0 <= z <= w with w = 1 (D8)
+    float cl[4];
+    mat4_point(U.VP, px, py, pz, cl);
+    const float invW = 1.0f / cl[3];
+    const float ndcx = cl[0] * invW, ndcy = cl[1] * invW, ndcz = cl[2] * invW;
+    if (!(ndcz >= 0.0f && ndcz <= 1.0f)) return 0;
+
+    // viewport transform (y down) and tile rectangle (D9)
+    const float cx = (ndcx * 0.5f + 0.5f) * U.W;
+    const float cy = (0.5f - 0.5f * ndcy) * U.H;
+    const float hx = fabsf(r1 * e1x) + fabsf(r2 * e1y);
+    const float hy = fabsf(r1 * e1y) + fabsf(r2 * e1x);
+    float fi0 = ceilf((cx - hx) - 0.5f), fi1 = floorf((cx + hx) - 0.5f);
+    float fj0 = ceilf((cy - hy) - 0.5f), fj1 = floorf((cy + hy) - 0.5f);
+    const float Wm1 = U.W - 1.0f, Hm1 = U.H - 1.0f;
+    if (!(fi1 >= 0.0f && fi0 <= Wm1 && fj1 >= 0.0f && fj0 <= Hm1 && fi1 >= fi0 && fj1 >= fj0)) return 0;
+    fi0 = fmaxf(fi0, 0.0f); fi1 = fminf(fi1, Wm1);
+    fj0 = fmaxf(fj0, 0.0f); fj1 = fminf(fj1, Hm1);
+    int tx0 = (int)fi0 >> 4, tx1 = (int)fi1 >> 4, ty0 = (int)fj0 >> 4, ty1 = (int)fj1 >> 4;
+    if (ty0 < U.row_begin) ty0 = U.row_begin;
+    if (ty1 > U.row_end - 1) ty1 = U.row_end - 1;
+    if (ty1 < ty0) return 0;
+
+    rec.cx = cx; rec.cy = cy;
+    rec.ux = e1x * is1;    rec.uy = -(e1y * is1);
+    rec.vx = -(e1y * is2); rec.vy = -(e1x * is2);
+    rec.opacity = opacity;
+    rec.rg = rg_half2;
+    rec.bd = b_half | ((unsigned int)__half_as_ushort(__float2half_rn(zFront)) << 16);
+    rec.z_front = zFront;
+    rec.rect_lo = (unsigned int)tx0 | ((unsigned int)ty0 << 16);
+    rec.rect_hi = (unsigned int)tx1 | ((unsigned int)ty1 << 16);
+    return (unsigned int)((tx1 - tx0 + 1) * (ty1 - ty0 + 1));
+}

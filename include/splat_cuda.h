@@ -32,7 +32,10 @@ enum {
     SPLAT_ORDER_REFERENCE  = 1  /* descending zFront: what the shader code literally does
                                    (gaussian_splat_tile.metal:244, 50layer.metal:201)  */
 };
-enum { SPLAT_FLAG_TIMING = 1 /* record per-stage CUDA events (adds event overhead) */ };
+enum {
+    SPLAT_FLAG_TIMING = 1,        /* record per-stage CUDA events (adds event overhead)          */
+    SPLAT_FLAG_KEEP_UNSORTED = 2  /* keep a copy of the unsorted pairs for splat_debug_fetch      */
+};
 
 /* Mirrors src/instanced_splat_renderer.h:6-11 (56 bytes, no padding). */
 typedef struct {
@@ -113,7 +116,7 @@ enum {
     SPLAT_FETCH_RECORDS = 0,     /* splat_record[n]  (culled entries zeroed)  */
     SPLAT_FETCH_TILES_TOUCHED,   /* uint32[n]                                 */
     SPLAT_FETCH_OFFSETS,         /* uint32[n] exclusive scan                  */
-    SPLAT_FETCH_KEYS_UNSORTED,   /* uint64[D]  (re-derived: runs duplication again) */
+    SPLAT_FETCH_KEYS_UNSORTED,   /* uint64[D]  (frame must use SPLAT_FLAG_KEEP_UNSORTED) */
     SPLAT_FETCH_VALS_UNSORTED,   /* uint32[D]                                 */
     SPLAT_FETCH_KEYS_SORTED,     /* uint64[D]                                 */
     SPLAT_FETCH_VALS_SORTED,     /* uint32[D]                                 */

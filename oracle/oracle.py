@@ -61,8 +61,13 @@ def lib():
         L.orb_float_to_half.restype = C.c_uint16; L.orb_float_to_half.argtypes = [C.c_float]
         L.orb_half_to_float.restype = C.c_float; L.orb_half_to_float.argtypes = [C.c_uint16]
         L.orb_sort_pairs.argtypes = [vp, vp, C.c_uint64]
+        L.orb_set_threads.argtypes = [C.c_int]
         _LIB = L
     return _LIB
+
+
+def set_threads(n: int):
+    lib().orb_set_threads(int(n))
 
 
 def _fp(a):

@@ -285,7 +285,11 @@ uint64_t blend_rows(const orb_frame& F, uint16_t* fb, int ty_begin, int ty_end) 
 
 } // namespace
 
+static int g_threads = 1;
+
 extern "C" {
+
+void orb_set_threads(int n) { g_threads = n < 1 ? 1 : n; }
 
 orb_frame* orb_frame_create(const float* inst, uint32_t n, const float* sh_rest,
                             const float* view, const float* proj, int w, int h,
@@ -304,11 +308,23 @@ orb_frame* orb_frame_create(const float* inst, uint32_t n, const float* sh_rest,
 
     /* K1 */
     F->rec.assign(n, orb_record{}); F->touched.assign(n, 0); F->offsets.assign(n, 0);
-    for (uint32_t i = 0; i < n; ++i) {
-        orb_record r{};
-        uint32_t t = preprocess_one(inst + (size_t)i * 14, U, r);
-        if (t) F->rec[i] = r;
-        F->touched[i] = t;
+    {
+        auto work = [&](uint32_t b, uint32_t e) {
+            for (uint32_t i = b; i < e; ++i) {
+                orb_record r{};
+                uint32_t t = preprocess_one(inst + (size_t)i * 14, U, r);
+                if (t) F->rec[i] = r;
+                F->touched[i] = t;
+            }
+        };
+        const int nt = g_threads;
+        if (nt <= 1 || n < 4096) work(0, n);
+        else {
+            std::vector<std::thread> th;
+            for (int t = 0; t < nt; ++t)
+                th.emplace_back(work, (uint32_t)((uint64_t)n * t / nt), (uint32_t)((uint64_t)n * (t + 1) / nt));
+            for (auto& x : th) x.join();
+        }
     }
     /* K2: exclusive scan + duplication, row-major (ty outer, tx inner) */
     uint64_t D = 0;

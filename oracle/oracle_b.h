@@ -69,6 +69,8 @@ orb_frame* orb_frame_create(const float* instances, uint32_t n, const float* sh_
                             const float* view, const float* proj, int w, int h,
                             const orb_opts* opts);
 void orb_frame_destroy(orb_frame*);
+/* Threads used by orb_frame_create's per-splat loop (default 1 = the named single-thread baseline). */
+void orb_set_threads(int n);
 
 uint32_t        orb_n(const orb_frame*);
 uint64_t        orb_num_pairs(const orb_frame*);

@@ -1,0 +1,156 @@
+"""GPU parity: every stage of the CUDA path, through the C ABI, against Oracle-B.
+
+Bar: integer/index work bit-exact (tiles touched, offsets, keys, sorted pairs, ranges);
+records bit-exact (fp32 under pinned arithmetic); image max|diff| <= 1/255 and PSNR >= 50 dB
+(bit-exact is expected and reported).
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _render(ctx, inst, V, P, w, h, **kw):
+    import torch
+    from gaussian_splat_b200 import capi
+    fb = torch.full((h, w, 4), 7.0, dtype=torch.float16, device="cuda:0")
+    opts = capi.make_opts(flags=capi.FLAG_KEEP_UNSORTED, **kw)
+    ctx.render(torch.cuda.current_stream().cuda_stream, fb.data_ptr(), V, P, w, h, opts)
+    torch.cuda.synchronize()
+    st = ctx.status()
+    if st.overflow:      # buffers were grown by status(); render again
+        ctx.render(torch.cuda.current_stream().cuda_stream, fb.data_ptr(), V, P, w, h, opts)
+        torch.cuda.synchronize()
+        st = ctx.status()
+    assert not st.overflow
+    return fb.cpu().numpy().view(np.uint16), st
+
+
+def _psnr(a, b):
+    mse = np.mean((a.astype(np.float64) - b.astype(np.float64)) ** 2)
+    return 200.0 if mse == 0 else 10 * np.log10(1.0 / mse)
+
+
+def _check_all(ctx, inst, V, P, w, h, mode, order, K=0, rows=(0, 0)):
+    from gaussian_splat_b200 import capi
+    from oracle import oracle as O
+    ctx.upload(inst)
+    got, st = _render(ctx, inst, V, P, w, h, mode=mode, order=order, max_fragments=K,
+                      tile_row_begin=rows[0], tile_row_end=rows[1])
+    F = O.Frame(inst, V, P, w, h, mode=mode, order=order, max_fragments=K or None,
+                tile_row_begin=rows[0], tile_row_end=rows[1])
+    assert st.n_pairs == F.D
+    assert np.array_equal(ctx.fetch(capi.FETCH_TILES_TOUCHED), F.tiles_touched)
+    assert np.array_equal(ctx.fetch(capi.FETCH_OFFSETS), F.offsets)
+    rec = ctx.fetch(capi.FETCH_RECORDS)
+    assert rec.tobytes() == F.records.tobytes()
+    assert np.array_equal(ctx.fetch(capi.FETCH_KEYS_UNSORTED), F.keys_unsorted)
+    assert np.array_equal(ctx.fetch(capi.FETCH_VALS_UNSORTED), F.vals_unsorted)
+    assert np.array_equal(ctx.fetch(capi.FETCH_KEYS_SORTED), F.keys_sorted)
+    assert np.array_equal(ctx.fetch(capi.FETCH_VALS_SORTED), F.vals_sorted)
+    assert np.array_equal(ctx.fetch(capi.FETCH_TILE_RANGES), F.tile_ranges)
+    ref = np.full((h, w, 4), np.float16(7.0).view(np.uint16), np.uint16)
+    F.blend(fb=ref)
+    a, b = O.half_bits_to_float(got), O.half_bits_to_float(ref)
+    assert np.abs(a - b).max() <= 1.0 / 255.0          # north_star tolerance
+    assert _psnr(a, b) >= 50.0
+    assert np.array_equal(got, ref), "image expected bit-exact under pinned arithmetic"
+    return F
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("order", [0, 1])
+def test_stages_and_image_small(gpu_ctx, small_scene, mode, order):
+    from oracle import oracle as O
+    w, h = 640, 360
+    V, P = O.app_camera(w, h)
+    F = _check_all(gpu_ctx, small_scene, V, P, w, h, mode, order)
+    assert F.D > 10000
+
+
+@pytest.mark.parametrize("K", [1, 24, 32, 50, 64])
+def test_fragment_caps(gpu_ctx, small_scene, K):
+    from oracle import oracle as O
+    w, h = 320, 200
+    V, P = O.app_camera(w, h, eye=(0.0, 1.0, 9.0))
+    for mode in (0, 1):
+        _check_all(gpu_ctx, small_scene, V, P, w, h, mode, 0, K=K)
+
+
+def test_ragged_viewport_and_band(gpu_ctx, small_scene):
+    """Width/height not multiples of 16, and a tile-row band (multi-GPU partition)."""
+    from oracle import oracle as O
+    w, h = 333, 217
+    V, P = O.app_camera(w, h)
+    _check_all(gpu_ctx, small_scene, V, P, w, h, 0, 0)
+    _check_all(gpu_ctx, small_scene, V, P, w, h, 0, 0, rows=(3, 9))
+    _check_all(gpu_ctx, small_scene, V, P, w, h, 1, 0, rows=(5, 14))
+
+
+def test_empty_and_tiny_scenes(gpu_ctx):
+    import torch
+    from gaussian_splat_b200 import capi, scene
+    from oracle import oracle as O
+    w, h = 128, 96
+    V, P = O.app_camera(w, h)
+    # empty scene: the whole framebuffer is overwritten with zeros
+    gpu_ctx.upload(np.zeros((0, 14), np.float32))
+    fb = torch.full((h, w, 4), 3.0, dtype=torch.float16, device="cuda:0")
+    gpu_ctx.render(torch.cuda.current_stream().cuda_stream, fb.data_ptr(), V, P, w, h, None)
+    torch.cuda.synchronize()
+    assert float(fb.abs().max()) == 0.0
+    # one splat, then three
+    for n in (1, 3, 1025):
+        inst, _ = scene.make_instances(n, 0x77)
+        inst[:, 7:10] *= 0.2
+        inst[:, 4:7] = 0.3
+        _check_all(gpu_ctx, inst, V, P, w, h, 0, 0)
+    # everything behind the camera
+    inst, _ = scene.make_instances(100, 0x78)
+    inst[:, 9] = 50.0
+    F = _check_all(gpu_ctx, inst, V, P, w, h, 0, 0)
+    assert F.D == 0
+
+
+def test_huge_splats_overflow_regrow(gpu_ctx):
+    """Splats covering the whole screen: D >> initial capacity exercises the overflow path."""
+    from gaussian_splat_b200 import scene
+    from oracle import oracle as O
+    w, h = 1024, 768
+    V, P = O.app_camera(w, h)
+    inst, _ = scene.make_instances(600, 0x79)
+    inst[:, 4:7] = 3.0
+    F = _check_all(gpu_ctx, inst, V, P, w, h, 0, 0)
+    assert F.D > (1 << 20)
+
+
+def test_sort_standalone(gpu_ctx):
+    import torch
+    from oracle import oracle as O
+    g = torch.Generator(device="cpu"); g.manual_seed(5)
+    for n, bits in ((1, 64), (4097, 64), (300001, 64), (100000, 48), (50000, 12)):
+        k = torch.randint(0, 2 ** 62, (n,), generator=g, dtype=torch.int64) * 4 + torch.randint(0, 4, (n,), generator=g)
+        if bits < 64:
+            k = k & ((1 << bits) - 1)
+        v = torch.arange(n, dtype=torch.int32)
+        kd, vd = k.cuda(), v.cuda()
+        ka, va = torch.empty_like(kd), torch.empty_like(vd)
+        alt = gpu_ctx.sort_pairs(torch.cuda.current_stream().cuda_stream, kd.data_ptr(), vd.data_ptr(),
+                                 ka.data_ptr(), va.data_ptr(), n, 0, bits)
+        torch.cuda.synchronize()
+        rk, rv = (ka, va) if alt else (kd, vd)
+        ek, ev = O.sort_pairs(k.numpy().view(np.uint64), v.numpy().view(np.uint32))
+        assert np.array_equal(rk.cpu().numpy().view(np.uint64), ek)
+        assert np.array_equal(rv.cpu().numpy().view(np.uint32), ev)
+
+
+def test_render_host_matches_device(gpu_ctx, small_scene):
+    from gaussian_splat_b200 import capi
+    from oracle import oracle as O
+    w, h = 640, 360
+    V, P = O.app_camera(w, h)
+    gpu_ctx.upload(small_scene)
+    dev, _ = _render(gpu_ctx, small_scene, V, P, w, h, mode=0)
+    host = np.zeros((h, w, 4), np.uint16)
+    gpu_ctx.render_host(host.ctypes.data, V, P, w, h, capi.make_opts())
+    assert np.array_equal(host, dev)
