@@ -108,7 +108,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
                     aB = __hadd_rn(aB, __hmul_rn(cb, src));
                     acc = __hadd_rn(acc, src);
                     ++cnt;
-                    if (__hge(acc, __ushort_as_half(0x3BEB)) || cnt >= K) { done = true; break; }
+                    if (__hge(acc, __ushort_as_half(0x3BEC)) || cnt >= K) { done = true; break; }
                 } else {
                     // gaussian_splat_50layer.metal:170-176: first K arrivals (instance order) kept
                     const unsigned int h = bd >> 16;

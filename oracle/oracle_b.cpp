@@ -25,7 +25,7 @@ inline uint16_t hsub(uint16_t a, uint16_t b) { return f2h(h2f(a) - h2f(b)); }
 inline uint16_t hmul(uint16_t a, uint16_t b) { return f2h(h2f(a) * h2f(b)); }
 const uint16_t H_ONE = 0x3C00;
 /* 0.99h and 0.01h as the Metal compiler would round the literals. */
-const uint16_t H_099 = 0x3BEB; /* 0.98974609375 */
+const uint16_t H_099 = 0x3BEC; /* 0.990234375 = RNE(0.99); SURVEY.md quotes the truncated 0x3BEB */
 const uint16_t H_001 = 0x211F; /* 0.010002136   */
 
 /* ------------------------------------------------------------ pinned exp */

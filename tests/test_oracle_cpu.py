@@ -1,0 +1,138 @@
+"""CPU tests of the oracle (Oracle-B) itself: pinned scalar pieces, camera known answers from
+SURVEY 8(c), pipeline invariants and the committed golden fixtures."""
+import math
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def test_half_constants_and_conversion():
+    L = O.lib()
+    assert L.orb_float_to_half(0.99) == 0x3BEC and L.orb_half_to_float(0x3BEC) == 0.990234375
+    assert L.orb_float_to_half(0.01) == 0x211F
+    assert abs(L.orb_half_to_float(0x211F) - 0.010002136) < 1e-9
+    rng = np.random.default_rng(1)
+    x = np.concatenate([rng.standard_normal(2000).astype(np.float32) * 10, np.float32([0, 1e-8, 65504, 1e-5, 6.1e-5])])
+    got = np.array([L.orb_float_to_half(float(v)) for v in x], np.uint16)
+    assert np.array_equal(got, x.astype(np.float16).view(np.uint16))     # RNE, subnormals kept
+
+
+def test_pinned_exp_accuracy():
+    L = O.lib()
+    q = np.linspace(0, 9.3, 4001, dtype=np.float32)
+    got = np.array([L.orb_exp_neg_half(float(v)) for v in q])
+    ref = np.exp(-0.5 * q.astype(np.float64))
+    assert np.max(np.abs(got - ref) / ref) < 3e-7
+    assert L.orb_exp_neg_half(0.0) == 1.0
+
+
+def test_camera_known_answers():
+    # focalX = focalY = 869.1169 @720p, 1303.6753 @1080p, 2607.3506 @4K
+    for (w, h), f in (((1280, 720), 869.1169), ((1920, 1080), 1303.6753), ((3840, 2160), 2607.3506)):
+        P = O.perspective(45.0, w, h)
+        assert abs(P[0] * w * 0.5 - f) < 2e-3 and abs(P[5] * h * 0.5 - f) < 2e-3
+        assert P[11] == -1.0 and P[15] == 0.0
+    # zNDC(zFront): -1 @0.1, ~0 @0.19998, 0.80018 @1, 0.960196 @5, 1 @1000
+    P = O.perspective(45.0, 1280, 720)
+    for z, want in ((0.1, -1.0), (0.19998, 0.0), (1.0, 0.80018), (5.0, 0.960196), (1000.0, 1.0)):
+        ndc = (P[10] * (-z) + P[14]) / z
+        assert abs(ndc - want) < 2e-4
+    V = O.look_at((0, 2, 5), (0, 0, 0), (0, -1, 0))
+    eye_view = V.reshape(4, 4).T @ np.array([0, 2, 5, 1], np.float32)
+    assert np.allclose(eye_view[:3], 0, atol=1e-6)
+    origin_view = V.reshape(4, 4).T @ np.array([0, 0, 0, 1], np.float32)
+    assert abs(-origin_view[2] - math.sqrt(29.0)) < 1e-5          # zFront of the target
+
+
+def test_product_camera_matches_oracle_bitwise():
+    from gaussian_splat_b200 import camera
+    for (w, h) in ((1280, 720), (1920, 1080), (3840, 2160), (333, 217)):
+        for k in range(8):
+            t = 2 * math.pi * k / 8
+            eye = (5 * math.sin(t), 2.0, 5 * math.cos(t))
+            V1, P1 = camera.app_camera(w, h, eye=eye)
+            V2, P2 = O.app_camera(w, h, eye=eye)
+            assert V1.tobytes() == V2.tobytes() and P1.tobytes() == P2.tobytes()
+
+
+def test_pipeline_invariants(small_scene):
+    w, h = 640, 360
+    V, P = O.app_camera(w, h)
+    for mode in (O.MODE_TILE, O.MODE_LAYER50):
+        F = O.Frame(small_scene, V, P, w, h, mode=mode)
+        t = F.tiles_touched.astype(np.int64)
+        assert F.D == t.sum()
+        assert np.array_equal(F.offsets, np.concatenate([[0], np.cumsum(t)[:-1]]).astype(np.uint32))
+        ks, vs = F.keys_sorted, F.vals_sorted
+        assert np.all(ks[1:] >= ks[:-1])
+        order = np.argsort(F.keys_unsorted, kind="stable")
+        assert np.array_equal(ks, F.keys_unsorted[order]) and np.array_equal(vs, F.vals_unsorted[order])
+        tiles = (ks >> np.uint64(32)).astype(np.int64)
+        assert tiles.max() < F.T
+        r = F.tile_ranges
+        cnt = np.bincount(tiles, minlength=F.T)
+        assert np.array_equal((r[:, 1] - r[:, 0]).astype(np.int64), cnt)
+        nz = cnt > 0
+        assert np.array_equal(r[nz, 0].astype(np.int64), (np.cumsum(cnt) - cnt)[nz])
+        rec = F.records
+        vis = t > 0
+        assert np.all(rec["z_front"][vis] >= 0.19) and np.all(rec["z_front"][~vis] == 0)
+        if mode == O.MODE_TILE:
+            assert np.array_equal((ks & np.uint64(0xFFFFFFFF)).astype(np.uint32), rec["bd"][vs] >> 16)
+        else:
+            assert np.array_equal((ks & np.uint64(0xFFFFFFFF)).astype(np.uint32), vs)
+
+
+def test_reference_order_reverses_depth_key(small_scene):
+    w, h = 320, 200
+    V, P = O.app_camera(w, h)
+    a = O.Frame(small_scene, V, P, w, h, order=O.ORDER_NEAR_FIRST)
+    b = O.Frame(small_scene, V, P, w, h, order=O.ORDER_REFERENCE)
+    ka, kb = a.keys_unsorted, b.keys_unsorted
+    assert np.array_equal(ka >> np.uint64(32), kb >> np.uint64(32))
+    assert np.all((ka & np.uint64(0xFFFF)) + (kb & np.uint64(0xFFFF)) == 0xFFFF)
+
+
+def test_bands_compose_to_full_frame(small_scene):
+    """Tile-row bands (the multi-GPU partition) reproduce the single-device image exactly."""
+    w, h = 333, 217
+    V, P = O.app_camera(w, h)
+    full, _ = O.Frame(small_scene, V, P, w, h).blend()
+    fb = np.zeros_like(full)
+    ty = (h + 15) // 16
+    cuts = [0, 3, 4, 9, ty]
+    D = 0
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        F = O.Frame(small_scene, V, P, w, h, tile_row_begin=a, tile_row_end=b)
+        F.blend(fb=fb); D += F.D
+    assert np.array_equal(fb, full)
+    assert D == O.Frame(small_scene, V, P, w, h).D
+
+
+def test_threads_do_not_change_results(small_scene):
+    w, h = 320, 200
+    V, P = O.app_camera(w, h)
+    O.set_threads(1); a = O.Frame(small_scene, V, P, w, h); ia, ta = a.blend(1)
+    O.set_threads(4); b = O.Frame(small_scene, V, P, w, h); ib, tb = b.blend(4)
+    O.set_threads(1)
+    assert np.array_equal(a.keys_sorted, b.keys_sorted) and np.array_equal(ia, ib) and ta == tb
+
+
+@pytest.mark.parametrize("name", ["tile_near", "tile_ref", "layer50_near", "layer50_ref"])
+def test_golden_fixtures(name):
+    """Committed vectors (tests/golden/make_golden.py): guards the oracle against silent drift."""
+    g = np.load(os.path.join(GOLDEN, "golden_small.npz"))
+    inst = g["instances"]; w, h = int(g["w"]), int(g["h"])
+    mode = O.MODE_LAYER50 if name.startswith("layer50") else O.MODE_TILE
+    order = O.ORDER_REFERENCE if name.endswith("ref") else O.ORDER_NEAR_FIRST
+    F = O.Frame(inst, g["view"], g["proj"], w, h, mode=mode, order=order)
+    assert np.array_equal(F.keys_sorted, g[name + "_keys"])
+    assert np.array_equal(F.vals_sorted, g[name + "_vals"])
+    assert np.array_equal(F.tile_ranges, g[name + "_ranges"])
+    img, _ = F.blend()
+    assert np.array_equal(img, g[name + "_image"])
