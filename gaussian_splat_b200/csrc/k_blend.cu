@@ -57,6 +57,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
     __shared__ float4 s_a[BLEND_BATCH];      // cx cy ux uy
     __shared__ float4 s_b[BLEND_BATCH];      // vx vy opacity rg
     __shared__ unsigned int s_c[BLEND_BATCH];// bd
+    __shared__ unsigned int s_m[BLEND_BATCH];// bit b: splat may touch the 8x4 pixel block of warp b
     extern __shared__ unsigned int s_list[]; // LAYER50: [K][256] key|vis, [K][256] rg, [K][256] b (as u32)
 
     const int tx = blockIdx.x, ty = U.row_begin + blockIdx.y;
@@ -75,50 +76,82 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
     int cnt = 0;
     bool done = !inside;
 
+    const unsigned int lane = tid & 31, warp = tid >> 5;
+    const float tox = (float)(tx * 16), toy = (float)(ty * 16);
     for (unsigned int b0 = range.x; b0 < range.y; b0 += BLEND_BATCH) {
         const unsigned int nb = min((unsigned int)BLEND_BATCH, range.y - b0);
+        unsigned int wmask = 0;
         if (tid < nb) {
             const unsigned int si = __ldg(vals + b0 + tid);
             const float4* r = reinterpret_cast<const float4*>(rec + si);
-            s_a[tid] = __ldg(r);
-            s_b[tid] = __ldg(r + 1);
+            const float4 A = __ldg(r), B = __ldg(r + 1);
+            s_a[tid] = A;
+            s_b[tid] = B;
             s_c[tid] = __float_as_uint(__ldg(reinterpret_cast<const float*>(r + 2)));
+            // Conservative pixel AABB of {q <= 9.2103404}: d = Winv (u,v), Winv = [vy -uy; -vx ux] / det.
+            // Only used to skip 8x4 pixel blocks the splat cannot touch; never changes a result.
+            const float det = A.z * B.y - A.w * B.x;
+            const float idet = 1.0f / det;
+            const float hx = 3.0351f * sqrtf(B.y * B.y + A.w * A.w) * fabsf(idet) + 0.01f;
+            const float hy = 3.0351f * sqrtf(B.x * B.x + A.z * A.z) * fabsf(idet) + 0.01f;
+            if (!(hx <= 1e6f && hy <= 1e6f)) wmask = 0xFFu;
+            else {
+                const float x0 = A.x - hx - tox, x1 = A.x + hx - tox, y0 = A.y - hy - toy, y1 = A.y + hy - toy;
+                unsigned int cm = 0, rm = 0;
+                if (x1 >= 0.5f && x0 <= 7.5f) cm |= 1u;
+                if (x1 >= 8.5f && x0 <= 15.5f) cm |= 2u;
+#pragma unroll
+                for (int by = 0; by < 4; ++by)
+                    if (y1 >= 4.0f * by + 0.5f && y0 <= 4.0f * by + 3.5f) rm |= 1u << by;
+#pragma unroll
+                for (int by = 0; by < 4; ++by)
+                    if (rm & (1u << by)) wmask |= cm << (2 * by);
+            }
         }
+        s_m[tid] = wmask;
         __syncthreads();
-        if (!done) {
-            for (unsigned int e = 0; e < nb; ++e) {
-                const float4 A = s_a[e];
-                const float dx = pxc - A.x, dy = pyc - A.y;
-                const float4 B = s_b[e];
-                const float u = fmaf(dx, A.z, dy * A.w);
-                const float v = fmaf(dx, B.x, dy * B.y);
-                const float q = fmaf(u, u, v * v);
-                if (!(fabsf(u) <= 3.0f && fabsf(v) <= 3.0f && q <= 9.2103404f)) continue;
-                const float alpha = exp_neg_half(q) * B.z;
-                const unsigned int rg = __float_as_uint(B.w), bd = s_c[e];
-                const __half cr = __ushort_as_half((unsigned short)(rg & 0xFFFFu));
-                const __half cg = __ushort_as_half((unsigned short)(rg >> 16));
-                const __half cb = __ushort_as_half((unsigned short)(bd & 0xFFFFu));
-                if (MODE == SPLAT_MODE_TILE) {
-                    // gaussian_splat_tile.metal:252-264, each half op rounded separately (D7)
-                    const __half ah = __float2half_rn(alpha);
-                    const __half src = __hmul_rn(ah, __hsub_rn(h_one, acc));
-                    aR = __hadd_rn(aR, __hmul_rn(cr, src));
-                    aG = __hadd_rn(aG, __hmul_rn(cg, src));
-                    aB = __hadd_rn(aB, __hmul_rn(cb, src));
-                    acc = __hadd_rn(acc, src);
-                    ++cnt;
-                    if (__hge(acc, __ushort_as_half(0x3BEC)) || cnt >= K) { done = true; break; }
-                } else {
-                    // gaussian_splat_50layer.metal:170-176: first K arrivals (instance order) kept
-                    const unsigned int h = bd >> 16;
-                    const unsigned int dk = U.order == SPLAT_ORDER_REFERENCE ? (0xFFFFu - h) : h;
-                    const unsigned int vis = hbits(__float2half_rn(1.0f - alpha));
-                    s_list[(0 * K + cnt) * BLEND_THREADS + tid] = (dk << 16) | vis;
-                    s_list[(1 * K + cnt) * BLEND_THREADS + tid] = rg;
-                    s_list[(2 * K + cnt) * BLEND_THREADS + tid] = bd & 0xFFFFu;
-                    if (++cnt >= K) { done = true; break; }
+        if (!__all_sync(0xFFFFFFFFu, done)) {
+            for (unsigned int c0 = 0; c0 < nb; c0 += 32) {
+                unsigned int bits = __ballot_sync(0xFFFFFFFFu, (s_m[c0 + lane] >> warp) & 1u);
+                while (bits) {
+                    const unsigned int e = c0 + __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    if (done) continue;
+                    const float4 A = s_a[e];
+                    const float dx = pxc - A.x, dy = pyc - A.y;
+                    const float4 B = s_b[e];
+                    const float u = fmaf(dx, A.z, dy * A.w);
+                    const float v = fmaf(dx, B.x, dy * B.y);
+                    const float q = fmaf(u, u, v * v);
+                    if (!(q <= 9.2103404f)) continue;
+                    if (!(fabsf(u) <= 3.0f && fabsf(v) <= 3.0f)) continue;
+                    const float alpha = exp_neg_half(q) * B.z;
+                    const unsigned int rg = __float_as_uint(B.w), bd = s_c[e];
+                    const __half cr = __ushort_as_half((unsigned short)(rg & 0xFFFFu));
+                    const __half cg = __ushort_as_half((unsigned short)(rg >> 16));
+                    const __half cb = __ushort_as_half((unsigned short)(bd & 0xFFFFu));
+                    if (MODE == SPLAT_MODE_TILE) {
+                        // gaussian_splat_tile.metal:252-264, each half op rounded separately (D7)
+                        const __half ah = __float2half_rn(alpha);
+                        const __half src = __hmul_rn(ah, __hsub_rn(h_one, acc));
+                        aR = __hadd_rn(aR, __hmul_rn(cr, src));
+                        aG = __hadd_rn(aG, __hmul_rn(cg, src));
+                        aB = __hadd_rn(aB, __hmul_rn(cb, src));
+                        acc = __hadd_rn(acc, src);
+                        ++cnt;
+                        if (__hge(acc, __ushort_as_half(0x3BEC)) || cnt >= K) done = true;
+                    } else {
+                        // gaussian_splat_50layer.metal:170-176: first K arrivals (instance order) kept
+                        const unsigned int h = bd >> 16;
+                        const unsigned int dk = U.order == SPLAT_ORDER_REFERENCE ? (0xFFFFu - h) : h;
+                        const unsigned int vis = hbits(__float2half_rn(1.0f - alpha));
+                        s_list[(0 * K + cnt) * BLEND_THREADS + tid] = (dk << 16) | vis;
+                        s_list[(1 * K + cnt) * BLEND_THREADS + tid] = rg;
+                        s_list[(2 * K + cnt) * BLEND_THREADS + tid] = bd & 0xFFFFu;
+                        if (++cnt >= K) done = true;
+                    }
                 }
+                if (__all_sync(0xFFFFFFFFu, done)) break;
             }
         }
         if (__syncthreads_and(done)) break;
