@@ -48,16 +48,36 @@ __device__ __forceinline__ void pixel_of_thread(int& lx, int& ly) {
     ly = (warp >> 1) * 4 + (lane >> 3);
 }
 
+// Shared-memory access by 32-bit shared-window address kept in a register: the compiler
+// otherwise rematerialises the window base (S2R SR_CgaCtaId + LEA) inside the hot loop.
+__device__ __forceinline__ unsigned int smem_addr(const void* p) {
+    unsigned int a = (unsigned int)__cvta_generic_to_shared(p), o;
+    asm volatile("mov.u32 %0, %1;" : "=r"(o) : "r"(a));     // opaque: not rematerialisable
+    return o;
+}
+template <int OFS>
+__device__ __forceinline__ float4 lds128(unsigned int a) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4+%5];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a), "n"(OFS));
+    return v;
+}
+template <int OFS>
+__device__ __forceinline__ unsigned int lds32(unsigned int a) {
+    unsigned int v;
+    asm volatile("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(a), "n"(OFS));
+    return v;
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
     const __grid_constant__ FrameUniforms U, const splat_record* __restrict__ rec,
     const unsigned int* __restrict__ vals, const uint2* __restrict__ ranges, const FrameCtl* __restrict__ ctl,
     uint2* __restrict__ fb)
 {
-    __shared__ float4 s_a[BLEND_BATCH];      // cx cy ux uy
-    __shared__ float4 s_b[BLEND_BATCH];      // vx vy opacity rg
-    __shared__ unsigned int s_c[BLEND_BATCH];// bd
-    __shared__ unsigned int s_m[BLEND_BATCH];// bit b: splat may touch the 8x4 pixel block of warp b
+    __shared__ float4 s_ab[2 * BLEND_BATCH];  // [0..B): cx cy ux uy   [B..2B): vx vy opacity rg
+    __shared__ unsigned int s_cm[2 * BLEND_BATCH];  // [0..B): bd   [B..2B): bit b = may touch the 8x4 block of warp b
+    float4* const s_a = s_ab; float4* const s_b = s_ab + BLEND_BATCH;
+    unsigned int* const s_c = s_cm; unsigned int* const s_m = s_cm + BLEND_BATCH;
     extern __shared__ unsigned int s_list[]; // LAYER50: [K][256] key|vis, [K][256] rg, [K][256] b (as u32)
 
     const int tx = blockIdx.x, ty = U.row_begin + blockIdx.y;
@@ -69,12 +89,19 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
     const uint2 range = ctl->overflow ? make_uint2(0, 0) : ranges[tile];
     const int K = U.K;
     const unsigned int tid = threadIdx.x;
+    const unsigned int a_ab = smem_addr(s_ab), a_cm = smem_addr(s_cm);
 
-    __half aR = __ushort_as_half(0), aG = aR, aB = aR;
+    // TILE: (aR, aG) and (aB, accumAlpha) as two half2 accumulators; every half op below is an
+    // _rn intrinsic (rounded separately, never contracted: DESIGN.md D7).
+    __half2 accRG = __halves2half2(__ushort_as_half(0), __ushort_as_half(0));
+    __half2 accBA = accRG;
     const __half h_one = __ushort_as_half(0x3C00);
-    __half acc = (MODE == SPLAT_MODE_LAYER50) ? h_one : __ushort_as_half(0);
-    int cnt = 0;
-    bool done = !inside;
+    // LAYER50 accumulators
+    __half aR = __ushort_as_half(0), aG = aR, aB = aR, acc = h_one;
+    // cnt counts kept fragments; cnt >= K doubles as "this pixel is finished" (cap reached,
+    // alpha saturated, or pixel outside the viewport), so the hot loop carries one counter only.
+    int cnt = inside ? 0 : K;
+#define done (cnt >= K)
 
     const unsigned int lane = tid & 31, warp = tid >> 5;
     const float tox = (float)(tx * 16), toy = (float)(ty * 16);
@@ -116,30 +143,24 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
                 while (bits) {
                     const unsigned int e = c0 + __ffs(bits) - 1;
                     bits &= bits - 1;
-                    if (done) continue;
-                    const float4 A = s_a[e];
+                    const float4 A = lds128<0>(a_ab + e * 16u);
+                    const float4 B = lds128<BLEND_BATCH * 16>(a_ab + e * 16u);
                     const float dx = pxc - A.x, dy = pyc - A.y;
-                    const float4 B = s_b[e];
                     const float u = fmaf(dx, A.z, dy * A.w);
                     const float v = fmaf(dx, B.x, dy * B.y);
                     const float q = fmaf(u, u, v * v);
-                    if (!(q <= 9.2103404f)) continue;
-                    if (!(fabsf(u) <= 3.0f && fabsf(v) <= 3.0f)) continue;
+                    if (done || !(q <= 9.2103404f) || !(fabsf(u) <= 3.0f) || !(fabsf(v) <= 3.0f)) continue;
                     const float alpha = exp_neg_half(q) * B.z;
-                    const unsigned int rg = __float_as_uint(B.w), bd = s_c[e];
-                    const __half cr = __ushort_as_half((unsigned short)(rg & 0xFFFFu));
-                    const __half cg = __ushort_as_half((unsigned short)(rg >> 16));
-                    const __half cb = __ushort_as_half((unsigned short)(bd & 0xFFFFu));
+                    const unsigned int rg = __float_as_uint(B.w), bd = lds32<0>(a_cm + e * 4u);
                     if (MODE == SPLAT_MODE_TILE) {
-                        // gaussian_splat_tile.metal:252-264, each half op rounded separately (D7)
+                        // gaussian_splat_tile.metal:252-264
                         const __half ah = __float2half_rn(alpha);
-                        const __half src = __hmul_rn(ah, __hsub_rn(h_one, acc));
-                        aR = __hadd_rn(aR, __hmul_rn(cr, src));
-                        aG = __hadd_rn(aG, __hmul_rn(cg, src));
-                        aB = __hadd_rn(aB, __hmul_rn(cb, src));
-                        acc = __hadd_rn(acc, src);
-                        ++cnt;
-                        if (__hge(acc, __ushort_as_half(0x3BEC)) || cnt >= K) done = true;
+                        const __half src = __hmul_rn(ah, __hsub_rn(h_one, __high2half(accBA)));
+                        const __half2 src2 = __half2half2(src);
+                        const unsigned int b1 = (bd & 0xFFFFu) | 0x3C000000u;      // (b, 1.0h): 1.0h * src == src
+                        accRG = __hadd2_rn(accRG, __hmul2_rn(*reinterpret_cast<const __half2*>(&rg), src2));
+                        accBA = __hadd2_rn(accBA, __hmul2_rn(*reinterpret_cast<const __half2*>(&b1), src2));
+                        cnt = __hge(__high2half(accBA), __ushort_as_half(0x3BEC)) ? K : cnt + 1;
                     } else {
                         // gaussian_splat_50layer.metal:170-176: first K arrivals (instance order) kept
                         const unsigned int h = bd >> 16;
@@ -148,7 +169,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
                         s_list[(0 * K + cnt) * BLEND_THREADS + tid] = (dk << 16) | vis;
                         s_list[(1 * K + cnt) * BLEND_THREADS + tid] = rg;
                         s_list[(2 * K + cnt) * BLEND_THREADS + tid] = bd & 0xFFFFu;
-                        if (++cnt >= K) done = true;
+                        ++cnt;
                     }
                 }
                 if (__all_sync(0xFFFFFFFFu, done)) break;
@@ -157,11 +178,12 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
         if (__syncthreads_and(done)) break;
     }
 
+#undef done
     if (!inside) return;
     uint2 out;
     if (MODE == SPLAT_MODE_TILE) {
-        out.x = (unsigned int)hbits(aR) | ((unsigned int)hbits(aG) << 16);
-        out.y = (unsigned int)hbits(aB) | ((unsigned int)hbits(acc) << 16);
+        out.x = *reinterpret_cast<const unsigned int*>(&accRG);
+        out.y = *reinterpret_cast<const unsigned int*>(&accBA);
     } else if (cnt == 0) {
         out = make_uint2(0, 0);
     } else {

@@ -29,25 +29,26 @@ const uint16_t H_099 = 0x3BEC; /* 0.990234375 = RNE(0.99); SURVEY.md quotes the 
 const uint16_t H_001 = 0x211F; /* 0.010002136   */
 
 /* ------------------------------------------------------------ pinned exp */
-/* exp(-0.5*q) for q in [0, ~9.3]: Cody-Waite reduction + degree-6 Horner in
- * explicit fmaf. The CUDA kernel carries the same constants and sequence. */
+/* exp(-0.5*q) for q in [0, ~9.3] as 2^t, t = q * (-0.5*log2 e): round-to-int by the
+ * 1.5*2^23 magic add (no cvt), f = t - n in [-0.5, 0.5] exact, degree-5 minimax 2^f in
+ * explicit fmaf (max rel. error 9e-8), exponent added as an integer. The CUDA kernel
+ * carries the same constants and sequence (splat_math.cuh). */
 inline float exp_neg_half(float q) {
-    const float x = -0.5f * q;
-    const float t = x * 1.44269502162933349609375f;          /* log2(e) */
-    const float n = std::rint(t);
-    float r = std::fmaf(n, -0.693145751953125f, x);           /* ln2 hi  */
-    r = std::fmaf(n, -1.428606765330187045037746429443359375e-06f, r); /* ln2 lo */
-    float p = 1.0f / 720.0f;
-    p = std::fmaf(p, r, 1.0f / 120.0f);
-    p = std::fmaf(p, r, 1.0f / 24.0f);
-    p = std::fmaf(p, r, 1.0f / 6.0f);
-    p = std::fmaf(p, r, 0.5f);
-    p = std::fmaf(p, r, 1.0f);
-    p = std::fmaf(p, r, 1.0f);
-    const int32_t e = (int32_t)n + 127;
-    uint32_t sb = (uint32_t)e << 23;
-    float s; std::memcpy(&s, &sb, 4);
-    return p * s;
+    const float t = q * -0.72134752044448170368f;
+    const float s = t + 12582912.0f;
+    const float n = s - 12582912.0f;
+    const float f = t - n;
+    float p = 0.0013264764565974474f;
+    p = std::fmaf(p, f, 0.009671512991189957f);
+    p = std::fmaf(p, f, 0.05550733581185341f);
+    p = std::fmaf(p, f, 0.24022242426872253f);
+    p = std::fmaf(p, f, 0.6931470036506653f);
+    p = std::fmaf(p, f, 1.0f);
+    uint32_t pb, sb;
+    std::memcpy(&pb, &p, 4); std::memcpy(&sb, &s, 4);
+    pb += sb << 23;                       /* low bits of s hold n (two's complement) */
+    float r; std::memcpy(&r, &pb, 4);
+    return r;
 }
 
 /* ------------------------------------------------------------ S1 helpers */

@@ -27,7 +27,7 @@ def test_pinned_exp_accuracy():
     q = np.linspace(0, 9.3, 4001, dtype=np.float32)
     got = np.array([L.orb_exp_neg_half(float(v)) for v in q])
     ref = np.exp(-0.5 * q.astype(np.float64))
-    assert np.max(np.abs(got - ref) / ref) < 3e-7
+    assert np.max(np.abs(got - ref) / ref) < 5e-7
     assert L.orb_exp_neg_half(0.0) == 1.0
 
 
