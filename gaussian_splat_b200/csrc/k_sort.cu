@@ -7,6 +7,7 @@
 #include "splat_internal.cuh"
 
 #define SORT_WARPS (SORT_THREADS / 32)
+#define LB_DEPTH 8
 
 __global__ void __launch_bounds__(256) sort_histogram_kernel(const unsigned long long* __restrict__ keys,
                                                              unsigned long long n, FrameCtl* ctl,
@@ -51,20 +52,22 @@ __device__ __forceinline__ unsigned int block_excl_scan_256(unsigned int v, unsi
     return base + incl - v;
 }
 
-__global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_pass_kernel(
+template <int ITEMS>
+__global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 4) onesweep_pass_kernel(
     const unsigned long long* __restrict__ keys_in, const unsigned int* __restrict__ vals_in,
     unsigned long long* __restrict__ keys_out, unsigned int* __restrict__ vals_out,
     FrameCtl* ctl, unsigned long long* status, unsigned int epoch, int pass, int shift, unsigned int mask)
 {
-    __shared__ unsigned long long s_keys[SORT_TILE_KEYS];          // reused for values
+    constexpr int TILE_KEYS = SORT_THREADS * ITEMS;
+    extern __shared__ unsigned long long s_keys[];                 // [TILE_KEYS] keys, then values
     __shared__ unsigned int s_wh[SORT_WARPS][256];
     __shared__ unsigned int s_gexcl[256], s_off[256], s_w[SORT_WARPS];
     __shared__ unsigned int s_tile;
-    unsigned int* s_vals = reinterpret_cast<unsigned int*>(s_keys);
+    unsigned int* s_vals = reinterpret_cast<unsigned int*>(s_keys + TILE_KEYS);
 
     if (ctl->overflow) return;
     const unsigned int n = ctl->n_sort;
-    const unsigned int n_tiles = (n + SORT_TILE_KEYS - 1) / SORT_TILE_KEYS;
+    const unsigned int n_tiles = (n + TILE_KEYS - 1) / TILE_KEYS;
     const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned int lt_mask = (1u << lane) - 1u;
 
@@ -79,20 +82,20 @@ __global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_pass_kernel(
         __syncthreads();
         const unsigned int tile = s_tile;
         if (tile >= n_tiles) break;
-        const unsigned int tbase = tile * SORT_TILE_KEYS;
-        const unsigned int tcount = min((unsigned int)SORT_TILE_KEYS, n - tbase);
+        const unsigned int tbase = tile * TILE_KEYS;
+        const unsigned int tcount = min((unsigned int)TILE_KEYS, n - tbase);
 
         // ---- load (warp-striped: order (warp, item, lane) == memory order)
-        unsigned long long key[SORT_ITEMS];
-        unsigned int val[SORT_ITEMS];
-        const unsigned int wofs = warp * (32 * SORT_ITEMS) + lane;
+        unsigned long long key[ITEMS];
+        unsigned int val[ITEMS];
+        const unsigned int wofs = warp * (32 * ITEMS) + lane;
 #pragma unroll
-        for (int i = 0; i < SORT_ITEMS; ++i) {
+        for (int i = 0; i < ITEMS; ++i) {
             const unsigned int li = wofs + i * 32;
             key[i] = li < tcount ? keys_in[tbase + li] : ~0ull;
         }
 #pragma unroll
-        for (int i = 0; i < SORT_ITEMS; ++i) {
+        for (int i = 0; i < ITEMS; ++i) {
             const unsigned int li = wofs + i * 32;
             val[i] = li < tcount ? vals_in[tbase + li] : 0u;
         }
@@ -101,9 +104,9 @@ __global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_pass_kernel(
         __syncwarp();
 
         // ---- per-warp ranks
-        unsigned int rank[SORT_ITEMS];
+        unsigned int rank[ITEMS];
 #pragma unroll
-        for (int i = 0; i < SORT_ITEMS; ++i) {
+        for (int i = 0; i < ITEMS; ++i) {
             const unsigned int d = (unsigned int)(key[i] >> shift) & mask;
             const unsigned int peers = __match_any_sync(0xFFFFFFFFu, d);
             const int leader = __ffs(peers) - 1;
@@ -119,7 +122,7 @@ __global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_pass_kernel(
         unsigned int cnt = 0;
 #pragma unroll
         for (int w = 0; w < SORT_WARPS; ++w) cnt += s_wh[w][tid];
-        const unsigned int valid_cnt = cnt - (tid == mask ? (SORT_TILE_KEYS - tcount) : 0u);
+        const unsigned int valid_cnt = cnt - (tid == mask ? (TILE_KEYS - tcount) : 0u);
         unsigned long long* st = status + (size_t)tile * 256 + tid;
         lb_store(st, lb_pack(epoch, tile == 0 ? LB_FLAG_INC : LB_FLAG_AGG, valid_cnt));
         unsigned int tot;
@@ -129,59 +132,80 @@ __global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_pass_kernel(
 #pragma unroll
             for (int w = 0; w < SORT_WARPS; ++w) { const unsigned int t = s_wh[w][tid]; s_wh[w][tid] = run; run += t; }
         }
+        __syncthreads();
+        // ---- pairs: registers -> shared at their tile-local rank (frees the registers before the
+        // lookback; global offsets are not needed yet)
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+            const unsigned int d = (unsigned int)(key[i] >> shift) & mask;
+            const unsigned int r = rank[i] + s_wh[warp][d];
+            s_keys[r] = key[i];
+            s_vals[r] = val[i];
+        }
+        // Decoupled lookback, LB_DEPTH predecessors in flight per step: with every tile of a small
+        // sort resident at once, a one-at-a-time walk is a serial chain of L2 round trips.
         unsigned int prefix = 0;
-        for (int look = (int)tile - 1; look >= 0; --look) {
-            const unsigned long long* p = status + (size_t)look * 256 + tid;
-            unsigned long long wd;
-            do { wd = lb_load(p); } while ((unsigned int)(wd >> 34) != epoch || ((wd >> 32) & 3ull) == 0);
-            prefix += (unsigned int)wd;
-            if (((wd >> 32) & 3ull) == LB_FLAG_INC) break;
+        for (int look = (int)tile - 1; look >= 0; look -= LB_DEPTH) {
+            unsigned long long wd[LB_DEPTH];
+#pragma unroll
+            for (int j = 0; j < LB_DEPTH; ++j)
+                if (look - j >= 0) wd[j] = lb_load(status + (size_t)(look - j) * 256 + tid);
+            bool stop = false;
+#pragma unroll
+            for (int j = 0; j < LB_DEPTH; ++j) {
+                if (look - j >= 0 && !stop) {
+                    while ((unsigned int)(wd[j] >> 34) != epoch || ((wd[j] >> 32) & 3ull) == 0)
+                        wd[j] = lb_load(status + (size_t)(look - j) * 256 + tid);
+                    prefix += (unsigned int)wd[j];
+                    stop = ((wd[j] >> 32) & 3ull) == LB_FLAG_INC;
+                }
+            }
+            if (stop) break;
         }
         if (tile != 0) lb_store(st, lb_pack(epoch, LB_FLAG_INC, prefix + valid_cnt));
         s_off[tid] = s_gexcl[tid] + prefix - lexcl;
         __syncthreads();
 
-        // ---- keys: registers -> shared (tile-sorted) -> global (coalesced per digit run)
+        // ---- shared (tile-sorted) -> global (contiguous per digit run)
 #pragma unroll
-        for (int i = 0; i < SORT_ITEMS; ++i) {
-            const unsigned int d = (unsigned int)(key[i] >> shift) & mask;
-            rank[i] += s_wh[warp][d];
-            s_keys[rank[i]] = key[i];
-        }
-        __syncthreads();
-        unsigned int goff[SORT_ITEMS];
-#pragma unroll
-        for (int i = 0; i < SORT_ITEMS; ++i) {
+        for (int i = 0; i < ITEMS; ++i) {
             const unsigned int j = tid + i * SORT_THREADS;
             if (j < tcount) {
                 const unsigned long long k = s_keys[j];
-                goff[i] = s_off[(unsigned int)(k >> shift) & mask] + j;
-                keys_out[goff[i]] = k;
+                const unsigned int g = s_off[(unsigned int)(k >> shift) & mask] + j;
+                keys_out[g] = k;
+                vals_out[g] = s_vals[j];
             }
-        }
-        __syncthreads();
-        // ---- values through the same shared buffer
-#pragma unroll
-        for (int i = 0; i < SORT_ITEMS; ++i) s_vals[rank[i]] = val[i];
-        __syncthreads();
-#pragma unroll
-        for (int i = 0; i < SORT_ITEMS; ++i) {
-            const unsigned int j = tid + i * SORT_THREADS;
-            if (j < tcount) vals_out[goff[i]] = s_vals[j];
         }
     }
 }
 
-void launch_radix_sort(unsigned long long* keys, unsigned int* vals, unsigned long long* keys_alt,
-                       unsigned int* vals_alt, FrameCtl* ctl, unsigned long long* sort_status,
-                       unsigned int epoch_base, SortPlan plan, int grid, cudaStream_t s)
+template <int ITEMS>
+static void run_passes(unsigned long long* ki, unsigned int* vi, unsigned long long* ko, unsigned int* vo, FrameCtl* ctl,
+                       unsigned long long* sort_status, unsigned int epoch_base, const SortPlan& plan, int grid,
+                       cudaStream_t s)
 {
-    unsigned long long* ki = keys; unsigned int* vi = vals;
-    unsigned long long* ko = keys_alt; unsigned int* vo = vals_alt;
+    constexpr int smem = SORT_THREADS * ITEMS * 12;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(onesweep_pass_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        attr_set = true;
+    }
     for (int p = 0; p < plan.n_pass; ++p) {
-        onesweep_pass_kernel<<<grid, SORT_THREADS, 0, s>>>(ki, vi, ko, vo, ctl, sort_status, epoch_base + p, p,
-                                                           plan.shift[p], plan.mask[p]);
+        onesweep_pass_kernel<ITEMS><<<grid, SORT_THREADS, smem, s>>>(ki, vi, ko, vo, ctl, sort_status, epoch_base + p, p,
+                                                                    plan.shift[p], plan.mask[p]);
         unsigned long long* tk = ki; ki = ko; ko = tk;
         unsigned int* tv = vi; vi = vo; vo = tv;
     }
+}
+
+// small_tiles: 2048-pair tiles, 4 CTAs per SM. A frame-sized sort (a few hundred 4096-pair tiles, all
+// resident at once) is bounded by the latency of ONE tile's rank/scan/scatter chain, which halves with
+// the tile; large sorts keep 4096-pair tiles for longer contiguous digit runs in the scatter.
+void launch_radix_sort(unsigned long long* keys, unsigned int* vals, unsigned long long* keys_alt,
+                       unsigned int* vals_alt, FrameCtl* ctl, unsigned long long* sort_status,
+                       unsigned int epoch_base, SortPlan plan, int sm_count, bool small_tiles, cudaStream_t s)
+{
+    if (small_tiles) run_passes<SORT_ITEMS_SMALL>(keys, vals, keys_alt, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * 4, s);
+    else run_passes<SORT_ITEMS>(keys, vals, keys_alt, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * 2, s);
 }

@@ -33,7 +33,7 @@ struct splat_ctx {
     unsigned long long* dbg_keys = nullptr; uint32_t* dbg_vals = nullptr; unsigned long long dbg_cap = 0;
     FrameCtl* ctl = nullptr; FrameCtl* ctl_host = nullptr;
     unsigned long long *scan_status = nullptr, *sort_status = nullptr; size_t sort_status_tiles = 0;
-    uint2* ranges = nullptr; uint32_t ranges_cap = 0;
+    uint32_t* bounds = nullptr; uint32_t ranges_cap = 0;   // [T+1] first sorted pair of every tile
     uint32_t frame_no = 0;
     FrameUniforms lastU{}; SortPlan lastPlan{}; int sorted_buf = 0; bool have_frame = false, kept_unsorted = false;
     cudaEvent_t ev[6] = {}; bool timed = false;
@@ -62,7 +62,7 @@ static int free_pairs(splat_ctx* c) {
 }
 
 static int ensure_sort_status(splat_ctx* c, unsigned long long n_keys) {
-    const size_t tiles = (size_t)((n_keys + SORT_TILE_KEYS - 1) / SORT_TILE_KEYS) + 1;
+    const size_t tiles = (size_t)((n_keys + SORT_TILE_KEYS_SMALL - 1) / SORT_TILE_KEYS_SMALL) + 1;
     if (tiles <= c->sort_status_tiles) return 0;
     CK(cudaDeviceSynchronize());
     cudaFree(c->sort_status); c->sort_status = nullptr;
@@ -125,7 +125,7 @@ int splat_destroy(splat_ctx* c) {
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     free_scene(c); free_pairs(c);
-    cudaFree(c->dbg_keys); cudaFree(c->dbg_vals); cudaFree(c->ranges); cudaFree(c->ctl); cudaFree(c->fb_scratch);
+    cudaFree(c->dbg_keys); cudaFree(c->dbg_vals); cudaFree(c->bounds); cudaFree(c->ctl); cudaFree(c->fb_scratch);
     cudaFreeHost(c->ctl_host);
     for (int k = 0; k < 6; ++k) if (c->ev[k]) cudaEventDestroy(c->ev[k]);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -231,8 +231,8 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
     const unsigned int T = (unsigned int)(U.tiles_x * U.tiles_y);
     if (T > c->ranges_cap) {
         CK(cudaDeviceSynchronize());
-        cudaFree(c->ranges); c->ranges = nullptr;
-        CK(cudaMalloc(&c->ranges, (size_t)T * 8));
+        cudaFree(c->bounds); c->bounds = nullptr;
+        CK(cudaMalloc(&c->bounds, ((size_t)T + 1) * 4));
         c->ranges_cap = T;
     }
     const bool timed = (flags & SPLAT_FLAG_TIMING) != 0;
@@ -259,14 +259,15 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
             CK(cudaMemcpyAsync(c->dbg_vals, c->vals[0], c->capacity * 4, cudaMemcpyDeviceToDevice, s));
         }
         if (timed) CK(cudaEventRecord(c->ev[2], s));
+        // tile size by the expected pair count (the exact D only exists on the device): ~3 pairs per splat
         launch_radix_sort(c->keys[0], c->vals[0], c->keys[1], c->vals[1], c->ctl, c->sort_status, epoch + 1, plan,
-                          c->sm_count * 2, s);
+                          c->sm_count, (unsigned long long)c->n * 2ull < 6000000ull, s);
     } else if (timed) { CK(cudaEventRecord(c->ev[1], s)); CK(cudaEventRecord(c->ev[2], s)); }
     if (timed) CK(cudaEventRecord(c->ev[3], s));
     const int sb = plan.n_pass & 1;
-    launch_tile_ranges(c->keys[sb], c->ctl, T, c->ranges, s);
+    launch_tile_bounds(c->keys[sb], c->ctl, T, c->bounds, s);
     if (timed) CK(cudaEventRecord(c->ev[4], s));
-    launch_blend(U, c->rec, c->vals[sb], c->ranges, c->ctl, fb, s);
+    launch_blend(U, c->rec, c->vals[sb], c->bounds, fb, s);
     if (timed) CK(cudaEventRecord(c->ev[5], s));
     CK(cudaGetLastError());
     c->lastU = U; c->lastPlan = plan; c->sorted_buf = sb; c->have_frame = true; c->timed = timed; c->kept_unsorted = keep;
@@ -375,7 +376,7 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
         case SPLAT_FETCH_VALS_UNSORTED: src = c->dbg_vals; need = D * 4; break;
         case SPLAT_FETCH_KEYS_SORTED:   src = c->keys[c->sorted_buf]; need = D * 8; break;
         case SPLAT_FETCH_VALS_SORTED:   src = c->vals[c->sorted_buf]; need = D * 4; break;
-        case SPLAT_FETCH_TILE_RANGES:   src = c->ranges;   need = T * 8; break;
+        case SPLAT_FETCH_TILE_RANGES:   src = nullptr;     need = T * 8; break;   // built from bounds below
         default: ARG_FAIL("splat_debug_fetch: unknown item");
     }
     if ((what == SPLAT_FETCH_KEYS_UNSORTED || what == SPLAT_FETCH_VALS_UNSORTED) && !c->kept_unsorted) {
@@ -383,7 +384,17 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
     }
     if (!dst) { *bytes = need; return SPLAT_OK; }
     if (*bytes < need) { *bytes = need; ARG_FAIL("splat_debug_fetch: destination too small"); }
-    if (need) CK(cudaMemcpy(dst, src, need, cudaMemcpyDeviceToHost));
+    if (what == SPLAT_FETCH_TILE_RANGES) {
+        uint32_t* b = new uint32_t[T + 1];
+        cudaError_t e = cudaMemcpy(b, c->bounds, (T + 1) * 4, cudaMemcpyDeviceToHost);
+        uint32_t* r = (uint32_t*)dst;
+        for (size_t t = 0; t < T && e == cudaSuccess; ++t) {
+            const bool any = b[t] < b[t + 1];
+            r[2 * t] = any ? b[t] : 0u; r[2 * t + 1] = any ? b[t + 1] : 0u;
+        }
+        delete[] b;
+        CK(e);
+    } else if (need) CK(cudaMemcpy(dst, src, need, cudaMemcpyDeviceToHost));
     if (what == SPLAT_FETCH_RECORDS && c->n) {
         // culled splats have no record written: present them zeroed
         uint32_t* t = new uint32_t[c->n];
@@ -433,7 +444,7 @@ int splat_sort_pairs_u64_u32(splat_ctx* c, void* stream, uint64_t* keys, uint32_
     set_n_sort_kernel<<<1, 1, 0, s>>>(c->ctl, (unsigned int)n);
     launch_sort_histogram((const unsigned long long*)keys, n, c->ctl, plan, c->sm_count, s);
     launch_radix_sort((unsigned long long*)keys, vals, (unsigned long long*)keys_alt, vals_alt, c->ctl, c->sort_status,
-                      c->frame_no * 16u + 1, plan, c->sm_count * 2, s);
+                      c->frame_no * 16u + 1, plan, c->sm_count, n < 6000000ull, s);
     CK(cudaGetLastError());
     c->have_frame = false;
     return SPLAT_OK;

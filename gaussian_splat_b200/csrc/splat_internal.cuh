@@ -8,7 +8,9 @@
 #define SPLAT_MAX_SORT_PASSES 8
 #define SORT_THREADS 256
 #define SORT_ITEMS 16
-#define SORT_TILE_KEYS (SORT_THREADS * SORT_ITEMS)   // keys per onesweep tile
+#define SORT_ITEMS_SMALL 8
+#define SORT_TILE_KEYS (SORT_THREADS * SORT_ITEMS)   // keys per onesweep tile (large sorts)
+#define SORT_TILE_KEYS_SMALL (SORT_THREADS * SORT_ITEMS_SMALL)  // frame-sized sorts
 #define SCAN_THREADS 256
 #define SCAN_ITEMS 4
 #define SCAN_TILE_ITEMS (SCAN_THREADS * SCAN_ITEMS)  // splats per scan/duplicate tile
@@ -86,9 +88,10 @@ void launch_sort_histogram(const unsigned long long* keys, unsigned long long n,
 // plan.n_pass is even, in (keys_alt, vals_alt) when odd. Uses epochs epoch_base .. +n_pass-1.
 void launch_radix_sort(unsigned long long* keys, unsigned int* vals, unsigned long long* keys_alt,
                        unsigned int* vals_alt, FrameCtl* ctl, unsigned long long* sort_status,
-                       unsigned int epoch_base, SortPlan plan, int grid, cudaStream_t s);
-void launch_tile_ranges(const unsigned long long* keys_sorted, const FrameCtl* ctl, unsigned int n_tiles,
-                        uint2* ranges, cudaStream_t s);
+                       unsigned int epoch_base, SortPlan plan, int sm_count, bool small_tiles, cudaStream_t s);
+// bounds[t] = first sorted pair of tile t (t = 0..n_tiles); tile t owns [bounds[t], bounds[t+1]).
+void launch_tile_bounds(const unsigned long long* keys_sorted, const FrameCtl* ctl, unsigned int n_tiles,
+                        unsigned int* bounds, cudaStream_t s);
 void launch_blend(const FrameUniforms& U, const splat_record* rec, const unsigned int* vals_sorted,
-                  const uint2* ranges, const FrameCtl* ctl, void* fb_half4, cudaStream_t s);
+                  const unsigned int* bounds, void* fb_half4, cudaStream_t s);
 int blend_layer_smem_bytes(int K);
