@@ -17,7 +17,7 @@ MODE_TILE, MODE_LAYER50 = 0, 1
 ORDER_NEAR_FIRST, ORDER_REFERENCE = 0, 1
 FLAG_TIMING, FLAG_KEEP_UNSORTED = 1, 2
 (FETCH_RECORDS, FETCH_TILES_TOUCHED, FETCH_OFFSETS, FETCH_KEYS_UNSORTED, FETCH_VALS_UNSORTED,
- FETCH_KEYS_SORTED, FETCH_VALS_SORTED, FETCH_TILE_RANGES) = range(8)
+ FETCH_KEYS_SORTED, FETCH_VALS_SORTED, FETCH_TILE_RANGES, FETCH_DIGIT_HISTOGRAMS) = range(9)
 
 RECORD_DTYPE = np.dtype([
     ("cx", "<f4"), ("cy", "<f4"), ("ux", "<f4"), ("uy", "<f4"), ("vx", "<f4"), ("vy", "<f4"),
@@ -87,7 +87,8 @@ def make_opts(mode=MODE_TILE, max_fragments=0, order=ORDER_NEAR_FIRST, sh_degree
 
 _FETCH_DTYPE = {FETCH_RECORDS: RECORD_DTYPE, FETCH_TILES_TOUCHED: np.uint32, FETCH_OFFSETS: np.uint32,
                 FETCH_KEYS_UNSORTED: np.uint64, FETCH_VALS_UNSORTED: np.uint32, FETCH_KEYS_SORTED: np.uint64,
-                FETCH_VALS_SORTED: np.uint32, FETCH_TILE_RANGES: np.uint32}
+                FETCH_VALS_SORTED: np.uint32, FETCH_TILE_RANGES: np.uint32,
+                FETCH_DIGIT_HISTOGRAMS: np.uint32}
 
 
 class Context:
@@ -104,7 +105,11 @@ class Context:
             lib().splat_destroy(self._h)
             self._h = C.c_void_p()
 
-    __del__ = close
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
     def upload(self, instances: np.ndarray):
         a = np.ascontiguousarray(instances, np.float32).reshape(-1, 14)
@@ -145,6 +150,8 @@ class Context:
         out = np.zeros(nbytes.value // dt.itemsize, dt)
         if nbytes.value:
             _check(lib().splat_debug_fetch(self._h, what, out.ctypes.data, C.byref(nbytes)), "splat_debug_fetch")
+        if what == FETCH_DIGIT_HISTOGRAMS:
+            return out.reshape(8, 256)
         return out.reshape(-1, 2) if what == FETCH_TILE_RANGES else out
 
     def stage_times(self):

@@ -5,9 +5,19 @@
 // shaders/gaussian_splat_tile.metal:240-249 / gaussian_splat_50layer.metal:198-206 with
 // one global (tile | depth) sort.
 #include "splat_internal.cuh"
+#include <cstdlib>
 
 #define SORT_WARPS (SORT_THREADS / 32)
 #define LB_DEPTH 8
+#ifndef RANK_SETS
+#define RANK_SETS 4
+#endif
+// -DSORT_PROFILE: thread 0 of every CTA accumulates clock64() per phase into ctl->hist[7][0..7] (tuning aid).
+#ifdef SORT_PROFILE
+#define PROF(k) do { if (tid == 0) { const long long t_ = clock64(); prof_acc[k] += t_ - prof_last; prof_last = t_; } } while (0)
+#else
+#define PROF(k) do {} while (0)
+#endif
 
 __global__ void __launch_bounds__(256) sort_histogram_kernel(const unsigned long long* __restrict__ keys,
                                                              unsigned long long n, FrameCtl* ctl,
@@ -37,6 +47,10 @@ void launch_sort_histogram(const unsigned long long* keys, unsigned long long n,
     sort_histogram_kernel<<<(unsigned int)blocks, 256, 0, s>>>(keys, n, ctl, plan);
 }
 
+__device__ __forceinline__ void bulk_prefetch_l2(const void* gptr, unsigned int bytes) {   // bytes % 16 == 0
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gptr), "r"(bytes) : "memory");
+}
+
 // Exclusive scan of one value per thread over a 256-thread block. s_w: SORT_WARPS words.
 __device__ __forceinline__ unsigned int block_excl_scan_256(unsigned int v, unsigned int* s_w, unsigned int& total) {
     const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -53,17 +67,19 @@ __device__ __forceinline__ unsigned int block_excl_scan_256(unsigned int v, unsi
 }
 
 template <int ITEMS>
-__global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 4) onesweep_pass_kernel(
+__global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 3) onesweep_pass_kernel(
     const unsigned long long* __restrict__ keys_in, const unsigned int* __restrict__ vals_in,
     unsigned long long* __restrict__ keys_out, unsigned int* __restrict__ vals_out,
     FrameCtl* ctl, unsigned long long* status, unsigned int epoch, int pass, int shift, unsigned int mask)
 {
     constexpr int TILE_KEYS = SORT_THREADS * ITEMS;
     extern __shared__ unsigned long long s_keys[];                 // [TILE_KEYS] keys, then values
-    __shared__ unsigned int s_wh[SORT_WARPS][256];
     __shared__ unsigned int s_gexcl[256], s_off[256], s_w[SORT_WARPS];
     __shared__ unsigned int s_tile;
     unsigned int* s_vals = reinterpret_cast<unsigned int*>(s_keys + TILE_KEYS);
+    // per set, warp, digit: peer bitmap of the current round / keys of that digit seen so far (later: tile-local offsets)
+    unsigned int (*s_bm)[SORT_WARPS][256] = reinterpret_cast<unsigned int (*)[SORT_WARPS][256]>(s_vals + TILE_KEYS);
+    unsigned short (*s_wh)[SORT_WARPS][256] = reinterpret_cast<unsigned short (*)[SORT_WARPS][256]>(s_bm + RANK_SETS);
 
     if (ctl->overflow) return;
     const unsigned int n = ctl->n_sort;
@@ -76,11 +92,21 @@ __global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 4) onesweep_pa
         s_gexcl[tid] = block_excl_scan_256(ctl->hist[pass][tid], s_w, tot);
     }
 
+#ifdef SORT_PROFILE
+    long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, prof_last = clock64();
+#endif
+    // Tickets are drawn one tile ahead so the atomic's round trip hides behind the current tile.
+    // A CTA works through its tickets in increasing order, so every predecessor of a tile it waits
+    // on in the lookback is owned by a running CTA: no deadlock.
+    unsigned int next_ticket = 0;
+    if (tid == 0) next_ticket = atomicAdd(&ctl->sort_ticket[pass], 1u);
     while (true) {
         __syncthreads();
-        if (tid == 0) s_tile = atomicAdd(&ctl->sort_ticket[pass], 1u);
+        PROF(6);
+        if (tid == 0) s_tile = next_ticket;
         __syncthreads();
         const unsigned int tile = s_tile;
+        PROF(0);
         if (tile >= n_tiles) break;
         const unsigned int tbase = tile * TILE_KEYS;
         const unsigned int tcount = min((unsigned int)TILE_KEYS, n - tbase);
@@ -99,29 +125,75 @@ __global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 4) onesweep_pa
             const unsigned int li = wofs + i * 32;
             val[i] = li < tcount ? vals_in[tbase + li] : 0u;
         }
+        if (tid == 0) {
+            // next ticket, and its tile pulled into L2 by the TMA unit while this tile is processed: the
+            // plain loads above otherwise wait ~10K cycles on DRAM with nothing else of this CTA to run
+            next_ticket = atomicAdd(&ctl->sort_ticket[pass], 1u);
+            if (next_ticket < n_tiles) {
+                const unsigned int nb = next_ticket * TILE_KEYS;
+                const unsigned int nc = min((unsigned int)TILE_KEYS, n - nb) & ~3u;
+                if (nc) {
+                    bulk_prefetch_l2(keys_in + nb, nc * 8u);
+                    bulk_prefetch_l2(vals_in + nb, nc * 4u);
+                }
+            }
+        }
 #pragma unroll
-        for (int k = 0; k < 8; ++k) s_wh[warp][lane + k * 32] = 0;
+        for (int k = 0; k < 8; ++k)
+#pragma unroll
+            for (int c = 0; c < RANK_SETS; ++c) { s_wh[c][warp][lane + k * 32] = 0; s_bm[c][warp][lane + k * 32] = 0; }
         __syncwarp();
-
-        // ---- per-warp ranks
-        unsigned int rank[ITEMS];
+#ifdef SORT_PROFILE
+        { unsigned long long x_ = 0;
 #pragma unroll
-        for (int i = 0; i < ITEMS; ++i) {
-            const unsigned int d = (unsigned int)(key[i] >> shift) & mask;
-            const unsigned int peers = __match_any_sync(0xFFFFFFFFu, d);
-            const int leader = __ffs(peers) - 1;
-            unsigned int old = 0;
-            if ((int)lane == leader) { old = s_wh[warp][d]; s_wh[warp][d] = old + __popc(peers); }
-            old = __shfl_sync(0xFFFFFFFFu, old, leader);
-            rank[i] = old + __popc(peers & lt_mask);
+          for (int i = 0; i < ITEMS; ++i) x_ ^= key[i] ^ val[i];
+          if (x_ == 0xdeadbeefcafe1234ull) prof_acc[7]++; }
+        PROF(1);
+#endif
+
+        // ---- per-warp ranks through a shared-memory "match": every lane ORs its lane bit into the
+        // word of its digit, reads back the peer mask together with the running count of that digit
+        // (one 64-bit word: lo = peers of this round, hi = keys of this digit in earlier rounds), and
+        // the lowest peer folds the round into the count. 3 shared-memory instructions per key instead
+        // of a hardware match.any (ADU-bound: 70% of that pipe at 64M pairs) or 8 ballots + 8 logic ops.
+        // RANK_SETS independent counter sets (items [c*ITEMS/SETS, (c+1)*ITEMS/SETS) use set c) give
+        // that many independent shared-memory chains per warp and share the three warp barriers
+        // (measured at 64M pairs: 11.9K -> 6.8K cycles per tile going from 1 to 2 sets).
+        unsigned int rank[ITEMS];
+        constexpr int PER_SET = ITEMS / RANK_SETS;
+#pragma unroll
+        for (int i = 0; i < PER_SET; ++i) {
+            unsigned int dd[RANK_SETS], peers[RANK_SETS], before[RANK_SETS];
+#pragma unroll
+            for (int c = 0; c < RANK_SETS; ++c) {
+                dd[c] = (unsigned int)(key[c * PER_SET + i] >> shift) & mask;
+                atomicOr(&s_bm[c][warp][dd[c]], 1u << lane);
+            }
+            __syncwarp();
+#pragma unroll
+            for (int c = 0; c < RANK_SETS; ++c) {
+                peers[c] = *reinterpret_cast<volatile unsigned int*>(&s_bm[c][warp][dd[c]]);
+                before[c] = *reinterpret_cast<volatile unsigned short*>(&s_wh[c][warp][dd[c]]);
+                rank[c * PER_SET + i] = before[c] + __popc(peers[c] & lt_mask);
+            }
+            __syncwarp();
+#pragma unroll
+            for (int c = 0; c < RANK_SETS; ++c)
+                if ((peers[c] & lt_mask) == 0) {
+                    *reinterpret_cast<volatile unsigned int*>(&s_bm[c][warp][dd[c]]) = 0u;
+                    *reinterpret_cast<volatile unsigned short*>(&s_wh[c][warp][dd[c]]) = (unsigned short)(before[c] + __popc(peers[c]));
+                }
             __syncwarp();
         }
         __syncthreads();
+        PROF(2);
 
         // ---- digit column: totals over warps, tile-local exclusive scan, lookback
         unsigned int cnt = 0;
 #pragma unroll
-        for (int w = 0; w < SORT_WARPS; ++w) cnt += s_wh[w][tid];
+        for (int w = 0; w < SORT_WARPS; ++w)
+#pragma unroll
+            for (int c = 0; c < RANK_SETS; ++c) cnt += s_wh[c][w][tid];
         const unsigned int valid_cnt = cnt - (tid == mask ? (TILE_KEYS - tcount) : 0u);
         unsigned long long* st = status + (size_t)tile * 256 + tid;
         lb_store(st, lb_pack(epoch, tile == 0 ? LB_FLAG_INC : LB_FLAG_AGG, valid_cnt));
@@ -130,18 +202,24 @@ __global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 4) onesweep_pa
         {
             unsigned int run = lexcl;
 #pragma unroll
-            for (int w = 0; w < SORT_WARPS; ++w) { const unsigned int t = s_wh[w][tid]; s_wh[w][tid] = run; run += t; }
+            for (int w = 0; w < SORT_WARPS; ++w)
+#pragma unroll
+                for (int c = 0; c < RANK_SETS; ++c) {
+                    const unsigned int t = s_wh[c][w][tid]; s_wh[c][w][tid] = (unsigned short)run; run += t;
+                }
         }
         __syncthreads();
+        PROF(3);
         // ---- pairs: registers -> shared at their tile-local rank (frees the registers before the
         // lookback; global offsets are not needed yet)
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) {
             const unsigned int d = (unsigned int)(key[i] >> shift) & mask;
-            const unsigned int r = rank[i] + s_wh[warp][d];
+            const unsigned int r = rank[i] + (unsigned int)s_wh[i / PER_SET][warp][d];
             s_keys[r] = key[i];
             s_vals[r] = val[i];
         }
+        PROF(4);
         // Decoupled lookback, LB_DEPTH predecessors in flight per step: with every tile of a small
         // sort resident at once, a one-at-a-time walk is a serial chain of L2 round trips.
         unsigned int prefix = 0;
@@ -165,6 +243,7 @@ __global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 4) onesweep_pa
         if (tile != 0) lb_store(st, lb_pack(epoch, LB_FLAG_INC, prefix + valid_cnt));
         s_off[tid] = s_gexcl[tid] + prefix - lexcl;
         __syncthreads();
+        PROF(5);
 
         // ---- shared (tile-sorted) -> global (contiguous per digit run)
 #pragma unroll
@@ -178,6 +257,9 @@ __global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 4) onesweep_pa
             }
         }
     }
+#ifdef SORT_PROFILE
+    if (tid == 0) for (int k = 0; k < 8; ++k) atomicAdd(&ctl->hist[7][k], (unsigned int)(prof_acc[k] >> 4));
+#endif
 }
 
 template <int ITEMS>
@@ -185,7 +267,7 @@ static void run_passes(unsigned long long* ki, unsigned int* vi, unsigned long l
                        unsigned long long* sort_status, unsigned int epoch_base, const SortPlan& plan, int grid,
                        cudaStream_t s)
 {
-    constexpr int smem = SORT_THREADS * ITEMS * 12;
+    constexpr int smem = SORT_THREADS * ITEMS * 12 + RANK_SETS * SORT_WARPS * 256 * 6;
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(onesweep_pass_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -199,13 +281,16 @@ static void run_passes(unsigned long long* ki, unsigned int* vi, unsigned long l
     }
 }
 
-// small_tiles: 2048-pair tiles, 4 CTAs per SM. A frame-sized sort (a few hundred 4096-pair tiles, all
-// resident at once) is bounded by the latency of ONE tile's rank/scan/scatter chain, which halves with
-// the tile; large sorts keep 4096-pair tiles for longer contiguous digit runs in the scatter.
+// small_tiles: 2048-pair tiles, 3 CTAs per SM. Measured slower than 4096-pair tiles at every size tried
+// (1.6M, 12M, 64M pairs: the per-tile fixed costs dominate), so callers pass false; kept as a tuning
+// knob (SPLAT_SORT_TILE=small|large).
 void launch_radix_sort(unsigned long long* keys, unsigned int* vals, unsigned long long* keys_alt,
                        unsigned int* vals_alt, FrameCtl* ctl, unsigned long long* sort_status,
                        unsigned int epoch_base, SortPlan plan, int sm_count, bool small_tiles, cudaStream_t s)
 {
-    if (small_tiles) run_passes<SORT_ITEMS_SMALL>(keys, vals, keys_alt, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * 4, s);
+    static const char* force = getenv("SPLAT_SORT_TILE");    // tuning knob: "small" | "large"
+    if (force && force[0] == 's') small_tiles = true;
+    if (force && force[0] == 'l') small_tiles = false;
+    if (small_tiles) run_passes<SORT_ITEMS_SMALL>(keys, vals, keys_alt, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * 3, s);
     else run_passes<SORT_ITEMS>(keys, vals, keys_alt, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * 2, s);
 }

@@ -259,9 +259,8 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
             CK(cudaMemcpyAsync(c->dbg_vals, c->vals[0], c->capacity * 4, cudaMemcpyDeviceToDevice, s));
         }
         if (timed) CK(cudaEventRecord(c->ev[2], s));
-        // tile size by the expected pair count (the exact D only exists on the device): ~3 pairs per splat
         launch_radix_sort(c->keys[0], c->vals[0], c->keys[1], c->vals[1], c->ctl, c->sort_status, epoch + 1, plan,
-                          c->sm_count, (unsigned long long)c->n * 2ull < 6000000ull, s);
+                          c->sm_count, false, s);
     } else if (timed) { CK(cudaEventRecord(c->ev[1], s)); CK(cudaEventRecord(c->ev[2], s)); }
     if (timed) CK(cudaEventRecord(c->ev[3], s));
     const int sb = plan.n_pass & 1;
@@ -360,9 +359,17 @@ extern "C" {
 
 int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
     if (!c || !bytes) ARG_FAIL("splat_debug_fetch: NULL argument");
-    if (!c->have_frame) { g_err = "splat_debug_fetch: no frame rendered"; return SPLAT_ERR_STATE; }
     CK(cudaSetDevice(c->device));
     CK(cudaDeviceSynchronize());
+    if (what == SPLAT_FETCH_DIGIT_HISTOGRAMS) {
+        const size_t need = sizeof(c->ctl->hist);
+        if (!dst) { *bytes = need; return SPLAT_OK; }
+        if (*bytes < need) { *bytes = need; ARG_FAIL("splat_debug_fetch: destination too small"); }
+        CK(cudaMemcpy(dst, c->ctl->hist, need, cudaMemcpyDeviceToHost));
+        *bytes = need;
+        return SPLAT_OK;
+    }
+    if (!c->have_frame) { g_err = "splat_debug_fetch: no frame rendered"; return SPLAT_ERR_STATE; }
     CK(cudaMemcpy(c->ctl_host, c->ctl, 64, cudaMemcpyDeviceToHost));
     if (c->ctl_host->overflow) { g_err = "splat_debug_fetch: last frame overflowed the pair buffers"; return SPLAT_ERR_OVERFLOW; }
     const size_t D = (size_t)c->ctl_host->n_sort;
@@ -444,7 +451,7 @@ int splat_sort_pairs_u64_u32(splat_ctx* c, void* stream, uint64_t* keys, uint32_
     set_n_sort_kernel<<<1, 1, 0, s>>>(c->ctl, (unsigned int)n);
     launch_sort_histogram((const unsigned long long*)keys, n, c->ctl, plan, c->sm_count, s);
     launch_radix_sort((unsigned long long*)keys, vals, (unsigned long long*)keys_alt, vals_alt, c->ctl, c->sort_status,
-                      c->frame_no * 16u + 1, plan, c->sm_count, n < 6000000ull, s);
+                      c->frame_no * 16u + 1, plan, c->sm_count, false, s);
     CK(cudaGetLastError());
     c->have_frame = false;
     return SPLAT_OK;

@@ -120,7 +120,8 @@ enum {
     SPLAT_FETCH_VALS_UNSORTED,   /* uint32[D]                                 */
     SPLAT_FETCH_KEYS_SORTED,     /* uint64[D]                                 */
     SPLAT_FETCH_VALS_SORTED,     /* uint32[D]                                 */
-    SPLAT_FETCH_TILE_RANGES      /* uint32[T][2]                              */
+    SPLAT_FETCH_TILE_RANGES,     /* uint32[T][2]                              */
+    SPLAT_FETCH_DIGIT_HISTOGRAMS /* uint32[8][256]: per-pass digit counts of the last frame or stand-alone sort */
 };
 int splat_debug_fetch(splat_ctx* ctx, int what, void* host_dst, size_t* bytes);
 
