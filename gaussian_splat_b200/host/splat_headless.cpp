@@ -1,0 +1,95 @@
+// Headless driver: the role of the reference's src/main.mm (construct + initialize once :71-72,
+// render once per frame :192-198) and of MetalRenderer (owns the stream, the drawable and the
+// timing), without a window. Renders an orbit of frames of a 3DGS PLY and optionally writes the
+// last one as a binary PPM.
+//
+//   splat_headless scene.ply [--width 1920] [--height 1080] [--frames 64] [--mode tile|layer50]
+//                  [--k N] [--order near|reference] [--sh 0..3] [--device 0] [--out frame.ppm]
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "instanced_splat_renderer.h"
+#include "trackball_camera.h"
+
+static bool write_ppm(const char* path, const std::vector<_Float16>& px, int w, int h) {
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return false;
+    std::fprintf(f, "P6\n%d %d\n255\n", w, h);
+    std::vector<unsigned char> row((size_t)w * 3);
+    for (int j = 0; j < h; ++j) {
+        for (int i = 0; i < w; ++i)
+            for (int c = 0; c < 3; ++c) {
+                const float v = (float)px[((size_t)j * w + i) * 4 + c];
+                row[(size_t)i * 3 + c] = (unsigned char)std::lround(std::min(1.0f, std::max(0.0f, v)) * 255.0f);
+            }
+        std::fwrite(row.data(), 1, row.size(), f);
+    }
+    std::fclose(f);
+    return true;
+}
+
+int main(int argc, char** argv) {
+    if (argc < 2) { std::fprintf(stderr, "usage: %s scene.ply [options]\n", argv[0]); return 2; }
+    int w = 1920, h = 1080, frames = 64, device = 0;
+    const char* out = nullptr;
+    splat_opts opts{};
+    opts.flags = SPLAT_FLAG_TIMING;
+    for (int a = 2; a + 1 < argc; a += 2) {
+        const std::string k = argv[a]; const char* v = argv[a + 1];
+        if (k == "--width") w = std::atoi(v);
+        else if (k == "--height") h = std::atoi(v);
+        else if (k == "--frames") frames = std::atoi(v);
+        else if (k == "--device") device = std::atoi(v);
+        else if (k == "--k") opts.max_fragments = std::atoi(v);
+        else if (k == "--sh") opts.sh_degree = std::atoi(v);
+        else if (k == "--out") out = v;
+        else if (k == "--mode") opts.mode = std::strcmp(v, "layer50") == 0 ? SPLAT_MODE_LAYER50 : SPLAT_MODE_TILE;
+        else if (k == "--order") opts.order = std::strcmp(v, "reference") == 0 ? SPLAT_ORDER_REFERENCE : SPLAT_ORDER_NEAR_FIRST;
+        else { std::fprintf(stderr, "unknown option %s\n", k.c_str()); return 2; }
+    }
+
+    InstancedSplatRenderer renderer(argv[1]);
+    SplatDevice dev{device};
+    if (!renderer.initialize(&dev)) return 1;
+    renderer.setOptions(opts);
+    std::printf("points: %d\n", renderer.getPointCount());
+
+    TrackballCamera camera;                       // src/main.mm:55-58
+    camera.setViewportSize(w, h);
+    camera.setTarget(simd_make_float3(0, 0, 0));
+
+    cudaStream_t stream; cudaStreamCreate(&stream);
+    void* fb = nullptr;
+    if (cudaMalloc(&fb, (size_t)w * h * 8) != cudaSuccess) { std::fprintf(stderr, "cudaMalloc failed\n"); return 1; }
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    double total_ms = 0;
+    for (int f = 0; f < frames; ++f) {
+        const float t = 6.28318530718f * (float)f / (float)std::max(frames, 1);
+        camera.setPosition(simd_make_float3(5.0f * std::sin(t), 2.0f, 5.0f * std::cos(t)));
+        cudaEventRecord(e0, stream);
+        renderer.render(stream, fb, camera.getViewMatrix(), camera.getProjectionMatrix(), (float)w, (float)h);
+        cudaEventRecord(e1, stream);
+        cudaEventSynchronize(e1);
+        float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+        if (f > 0 || frames == 1) total_ms += ms;
+        splat_status st;
+        if (splat_frame_status(renderer.context(), &st) == SPLAT_OK && st.overflow) { --f; continue; }   // buffers grown: redo
+    }
+    const int timed = frames > 1 ? frames - 1 : frames;
+    if (timed > 0) std::printf("%d frames, %.3f ms/frame, %.1f frames/s\n", timed, total_ms / timed, 1e3 * timed / total_ms);
+    if (out) {
+        std::vector<_Float16> host((size_t)w * h * 4);
+        cudaMemcpy(host.data(), fb, host.size() * 2, cudaMemcpyDeviceToHost);
+        if (!write_ppm(out, host, w, h)) { std::fprintf(stderr, "cannot write %s\n", out); return 1; }
+        std::printf("wrote %s\n", out);
+    }
+    cudaFree(fb);
+    return 0;
+}
