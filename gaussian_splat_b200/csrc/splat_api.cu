@@ -25,7 +25,7 @@ __global__ void set_n_sort_kernel(FrameCtl* ctl, unsigned int n) { ctl->n_sort =
 struct splat_ctx {
     int device = 0, sm_count = 148;
     uint32_t n = 0; size_t n_pad = 0;
-    float4 *rot = nullptr, *pos_sx = nullptr, *syz = nullptr; uint16_t* bq = nullptr; float* sh = nullptr;
+    float4 *rot = nullptr, *pos_sx = nullptr, *syz = nullptr, *base_rgb = nullptr, *sh = nullptr; uint16_t* bq = nullptr;
     int sh_degree = 0;
     splat_record* rec = nullptr; uint32_t *touched = nullptr, *offsets = nullptr;
     unsigned long long* keys[2] = {nullptr, nullptr}; uint32_t* vals[2] = {nullptr, nullptr};
@@ -114,9 +114,9 @@ int splat_create(int device, splat_ctx** out) {
 }
 
 static void free_scene(splat_ctx* c) {
-    cudaFree(c->rot); cudaFree(c->pos_sx); cudaFree(c->syz); cudaFree(c->bq); cudaFree(c->sh);
+    cudaFree(c->rot); cudaFree(c->pos_sx); cudaFree(c->syz); cudaFree(c->bq); cudaFree(c->sh); cudaFree(c->base_rgb);
     cudaFree(c->rec); cudaFree(c->touched); cudaFree(c->offsets); cudaFree(c->scan_status);
-    c->rot = c->pos_sx = c->syz = nullptr; c->bq = nullptr; c->sh = nullptr; c->rec = nullptr;
+    c->rot = c->pos_sx = c->syz = c->base_rgb = c->sh = nullptr; c->bq = nullptr; c->rec = nullptr;
     c->touched = c->offsets = nullptr; c->scan_status = nullptr; c->n = 0; c->n_pad = 0; c->sh_degree = 0;
 }
 
@@ -143,7 +143,7 @@ int splat_upload(splat_ctx* c, const void* aos_host, uint32_t n) {
     if (n == 0) return SPLAT_OK;
     const size_t n_pad = ((size_t)n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS * SCAN_TILE_ITEMS;
     CK(cudaMalloc(&c->rot, n_pad * 16)); CK(cudaMalloc(&c->pos_sx, n_pad * 16)); CK(cudaMalloc(&c->syz, n_pad * 16));
-    CK(cudaMalloc(&c->bq, n_pad * 2));
+    CK(cudaMalloc(&c->bq, n_pad * 2)); CK(cudaMalloc(&c->base_rgb, n_pad * 16));
     CK(cudaMalloc(&c->rec, n_pad * sizeof(splat_record)));
     CK(cudaMalloc(&c->touched, n_pad * 4)); CK(cudaMalloc(&c->offsets, n_pad * 4));
     CK(cudaMemset(c->touched, 0, n_pad * 4));
@@ -154,7 +154,7 @@ int splat_upload(splat_ctx* c, const void* aos_host, uint32_t n) {
     float* aos_dev = nullptr;
     CK(cudaMalloc(&aos_dev, (size_t)n * 56));
     CK(cudaMemcpy(aos_dev, aos_host, (size_t)n * 56, cudaMemcpyHostToDevice));
-    launch_upload_soa(aos_dev, n, c->rot, c->pos_sx, c->syz, c->bq, 0);
+    launch_upload_soa(aos_dev, n, c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, 0);
     CK(cudaGetLastError());
     CK(cudaDeviceSynchronize());
     cudaFree(aos_dev);
@@ -176,8 +176,14 @@ int splat_upload_sh(splat_ctx* c, const float* sh_host, uint32_t n, int degree) 
     cudaFree(c->sh); c->sh = nullptr; c->sh_degree = 0;
     if (degree == 0 || n == 0) return SPLAT_OK;
     if (!sh_host) ARG_FAIL("splat_upload_sh: sh_rest45_host is NULL");
-    CK(cudaMalloc(&c->sh, (size_t)n * 45 * 4));
-    CK(cudaMemcpy(c->sh, sh_host, (size_t)n * 45 * 4, cudaMemcpyHostToDevice));
+    float* staging = nullptr;
+    CK(cudaMalloc(&staging, (size_t)n * 45 * 4));
+    CK(cudaMemcpy(staging, sh_host, (size_t)n * 45 * 4, cudaMemcpyHostToDevice));
+    CK(cudaMalloc(&c->sh, c->n_pad * 12 * 16));
+    launch_upload_sh(staging, n, c->n_pad, c->sh, 0);
+    CK(cudaGetLastError());
+    CK(cudaDeviceSynchronize());
+    cudaFree(staging);
     c->sh_degree = degree;
     return SPLAT_OK;
 }
@@ -210,7 +216,11 @@ static int build_frame(splat_ctx* c, const float* view, const float* proj, int w
         if (U.row_begin > U.row_end) U.row_begin = U.row_end;
     }
     U.mode = d.mode; U.order = d.order; U.K = K; U.sh_degree = d.sh_degree;
-    U.cam[0] = U.cam[1] = U.cam[2] = 0.0f;
+    for (int j = 0; j < 3; ++j) {                      // camera position = -R^T t of the view matrix (SH view direction)
+        volatile float m0 = view[j * 4 + 0] * view[12], m1 = view[j * 4 + 1] * view[13], m2 = view[j * 4 + 2] * view[14];
+        volatile float acc = m0 + m1; acc = acc + m2;
+        U.cam[j] = -acc;
+    }
     U.n = c->n;
     const unsigned int T = (unsigned int)(U.tiles_x * U.tiles_y);
     const int tb = tile_bits(T);
@@ -249,7 +259,7 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
     if (timed) CK(cudaEventRecord(c->ev[0], s));
     CK(cudaMemsetAsync(c->ctl, 0, sizeof(FrameCtl), s));
     if (c->n) {
-        ScenePlanes sp{c->rot, c->pos_sx, c->syz, c->bq, c->sh};
+        ScenePlanes sp{c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->sh, c->n_pad};
         launch_preprocess(sp, U, c->rec, c->touched, s);
         if (timed) CK(cudaEventRecord(c->ev[1], s));
         launch_scan_duplicate(U, c->rec, c->touched, c->offsets, c->keys[0], c->vals[0], c->capacity, c->ctl,

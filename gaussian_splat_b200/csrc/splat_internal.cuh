@@ -45,7 +45,10 @@ struct ScenePlanes {
     const float4* pos_sx;     // position.xyz, scale.x
     const float4* syz_op_rg;  // scale.y, scale.z, opacity, bits(half r | half g << 16)
     const uint16_t* b;        // half(b)
-    const float* sh;          // [n][45] or nullptr
+    const float4* base_rgb;   // fp32 r g b (loader colour) for the SH extension; .w unused
+    const float4* sh;         // SH planes [12][n_pad]: float4 j of splat i holds coefficients f' = 4j..4j+3,
+                              // f' = 3*k + channel (coefficient-major, so degree L reads planes 0 .. 3*((L+1)^2-1)/4)
+    size_t n_pad;
 };
 
 struct SortPlan {
@@ -73,7 +76,9 @@ __device__ __forceinline__ void lb_store(unsigned long long* p, unsigned long lo
 
 // Launchers (each enqueues on `s` and returns).
 void launch_upload_soa(const float* aos_dev, unsigned int n, float4* rot, float4* pos_sx, float4* syz_op_rg,
-                       uint16_t* b, cudaStream_t s);
+                       uint16_t* b, float4* base_rgb, cudaStream_t s);
+// sh_rest45_dev: [n][45] as the loader stores it (channel-major: f = channel*15 + k) -> coefficient-major planes
+void launch_upload_sh(const float* sh_rest45_dev, unsigned int n, size_t n_pad, float4* planes, cudaStream_t s);
 void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record* rec, unsigned int* touched,
                        cudaStream_t s);
 void launch_scan_duplicate(const FrameUniforms& U, const splat_record* rec, const unsigned int* touched,

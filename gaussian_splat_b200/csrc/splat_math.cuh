@@ -29,6 +29,31 @@ __device__ __forceinline__ void mat4_point(const float* M, float x, float y, flo
         out[r] = ((M[0 * 4 + r] * x + M[1 * 4 + r] * y) + M[2 * 4 + r] * z) + M[3 * 4 + r];
 }
 
+// View-dependent colour, SH degree 1..3 (build-side extension, the reference drops
+// f_rest at src/instanced_splat_renderer.mm:367-370). Standard 3DGS real-SH basis on
+// dir = normalize(pos - camera). b[k] = basis function k+1; every product/sum below is rounded
+// separately in the written order (the CPU restatement carries the same text).
+__device__ __forceinline__ void sh_basis(float x, float y, float z, int degree, float b[15]) {
+    b[0] = -0.4886025119029199f * y;
+    b[1] = 0.4886025119029199f * z;
+    b[2] = -0.4886025119029199f * x;
+    if (degree < 2) return;
+    const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+    b[3] = 1.0925484305920792f * xy;
+    b[4] = -1.0925484305920792f * yz;
+    b[5] = 0.31539156525252005f * ((2.0f * zz - xx) - yy);
+    b[6] = -1.0925484305920792f * xz;
+    b[7] = 0.5462742152960396f * (xx - yy);
+    if (degree < 3) return;
+    b[8] = (-0.5900435899266435f * y) * (3.0f * xx - yy);
+    b[9] = (2.890611442640554f * xy) * z;
+    b[10] = (-0.4570457994644658f * y) * ((4.0f * zz - xx) - yy);
+    b[11] = (0.3731763325901154f * z) * ((2.0f * zz - 3.0f * xx) - 3.0f * yy);
+    b[12] = (-0.4570457994644658f * x) * ((4.0f * zz - xx) - yy);
+    b[13] = (1.445305721320277f * z) * (xx - yy);
+    b[14] = (-0.5900435899266435f * x) * (xx - 3.0f * yy);
+}
+
 // One splat -> 48-byte record. Returns tiles touched (0 = culled; rec untouched).
 __device__ __forceinline__ unsigned int preprocess_one(
     float qw, float qx, float qy, float qz, float s0, float s1, float s2,

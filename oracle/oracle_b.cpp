@@ -56,12 +56,51 @@ struct Uni {
     float V[16], P[16], VP[16];
     float W, H;
     int w, h, tiles_x, tiles_y, row_begin, row_end;
+    float cam[3];
 };
 
 /* M * (x,y,z,1), column-major, k = 0,1,2,3 left to right (D5). */
 inline void mat4_point(const float* M, float x, float y, float z, float out[4]) {
     for (int r = 0; r < 4; ++r)
         out[r] = ((M[0 * 4 + r] * x + M[1 * 4 + r] * y) + M[2 * 4 + r] * z) + M[3 * 4 + r];
+}
+
+/* D11 extension: real-SH basis functions 1..15 on a unit direction (standard 3DGS constants);
+ * same text as gaussian_splat_b200/csrc/splat_math.cuh: sh_basis. */
+void sh_basis(float x, float y, float z, int degree, float b[15]) {
+    b[0] = -0.4886025119029199f * y;
+    b[1] = 0.4886025119029199f * z;
+    b[2] = -0.4886025119029199f * x;
+    if (degree < 2) return;
+    const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+    b[3] = 1.0925484305920792f * xy;
+    b[4] = -1.0925484305920792f * yz;
+    b[5] = 0.31539156525252005f * ((2.0f * zz - xx) - yy);
+    b[6] = -1.0925484305920792f * xz;
+    b[7] = 0.5462742152960396f * (xx - yy);
+    if (degree < 3) return;
+    b[8] = (-0.5900435899266435f * y) * (3.0f * xx - yy);
+    b[9] = (2.890611442640554f * xy) * z;
+    b[10] = (-0.4570457994644658f * y) * ((4.0f * zz - xx) - yy);
+    b[11] = (0.3731763325901154f * z) * ((2.0f * zz - 3.0f * xx) - 3.0f * yy);
+    b[12] = (-0.4570457994644658f * x) * ((4.0f * zz - xx) - yy);
+    b[13] = (1.445305721320277f * z) * (xx - yy);
+    b[14] = (-0.5900435899266435f * x) * (xx - 3.0f * yy);
+}
+
+/* colour = max(0, loader colour + sum_k basis_k(dir) * f_rest[channel*15 + k]), accumulated in
+ * coefficient-major order (k outer, channel inner), then rounded to half. */
+void sh_colour(const float* inst, const float* sh45, const float cam[3], int degree, orb_record& rec) {
+    const float dx = inst[7] - cam[0], dy = inst[8] - cam[1], dz = inst[9] - cam[2];
+    const float dl = std::sqrt((dx * dx + dy * dy) + dz * dz);
+    float bs[15];
+    sh_basis(dx / dl, dy / dl, dz / dl, degree, bs);
+    float col[3] = {inst[10], inst[11], inst[12]};
+    const int n_coef = (degree + 1) * (degree + 1) - 1;
+    for (int k = 0; k < n_coef; ++k)
+        for (int c = 0; c < 3; ++c) col[c] = col[c] + bs[k] * sh45[c * 15 + k];
+    rec.rg = (uint32_t)f2h(std::fmax(col[0], 0.0f)) | ((uint32_t)f2h(std::fmax(col[1], 0.0f)) << 16);
+    rec.bd = (rec.bd & 0xFFFF0000u) | (uint32_t)f2h(std::fmax(col[2], 0.0f));
 }
 
 /* One splat. Returns tiles touched (0 = culled) and fills rec. */
@@ -295,7 +334,6 @@ void orb_set_threads(int n) { g_threads = n < 1 ? 1 : n; }
 orb_frame* orb_frame_create(const float* inst, uint32_t n, const float* sh_rest,
                             const float* view, const float* proj, int w, int h,
                             const orb_opts* opts) {
-    (void)sh_rest;
     orb_frame* F = new orb_frame();
     F->opts = *opts;
     Uni& U = F->U;
@@ -306,6 +344,12 @@ orb_frame* orb_frame_create(const float* inst, uint32_t n, const float* sh_rest,
     U.row_begin = 0; U.row_end = U.tiles_y;
     if (opts->tile_row_end > 0) { U.row_begin = opts->tile_row_begin; U.row_end = std::min(opts->tile_row_end, U.tiles_y); }
     F->n = n; F->T = (uint32_t)(U.tiles_x * U.tiles_y);
+    for (int j = 0; j < 3; ++j) {                   /* camera position = -R^T t */
+        const float m0 = view[j * 4 + 0] * view[12], m1 = view[j * 4 + 1] * view[13], m2 = view[j * 4 + 2] * view[14];
+        float acc = m0 + m1; acc = acc + m2;
+        U.cam[j] = -acc;
+    }
+    const int sh_degree = (sh_rest && opts->sh_degree > 0) ? opts->sh_degree : 0;
 
     /* K1 */
     F->rec.assign(n, orb_record{}); F->touched.assign(n, 0); F->offsets.assign(n, 0);
@@ -314,6 +358,7 @@ orb_frame* orb_frame_create(const float* inst, uint32_t n, const float* sh_rest,
             for (uint32_t i = b; i < e; ++i) {
                 orb_record r{};
                 uint32_t t = preprocess_one(inst + (size_t)i * 14, U, r);
+                if (t && sh_degree) sh_colour(inst + (size_t)i * 14, sh_rest + (size_t)i * 45, U.cam, sh_degree, r);
                 if (t) F->rec[i] = r;
                 F->touched[i] = t;
             }

@@ -31,14 +31,16 @@ def _psnr(a, b):
     return 200.0 if mse == 0 else 10 * np.log10(1.0 / mse)
 
 
-def _check_all(ctx, inst, V, P, w, h, mode, order, K=0, rows=(0, 0)):
+def _check_all(ctx, inst, V, P, w, h, mode, order, K=0, rows=(0, 0), sh=None, sh_degree=0):
     from gaussian_splat_b200 import capi
     from oracle import oracle as O
     ctx.upload(inst)
+    if sh is not None:
+        ctx.upload_sh(sh, 3)
     got, st = _render(ctx, inst, V, P, w, h, mode=mode, order=order, max_fragments=K,
-                      tile_row_begin=rows[0], tile_row_end=rows[1])
+                      tile_row_begin=rows[0], tile_row_end=rows[1], sh_degree=sh_degree)
     F = O.Frame(inst, V, P, w, h, mode=mode, order=order, max_fragments=K or None,
-                tile_row_begin=rows[0], tile_row_end=rows[1])
+                tile_row_begin=rows[0], tile_row_end=rows[1], sh_rest=sh, sh_degree=sh_degree)
     assert st.n_pairs == F.D
     assert np.array_equal(ctx.fetch(capi.FETCH_TILES_TOUCHED), F.tiles_touched)
     assert np.array_equal(ctx.fetch(capi.FETCH_OFFSETS), F.offsets)
@@ -75,6 +77,21 @@ def test_fragment_caps(gpu_ctx, small_scene, K):
     V, P = O.app_camera(w, h, eye=(0.0, 1.0, 9.0))
     for mode in (0, 1):
         _check_all(gpu_ctx, small_scene, V, P, w, h, mode, 0, K=K)
+
+
+@pytest.mark.parametrize("degree", [1, 2, 3])
+def test_sh_view_dependent_colour(gpu_ctx, degree):
+    """Extension D11: SH degree 1..3 evaluated in K1; records (colour halves) and image bit-exact."""
+    from gaussian_splat_b200 import scene
+    from oracle import oracle as O
+    inst, sh = scene.make_instances(20000, 0x5EED0001, sh_rest=True)
+    w, h = 480, 270
+    V, P = O.app_camera(w, h, eye=(3.0, 2.0, -4.0))
+    F = _check_all(gpu_ctx, inst, V, P, w, h, 0, 0, sh=sh, sh_degree=degree)
+    F0 = O.Frame(inst, V, P, w, h)
+    assert (F.records["rg"] != F0.records["rg"]).mean() > 0.3       # the extension really changes colours
+    # degree 0 with SH uploaded is the reference-parity path, untouched
+    _check_all(gpu_ctx, inst, V, P, w, h, 0, 0, sh=sh, sh_degree=0)
 
 
 def test_ragged_viewport_and_band(gpu_ctx, small_scene):

@@ -136,3 +136,34 @@ def test_golden_fixtures(name):
     assert np.array_equal(F.tile_ranges, g[name + "_ranges"])
     img, _ = F.blend()
     assert np.array_equal(img, g[name + "_image"])
+
+
+def test_sh_extension_against_float64_evaluation():
+    """D11: max(0, loader colour + SH degrees 1..3 on normalize(pos - camera)), standard 3DGS basis."""
+    from gaussian_splat_b200 import scene
+    inst, sh = scene.make_instances(3000, 0x5EED0001, sh_rest=True)
+    w, h = 320, 200
+    eye = np.array([3.0, 2.0, -4.0])
+    V, P = O.app_camera(w, h, eye=tuple(eye))
+    C1 = 0.4886025119029199
+    C2 = [1.0925484305920792, -1.0925484305920792, 0.31539156525252005, -1.0925484305920792, 0.5462742152960396]
+    C3 = [-0.5900435899266435, 2.890611442640554, -0.4570457994644658, 0.3731763325901154, -0.4570457994644658,
+          1.445305721320277, -0.5900435899266435]
+    d = inst[:, 7:10].astype(np.float64) - eye
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    x, y, z = d.T
+    xx, yy, zz, xy, yz, xz = x * x, y * y, z * z, x * y, y * z, x * z
+    basis = np.stack([-C1 * y, C1 * z, -C1 * x,
+                      C2[0] * xy, C2[1] * yz, C2[2] * (2 * zz - xx - yy), C2[3] * xz, C2[4] * (xx - yy),
+                      C3[0] * y * (3 * xx - yy), C3[1] * xy * z, C3[2] * y * (4 * zz - xx - yy),
+                      C3[3] * z * (2 * zz - 3 * xx - 3 * yy), C3[4] * x * (4 * zz - xx - yy), C3[5] * z * (xx - yy),
+                      C3[6] * x * (xx - 3 * yy)], axis=1)
+    coef = sh.astype(np.float64).reshape(-1, 3, 15)
+    for degree, nk in ((1, 3), (2, 8), (3, 15)):
+        F = O.Frame(inst, V, P, w, h, sh_rest=sh, sh_degree=degree)
+        want = np.maximum(0.0, inst[:, 10:13] + np.einsum("nk,nck->nc", basis[:, :nk], coef[:, :, :nk]))
+        rec = F.records; vis = F.tiles_touched > 0
+        got = np.stack([(rec["rg"] & 0xFFFF), (rec["rg"] >> 16), (rec["bd"] & 0xFFFF)], axis=1).astype(np.uint16)
+        got = got.view(np.float16).astype(np.float64)
+        assert vis.sum() > 500
+        assert np.abs(got[vis] - want[vis]).max() <= 1e-3 * max(1.0, want[vis].max())      # half rounding
