@@ -26,7 +26,7 @@ RECORD_DTYPE = np.dtype([
 
 EXPORTS = [
     "splat_create", "splat_destroy", "splat_upload", "splat_upload_sh", "splat_render",
-    "splat_render_host", "splat_render_batch", "splat_frame_status", "splat_debug_fetch",
+    "splat_render_host", "splat_render_batch", "splat_render_batch_host", "splat_frame_status", "splat_debug_fetch",
     "splat_stage_times", "splat_sort_pairs_u64_u32", "splat_last_error_string", "splat_version",
 ]
 
@@ -64,6 +64,7 @@ def lib():
         L.splat_render.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.POINTER(SplatOpts)]
         L.splat_render_host.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.POINTER(SplatOpts)]
         L.splat_render_batch.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.POINTER(SplatOpts)]
+        L.splat_render_batch_host.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.POINTER(SplatOpts)]
         L.splat_frame_status.argtypes = [vp, C.POINTER(SplatStatus)]
         L.splat_debug_fetch.argtypes = [vp, C.c_int, vp, C.POINTER(C.c_size_t)]
         L.splat_stage_times.argtypes = [vp, C.POINTER(C.c_float)]
@@ -137,6 +138,15 @@ class Context:
         p = np.ascontiguousarray(projs, np.float32).reshape(n, 16)
         _check(lib().splat_render_batch(self._h, stream_ptr, arr, v.ctypes.data, p.ctypes.data, n, w, h,
                                         C.byref(opts) if opts is not None else None), "splat_render_batch")
+
+    def render_batch_host(self, fb_host_ptrs, views, projs, w: int, h: int, opts=None):
+        """n views end to end into host framebuffers (pinned for overlap), copies pipelined behind rendering."""
+        n = len(fb_host_ptrs)
+        arr = (C.c_void_p * n)(*fb_host_ptrs)
+        v = np.ascontiguousarray(views, np.float32).reshape(n, 16)
+        p = np.ascontiguousarray(projs, np.float32).reshape(n, 16)
+        _check(lib().splat_render_batch_host(self._h, arr, v.ctypes.data, p.ctypes.data, n, w, h,
+                                             C.byref(opts) if opts is not None else None), "splat_render_batch_host")
 
     def status(self) -> SplatStatus:
         s = SplatStatus()

@@ -38,6 +38,10 @@ struct splat_ctx {
     FrameUniforms lastU{}; SortPlan lastPlan{}; int sorted_buf = 0; bool have_frame = false, kept_unsorted = false;
     cudaEvent_t ev[6] = {}; bool timed = false;
     cudaStream_t own_stream = nullptr; void* fb_scratch = nullptr; size_t fb_scratch_bytes = 0;
+    // camera-batch pipeline (splat_render_batch_host): second framebuffer, copy stream, per-buffer events
+    cudaStream_t copy_stream = nullptr; void* fb_scratch2 = nullptr; size_t fb_scratch2_bytes = 0;
+    cudaEvent_t ev_rendered[2] = {}, ev_copied[2] = {};
+    unsigned int* batch_flags = nullptr; int batch_flags_cap = 0;   // pinned: overflow word + D of every view
 };
 
 static void mat4_mul_host(const float* a, const float* b, float* o) {
@@ -109,6 +113,11 @@ int splat_create(int device, splat_ctx** out) {
     std::memset(c->ctl_host, 0, sizeof(FrameCtl));
     for (int k = 0; k < 6; ++k) CK(cudaEventCreate(&c->ev[k]));
     CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    for (int k = 0; k < 2; ++k) {
+        CK(cudaEventCreateWithFlags(&c->ev_rendered[k], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&c->ev_copied[k], cudaEventDisableTiming));
+    }
     *out = c;
     return SPLAT_OK;
 }
@@ -129,6 +138,9 @@ int splat_destroy(splat_ctx* c) {
     cudaFreeHost(c->ctl_host);
     for (int k = 0; k < 6; ++k) if (c->ev[k]) cudaEventDestroy(c->ev[k]);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    for (int k = 0; k < 2; ++k) { if (c->ev_rendered[k]) cudaEventDestroy(c->ev_rendered[k]); if (c->ev_copied[k]) cudaEventDestroy(c->ev_copied[k]); }
+    cudaFree(c->fb_scratch2); cudaFreeHost(c->batch_flags);
     delete c;
     return SPLAT_OK;
 }
@@ -359,6 +371,66 @@ int splat_render_host(splat_ctx* c, void* fb_host, const float* view, const floa
         if (rc) return rc;
     }
     g_err = "splat_render_host: pair buffers still overflow after regrowth";
+    return SPLAT_ERR_OVERFLOW;
+}
+
+int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* views, const float* projs, int n_views,
+                            int w, int h, const splat_opts* o) {
+    if (!c) ARG_FAIL("splat_render_batch_host: ctx is NULL");
+    if (n_views < 0 || (n_views && (!fb_host || !views || !projs))) ARG_FAIL("splat_render_batch_host: bad arguments");
+    if (n_views == 0) return SPLAT_OK;
+    CK(cudaSetDevice(c->device));
+    const size_t bytes = (size_t)w * h * 8;
+    if (w <= 0 || h <= 0) ARG_FAIL("splat_render: bad viewport");
+    if (bytes > c->fb_scratch_bytes) {
+        CK(cudaDeviceSynchronize());
+        cudaFree(c->fb_scratch); c->fb_scratch = nullptr;
+        CK(cudaMalloc(&c->fb_scratch, bytes)); c->fb_scratch_bytes = bytes;
+    }
+    if (bytes > c->fb_scratch2_bytes) {
+        CK(cudaDeviceSynchronize());
+        cudaFree(c->fb_scratch2); c->fb_scratch2 = nullptr;
+        CK(cudaMalloc(&c->fb_scratch2, bytes)); c->fb_scratch2_bytes = bytes;
+    }
+    if (n_views > c->batch_flags_cap) {
+        cudaFreeHost(c->batch_flags); c->batch_flags = nullptr;
+        CK(cudaMallocHost(&c->batch_flags, (size_t)n_views * 16));
+        c->batch_flags_cap = n_views;
+    }
+    if (c->capacity == 0) { const int rc = ensure_pairs(c, 1ull << 20); if (rc) return rc; }
+    void* buf[2] = {c->fb_scratch, c->fb_scratch2};
+    for (int attempt = 0; attempt < 4; ++attempt) {
+        for (int v = 0; v < n_views; ++v) {
+            if (!fb_host[v]) ARG_FAIL("splat_render_batch_host: NULL framebuffer");
+            FrameUniforms U; SortPlan plan;
+            int rc = build_frame(c, views + 16 * v, projs + 16 * v, w, h, o, U, plan);
+            if (rc) return rc;
+            const int b = v & 1;
+            if (v >= 2) CK(cudaStreamWaitEvent(c->own_stream, c->ev_copied[b], 0));     // buffer b is free again
+            rc = enqueue_frame(c, c->own_stream, buf[b], U, plan, o ? (o->flags & ~SPLAT_FLAG_TIMING) : 0);
+            if (rc) return rc;
+            CK(cudaMemcpyAsync(c->batch_flags + 4 * v, c->ctl, 16, cudaMemcpyDeviceToHost, c->own_stream));   // D, overflow
+            CK(cudaEventRecord(c->ev_rendered[b], c->own_stream));
+            CK(cudaStreamWaitEvent(c->copy_stream, c->ev_rendered[b], 0));
+            const size_t row0 = (size_t)U.row_begin * SPLAT_TILE;
+            const size_t row1 = (size_t)U.row_end * SPLAT_TILE < (size_t)h ? (size_t)U.row_end * SPLAT_TILE : (size_t)h;
+            if (row1 > row0)
+                CK(cudaMemcpyAsync((char*)fb_host[v] + row0 * w * 8, (char*)buf[b] + row0 * w * 8, (row1 - row0) * w * 8,
+                                   cudaMemcpyDeviceToHost, c->copy_stream));
+            CK(cudaEventRecord(c->ev_copied[b], c->copy_stream));
+        }
+        CK(cudaStreamSynchronize(c->own_stream));
+        CK(cudaStreamSynchronize(c->copy_stream));
+        unsigned long long worst = 0; bool over = false;
+        for (int v = 0; v < n_views; ++v) {
+            unsigned long long D; std::memcpy(&D, c->batch_flags + 4 * v, 8);
+            if (c->batch_flags[4 * v + 2]) { over = true; if (D > worst) worst = D; }
+        }
+        if (!over) return SPLAT_OK;
+        const int rc = ensure_pairs(c, worst + worst / 4 + SORT_TILE_KEYS);
+        if (rc) return rc;
+    }
+    g_err = "splat_render_batch_host: pair buffers still overflow after regrowth";
     return SPLAT_ERR_OVERFLOW;
 }
 

@@ -106,6 +106,13 @@ int splat_render_batch(splat_ctx* ctx, void* stream, void* const* fb_half4_dev,
                        const float* views16, const float* projs16, int n_views, int w, int h,
                        const splat_opts* opts);
 
+/* Camera batch end to end with HOST buffers: n_views frames rendered back to back on an internal
+ * stream while a second stream copies each finished frame to fb_half4_host[i] (pinned memory for
+ * real overlap); two device framebuffers alternate. Synchronises before returning and re-runs the
+ * batch if the pair buffers overflowed. */
+int splat_render_batch_host(splat_ctx* ctx, void* const* fb_half4_host, const float* views16,
+                            const float* projs16, int n_views, int w, int h, const splat_opts* opts);
+
 /* After the stream has been synchronised: D, capacity and overflow of the last frame.
  * If overflow is set the buffers have been grown; render the frame again. */
 int splat_frame_status(splat_ctx* ctx, splat_status* out);

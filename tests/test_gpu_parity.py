@@ -171,3 +171,24 @@ def test_render_host_matches_device(gpu_ctx, small_scene):
     host = np.zeros((h, w, 4), np.uint16)
     gpu_ctx.render_host(host.ctypes.data, V, P, w, h, capi.make_opts())
     assert np.array_equal(host, dev)
+
+
+def test_render_batch_host_pipeline_matches_single_frames(gpu_ctx, small_scene):
+    """Camera batch (config 4 shape): pipelined copies must not disturb any frame."""
+    import math
+    import torch
+    from gaussian_splat_b200 import capi
+    from oracle import oracle as O
+    w, h, n = 400, 240, 7
+    gpu_ctx.upload(small_scene)
+    cams = [O.app_camera(w, h, eye=(5 * math.sin(2 * math.pi * k / n), 2.0, 5 * math.cos(2 * math.pi * k / n))) for k in range(n)]
+    views = np.stack([c[0] for c in cams]); projs = np.stack([c[1] for c in cams])
+    out = torch.zeros((n, h, w, 4), dtype=torch.float16).pin_memory()
+    gpu_ctx.render_batch_host([out[k].data_ptr() for k in range(n)], views, projs, w, h, capi.make_opts())
+    for k in range(n):
+        one = np.zeros((h, w, 4), np.uint16)
+        gpu_ctx.render_host(one.ctypes.data, views[k], projs[k], w, h, capi.make_opts())
+        assert np.array_equal(out[k].numpy().view(np.uint16), one), k
+    F = O.Frame(small_scene, views[3], projs[3], w, h)
+    ref, _ = F.blend()
+    assert np.array_equal(out[3].numpy().view(np.uint16), ref)
