@@ -103,16 +103,28 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(self.sm)}
 
 
-def algorithmic_bytes(n, visible, D, n_pass, P, sh_degree=0):
-    """SURVEY 8(d) per-stage algorithmic bytes of one frame."""
+def algorithmic_bytes(n, visible, D, n_pass, P, sh_degree=0, layer=False):
+    """SURVEY 8(d) per-stage algorithmic bytes of one frame. LAYER50 keeps the pairs in two orders
+    (arrival and depth): the duplication writes both, the sort passes are counted over both lists, the
+    blend walks both."""
     sh = {0: 0, 1: 36, 2: 96, 3: 180}[sh_degree]
+    lists = 2 if layer else 1
     return {
         "preprocess": n * (56 + 4) + visible * (48 + sh),
-        "scan_duplicate": n * 8 + n * 4 + visible * 12 + D * 12,
-        "sort": D * (8 + n_pass * 24),
+        "scan_duplicate": n * 8 + n * 4 + visible * 12 + D * 12 * lists,
+        "sort": D * (8 * lists + n_pass * 24),
         "ranges": D * 8,
-        "blend": D * (4 + 48) + P * 8,
+        "blend": D * (4 + 48) * lists + P * 8,
     }
+
+
+_REAL_STDOUT = None
+
+
+def emit(line):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
 
 
 def _cpu_frame(O, inst, V, P, w, h, mode, threads, rows=None):
@@ -171,7 +183,7 @@ def run_reference(args):
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def cpu_baseline_leg(inst, V, P, w, h, mode, name):
@@ -236,6 +248,12 @@ def main():
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
+    # stdout carries exactly ONE line (the JSON): libraries that print there (NCCL's version banner,
+    # the reference loader's progress) are sent to stderr for the duration of the run.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         return run_reference(args)
 
@@ -390,7 +408,7 @@ def main():
         hbm_peak, peak_kind, sm_max = peaks()
         visible = int((ctx.fetch(capi.FETCH_TILES_TOUCHED) > 0).sum())
         P = band_px if bands else w * h
-        ab = algorithmic_bytes(n, visible, D, n_pass, P, args.sh_degree)
+        ab = algorithmic_bytes(n, visible, D, n_pass, P, args.sh_degree, layer=bool(mode))
         stage_ms = {k: v / args.steps for k, v in stage_acc.items()}
         stages = {}
         for k in STAGES:
@@ -430,7 +448,7 @@ def main():
             "roofline": roof, "stages": stages,
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": 128, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps, "single_frame_ms": lat_ms, "note": e2e_note},
-            "gpu_launches": args.steps * (4 + n_pass),
+            "gpu_launches": args.steps * (4 + n_pass),      # K1, K2, K3 x n_pass, K4, K5 (+1 memset node, not counted)
             "clocks": clocks, "wall_s": t_wall,
         }
         if world == 1 and not args.no_sort_bench:
@@ -440,7 +458,7 @@ def main():
             line["sort_bench"] = sb
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_leg(inst, *camera.app_camera(w, h), w, h, mode, name)
-        print(json.dumps(line))
+        emit(line)
     ctx.close()
     if world > 1:
         dist.barrier()

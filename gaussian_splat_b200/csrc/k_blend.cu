@@ -70,42 +70,35 @@ __device__ __forceinline__ unsigned int lds32(unsigned int a) {
     return v;
 }
 
-template <int MODE>
-__global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
-    const __grid_constant__ FrameUniforms U, const splat_record* __restrict__ rec,
-    const unsigned int* __restrict__ vals, const unsigned int* __restrict__ bounds, uint2* __restrict__ fb)
+// What the walker does with a covering fragment:
+//   WALK_TILE     composite in list order                         gaussian_splat_tile.metal:252-264
+//   WALK_COUNT    LAYER50 phase 1: count arrivals (instance order), remember the K-th arrival
+//                                                                  gaussian_splat_50layer.metal:170-176
+//   WALK_UNDER    LAYER50 phase 2: "under" composite in depth order of the arrivals that were kept
+//                                                                  gaussian_splat_50layer.metal:209-220
+enum { WALK_TILE = 0, WALK_COUNT = 1, WALK_UNDER = 2 };
+
+struct PixelState {
+    __half2 accRG, accBA;     // (aR, aG) and (aB, accumAlpha | accumVis): every op an _rn intrinsic (D7)
+    int cnt;                  // kept fragments; cnt >= K doubles as "this pixel is finished"
+    unsigned int cutoff;      // LAYER50: instance index of the K-th arrival (fragments after it were dropped)
+};
+
+// Walks one tile's pair list [range.x, range.y) in batches of BLEND_BATCH staged through shared
+// memory. Each staging thread also derives a conservative pixel AABB of its splat and an 8-bit mask
+// of the 8x4-pixel warp blocks it can touch; each warp ballots the masks and visits only its own
+// candidates. Returns when every pixel of the tile is finished or the list ends.
+template <int WALK>
+__device__ __forceinline__ void walk_list(const splat_record* __restrict__ rec, const unsigned int* __restrict__ vals,
+                                          uint2 range, int K, float pxc, float pyc, float tox, float toy,
+                                          float4* s_ab, unsigned int* s_cm, PixelState& px)
 {
-    __shared__ float4 s_ab[2 * BLEND_BATCH];  // [0..B): cx cy ux uy   [B..2B): vx vy opacity rg
-    __shared__ unsigned int s_cm[2 * BLEND_BATCH];  // [0..B): bd   [B..2B): bit b = may touch the 8x4 block of warp b
     float4* const s_a = s_ab; float4* const s_b = s_ab + BLEND_BATCH;
-    unsigned int* const s_c = s_cm; unsigned int* const s_m = s_cm + BLEND_BATCH;
-    extern __shared__ unsigned int s_list[]; // LAYER50: [K][256] key|vis, [K][256] rg, [K][256] b (as u32)
-
-    const int tx = blockIdx.x, ty = U.row_begin + blockIdx.y;
-    const unsigned int tile = (unsigned int)(ty * U.tiles_x + tx);
-    int lx, ly; pixel_of_thread(lx, ly);
-    const int pi = tx * 16 + lx, pj = ty * 16 + ly;
-    const bool inside = pi < U.w && pj < U.h;
-    const float pxc = (float)pi + 0.5f, pyc = (float)pj + 0.5f;
-    const uint2 range = make_uint2(__ldg(bounds + tile), __ldg(bounds + tile + 1));
-    const int K = U.K;
-    const unsigned int tid = threadIdx.x;
+    unsigned int* const s_c = s_cm; unsigned int* const s_m = s_cm + BLEND_BATCH; unsigned int* const s_i = s_cm + 2 * BLEND_BATCH;
     const unsigned int a_ab = smem_addr(s_ab), a_cm = smem_addr(s_cm);
-
-    // TILE: (aR, aG) and (aB, accumAlpha) as two half2 accumulators; every half op below is an
-    // _rn intrinsic (rounded separately, never contracted: DESIGN.md D7).
-    __half2 accRG = __halves2half2(__ushort_as_half(0), __ushort_as_half(0));
-    __half2 accBA = accRG;
+    const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const __half h_one = __ushort_as_half(0x3C00);
-    // LAYER50 accumulators
-    __half aR = __ushort_as_half(0), aG = aR, aB = aR, acc = h_one;
-    // cnt counts kept fragments; cnt >= K doubles as "this pixel is finished" (cap reached,
-    // alpha saturated, or pixel outside the viewport), so the hot loop carries one counter only.
-    int cnt = inside ? 0 : K;
-#define done (cnt >= K)
-
-    const unsigned int lane = tid & 31, warp = tid >> 5;
-    const float tox = (float)(tx * 16), toy = (float)(ty * 16);
+#define done (px.cnt >= K)
     for (unsigned int b0 = range.x; b0 < range.y; b0 += BLEND_BATCH) {
         const unsigned int nb = min((unsigned int)BLEND_BATCH, range.y - b0);
         unsigned int wmask = 0;
@@ -115,7 +108,8 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
             const float4 A = __ldg(r), B = __ldg(r + 1);
             s_a[tid] = A;
             s_b[tid] = B;
-            s_c[tid] = __float_as_uint(__ldg(reinterpret_cast<const float*>(r + 2)));
+            if (WALK != WALK_COUNT) s_c[tid] = __float_as_uint(__ldg(reinterpret_cast<const float*>(r + 2)));
+            if (WALK != WALK_TILE) s_i[tid] = si;
             // Conservative pixel AABB of {q <= 9.2103404}: d = Winv (u,v), Winv = [vy -uy; -vx ux] / det.
             // Only used to skip 8x4 pixel blocks the splat cannot touch; never changes a result.
             const float det = A.z * B.y - A.w * B.x;
@@ -151,26 +145,33 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
                     const float v = fmaf(dx, B.x, dy * B.y);
                     const float q = fmaf(u, u, v * v);
                     if (done || !(q <= 9.2103404f) || !(fabsf(u) <= 3.0f) || !(fabsf(v) <= 3.0f)) continue;
+                    if (WALK == WALK_COUNT) {
+                        // arrival number cnt+1; the K-th closes the pixel's list
+                        if (++px.cnt >= K) px.cutoff = lds32<2 * BLEND_BATCH * 4>(a_cm + e * 4u);
+                        continue;
+                    }
+                    if (WALK == WALK_UNDER && lds32<2 * BLEND_BATCH * 4>(a_cm + e * 4u) > px.cutoff) continue;   // arrived after the cap
                     const float alpha = exp_neg_half(q) * B.z;
                     const unsigned int rg = __float_as_uint(B.w), bd = lds32<0>(a_cm + e * 4u);
-                    if (MODE == SPLAT_MODE_TILE) {
-                        // gaussian_splat_tile.metal:252-264
+                    if (WALK == WALK_TILE) {
                         const __half ah = __float2half_rn(alpha);
-                        const __half src = __hmul_rn(ah, __hsub_rn(h_one, __high2half(accBA)));
+                        const __half src = __hmul_rn(ah, __hsub_rn(h_one, __high2half(px.accBA)));
                         const __half2 src2 = __half2half2(src);
                         const unsigned int b1 = (bd & 0xFFFFu) | 0x3C000000u;      // (b, 1.0h): 1.0h * src == src
-                        accRG = __hadd2_rn(accRG, __hmul2_rn(*reinterpret_cast<const __half2*>(&rg), src2));
-                        accBA = __hadd2_rn(accBA, __hmul2_rn(*reinterpret_cast<const __half2*>(&b1), src2));
-                        cnt = __hge(__high2half(accBA), __ushort_as_half(0x3BEC)) ? K : cnt + 1;
+                        px.accRG = __hadd2_rn(px.accRG, __hmul2_rn(*reinterpret_cast<const __half2*>(&rg), src2));
+                        px.accBA = __hadd2_rn(px.accBA, __hmul2_rn(*reinterpret_cast<const __half2*>(&b1), src2));
+                        px.cnt = __hge(__high2half(px.accBA), __ushort_as_half(0x3BEC)) ? K : px.cnt + 1;
                     } else {
-                        // gaussian_splat_50layer.metal:170-176: first K arrivals (instance order) kept
-                        const unsigned int h = bd >> 16;
-                        const unsigned int dk = U.order == SPLAT_ORDER_REFERENCE ? (0xFFFFu - h) : h;
-                        const unsigned int vis = hbits(__float2half_rn(1.0f - alpha));
-                        s_list[(0 * K + cnt) * BLEND_THREADS + tid] = (dk << 16) | vis;
-                        s_list[(1 * K + cnt) * BLEND_THREADS + tid] = rg;
-                        s_list[(2 * K + cnt) * BLEND_THREADS + tid] = bd & 0xFFFFu;
-                        ++cnt;
+                        // accumColor += color * accumVis; accumVis *= visibility; stop below 0.01h.
+                        // visibility = half(1 - alpha), float subtract then round (50layer.metal:174).
+                        const __half vis = __high2half(px.accBA);
+                        const __half2 vis2 = __half2half2(vis);
+                        const unsigned int b0h = bd & 0xFFFFu;                    // (b, 0): the alpha lane is replaced below
+                        px.accRG = __hadd2_rn(px.accRG, __hmul2_rn(*reinterpret_cast<const __half2*>(&rg), vis2));
+                        const __half2 bsum = __hadd2_rn(px.accBA, __hmul2_rn(*reinterpret_cast<const __half2*>(&b0h), vis2));
+                        const __half nvis = __hmul_rn(vis, __float2half_rn(1.0f - alpha));
+                        px.accBA = __halves2half2(__low2half(bsum), nvis);
+                        if (__hlt(nvis, __ushort_as_half(0x211F))) px.cnt = K;
                     }
                 }
                 if (__all_sync(0xFFFFFFFFu, done)) break;
@@ -178,58 +179,72 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
         }
         if (__syncthreads_and(done)) break;
     }
-
 #undef done
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
+    const __grid_constant__ FrameUniforms U, const splat_record* __restrict__ rec,
+    const unsigned int* __restrict__ vals, const unsigned int* __restrict__ vals_depth,
+    const unsigned int* __restrict__ bounds, uint2* __restrict__ fb)
+{
+    __shared__ float4 s_ab[2 * BLEND_BATCH];        // [0..B): cx cy ux uy   [B..2B): vx vy opacity rg
+    __shared__ unsigned int s_cm[3 * BLEND_BATCH];  // [0..B): bd   [B..2B): 8x4-block mask   [2B..3B): instance index
+
+    const int tx = blockIdx.x, ty = U.row_begin + blockIdx.y;
+    const unsigned int tile = (unsigned int)(ty * U.tiles_x + tx);
+    int lx, ly; pixel_of_thread(lx, ly);
+    const int pi = tx * 16 + lx, pj = ty * 16 + ly;
+    const bool inside = pi < U.w && pj < U.h;
+    const float pxc = (float)pi + 0.5f, pyc = (float)pj + 0.5f;
+    const float tox = (float)(tx * 16), toy = (float)(ty * 16);
+    const uint2 range = make_uint2(__ldg(bounds + tile), __ldg(bounds + tile + 1));
+    const int K = U.K;
+
+    PixelState px;
+    px.accRG = __halves2half2(__ushort_as_half(0), __ushort_as_half(0));
+    px.cutoff = 0xFFFFFFFFu;
+    if (MODE == SPLAT_MODE_TILE) {
+        px.accBA = px.accRG;
+        px.cnt = inside ? 0 : K;
+        walk_list<WALK_TILE>(rec, vals, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px);
+    } else {
+        // Phase 1 (arrival = instance order): only a counter per pixel; a tile with at most K pairs cannot
+        // overflow any list. Phase 2 (depth order, ties in arrival order because the sort is stable):
+        // composite the kept arrivals front to back with the shader's early exit. The per-pixel lists of
+        // the reference (504 B/pixel in device memory) are never materialised.
+        if (range.y - range.x > (unsigned int)K) {
+            px.cnt = inside ? 0 : K;
+            walk_list<WALK_COUNT>(rec, vals, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px);
+            __syncthreads();
+        }
+        px.accBA = __halves2half2(__ushort_as_half(0), __ushort_as_half(0x3C00));   // accumVis = 1
+        px.cnt = inside ? 0 : K;
+        walk_list<WALK_UNDER>(rec, vals_depth, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px);
+    }
     if (!inside) return;
     uint2 out;
+    out.x = *reinterpret_cast<const unsigned int*>(&px.accRG);
     if (MODE == SPLAT_MODE_TILE) {
-        out.x = *reinterpret_cast<const unsigned int*>(&accRG);
-        out.y = *reinterpret_cast<const unsigned int*>(&accBA);
-    } else if (cnt == 0) {
-        out = make_uint2(0, 0);
+        out.y = *reinterpret_cast<const unsigned int*>(&px.accBA);
     } else {
-        // gaussian_splat_50layer.metal:198-220. The stable descending insertion sort equals an
-        // ascending order on (depth key, arrival slot); walk it by repeated selection so an
-        // early exit (accumVis < 0.01h) skips the rest of the sort.
-        unsigned int last = 0;      // (dk << 8 | slot) + 1 of the previous pick
-        for (int step = 0; step < cnt; ++step) {
-            unsigned int best = 0xFFFFFFFFu;
-            for (int s = 0; s < cnt; ++s) {
-                const unsigned int kk = ((s_list[(0 * K + s) * BLEND_THREADS + tid] >> 16) << 8 | (unsigned int)s) + 1u;
-                if (kk > last && kk < best) best = kk;
-            }
-            last = best;
-            const int s = (int)((best - 1u) & 0xFFu);
-            const unsigned int w0 = s_list[(0 * K + s) * BLEND_THREADS + tid];
-            const unsigned int rg = s_list[(1 * K + s) * BLEND_THREADS + tid];
-            const unsigned int bb = s_list[(2 * K + s) * BLEND_THREADS + tid];
-            aR = __hadd_rn(aR, __hmul_rn(__ushort_as_half((unsigned short)(rg & 0xFFFFu)), acc));
-            aG = __hadd_rn(aG, __hmul_rn(__ushort_as_half((unsigned short)(rg >> 16)), acc));
-            aB = __hadd_rn(aB, __hmul_rn(__ushort_as_half((unsigned short)bb), acc));
-            acc = __hmul_rn(acc, __ushort_as_half((unsigned short)(w0 & 0xFFFFu)));
-            if (__hlt(acc, __ushort_as_half(0x211F))) break;
-        }
-        out.x = (unsigned int)hbits(aR) | ((unsigned int)hbits(aG) << 16);
-        out.y = (unsigned int)hbits(aB) | ((unsigned int)hbits(__hsub_rn(h_one, acc)) << 16);
+        // half4(accumColor, 1h - accumVis); an empty pixel gives (0,0,0,0) either way (50layer.metal:192-195,222)
+        const __half a = __hsub_rn(__ushort_as_half(0x3C00), __high2half(px.accBA));
+        out.y = (unsigned int)hbits(__low2half(px.accBA)) | ((unsigned int)hbits(a) << 16);
     }
     fb[(size_t)pj * U.w + pi] = out;
 }
 
-int blend_layer_smem_bytes(int K) { return 3 * K * BLEND_THREADS * 4; }
-
 void launch_blend(const FrameUniforms& U, const splat_record* rec, const unsigned int* vals_sorted,
-                  const unsigned int* bounds, void* fb_half4, cudaStream_t s)
+                  const unsigned int* vals_depth_sorted, const unsigned int* bounds, void* fb_half4, cudaStream_t s)
 {
     const int rows = U.row_end - U.row_begin;
     if (rows <= 0 || U.tiles_x <= 0) return;
     const dim3 grid(U.tiles_x, rows);
-    if (U.mode == SPLAT_MODE_LAYER50) {
-        const int smem = blend_layer_smem_bytes(U.K);
-        cudaFuncSetAttribute(blend_kernel<SPLAT_MODE_LAYER50>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        blend_kernel<SPLAT_MODE_LAYER50><<<grid, BLEND_THREADS, smem, s>>>(U, rec, vals_sorted, bounds,
-                                                                          reinterpret_cast<uint2*>(fb_half4));
-    } else {
-        blend_kernel<SPLAT_MODE_TILE><<<grid, BLEND_THREADS, 0, s>>>(U, rec, vals_sorted, bounds,
-                                                                     reinterpret_cast<uint2*>(fb_half4));
-    }
+    if (U.mode == SPLAT_MODE_LAYER50)
+        blend_kernel<SPLAT_MODE_LAYER50><<<grid, BLEND_THREADS, 0, s>>>(U, rec, vals_sorted, vals_depth_sorted, bounds,
+                                                                       reinterpret_cast<uint2*>(fb_half4));
+    else
+        blend_kernel<SPLAT_MODE_TILE><<<grid, BLEND_THREADS, 0, s>>>(U, rec, vals_sorted, vals_sorted, bounds,
+                                                                    reinterpret_cast<uint2*>(fb_half4));
 }

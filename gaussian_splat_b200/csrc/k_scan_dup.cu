@@ -19,7 +19,8 @@ __device__ __forceinline__ void warp_hist_inc(unsigned int* hist, unsigned int d
 __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
     const __grid_constant__ FrameUniforms U, const splat_record* __restrict__ rec,
     const unsigned int* __restrict__ touched, unsigned int* __restrict__ offsets,
-    unsigned long long* __restrict__ keys, unsigned int* __restrict__ vals, unsigned long long capacity,
+    unsigned long long* __restrict__ keys, unsigned int* __restrict__ vals,
+    unsigned long long* __restrict__ keys_depth, unsigned int* __restrict__ vals_depth, unsigned long long capacity,
     FrameCtl* ctl, unsigned long long* status, unsigned int epoch, const __grid_constant__ SortPlan plan,
     unsigned int n_tiles)
 {
@@ -61,13 +62,12 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
         if (cnt[k]) {
             const float4 tail = __ldg(reinterpret_cast<const float4*>(rec + base + li) + 2);  // bd, z, rect_lo, rect_hi
             const unsigned int h = __float_as_uint(tail.x) >> 16;
-            const unsigned int df = U.mode == SPLAT_MODE_LAYER50 ? (base + li)
-                                  : (U.order == SPLAT_ORDER_REFERENCE ? (0xFFFFu - h) : h);
+            const unsigned int df = U.order == SPLAT_ORDER_REFERENCE ? (0xFFFFu - h) : h;   // half-depth field (D3)
             s_df[li] = df;
             s_rlo[li] = __float_as_uint(tail.z);
             s_rhi[li] = __float_as_uint(tail.w);
             for (int p = 0; p < plan.n_pass; ++p)
-                if (plan.shift[p] < 32) atomicAdd(&s_hist[p][(df >> plan.shift[p]) & plan.mask[p]], cnt[k]);
+                if (plan.shift[p] < 32) atomicAdd(&s_hist[plan.slot[p]][(df >> plan.shift[p]) & plan.mask[p]], cnt[k]);
         }
     }
 
@@ -118,6 +118,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
     // ---- cooperative expansion: output slot j -> (splat, k-th tile of its rectangle)
     int tile_pass[2], n_tile_pass = 0;
     for (int p = 0; p < plan.n_pass; ++p) if (plan.shift[p] >= 32 && n_tile_pass < 2) tile_pass[n_tile_pass++] = p;
+    const bool layer = U.mode == SPLAT_MODE_LAYER50;
     for (unsigned int j = tid; j < btotal; j += SCAN_THREADS) {
         unsigned int lo = 0, hi = SCAN_TILE_ITEMS;
         while (lo < hi) { const unsigned int mid = (lo + hi) >> 1; if (s_scan[mid] <= j) lo = mid + 1; else hi = mid; }
@@ -129,15 +130,21 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
         const unsigned int ry = k / wdt, rx = k - ry * wdt;
         const unsigned int t = (ty0 + ry) * (unsigned int)U.tiles_x + (tx0 + rx);
         for (int q = 0; q < n_tile_pass; ++q)
-            warp_hist_inc(s_hist[tile_pass[q]], (t >> (plan.shift[tile_pass[q]] - 32)) & plan.mask[tile_pass[q]]);
+            warp_hist_inc(s_hist[plan.slot[tile_pass[q]]], (t >> (plan.shift[tile_pass[q]] - 32)) & plan.mask[tile_pass[q]]);
         const unsigned long long g = (unsigned long long)prefix + j;
         if (g < capacity) {
-            keys[g] = ((unsigned long long)t << 32) | s_df[sidx];
+            // TILE: tile | depth. LAYER50: tile | instance index (arrival order made explicit) plus a second
+            // copy in tile | depth order for the composite.
+            keys[g] = ((unsigned long long)t << 32) | (layer ? base + sidx : s_df[sidx]);
             vals[g] = base + sidx;
+            if (layer) {
+                keys_depth[g] = ((unsigned long long)t << 32) | s_df[sidx];
+                vals_depth[g] = base + sidx;
+            }
         }
     }
     __syncthreads();
-    for (int p = 0; p < plan.n_pass; ++p) {
+    for (int p = 0; p < FRAME_MAX_PASSES; ++p) {
         const unsigned int v = s_hist[p][tid];
         if (v) atomicAdd(&ctl->hist[p][tid], v);
     }
@@ -145,11 +152,12 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
 
 void launch_scan_duplicate(const FrameUniforms& U, const splat_record* rec, const unsigned int* touched,
                            unsigned int* offsets, unsigned long long* keys, unsigned int* vals,
+                           unsigned long long* keys_depth, unsigned int* vals_depth,
                            unsigned long long capacity, FrameCtl* ctl, unsigned long long* scan_status,
                            unsigned int epoch, SortPlan plan, cudaStream_t s)
 {
     if (U.n == 0) return;
     const unsigned int n_tiles = (U.n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS;
-    scan_duplicate_kernel<<<n_tiles, SCAN_THREADS, 0, s>>>(U, rec, touched, offsets, keys, vals, capacity, ctl,
+    scan_duplicate_kernel<<<n_tiles, SCAN_THREADS, 0, s>>>(U, rec, touched, offsets, keys, vals, keys_depth, vals_depth, capacity, ctl,
                                                            scan_status, epoch, plan, n_tiles);
 }

@@ -29,10 +29,10 @@ __global__ void __launch_bounds__(256) sort_histogram_kernel(const unsigned long
     const unsigned long long stride = (unsigned long long)gridDim.x * 256ull;
     for (unsigned long long i = (unsigned long long)blockIdx.x * 256ull + threadIdx.x; i < n; i += stride) {
         const unsigned long long k = __ldg(keys + i);
-        for (int p = 0; p < plan.n_pass; ++p) atomicAdd(&h[p][(unsigned int)(k >> plan.shift[p]) & plan.mask[p]], 1u);
+        for (int p = 0; p < plan.n_pass; ++p) atomicAdd(&h[plan.slot[p]][(unsigned int)(k >> plan.shift[p]) & plan.mask[p]], 1u);
     }
     __syncthreads();
-    for (int p = 0; p < plan.n_pass; ++p) {
+    for (int p = 0; p < SPLAT_MAX_SORT_PASSES; ++p) {
         const unsigned int v = h[p][threadIdx.x];
         if (v) atomicAdd(&ctl->hist[p][threadIdx.x], v);
     }
@@ -70,7 +70,7 @@ template <int ITEMS>
 __global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 3) onesweep_pass_kernel(
     const unsigned long long* __restrict__ keys_in, const unsigned int* __restrict__ vals_in,
     unsigned long long* __restrict__ keys_out, unsigned int* __restrict__ vals_out,
-    FrameCtl* ctl, unsigned long long* status, unsigned int epoch, int pass, int shift, unsigned int mask)
+    FrameCtl* ctl, unsigned long long* status, unsigned int epoch, int pass, int tix, int shift, unsigned int mask)
 {
     constexpr int TILE_KEYS = SORT_THREADS * ITEMS;
     extern __shared__ unsigned long long s_keys[];                 // [TILE_KEYS] keys, then values
@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 3) onesweep_pa
     // A CTA works through its tickets in increasing order, so every predecessor of a tile it waits
     // on in the lookback is owned by a running CTA: no deadlock.
     unsigned int next_ticket = 0;
-    if (tid == 0) next_ticket = atomicAdd(&ctl->sort_ticket[pass], 1u);
+    if (tid == 0) next_ticket = atomicAdd(&ctl->sort_ticket[tix], 1u);
     while (true) {
         __syncthreads();
         PROF(6);
@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 3) onesweep_pa
         if (tid == 0) {
             // next ticket, and its tile pulled into L2 by the TMA unit while this tile is processed: the
             // plain loads above otherwise wait ~10K cycles on DRAM with nothing else of this CTA to run
-            next_ticket = atomicAdd(&ctl->sort_ticket[pass], 1u);
+            next_ticket = atomicAdd(&ctl->sort_ticket[tix], 1u);
             if (next_ticket < n_tiles) {
                 const unsigned int nb = next_ticket * TILE_KEYS;
                 const unsigned int nc = min((unsigned int)TILE_KEYS, n - nb) & ~3u;
@@ -274,8 +274,8 @@ static void run_passes(unsigned long long* ki, unsigned int* vi, unsigned long l
         attr_set = true;
     }
     for (int p = 0; p < plan.n_pass; ++p) {
-        onesweep_pass_kernel<ITEMS><<<grid, SORT_THREADS, smem, s>>>(ki, vi, ko, vo, ctl, sort_status, epoch_base + p, p,
-                                                                    plan.shift[p], plan.mask[p]);
+        onesweep_pass_kernel<ITEMS><<<grid, SORT_THREADS, smem, s>>>(ki, vi, ko, vo, ctl, sort_status, epoch_base + p,
+                                                                    plan.slot[p], plan.ticket[p], plan.shift[p], plan.mask[p]);
         unsigned long long* tk = ki; ki = ko; ko = tk;
         unsigned int* tv = vi; vi = vo; vo = tv;
     }

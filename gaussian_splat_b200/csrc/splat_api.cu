@@ -30,6 +30,8 @@ struct splat_ctx {
     splat_record* rec = nullptr; uint32_t *touched = nullptr, *offsets = nullptr;
     unsigned long long* keys[2] = {nullptr, nullptr}; uint32_t* vals[2] = {nullptr, nullptr};
     unsigned long long capacity = 0;
+    // LAYER50 only: the same pairs in tile | depth order (allocated on the first LAYER50 frame)
+    unsigned long long* keys_d[2] = {nullptr, nullptr}; uint32_t* vals_d[2] = {nullptr, nullptr}; unsigned long long capacity_d = 0;
     unsigned long long* dbg_keys = nullptr; uint32_t* dbg_vals = nullptr; unsigned long long dbg_cap = 0;
     FrameCtl* ctl = nullptr; FrameCtl* ctl_host = nullptr;
     unsigned long long *scan_status = nullptr, *sort_status = nullptr; size_t sort_status_tiles = 0;
@@ -60,6 +62,8 @@ static void mat4_mul_host(const float* a, const float* b, float* o) {
 
 static int free_pairs(splat_ctx* c) {
     for (int k = 0; k < 2; ++k) { cudaFree(c->keys[k]); cudaFree(c->vals[k]); c->keys[k] = nullptr; c->vals[k] = nullptr; }
+    for (int k = 0; k < 2; ++k) { cudaFree(c->keys_d[k]); cudaFree(c->vals_d[k]); c->keys_d[k] = nullptr; c->vals_d[k] = nullptr; }
+    c->capacity_d = 0;
     cudaFree(c->sort_status); c->sort_status = nullptr; c->sort_status_tiles = 0;
     c->capacity = 0;
     return 0;
@@ -237,16 +241,32 @@ static int build_frame(splat_ctx* c, const float* view, const float* proj, int w
     const unsigned int T = (unsigned int)(U.tiles_x * U.tiles_y);
     const int tb = tile_bits(T);
     if (tb > 16) ARG_FAIL("splat_render: more than 65536 tiles");
+    // Digit passes of the (tile | half-depth) order: 15 significant depth bits (the sign bit is 0) then the
+    // tile bits. TILE sorts its pairs with all of them. LAYER50 sorts the depth-ordered copy the same way and
+    // the arrival-ordered list by the tile digits only (pairs are emitted in instance order and the sort is
+    // stable); see layer_plan().
     plan = SortPlan{};
     int p = 0;
-    if (d.mode == SPLAT_MODE_TILE) {       // 15 significant half-depth bits (sign bit is 0)
-        plan.shift[p] = 0; plan.mask[p++] = 0xFF;
-        plan.shift[p] = 8; plan.mask[p++] = 0xFF;
-    }                                       // LAYER50: pairs are emitted in instance order and the sort is stable
+    plan.shift[p] = 0; plan.mask[p++] = 0xFF;
+    plan.shift[p] = 8; plan.mask[p++] = 0xFF;
     if (tb > 0) { plan.shift[p] = 32; plan.mask[p++] = tb >= 8 ? 0xFFu : ((1u << tb) - 1u); }
     if (tb > 8) { plan.shift[p] = 40; plan.mask[p++] = (1u << (tb - 8)) - 1u; }
+    for (int k = 0; k < SPLAT_MAX_SORT_PASSES; ++k) { plan.slot[k] = k; plan.ticket[k] = k; }
     plan.n_pass = p;
     return SPLAT_OK;
+}
+
+// LAYER50's arrival-ordered list: only the tile-digit passes of `full`, reading their histograms (same
+// digits, same counts) and drawing tickets from the upper half of the ticket array.
+static SortPlan layer_plan(const SortPlan& full) {
+    SortPlan a{};
+    for (int p = 0; p < full.n_pass; ++p)
+        if (full.shift[p] >= 32) {
+            a.shift[a.n_pass] = full.shift[p]; a.mask[a.n_pass] = full.mask[p];
+            a.slot[a.n_pass] = full.slot[p]; a.ticket[a.n_pass] = 4 + a.n_pass;
+            ++a.n_pass;
+        }
+    return a;
 }
 
 static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUniforms& U, const SortPlan& plan, int flags) {
@@ -265,6 +285,16 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
         CK(cudaMalloc(&c->dbg_keys, c->capacity * 8)); CK(cudaMalloc(&c->dbg_vals, c->capacity * 4));
         c->dbg_cap = c->capacity;
     }
+    const bool layer = U.mode == SPLAT_MODE_LAYER50;
+    if (layer && c->capacity_d < c->capacity) {
+        CK(cudaDeviceSynchronize());
+        for (int k = 0; k < 2; ++k) {
+            cudaFree(c->keys_d[k]); cudaFree(c->vals_d[k]); c->keys_d[k] = nullptr; c->vals_d[k] = nullptr;
+            CK(cudaMalloc(&c->keys_d[k], c->capacity * 8)); CK(cudaMalloc(&c->vals_d[k], c->capacity * 4));
+            CK(cudaMemset(c->vals_d[k], 0, c->capacity * 4)); CK(cudaMemset(c->keys_d[k], 0, c->capacity * 8));
+        }
+        c->capacity_d = c->capacity;
+    }
     c->frame_no = c->frame_no + 1;
     if (c->frame_no >= (1u << 25)) c->frame_no = 1;
     const unsigned int epoch = c->frame_no * 16u;       // < 2^30; +0 scan, +1.. sort passes
@@ -274,24 +304,32 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
         ScenePlanes sp{c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->sh, c->n_pad};
         launch_preprocess(sp, U, c->rec, c->touched, s);
         if (timed) CK(cudaEventRecord(c->ev[1], s));
-        launch_scan_duplicate(U, c->rec, c->touched, c->offsets, c->keys[0], c->vals[0], c->capacity, c->ctl,
-                              c->scan_status, epoch, plan, s);
+        launch_scan_duplicate(U, c->rec, c->touched, c->offsets, c->keys[0], c->vals[0], layer ? c->keys_d[0] : nullptr,
+                              layer ? c->vals_d[0] : nullptr, c->capacity, c->ctl, c->scan_status, epoch, plan, s);
         if (keep) {
             CK(cudaMemcpyAsync(c->dbg_keys, c->keys[0], c->capacity * 8, cudaMemcpyDeviceToDevice, s));
             CK(cudaMemcpyAsync(c->dbg_vals, c->vals[0], c->capacity * 4, cudaMemcpyDeviceToDevice, s));
         }
         if (timed) CK(cudaEventRecord(c->ev[2], s));
-        launch_radix_sort(c->keys[0], c->vals[0], c->keys[1], c->vals[1], c->ctl, c->sort_status, epoch + 1, plan,
-                          c->sm_count, false, s);
+        if (layer) {
+            launch_radix_sort(c->keys_d[0], c->vals_d[0], c->keys_d[1], c->vals_d[1], c->ctl, c->sort_status, epoch + 1, plan,
+                              c->sm_count, false, s);
+            launch_radix_sort(c->keys[0], c->vals[0], c->keys[1], c->vals[1], c->ctl, c->sort_status, epoch + 1 + plan.n_pass,
+                              layer_plan(plan), c->sm_count, false, s);
+        } else {
+            launch_radix_sort(c->keys[0], c->vals[0], c->keys[1], c->vals[1], c->ctl, c->sort_status, epoch + 1, plan,
+                              c->sm_count, false, s);
+        }
     } else if (timed) { CK(cudaEventRecord(c->ev[1], s)); CK(cudaEventRecord(c->ev[2], s)); }
     if (timed) CK(cudaEventRecord(c->ev[3], s));
-    const int sb = plan.n_pass & 1;
+    const int sb = (layer ? layer_plan(plan).n_pass : plan.n_pass) & 1;    // arrival-ordered (LAYER50) or the only (TILE) list
+    const int sd = plan.n_pass & 1;
     launch_tile_bounds(c->keys[sb], c->ctl, T, c->bounds, s);
     if (timed) CK(cudaEventRecord(c->ev[4], s));
-    launch_blend(U, c->rec, c->vals[sb], c->bounds, fb, s);
+    launch_blend(U, c->rec, c->vals[sb], layer ? c->vals_d[sd] : nullptr, c->bounds, fb, s);
     if (timed) CK(cudaEventRecord(c->ev[5], s));
     CK(cudaGetLastError());
-    c->lastU = U; c->lastPlan = plan; c->sorted_buf = sb; c->have_frame = true; c->timed = timed; c->kept_unsorted = keep;
+    c->lastU = U; c->lastPlan = plan; if (layer) c->lastPlan.n_pass = plan.n_pass + layer_plan(plan).n_pass; c->sorted_buf = sb; c->have_frame = true; c->timed = timed; c->kept_unsorted = keep;
     return SPLAT_OK;
 }
 
@@ -522,6 +560,7 @@ int splat_sort_pairs_u64_u32(splat_ctx* c, void* stream, uint64_t* keys, uint32_
         const int bits = end_bit - b < 8 ? end_bit - b : 8;
         plan.shift[plan.n_pass] = b; plan.mask[plan.n_pass] = (1u << bits) - 1u; ++plan.n_pass;
     }
+    for (int k = 0; k < SPLAT_MAX_SORT_PASSES; ++k) { plan.slot[k] = k; plan.ticket[k] = k; }
     if (result_in_alt) *result_in_alt = plan.n_pass & 1;
     if (n == 0 || plan.n_pass == 0) return SPLAT_OK;
     int rc = ensure_sort_status(c, n);

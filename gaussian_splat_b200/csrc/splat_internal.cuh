@@ -55,6 +55,8 @@ struct SortPlan {
     int n_pass;
     int shift[SPLAT_MAX_SORT_PASSES];   // digit = (key >> shift) & mask
     unsigned int mask[SPLAT_MAX_SORT_PASSES];  // (1 << bits) - 1, bits <= 8
+    int slot[SPLAT_MAX_SORT_PASSES];    // which FrameCtl::hist row holds this pass's digit counts
+    int ticket[SPLAT_MAX_SORT_PASSES];  // which FrameCtl::sort_ticket this pass draws from
 };
 
 // Epoch-tagged 64-bit lookback word: [63:34] epoch, [33:32] flag, [31:0] value.
@@ -83,8 +85,11 @@ void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_reco
                        cudaStream_t s);
 void launch_scan_duplicate(const FrameUniforms& U, const splat_record* rec, const unsigned int* touched,
                            unsigned int* offsets, unsigned long long* keys, unsigned int* vals,
+                           unsigned long long* keys_depth, unsigned int* vals_depth,
                            unsigned long long capacity, FrameCtl* ctl, unsigned long long* scan_status,
                            unsigned int epoch, SortPlan plan, cudaStream_t s);
+// LAYER50 keeps two orders of the same pairs: (keys, vals) = tile | instance index (arrival order, D3) and
+// (keys_depth, vals_depth) = tile | half-depth field (composite order). keys_depth may be NULL (TILE mode).
 // Per-pass digit histograms of keys[0..n) into ctl->hist (stand-alone sort only; frames get
 // them from the duplication kernel).
 void launch_sort_histogram(const unsigned long long* keys, unsigned long long n, FrameCtl* ctl, SortPlan plan,
@@ -98,5 +103,4 @@ void launch_radix_sort(unsigned long long* keys, unsigned int* vals, unsigned lo
 void launch_tile_bounds(const unsigned long long* keys_sorted, const FrameCtl* ctl, unsigned int n_tiles,
                         unsigned int* bounds, cudaStream_t s);
 void launch_blend(const FrameUniforms& U, const splat_record* rec, const unsigned int* vals_sorted,
-                  const unsigned int* bounds, void* fb_half4, cudaStream_t s);
-int blend_layer_smem_bytes(int K);
+                  const unsigned int* vals_depth_sorted, const unsigned int* bounds, void* fb_half4, cudaStream_t s);

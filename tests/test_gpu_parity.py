@@ -192,3 +192,19 @@ def test_render_batch_host_pipeline_matches_single_frames(gpu_ctx, small_scene):
     F = O.Frame(small_scene, views[3], projs[3], w, h)
     ref, _ = F.blend()
     assert np.array_equal(out[3].numpy().view(np.uint16), ref)
+
+
+@pytest.mark.parametrize("name,mode,order", [("tile_near", 0, 0), ("tile_ref", 0, 1), ("layer50_near", 1, 0), ("layer50_ref", 1, 1)])
+def test_committed_golden_fixture(gpu_ctx, name, mode, order):
+    """tests/golden/golden_small.npz (made by tests/golden/make_golden.py): lists overflow K and early
+    termination triggers in this scene. Sorted pairs, ranges and image bit-exact."""
+    import os
+    from gaussian_splat_b200 import capi
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "golden_small.npz"))
+    w, h = int(g["w"]), int(g["h"])
+    gpu_ctx.upload(g["instances"])
+    got, st = _render(gpu_ctx, g["instances"], g["view"], g["proj"], w, h, mode=mode, order=order)
+    assert np.array_equal(gpu_ctx.fetch(capi.FETCH_KEYS_SORTED), g[name + "_keys"])
+    assert np.array_equal(gpu_ctx.fetch(capi.FETCH_VALS_SORTED), g[name + "_vals"])
+    assert np.array_equal(gpu_ctx.fetch(capi.FETCH_TILE_RANGES), g[name + "_ranges"])
+    assert np.array_equal(got, g[name + "_image"])
