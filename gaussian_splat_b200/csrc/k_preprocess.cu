@@ -72,9 +72,28 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
 {
     const unsigned int i = blockIdx.x * 256u + threadIdx.x;
     if (i >= U.n) return;
-    const float4 q = __ldg(sp.rot + i);
     const float4 p = __ldg(sp.pos_sx + i);
     const float4 t = __ldg(sp.syz_op_rg + i);
+    if (U.band_bound > 0.0f) {
+        // Tile-row band (multi-GPU): drop splats that provably cannot reach the band before the ~200-op
+        // covariance pipeline. The quad's pixel half-height is at most 3*sqrt(trace(Cov2D)) and
+        // trace(J C J^T) <= ||J||_F^2 * ||V3x3||_F^2 * max(scale)^2 (+2e-4 for the two epsilons), so the test
+        // is conservative (2% + 1 px slack for rounding) and never changes a result: the full path would
+        // have clamped such a rectangle to an empty row range.
+        float vp[4], cl[4];
+        mat4_point(U.V, p.x, p.y, p.z, vp);
+        const float zf = -vp[2];
+        if (!(zf >= 1e-4f)) { touched[i] = 0; return; }
+        mat4_point(U.VP, p.x, p.y, p.z, cl);
+        const float cy = (0.5f - 0.5f * (cl[1] * (1.0f / cl[3]))) * U.H;
+        const float iz = 1.0f / zf, fx = U.P[0] * (U.W * 0.5f) * iz, fy = U.P[5] * (U.H * 0.5f) * iz;
+        const float jx = fx * vp[0] * iz, jy = fy * vp[1] * iz;
+        const float smax = fmaxf(p.w, fmaxf(t.x, t.y));
+        const float tr = (fx * fx + fy * fy + jx * jx + jy * jy) * U.band_bound * (smax * smax) + 2e-4f;
+        const float hb = 3.0f * sqrtf(tr) + 1.0f;
+        if (!(cy + hb >= (float)(U.row_begin * 16) && cy - hb <= (float)(U.row_end * 16))) { touched[i] = 0; return; }
+    }
+    const float4 q = __ldg(sp.rot + i);
     const unsigned int bh = __ldg(sp.b + i);
     splat_record r;
     const unsigned int cnt = preprocess_one(q.x, q.y, q.z, q.w, p.w, t.x, t.y, p.x, p.y, p.z,
