@@ -114,6 +114,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
         o.z = sat_add(prefix, s_scan[tid * 4 + 2]); o.w = sat_add(prefix, s_scan[tid * 4 + 3]);
         *reinterpret_cast<uint4*>(offsets + base + tid * SCAN_ITEMS) = o;
     }
+    if (btotal == 0) return;      // nothing visible in this tile of splats (common with tile-row bands): no pairs, no histogram
 
     // ---- cooperative expansion: output slot j -> (splat, k-th tile of its rectangle)
     int tile_pass[2], n_tile_pass = 0;

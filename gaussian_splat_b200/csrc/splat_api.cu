@@ -238,8 +238,7 @@ static int build_frame(splat_ctx* c, const float* view, const float* proj, int w
         U.cam[j] = -acc;
     }
     U.n = c->n;
-    U.band_bound = 0.0f;
-    if (U.row_begin > 0 || U.row_end < U.tiles_y) {
+    {   // ||V3x3||_F^2 with slack, for K1's conservative screening bound
         float f2 = 0.0f;
         for (int cc = 0; cc < 3; ++cc) for (int r = 0; r < 3; ++r) f2 += view[cc * 4 + r] * view[cc * 4 + r];
         U.band_bound = f2 * 1.02f;

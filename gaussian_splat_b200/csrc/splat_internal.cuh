@@ -26,7 +26,7 @@ struct FrameUniforms {
     int mode, order, K, sh_degree;
     float cam[3];
     unsigned int n;
-    float band_bound;   // tile-row bands only: ||V3x3||_F^2 * 1.02 for the conservative pre-cull in K1 (0 = off)
+    float band_bound;   // ||V3x3||_F^2 * 1.02 for K1's conservative screening bound
 };
 
 // Device control block, zeroed by one memsetAsync at the start of every frame.
