@@ -22,29 +22,46 @@ static thread_local std::string g_err;
 
 __global__ void set_n_sort_kernel(FrameCtl* ctl, unsigned int n) { ctl->n_sort = n; ctl->total_pairs = n; }
 
-struct splat_ctx {
-    int device = 0, sm_count = 148;
-    uint32_t n = 0; size_t n_pad = 0;
-    float4 *rot = nullptr, *pos_sx = nullptr, *syz = nullptr, *base_rgb = nullptr, *sh = nullptr; uint16_t* bq = nullptr;
-    int sh_degree = 0;
+// Everything one frame in flight writes: two such sets let the camera-batch entry points keep two frames
+// in flight on two streams (at frame sizes K2-K4 are latency-bound and leave most SMs idle). The single
+// frame entry points use set 0 only; the second set is allocated on the first batch call.
+struct FrameSet {
     splat_record* rec = nullptr; uint32_t *touched = nullptr, *offsets = nullptr;
     unsigned long long* keys[2] = {nullptr, nullptr}; uint32_t* vals[2] = {nullptr, nullptr};
     unsigned long long capacity = 0;
     // LAYER50 only: the same pairs in tile | depth order (allocated on the first LAYER50 frame)
     unsigned long long* keys_d[2] = {nullptr, nullptr}; uint32_t* vals_d[2] = {nullptr, nullptr}; unsigned long long capacity_d = 0;
-    unsigned long long* dbg_keys = nullptr; uint32_t* dbg_vals = nullptr; unsigned long long dbg_cap = 0;
-    FrameCtl* ctl = nullptr; FrameCtl* ctl_host = nullptr;
+    FrameCtl* ctl = nullptr;
     unsigned long long *scan_status = nullptr, *sort_status = nullptr; size_t sort_status_tiles = 0;
     uint32_t* bounds = nullptr; uint32_t ranges_cap = 0;   // [T+1] first sorted pair of every tile
+    cudaStream_t own_stream = nullptr;
+};
+
+struct splat_ctx : FrameSet {
+    FrameSet alt; bool alt_ready = false; int cur_set = 0;
+    int device = 0, sm_count = 148;
+    uint32_t n = 0; size_t n_pad = 0;
+    float4 *rot = nullptr, *pos_sx = nullptr, *syz = nullptr, *base_rgb = nullptr, *sh = nullptr; uint16_t* bq = nullptr;
+    int sh_degree = 0;
+    unsigned long long* dbg_keys = nullptr; uint32_t* dbg_vals = nullptr; unsigned long long dbg_cap = 0;
+    FrameCtl* ctl_host = nullptr;
     uint32_t frame_no = 0;
     FrameUniforms lastU{}; SortPlan lastPlan{}; int sorted_buf = 0; bool have_frame = false, kept_unsorted = false;
     cudaEvent_t ev[6] = {}; bool timed = false;
-    cudaStream_t own_stream = nullptr; void* fb_scratch = nullptr; size_t fb_scratch_bytes = 0;
+    void* fb_scratch = nullptr; size_t fb_scratch_bytes = 0;
     // camera-batch pipeline (splat_render_batch_host): second framebuffer, copy stream, per-buffer events
     cudaStream_t copy_stream = nullptr; void* fb_scratch2 = nullptr; size_t fb_scratch2_bytes = 0;
-    cudaEvent_t ev_rendered[2] = {}, ev_copied[2] = {};
+    cudaEvent_t ev_rendered[2] = {}, ev_copied[2] = {}, ev_fork = nullptr;
     unsigned int* batch_flags = nullptr; int batch_flags_cap = 0;   // pinned: overflow word + D of every view
 };
+
+static void swap_sets(splat_ctx* c) {
+    FrameSet tmp = *static_cast<FrameSet*>(c);
+    *static_cast<FrameSet*>(c) = c->alt;
+    c->alt = tmp;
+    c->cur_set ^= 1;
+}
+static void use_set(splat_ctx* c, int k) { if (c->cur_set != k) swap_sets(c); }
 
 static void mat4_mul_host(const float* a, const float* b, float* o) {
     // simd_mul(a, b), k = 0..3 left to right (column-major)
@@ -118,6 +135,7 @@ int splat_create(int device, splat_ctx** out) {
     for (int k = 0; k < 6; ++k) CK(cudaEventCreate(&c->ev[k]));
     CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     for (int k = 0; k < 2; ++k) {
         CK(cudaEventCreateWithFlags(&c->ev_rendered[k], cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&c->ev_copied[k], cudaEventDisableTiming));
@@ -126,11 +144,63 @@ int splat_create(int device, splat_ctx** out) {
     return SPLAT_OK;
 }
 
-static void free_scene(splat_ctx* c) {
-    cudaFree(c->rot); cudaFree(c->pos_sx); cudaFree(c->syz); cudaFree(c->bq); cudaFree(c->sh); cudaFree(c->base_rgb);
+// Per-splat scratch of the CURRENT frame set (records, counts, offsets, scan lookback words).
+static void free_scene_scratch(splat_ctx* c) {
     cudaFree(c->rec); cudaFree(c->touched); cudaFree(c->offsets); cudaFree(c->scan_status);
-    c->rot = c->pos_sx = c->syz = c->base_rgb = c->sh = nullptr; c->bq = nullptr; c->rec = nullptr;
-    c->touched = c->offsets = nullptr; c->scan_status = nullptr; c->n = 0; c->n_pad = 0; c->sh_degree = 0;
+    c->rec = nullptr; c->touched = c->offsets = nullptr; c->scan_status = nullptr;
+}
+static int alloc_scene_scratch(splat_ctx* c, size_t n_pad) {
+    CK(cudaMalloc(&c->rec, n_pad * sizeof(splat_record)));
+    CK(cudaMalloc(&c->touched, n_pad * 4)); CK(cudaMalloc(&c->offsets, n_pad * 4));
+    CK(cudaMemset(c->touched, 0, n_pad * 4));
+    CK(cudaMemset(c->rec, 0, n_pad * sizeof(splat_record)));
+    const size_t scan_tiles = n_pad / SCAN_TILE_ITEMS + 1;
+    CK(cudaMalloc(&c->scan_status, scan_tiles * 8));
+    CK(cudaMemset(c->scan_status, 0, scan_tiles * 8));
+    return SPLAT_OK;
+}
+// Releases the second frame set completely (it is rebuilt by the next camera-batch call).
+static void drop_alt(splat_ctx* c) {
+    use_set(c, 0);
+    if (!c->alt_ready) return;
+    swap_sets(c);
+    free_scene_scratch(c); free_pairs(c);
+    cudaFree(c->bounds); cudaFree(c->ctl);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    *static_cast<FrameSet*>(c) = FrameSet{};
+    swap_sets(c);
+    c->alt_ready = false;
+}
+static int ensure_alt(splat_ctx* c) {
+    use_set(c, 0);
+    if (c->alt_ready) return SPLAT_OK;
+    const unsigned long long cap = c->capacity;
+    swap_sets(c);
+    int rc = SPLAT_OK;
+    do {
+        if (cudaMalloc(&c->ctl, sizeof(FrameCtl)) != cudaSuccess || cudaMemset(c->ctl, 0, sizeof(FrameCtl)) != cudaSuccess ||
+            cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) { g_err = "second frame set: allocation failed"; rc = SPLAT_ERR_CUDA; break; }
+        if (c->n_pad) { rc = alloc_scene_scratch(c, c->n_pad); if (rc) break; }
+        rc = ensure_pairs(c, cap ? cap : (1ull << 20));
+    } while (0);
+    swap_sets(c);
+    if (rc == SPLAT_OK) c->alt_ready = true;
+    return rc;
+}
+
+// Grows the pair buffers of every live frame set; leaves the current set selected.
+static int ensure_pairs_all(splat_ctx* c, unsigned long long cap) {
+    int rc = ensure_pairs(c, cap);
+    if (rc == SPLAT_OK && c->alt_ready) { swap_sets(c); rc = ensure_pairs(c, cap); swap_sets(c); }
+    return rc;
+}
+
+static void free_scene(splat_ctx* c) {
+    drop_alt(c);
+    cudaFree(c->rot); cudaFree(c->pos_sx); cudaFree(c->syz); cudaFree(c->bq); cudaFree(c->sh); cudaFree(c->base_rgb);
+    free_scene_scratch(c);
+    c->rot = c->pos_sx = c->syz = c->base_rgb = c->sh = nullptr; c->bq = nullptr;
+    c->n = 0; c->n_pad = 0; c->sh_degree = 0;
 }
 
 int splat_destroy(splat_ctx* c) {
@@ -144,6 +214,7 @@ int splat_destroy(splat_ctx* c) {
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     for (int k = 0; k < 2; ++k) { if (c->ev_rendered[k]) cudaEventDestroy(c->ev_rendered[k]); if (c->ev_copied[k]) cudaEventDestroy(c->ev_copied[k]); }
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     cudaFree(c->fb_scratch2); cudaFreeHost(c->batch_flags);
     delete c;
     return SPLAT_OK;
@@ -160,13 +231,7 @@ int splat_upload(splat_ctx* c, const void* aos_host, uint32_t n) {
     const size_t n_pad = ((size_t)n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS * SCAN_TILE_ITEMS;
     CK(cudaMalloc(&c->rot, n_pad * 16)); CK(cudaMalloc(&c->pos_sx, n_pad * 16)); CK(cudaMalloc(&c->syz, n_pad * 16));
     CK(cudaMalloc(&c->bq, n_pad * 2)); CK(cudaMalloc(&c->base_rgb, n_pad * 16));
-    CK(cudaMalloc(&c->rec, n_pad * sizeof(splat_record)));
-    CK(cudaMalloc(&c->touched, n_pad * 4)); CK(cudaMalloc(&c->offsets, n_pad * 4));
-    CK(cudaMemset(c->touched, 0, n_pad * 4));
-    CK(cudaMemset(c->rec, 0, n_pad * sizeof(splat_record)));
-    const size_t scan_tiles = n_pad / SCAN_TILE_ITEMS + 1;
-    CK(cudaMalloc(&c->scan_status, scan_tiles * 8));
-    CK(cudaMemset(c->scan_status, 0, scan_tiles * 8));
+    { const int rc = alloc_scene_scratch(c, n_pad); if (rc) return rc; }
     float* aos_dev = nullptr;
     CK(cudaMalloc(&aos_dev, (size_t)n * 56));
     CK(cudaMemcpy(aos_dev, aos_host, (size_t)n * 56, cudaMemcpyHostToDevice));
@@ -180,7 +245,7 @@ int splat_upload(splat_ctx* c, const void* aos_host, uint32_t n) {
     unsigned long long want = (unsigned long long)n * 12ull;
     if (want < (1ull << 20)) want = 1ull << 20;
     if (want > 0xC0000000ull) want = 0xC0000000ull;
-    return ensure_pairs(c, want);
+    return ensure_pairs_all(c, want);
 }
 
 int splat_upload_sh(splat_ctx* c, const float* sh_host, uint32_t n, int degree) {
@@ -345,6 +410,7 @@ int splat_render(splat_ctx* c, void* stream, void* fb, const float* view, const 
     if (!c) ARG_FAIL("splat_render: ctx is NULL");
     if (!fb) ARG_FAIL("splat_render: framebuffer is NULL");
     CK(cudaSetDevice(c->device));
+    use_set(c, 0);
     FrameUniforms U; SortPlan plan;
     int rc = build_frame(c, view, proj, w, h, o, U, plan);
     if (rc) return rc;
@@ -352,15 +418,44 @@ int splat_render(splat_ctx* c, void* stream, void* fb, const float* view, const 
     return enqueue_frame(c, (cudaStream_t)stream, fb, U, plan, o ? o->flags : 0);
 }
 
+// Camera batches keep two frames in flight: view v runs on frame set v & 1 (own scratch, own stream), so the
+// latency-bound stages of one frame (K2-K4) fill the SMs the other frame's tails leave idle.
 int splat_render_batch(splat_ctx* c, void* stream, void* const* fbs, const float* views, const float* projs,
                        int n_views, int w, int h, const splat_opts* o) {
     if (!c) ARG_FAIL("splat_render_batch: ctx is NULL");
     if (n_views < 0 || (n_views && (!fbs || !views || !projs))) ARG_FAIL("splat_render_batch: bad arguments");
-    for (int v = 0; v < n_views; ++v) {
-        const int rc = splat_render(c, stream, fbs[v], views + 16 * v, projs + 16 * v, w, h, o);
-        if (rc) return rc;
+    if (n_views == 0) return SPLAT_OK;
+    CK(cudaSetDevice(c->device));
+    // LAYER50 frames are dominated by a blend that already fills the machine twice over; measured on B200,
+    // overlapping two of them loses 14% (L2 contention), so that mode stays serial on the caller's stream.
+    if (n_views == 1 || (o && o->mode == SPLAT_MODE_LAYER50)) {
+        for (int v = 0; v < n_views; ++v) {
+            const int rc = splat_render(c, stream, fbs[v], views + 16 * v, projs + 16 * v, w, h, o);
+            if (rc) return rc;
+        }
+        return SPLAT_OK;
     }
-    return SPLAT_OK;
+    use_set(c, 0);
+    if (c->capacity == 0) { const int rc = ensure_pairs(c, 1ull << 20); if (rc) return rc; }
+    { const int rc = ensure_alt(c); if (rc) return rc; }
+    const int flags = o ? (o->flags & ~(SPLAT_FLAG_TIMING | SPLAT_FLAG_KEEP_UNSORTED)) : 0;
+    cudaStream_t user = (cudaStream_t)stream;
+    CK(cudaEventRecord(c->ev_fork, user));
+    for (int v = 0; v < n_views; ++v) {
+        if (!fbs[v]) ARG_FAIL("splat_render_batch: NULL framebuffer");
+        use_set(c, v & 1);
+        if (v < 2) CK(cudaStreamWaitEvent(c->own_stream, c->ev_fork, 0));
+        FrameUniforms U; SortPlan plan;
+        int rc = build_frame(c, views + 16 * v, projs + 16 * v, w, h, o, U, plan);
+        if (rc) return rc;
+        rc = enqueue_frame(c, c->own_stream, fbs[v], U, plan, flags);
+        if (rc) return rc;
+        if (v >= n_views - 2) {                      // join: the caller's stream continues after both sets drain
+            CK(cudaEventRecord(c->ev_rendered[v & 1], c->own_stream));
+            CK(cudaStreamWaitEvent(user, c->ev_rendered[v & 1], 0));
+        }
+    }
+    return SPLAT_OK;        // the current set is the last view's: splat_frame_status / debug fetch describe that frame
 }
 
 int splat_frame_status(splat_ctx* c, splat_status* out) {
@@ -376,7 +471,7 @@ int splat_frame_status(splat_ctx* c, splat_status* out) {
     out->sort_passes = (uint32_t)c->lastPlan.n_pass;
     if (out->overflow) {
         unsigned long long want = out->n_pairs + out->n_pairs / 4 + SORT_TILE_KEYS;
-        const int rc = ensure_pairs(c, want);
+        const int rc = ensure_pairs_all(c, want);
         if (rc) return rc;
     }
     return SPLAT_OK;
@@ -387,6 +482,7 @@ int splat_render_host(splat_ctx* c, void* fb_host, const float* view, const floa
     if (!c) ARG_FAIL("splat_render_host: ctx is NULL");
     if (!fb_host) ARG_FAIL("splat_render_host: framebuffer is NULL");
     CK(cudaSetDevice(c->device));
+    use_set(c, 0);
     FrameUniforms U; SortPlan plan;
     int rc = build_frame(c, view, proj, w, h, o, U, plan);
     if (rc) return rc;
@@ -410,7 +506,7 @@ int splat_render_host(splat_ctx* c, void* fb_host, const float* view, const floa
         CK(cudaStreamSynchronize(c->own_stream));
         if (!c->ctl_host->overflow) return SPLAT_OK;
         const unsigned long long D = c->ctl_host->total_pairs;
-        rc = ensure_pairs(c, D + D / 4 + SORT_TILE_KEYS);
+        rc = ensure_pairs_all(c, D + D / 4 + SORT_TILE_KEYS);
         if (rc) return rc;
     }
     g_err = "splat_render_host: pair buffers still overflow after regrowth";
@@ -440,17 +536,21 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
         CK(cudaMallocHost(&c->batch_flags, (size_t)n_views * 16));
         c->batch_flags_cap = n_views;
     }
+    use_set(c, 0);
     if (c->capacity == 0) { const int rc = ensure_pairs(c, 1ull << 20); if (rc) return rc; }
+    if (n_views > 1) { const int rc = ensure_alt(c); if (rc) return rc; }
+    const int flags = o ? (o->flags & ~(SPLAT_FLAG_TIMING | SPLAT_FLAG_KEEP_UNSORTED)) : 0;
     void* buf[2] = {c->fb_scratch, c->fb_scratch2};
     for (int attempt = 0; attempt < 4; ++attempt) {
         for (int v = 0; v < n_views; ++v) {
             if (!fb_host[v]) ARG_FAIL("splat_render_batch_host: NULL framebuffer");
+            const int b = v & 1;
+            use_set(c, b);                                  // frame set, stream and framebuffer b
             FrameUniforms U; SortPlan plan;
             int rc = build_frame(c, views + 16 * v, projs + 16 * v, w, h, o, U, plan);
             if (rc) return rc;
-            const int b = v & 1;
             if (v >= 2) CK(cudaStreamWaitEvent(c->own_stream, c->ev_copied[b], 0));     // buffer b is free again
-            rc = enqueue_frame(c, c->own_stream, buf[b], U, plan, o ? (o->flags & ~SPLAT_FLAG_TIMING) : 0);
+            rc = enqueue_frame(c, c->own_stream, buf[b], U, plan, flags);
             if (rc) return rc;
             CK(cudaMemcpyAsync(c->batch_flags + 4 * v, c->ctl, 16, cudaMemcpyDeviceToHost, c->own_stream));   // D, overflow
             CK(cudaEventRecord(c->ev_rendered[b], c->own_stream));
@@ -463,6 +563,7 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
             CK(cudaEventRecord(c->ev_copied[b], c->copy_stream));
         }
         CK(cudaStreamSynchronize(c->own_stream));
+        if (c->alt_ready) CK(cudaStreamSynchronize(c->alt.own_stream));
         CK(cudaStreamSynchronize(c->copy_stream));
         unsigned long long worst = 0; bool over = false;
         for (int v = 0; v < n_views; ++v) {
@@ -470,7 +571,7 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
             if (c->batch_flags[4 * v + 2]) { over = true; if (D > worst) worst = D; }
         }
         if (!over) return SPLAT_OK;
-        const int rc = ensure_pairs(c, worst + worst / 4 + SORT_TILE_KEYS);
+        const int rc = ensure_pairs_all(c, worst + worst / 4 + SORT_TILE_KEYS);
         if (rc) return rc;
     }
     g_err = "splat_render_batch_host: pair buffers still overflow after regrowth";

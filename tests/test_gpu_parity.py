@@ -194,6 +194,36 @@ def test_render_batch_host_pipeline_matches_single_frames(gpu_ctx, small_scene):
     assert np.array_equal(out[3].numpy().view(np.uint16), ref)
 
 
+@pytest.mark.parametrize("mode", [0, 1])
+def test_render_batch_two_frames_in_flight(gpu_ctx, small_scene, mode):
+    """splat_render_batch alternates two frame sets on two internal streams; every frame must equal the
+    single-frame render, and a later upload (which drops the second set) must still work."""
+    import math
+    import torch
+    from gaussian_splat_b200 import capi
+    from oracle import oracle as O
+    w, h, n = 320, 200, 5
+    gpu_ctx.upload(small_scene)
+    cams = [O.app_camera(w, h, eye=(5 * math.sin(2 * math.pi * k / n), 1.0 + 0.3 * k, 5 * math.cos(2 * math.pi * k / n))) for k in range(n)]
+    views = np.stack([c[0] for c in cams]); projs = np.stack([c[1] for c in cams])
+    fbs = torch.zeros((n, h, w, 4), dtype=torch.float16, device="cuda")
+    s = torch.cuda.current_stream().cuda_stream
+    for rep in range(2):
+        fbs.zero_()
+        gpu_ctx.render_batch(s, [fbs[k].data_ptr() for k in range(n)], views, projs, w, h, capi.make_opts(mode=mode))
+        got = fbs.cpu().numpy().view(np.uint16)       # ordered after the batch on the caller's stream
+        for k in range(n):
+            one, _ = _render(gpu_ctx, small_scene, views[k], projs[k], w, h, mode=mode)
+            assert np.array_equal(got[k], one), (rep, k)
+    F = O.Frame(small_scene, views[n - 1], projs[n - 1], w, h, mode=mode)
+    ref, _ = F.blend()
+    assert np.array_equal(got[n - 1], ref)
+    gpu_ctx.upload(small_scene[: len(small_scene) // 2])
+    gpu_ctx.render_batch(s, [fbs[k].data_ptr() for k in range(2)], views[:2], projs[:2], w, h, capi.make_opts(mode=mode))
+    half, _ = _render(gpu_ctx, small_scene[: len(small_scene) // 2], views[1], projs[1], w, h, mode=mode)
+    assert np.array_equal(fbs[1].cpu().numpy().view(np.uint16), half)
+
+
 @pytest.mark.parametrize("name,mode,order", [("tile_near", 0, 0), ("tile_ref", 0, 1), ("layer50_near", 1, 0), ("layer50_ref", 1, 1)])
 def test_committed_golden_fixture(gpu_ctx, name, mode, order):
     """tests/golden/golden_small.npz (made by tests/golden/make_golden.py): lists overflow K and early
