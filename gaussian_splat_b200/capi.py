@@ -13,7 +13,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libsplat_cuda.so")
 
-MODE_TILE, MODE_LAYER50 = 0, 1
+MODE_TILE, MODE_LAYER50, MODE_MLAB = 0, 1, 2
 ORDER_NEAR_FIRST, ORDER_REFERENCE = 0, 1
 FLAG_TIMING, FLAG_KEEP_UNSORTED = 1, 2
 (FETCH_RECORDS, FETCH_TILES_TOUCHED, FETCH_OFFSETS, FETCH_KEYS_UNSORTED, FETCH_VALS_UNSORTED,

@@ -3,6 +3,8 @@
 //   TILE    fragment_main + tile_sort_composite   shaders/gaussian_splat_tile.metal:178-267
 //   LAYER50 fragment_accumulate + compute_sort_composite
 //                                                 shaders/gaussian_splat_50layer.metal:149-223
+//   MLAB    fragment_main (6-layer K-buffer insert + merge) + resolve_main
+//                                                 shaders/gaussian_splat.metal:201-291, 329-361
 // Per-pixel fragment lists never touch HBM (the reference keeps 504 B/pixel there and
 // clears it every frame, src/instanced_splat_renderer.mm:256-262,475-477).
 #include "splat_math.cuh"
@@ -76,7 +78,17 @@ __device__ __forceinline__ unsigned int lds32(unsigned int a) {
 //                                                                  gaussian_splat_50layer.metal:170-176
 //   WALK_UNDER    LAYER50 phase 2: "under" composite in depth order of the arrivals that were kept
 //                                                                  gaussian_splat_50layer.metal:209-220
-enum { WALK_TILE = 0, WALK_COUNT = 1, WALK_UNDER = 2 };
+//   WALK_MLAB     insert into / merge with the 6-layer K-buffer in arrival (instance) order
+//                                                                  gaussian_splat.metal:221-276
+enum { WALK_TILE = 0, WALK_COUNT = 1, WALK_UNDER = 2, WALK_MLAB = 3 };
+
+// MLAB K-buffer of one pixel, in registers: six (premultiplied rgb, visibility) layers and their half depths.
+// The reference keeps them in eight RGBA16F attachments cleared to (0,0,0,1)
+// (src/instanced_splat_renderer.mm:536-541), so depth slot 3 - depths01.a - starts at 1.0h, the others at 0.
+struct KBuffer {
+    __half2 rg[6], ba[6];
+    __half d[6];
+};
 
 struct PixelState {
     __half2 accRG, accBA;     // (aR, aG) and (aB, accumAlpha | accumVis): every op an _rn intrinsic (D7)
@@ -91,7 +103,7 @@ struct PixelState {
 template <int WALK>
 __device__ __forceinline__ void walk_list(const splat_record* __restrict__ rec, const unsigned int* __restrict__ vals,
                                           uint2 range, int K, float pxc, float pyc, float tox, float toy,
-                                          float4* s_ab, unsigned int* s_cm, PixelState& px)
+                                          float4* s_ab, unsigned int* s_cm, PixelState& px, KBuffer& kb)
 {
     float4* const s_a = s_ab; float4* const s_b = s_ab + BLEND_BATCH;
     unsigned int* const s_c = s_cm; unsigned int* const s_m = s_cm + BLEND_BATCH; unsigned int* const s_i = s_cm + 2 * BLEND_BATCH;
@@ -109,6 +121,7 @@ __device__ __forceinline__ void walk_list(const splat_record* __restrict__ rec, 
             s_a[tid] = A;
             s_b[tid] = B;
             if (WALK != WALK_COUNT) s_c[tid] = __float_as_uint(__ldg(reinterpret_cast<const float*>(r + 2)));
+            const bool too_near = WALK == WALK_MLAB && __ldg(reinterpret_cast<const float*>(r + 2) + 1) < 0.001f;   // gaussian_splat.metal:209
             if (WALK != WALK_TILE) s_i[tid] = si;
             // Conservative pixel AABB of {q <= 9.2103404}: d = Winv (u,v), Winv = [vy -uy; -vx ux] / det.
             // Only used to skip 8x4 pixel blocks the splat cannot touch; never changes a result.
@@ -116,7 +129,8 @@ __device__ __forceinline__ void walk_list(const splat_record* __restrict__ rec, 
             const float idet = 1.0f / det;
             const float hx = 3.0351f * sqrtf(B.y * B.y + A.w * A.w) * fabsf(idet) + 0.01f;
             const float hy = 3.0351f * sqrtf(B.x * B.x + A.z * A.z) * fabsf(idet) + 0.01f;
-            if (!(hx <= 1e6f && hy <= 1e6f)) wmask = 0xFFu;
+            if (too_near) wmask = 0;
+            else if (!(hx <= 1e6f && hy <= 1e6f)) wmask = 0xFFu;
             else {
                 const float x0 = A.x - hx - tox, x1 = A.x + hx - tox, y0 = A.y - hy - toy, y1 = A.y + hy - toy;
                 unsigned int cm = 0, rm = 0;
@@ -153,6 +167,30 @@ __device__ __forceinline__ void walk_list(const splat_record* __restrict__ rec, 
                     if (WALK == WALK_UNDER && lds32<2 * BLEND_BATCH * 4>(a_cm + e * 4u) > px.cutoff) continue;   // arrived after the cap
                     const float alpha = exp_neg_half(q) * B.z;
                     const unsigned int rg = __float_as_uint(B.w), bd = lds32<0>(a_cm + e * 4u);
+                    if (WALK == WALK_MLAB) {
+                        // newLayer = half4(half3(color) * half(alpha), 1h - half(alpha)); newDepth = half(depth)
+                        const __half ah = __float2half_rn(alpha);
+                        __half2 nrg = __hmul2_rn(*reinterpret_cast<const __half2*>(&rg), __half2half2(ah));
+                        __half2 nba = __halves2half2(__hmul_rn(__ushort_as_half((unsigned short)(bd & 0xFFFFu)), ah), __hsub_rn(h_one, ah));
+                        __half nd = __ushort_as_half((unsigned short)(bd >> 16));
+#pragma unroll
+                        for (int k = 0; k < 6; ++k) {            // insertion: every slot the fragment passes shifts down
+                            const bool ins = __hge(nd, kb.d[k]);
+                            const __half2 trg = kb.rg[k], tba = kb.ba[k]; const __half td = kb.d[k];
+                            kb.rg[k] = ins ? nrg : trg; kb.ba[k] = ins ? nba : tba; kb.d[k] = ins ? nd : td;
+                            nrg = ins ? trg : nrg; nba = ins ? tba : nba; nd = ins ? td : nd;
+                        }
+                        // what fell out merges with the last layer: front UNDER back
+                        const bool closer = __hge(nd, kb.d[5]);
+                        const __half2 frg = closer ? nrg : kb.rg[5], fba = closer ? nba : kb.ba[5];
+                        const __half2 brg = closer ? kb.rg[5] : nrg, bba = closer ? kb.ba[5] : nba;
+                        const __half2 ba2 = __half2half2(__high2half(bba));
+                        const __half2 t = __hmul2_rn(fba, ba2);                       // (front.b * back.a, front.a * back.a)
+                        kb.rg[5] = __hadd2_rn(brg, __hmul2_rn(frg, ba2));
+                        kb.ba[5] = __halves2half2(__hadd_rn(__low2half(bba), __low2half(t)), __high2half(t));
+                        kb.d[5] = closer ? nd : kb.d[5];
+                        continue;
+                    }
                     if (WALK == WALK_TILE) {
                         const __half ah = __float2half_rn(alpha);
                         const __half src = __hmul_rn(ah, __hsub_rn(h_one, __high2half(px.accBA)));
@@ -202,12 +240,30 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
     const int K = U.K;
 
     PixelState px;
+    KBuffer kb;
     px.accRG = __halves2half2(__ushort_as_half(0), __ushort_as_half(0));
     px.cutoff = 0xFFFFFFFFu;
     if (MODE == SPLAT_MODE_TILE) {
         px.accBA = px.accRG;
         px.cnt = inside ? 0 : K;
-        walk_list<WALK_TILE>(rec, vals, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px);
+        walk_list<WALK_TILE>(rec, vals, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
+    } else if (MODE == SPLAT_MODE_MLAB) {
+        const __half h0 = __ushort_as_half(0), h1 = __ushort_as_half(0x3C00);
+#pragma unroll
+        for (int k = 0; k < 6; ++k) { kb.rg[k] = __halves2half2(h0, h0); kb.ba[k] = __halves2half2(h0, h1); kb.d[k] = k == 3 ? h1 : h0; }
+        px.accBA = px.accRG;
+        px.cnt = inside ? 0 : K;                       // K = INT_MAX: a pixel never closes
+        walk_list<WALK_MLAB>(rec, vals, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
+        // resolve_main: composite the six layers front to back
+        __half2 crg = __halves2half2(h0, h0); __half cb = h0, at = h1;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            crg = __hadd2_rn(crg, __hmul2_rn(kb.rg[k], __half2half2(at)));
+            cb = __hadd_rn(cb, __hmul_rn(__low2half(kb.ba[k]), at));
+            at = __hmul_rn(at, __high2half(kb.ba[k]));
+        }
+        px.accRG = crg;
+        px.accBA = __halves2half2(cb, __hsub_rn(h1, at));
     } else {
         // Phase 1 (arrival = instance order): only a counter per pixel; a tile with at most K pairs cannot
         // overflow any list. Phase 2 (depth order, ties in arrival order because the sort is stable):
@@ -215,17 +271,17 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
         // the reference (504 B/pixel in device memory) are never materialised.
         if (range.y - range.x > (unsigned int)K) {
             px.cnt = inside ? 0 : K;
-            walk_list<WALK_COUNT>(rec, vals, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px);
+            walk_list<WALK_COUNT>(rec, vals, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
             __syncthreads();
         }
         px.accBA = __halves2half2(__ushort_as_half(0), __ushort_as_half(0x3C00));   // accumVis = 1
         px.cnt = inside ? 0 : K;
-        walk_list<WALK_UNDER>(rec, vals_depth, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px);
+        walk_list<WALK_UNDER>(rec, vals_depth, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
     }
     if (!inside) return;
     uint2 out;
     out.x = *reinterpret_cast<const unsigned int*>(&px.accRG);
-    if (MODE == SPLAT_MODE_TILE) {
+    if (MODE != SPLAT_MODE_LAYER50) {
         out.y = *reinterpret_cast<const unsigned int*>(&px.accBA);
     } else {
         // half4(accumColor, 1h - accumVis); an empty pixel gives (0,0,0,0) either way (50layer.metal:192-195,222)
@@ -241,7 +297,10 @@ void launch_blend(const FrameUniforms& U, const splat_record* rec, const unsigne
     const int rows = U.row_end - U.row_begin;
     if (rows <= 0 || U.tiles_x <= 0) return;
     const dim3 grid(U.tiles_x, rows);
-    if (U.mode == SPLAT_MODE_LAYER50)
+    if (U.mode == SPLAT_MODE_MLAB)
+        blend_kernel<SPLAT_MODE_MLAB><<<grid, BLEND_THREADS, 0, s>>>(U, rec, vals_sorted, vals_sorted, bounds,
+                                                                    reinterpret_cast<uint2*>(fb_half4));
+    else if (U.mode == SPLAT_MODE_LAYER50)
         blend_kernel<SPLAT_MODE_LAYER50><<<grid, BLEND_THREADS, 0, s>>>(U, rec, vals_sorted, vals_depth_sorted, bounds,
                                                                        reinterpret_cast<uint2*>(fb_half4));
     else

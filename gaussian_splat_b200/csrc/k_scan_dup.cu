@@ -119,7 +119,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
     // ---- cooperative expansion: output slot j -> (splat, k-th tile of its rectangle)
     int tile_pass[2], n_tile_pass = 0;
     for (int p = 0; p < plan.n_pass; ++p) if (plan.shift[p] >= 32 && n_tile_pass < 2) tile_pass[n_tile_pass++] = p;
-    const bool layer = U.mode == SPLAT_MODE_LAYER50;
+    const bool layer = U.mode == SPLAT_MODE_LAYER50;        // second, depth-ordered list
+    const bool arrival = U.mode != SPLAT_MODE_TILE;         // LAYER50 / MLAB: the list the pixels walk is in instance order
     for (unsigned int j = tid; j < btotal; j += SCAN_THREADS) {
         unsigned int lo = 0, hi = SCAN_TILE_ITEMS;
         while (lo < hi) { const unsigned int mid = (lo + hi) >> 1; if (s_scan[mid] <= j) lo = mid + 1; else hi = mid; }
@@ -134,9 +135,9 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
             warp_hist_inc(s_hist[plan.slot[tile_pass[q]]], (t >> (plan.shift[tile_pass[q]] - 32)) & plan.mask[tile_pass[q]]);
         const unsigned long long g = (unsigned long long)prefix + j;
         if (g < capacity) {
-            // TILE: tile | depth. LAYER50: tile | instance index (arrival order made explicit) plus a second
-            // copy in tile | depth order for the composite.
-            keys[g] = ((unsigned long long)t << 32) | (layer ? base + sidx : s_df[sidx]);
+            // TILE: tile | depth. LAYER50 / MLAB: tile | instance index (arrival order made explicit); LAYER50
+            // adds a second copy in tile | depth order for the composite.
+            keys[g] = ((unsigned long long)t << 32) | (arrival ? base + sidx : s_df[sidx]);
             vals[g] = base + sidx;
             if (layer) {
                 keys_depth[g] = ((unsigned long long)t << 32) | s_df[sidx];

@@ -279,11 +279,12 @@ static int build_frame(splat_ctx* c, const float* view, const float* proj, int w
     if (!view || !proj) ARG_FAIL("splat_render: view/proj is NULL");
     if (w <= 0 || h <= 0 || w > 65536 || h > 65536) ARG_FAIL("splat_render: bad viewport");
     splat_opts d{}; if (o) d = *o;
-    if (d.mode != SPLAT_MODE_TILE && d.mode != SPLAT_MODE_LAYER50) ARG_FAIL("splat_render: bad mode");
+    if (d.mode != SPLAT_MODE_TILE && d.mode != SPLAT_MODE_LAYER50 && d.mode != SPLAT_MODE_MLAB) ARG_FAIL("splat_render: bad mode");
     if (d.order != SPLAT_ORDER_NEAR_FIRST && d.order != SPLAT_ORDER_REFERENCE) ARG_FAIL("splat_render: bad order");
     int K = d.max_fragments;
     if (K == 0) K = d.mode == SPLAT_MODE_LAYER50 ? 50 : 32;
     if (K < 1 || K > 64) ARG_FAIL("splat_render: max_fragments must be 1..64");
+    if (d.mode == SPLAT_MODE_MLAB) K = 0x7FFFFFFF;      // the K-buffer never closes a pixel: every arrival is merged
     if (d.sh_degree < 0 || d.sh_degree > 3) ARG_FAIL("splat_render: sh_degree must be 0..3");
     if (d.sh_degree > c->sh_degree) ARG_FAIL("splat_render: sh_degree exceeds uploaded SH data");
     std::memcpy(U.V, view, 64); std::memcpy(U.P, proj, 64);
@@ -315,10 +316,13 @@ static int build_frame(splat_ctx* c, const float* view, const float* proj, int w
     // tile bits. TILE sorts its pairs with all of them. LAYER50 sorts the depth-ordered copy the same way and
     // the arrival-ordered list by the tile digits only (pairs are emitted in instance order and the sort is
     // stable); see layer_plan().
+    // MLAB walks its pairs in instance order only: tile-digit passes alone (as layer_plan()).
     plan = SortPlan{};
     int p = 0;
-    plan.shift[p] = 0; plan.mask[p++] = 0xFF;
-    plan.shift[p] = 8; plan.mask[p++] = 0xFF;
+    if (d.mode != SPLAT_MODE_MLAB) {
+        plan.shift[p] = 0; plan.mask[p++] = 0xFF;
+        plan.shift[p] = 8; plan.mask[p++] = 0xFF;
+    }
     if (tb > 0) { plan.shift[p] = 32; plan.mask[p++] = tb >= 8 ? 0xFFu : ((1u << tb) - 1u); }
     if (tb > 8) { plan.shift[p] = 40; plan.mask[p++] = (1u << (tb - 8)) - 1u; }
     for (int k = 0; k < SPLAT_MAX_SORT_PASSES; ++k) { plan.slot[k] = k; plan.ticket[k] = k; }

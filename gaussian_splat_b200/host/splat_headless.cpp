@@ -3,7 +3,7 @@
 // timing), without a window. Renders an orbit of frames of a 3DGS PLY and optionally writes the
 // last one as a binary PPM.
 //
-//   splat_headless scene.ply [--width 1920] [--height 1080] [--frames 64] [--mode tile|layer50]
+//   splat_headless scene.ply [--width 1920] [--height 1080] [--frames 64] [--mode tile|layer50|mlab]
 //                  [--k N] [--order near|reference] [--sh 0..3] [--device 0] [--out frame.ppm]
 #include <cuda_runtime.h>
 
@@ -50,7 +50,7 @@ int main(int argc, char** argv) {
         else if (k == "--k") opts.max_fragments = std::atoi(v);
         else if (k == "--sh") opts.sh_degree = std::atoi(v);
         else if (k == "--out") out = v;
-        else if (k == "--mode") opts.mode = std::strcmp(v, "layer50") == 0 ? SPLAT_MODE_LAYER50 : SPLAT_MODE_TILE;
+        else if (k == "--mode") opts.mode = std::strcmp(v, "layer50") == 0 ? SPLAT_MODE_LAYER50 : std::strcmp(v, "mlab") == 0 ? SPLAT_MODE_MLAB : SPLAT_MODE_TILE;
         else if (k == "--order") opts.order = std::strcmp(v, "reference") == 0 ? SPLAT_ORDER_REFERENCE : SPLAT_ORDER_NEAR_FIRST;
         else { std::fprintf(stderr, "unknown option %s\n", k.c_str()); return 2; }
     }

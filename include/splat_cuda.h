@@ -24,7 +24,10 @@ enum { SPLAT_OK = 0, SPLAT_ERR_ARG = -1, SPLAT_ERR_CUDA = -2, SPLAT_ERR_OVERFLOW
 /* Renderer mode: which reference shader's per-pixel rule is applied. */
 enum {
     SPLAT_MODE_TILE    = 0, /* shaders/gaussian_splat_tile.metal:178-267  (K = 32; 24 per gaussian_splat_types.h:10) */
-    SPLAT_MODE_LAYER50 = 1  /* shaders/gaussian_splat_50layer.metal:149-223 (K = 50) */
+    SPLAT_MODE_LAYER50 = 1, /* shaders/gaussian_splat_50layer.metal:149-223 (K = 50) */
+    SPLAT_MODE_MLAB    = 2  /* shaders/gaussian_splat.metal:201-291 + 329-361: streaming 6-layer K-buffer in
+                               instance order, then resolve_main; the framebuffer receives resolve_main's
+                               value (src/instanced_splat_renderer.mm:530-577; max_fragments / order unused) */
 };
 /* Depth order of the per-pixel sort. */
 enum {

@@ -14,7 +14,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
-MODE_TILE, MODE_LAYER50 = 0, 1
+MODE_TILE, MODE_LAYER50, MODE_MLAB = 0, 1, 2
 ORDER_NEAR_FIRST, ORDER_REFERENCE = 0, 1
 
 RECORD_DTYPE = np.dtype([

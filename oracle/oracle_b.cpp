@@ -235,7 +235,7 @@ namespace {
 
 /* D3: depth field of the 64-bit key. */
 inline uint32_t depth_field(const orb_opts& o, const orb_record& r, uint32_t idx) {
-    if (o.mode == ORB_MODE_LAYER50) return idx;
+    if (o.mode == ORB_MODE_LAYER50 || o.mode == ORB_MODE_MLAB) return idx;   /* arrival = instance order */
     const uint32_t h = r.bd >> 16;
     return o.order == ORB_ORDER_REFERENCE ? (0xFFFFu - h) : h;
 }
@@ -318,6 +318,61 @@ uint64_t blend_rows(const orb_frame& F, uint16_t* fb, int ty_begin, int ty_end) 
                 }
                 out[0] = aR; out[1] = aG; out[2] = aB; out[3] = hsub(H_ONE, acc);
             }
+        }
+    }
+    return tests;
+}
+
+/* MLAB mode: streaming 6-layer K-buffer in instance order, then the resolve pass
+ * (shaders/gaussian_splat.metal:201-291 fragment_main, :329-361 resolve_main; the eight RGBA16F attachments
+ * are cleared to (0,0,0,1), src/instanced_splat_renderer.mm:536-541, so the depth slot of layer 3 - the
+ * alpha channel of depths01 - starts at 1.0h and the others at 0). The framebuffer receives resolve_main's
+ * return value; the fixed-function SrcAlpha blend over the drawable (:182-185) is presentation, not
+ * part of this path. Fragment coverage is the pinned rule of the other two modes (D6). */
+uint64_t blend_rows_mlab(const orb_frame& F, uint16_t* fb, int ty_begin, int ty_end) {
+    const Uni& U = F.U;
+    uint64_t tests = 0;
+    struct Layer { uint16_t r, g, b, a; };
+    for (int ty = ty_begin; ty < ty_end; ++ty)
+    for (int tx = 0; tx < U.tiles_x; ++tx) {
+        const uint32_t tile = (uint32_t)(ty * U.tiles_x + tx);
+        const uint32_t beg = F.ranges[2 * tile], end = F.ranges[2 * tile + 1];
+        for (int ly = 0; ly < 16; ++ly) for (int lx = 0; lx < 16; ++lx) {
+            const int i = tx * 16 + lx, j = ty * 16 + ly;
+            if (i >= U.w || j >= U.h) continue;
+            const float pxc = (float)i + 0.5f, pyc = (float)j + 0.5f;
+            Layer L[6]; uint16_t Dp[6];
+            for (int k = 0; k < 6; ++k) { L[k] = Layer{0, 0, 0, H_ONE}; Dp[k] = 0; }
+            Dp[3] = H_ONE;                                              /* clear colour alpha of depths01 */
+            for (uint32_t e = beg; e < end; ++e) {
+                const orb_record& r = F.rec[F.vals_s[e]];
+                ++tests;
+                if (r.z_front < 0.001f) continue;                       /* :209-211 */
+                const float dx = pxc - r.cx, dy = pyc - r.cy;
+                const float u = std::fmaf(dx, r.ux, dy * r.uy);
+                const float v = std::fmaf(dx, r.vx, dy * r.vy);
+                const float q = std::fmaf(u, u, v * v);
+                if (!(std::fabs(u) <= 3.0f && std::fabs(v) <= 3.0f && q <= 9.2103404f)) continue;   /* :214-219 */
+                const float alpha = exp_neg_half(q) * r.opacity;        /* :222 */
+                const uint16_t ah = f2h(alpha);
+                Layer nl{hmul((uint16_t)(r.rg & 0xFFFF), ah), hmul((uint16_t)(r.rg >> 16), ah),
+                         hmul((uint16_t)(r.bd & 0xFFFF), ah), hsub(H_ONE, ah)};                     /* :226 */
+                uint16_t nd = (uint16_t)(r.bd >> 16);                   /* half(in.depth) :223 */
+                for (int k = 0; k < 6; ++k)                             /* :247-262 */
+                    if (h2f(nd) >= h2f(Dp[k])) { std::swap(L[k], nl); std::swap(Dp[k], nd); }
+                const bool closer = h2f(nd) >= h2f(Dp[5]);              /* :265-276 */
+                const Layer front = closer ? nl : L[5], back = closer ? L[5] : nl;
+                L[5] = Layer{hadd(back.r, hmul(front.r, back.a)), hadd(back.g, hmul(front.g, back.a)),
+                             hadd(back.b, hmul(front.b, back.a)), hmul(front.a, back.a)};
+                if (closer) Dp[5] = nd;
+            }
+            uint16_t cR = 0, cG = 0, cB = 0, at = H_ONE;                /* resolve_main :331-360 */
+            for (int k = 0; k < 6; ++k) {
+                cR = hadd(cR, hmul(L[k].r, at)); cG = hadd(cG, hmul(L[k].g, at)); cB = hadd(cB, hmul(L[k].b, at));
+                at = hmul(at, L[k].a);
+            }
+            uint16_t* out = fb + ((size_t)j * U.w + i) * 4;
+            out[0] = cR; out[1] = cG; out[2] = cB; out[3] = hsub(H_ONE, at);
         }
     }
     return tests;
@@ -415,6 +470,9 @@ const uint32_t* orb_tile_ranges(const orb_frame* F) { return F->ranges.data(); }
 
 uint64_t orb_blend(const orb_frame* F, uint16_t* fb, int n_threads) {
     const int rb = F->U.row_begin, re = F->U.row_end;
+    auto blend_rows = [](const orb_frame& f, uint16_t* o, int a, int b) {
+        return f.opts.mode == ORB_MODE_MLAB ? blend_rows_mlab(f, o, a, b) : ::blend_rows(f, o, a, b);
+    };
     if (n_threads <= 1) return blend_rows(*F, fb, rb, re);
     std::vector<std::thread> th; std::vector<uint64_t> cnt((size_t)n_threads, 0);
     /* interleave rows for balance */

@@ -17,6 +17,7 @@
  *                     shaders/gaussian_splat_50layer.metal:149-176
  *   S3 TILE           shaders/gaussian_splat_tile.metal:215-267
  *   S3 LAYER50        shaders/gaussian_splat_50layer.metal:180-223
+ *   MLAB              shaders/gaussian_splat.metal:201-291 (K-buffer insert + merge), :329-361 (resolve)
  *   uniforms / VP     src/instanced_splat_renderer.mm:453-469
  *   camera            src/trackball_camera.mm:127-163
  *   SplatInstance     src/instanced_splat_renderer.h:6-11
@@ -33,7 +34,7 @@
 extern "C" {
 #endif
 
-enum { ORB_MODE_TILE = 0, ORB_MODE_LAYER50 = 1 };
+enum { ORB_MODE_TILE = 0, ORB_MODE_LAYER50 = 1, ORB_MODE_MLAB = 2 };
 enum { ORB_ORDER_NEAR_FIRST = 0, ORB_ORDER_REFERENCE = 1 };
 
 typedef struct {

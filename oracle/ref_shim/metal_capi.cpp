@@ -4,7 +4,8 @@
 //
 // What is the reference's: every statement of vertex_main, fragment_main /
 // fragment_accumulate and tile_sort_composite / compute_sort_composite
-// (shaders/gaussian_splat_tile.metal, shaders/gaussian_splat_50layer.metal).
+// (shaders/gaussian_splat_tile.metal, shaders/gaussian_splat_50layer.metal), and of the MLAB
+// mode's vertex_main, fragment_main and resolve_main (shaders/gaussian_splat.metal).
 // What is ours (the fixed-function stages Metal supplies): clip 0 <= z <= w,
 // viewport transform, pixel-centre coverage of the two triangles of each instanced quad,
 // barycentric interpolation of the varyings, per-pixel list plumbing,
@@ -26,6 +27,10 @@ namespace ref_layer {
 #include "gaussian_splat_50layer.metal"
 }
 #undef MAX_FRAGMENTS_PER_PIXEL
+namespace ref_mlab {
+#include "gaussian_splat.metal"
+}
+#undef NUM_OIT_LAYERS
 #undef constant
 #undef device
 #undef thread
@@ -97,13 +102,19 @@ void raster(uint32_t n, int w, int h, VS&& vs, FS&& frag) {
     }
 }
 
-void store(const std::vector<half4>& img, uint16_t* fb) { std::memcpy(fb, img.data(), img.size() * sizeof(half4)); }
+void store(const std::vector<half4>& img, uint16_t* fb) {
+    for (size_t p = 0; p < img.size(); ++p) {
+        const _Float16 c[4] = {img[p].x.v, img[p].y.v, img[p].z.v, img[p].w.v};
+        std::memcpy(fb + 4 * p, c, 8);
+    }
+}
 
 }  // namespace
 
 extern "C" {
 
-// mode 0: gaussian_splat_tile.metal (K = 32), mode 1: gaussian_splat_50layer.metal (K = 50).
+// mode 0: gaussian_splat_tile.metal (K = 32), mode 1: gaussian_splat_50layer.metal (K = 50),
+// mode 2: gaussian_splat.metal (MLAB, 6-layer K-buffer).
 // fb_half4: w*h*4 half bit patterns; counts (nullable): fragments that ARRIVED per pixel
 // (can exceed K: the shaders keep counting, gaussian_splat_tile.metal:200-206).
 int ora_render(const float* instances, uint32_t n, const float* view16, const float* proj16, int w, int h,
@@ -148,6 +159,38 @@ int ora_render(const float* instances, uint32_t n, const float* view16, const fl
         for (unsigned y = 0; y < (unsigned)h; ++y) for (unsigned x = 0; x < (unsigned)w; ++x) {
             if (counts) counts[(size_t)y * w + x] = lists[(size_t)y * w + x].count.v;   // before the in-place sort
             compute_sort_composite(lists.data(), tex, U, uint2(x, y));
+        }
+    } else if (mode == 2) {
+        // MLAB: K-buffer pass over 8 attachments cleared to (0,0,0,1), then the resolve pass
+        // (src/instanced_splat_renderer.mm:530-577). Raster order groups = primitive (instance) order
+        // per pixel, which is the order raster() submits fragments in. The image is resolve_main's
+        // return value (the SrcAlpha blend over the drawable is not applied).
+        using namespace ref_mlab;
+        static_assert(sizeof(ref_mlab::SplatInstance) == 56, "SplatInstance layout");
+        Uniforms U;
+        load_mat(U.viewMatrix, view16); load_mat(U.projectionMatrix, proj16);
+        mul_mat(U.viewProjectionMatrix, U.projectionMatrix, U.viewMatrix);
+        U.viewportSize = float2((float)w, (float)h);
+        const SplatInstance* inst = reinterpret_cast<const SplatInstance*>(instances);
+        const half4 clear(metal::half(0.0f), metal::half(0.0f), metal::half(0.0f), metal::half(1.0f));
+        KBuffer init;
+        init.layer0 = init.layer1 = init.layer2 = init.layer3 = init.layer4 = init.layer5 = clear;
+        init.depths01 = init.depths23 = clear;
+        std::vector<KBuffer> kb(P, init);
+        std::vector<uint32_t> arrived(counts ? P : 0, 0);
+        raster<VertexOut>(n, w, h,
+            [&](unsigned vid, unsigned iid) { return vertex_main(vid, iid, inst, U); },
+            [&](const VertexOut& in, unsigned x, unsigned y) {
+                const size_t p = (size_t)y * w + x;
+                kb[p] = fragment_main(in, kb[p]);
+                if (counts) ++arrived[p];
+            });
+        for (size_t p = 0; p < P; ++p) {
+            KBufferNoDepth k;
+            k.layer0 = kb[p].layer0; k.layer1 = kb[p].layer1; k.layer2 = kb[p].layer2;
+            k.layer3 = kb[p].layer3; k.layer4 = kb[p].layer4; k.layer5 = kb[p].layer5;
+            img[p] = resolve_main(k).color;
+            if (counts) counts[p] = arrived[p];
         }
     } else return -1;
     store(img, fb_half4);

@@ -224,7 +224,35 @@ def test_render_batch_two_frames_in_flight(gpu_ctx, small_scene, mode):
     assert np.array_equal(fbs[1].cpu().numpy().view(np.uint16), half)
 
 
-@pytest.mark.parametrize("name,mode,order", [("tile_near", 0, 0), ("tile_ref", 0, 1), ("layer50_near", 1, 0), ("layer50_ref", 1, 1)])
+def test_mlab_mode_stages_and_image(gpu_ctx, small_scene):
+    """the 6-layer K-buffer mode (shaders/gaussian_splat.metal), every stage bit-exact."""
+    from oracle import oracle as O
+    w, h = 640, 360
+    V, P = O.app_camera(w, h)
+    F = _check_all(gpu_ctx, small_scene, V, P, w, h, mode=2, order=0)
+    assert F.D > 0
+    _check_all(gpu_ctx, small_scene, V, P, 333, 217, mode=2, order=0, rows=(3, 9))      # ragged viewport + band
+    _check_all(gpu_ctx, small_scene[:50], V, P, 16, 16, mode=2, order=0)               # one tile: no sort pass at all
+
+
+@pytest.mark.parametrize("name,mode,K", [("tile", 0, 32), ("layer50", 1, 50), ("mlab", 2, 1 << 30)])
+def test_reference_shader_golden_images(gpu_ctx, name, mode, K):
+    """The CUDA path against committed images of the REFERENCE's own shader statements (Oracle-A; see
+    tests/golden/make_golden.py): 1/255 on every pixel whose list stayed under the cap."""
+    import os
+    from oracle import oracle as O
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "golden_small.npz"))
+    w, h = int(g["w"]), int(g["h"])
+    gpu_ctx.upload(g["ora_instances"])
+    got, _ = _render(gpu_ctx, g["ora_instances"], g["view"], g["proj"], w, h, mode=mode, order=1)
+    ref = g["ora_" + name + "_image"]; under = g["ora_" + name + "_arrivals"] <= K
+    d = np.abs(O.half_bits_to_float(got) - O.half_bits_to_float(ref)).max(axis=2)
+    assert d[under].max() <= 1.0 / 255.0
+    assert (got == ref).all(axis=2)[under].mean() > 0.99
+
+
+@pytest.mark.parametrize("name,mode,order", [("tile_near", 0, 0), ("tile_ref", 0, 1), ("layer50_near", 1, 0), ("layer50_ref", 1, 1),
+                                             ("mlab", 2, 0)])
 def test_committed_golden_fixture(gpu_ctx, name, mode, order):
     """tests/golden/golden_small.npz (made by tests/golden/make_golden.py): lists overflow K and early
     termination triggers in this scene. Sorted pairs, ranges and image bit-exact."""

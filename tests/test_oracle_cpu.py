@@ -123,12 +123,28 @@ def test_threads_do_not_change_results(small_scene):
     assert np.array_equal(a.keys_sorted, b.keys_sorted) and np.array_equal(ia, ib) and ta == tb
 
 
-@pytest.mark.parametrize("name", ["tile_near", "tile_ref", "layer50_near", "layer50_ref"])
+@pytest.mark.parametrize("name,mode,K", [("tile", 0, 32), ("layer50", 1, 50), ("mlab", 2, 1 << 30)])
+def test_reference_shader_golden_images(name, mode, K):
+    """Committed images of the REFERENCE's own shader statements (Oracle-A, generated where /root/reference
+    exists by tests/golden/make_golden.py). Oracle-B, in the shaders' literal depth order, must agree on
+    every pixel whose list stayed under the cap: north_star tolerance 1/255, and mostly bit-identical."""
+    g = np.load(os.path.join(GOLDEN, "golden_small.npz"))
+    w, h = int(g["w"]), int(g["h"])
+    F = O.Frame(g["ora_instances"], g["view"], g["proj"], w, h, mode=mode, order=O.ORDER_REFERENCE)
+    img, _ = F.blend()
+    ref = g["ora_" + name + "_image"]; under = g["ora_" + name + "_arrivals"] <= K
+    assert under.mean() > 0.95
+    d = np.abs(O.half_bits_to_float(img) - O.half_bits_to_float(ref)).max(axis=2)
+    assert d[under].max() <= 1.0 / 255.0
+    assert (img == ref).all(axis=2)[under].mean() > 0.99
+
+
+@pytest.mark.parametrize("name", ["tile_near", "tile_ref", "layer50_near", "layer50_ref", "mlab"])
 def test_golden_fixtures(name):
     """Committed vectors (tests/golden/make_golden.py): guards the oracle against silent drift."""
     g = np.load(os.path.join(GOLDEN, "golden_small.npz"))
     inst = g["instances"]; w, h = int(g["w"]), int(g["h"])
-    mode = O.MODE_LAYER50 if name.startswith("layer50") else O.MODE_TILE
+    mode = O.MODE_LAYER50 if name.startswith("layer50") else (O.MODE_MLAB if name == "mlab" else O.MODE_TILE)
     order = O.ORDER_REFERENCE if name.endswith("ref") else O.ORDER_NEAR_FIRST
     F = O.Frame(inst, g["view"], g["proj"], w, h, mode=mode, order=order)
     assert np.array_equal(F.keys_sorted, g[name + "_keys"])
