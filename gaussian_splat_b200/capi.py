@@ -17,7 +17,8 @@ MODE_TILE, MODE_LAYER50, MODE_MLAB = 0, 1, 2
 ORDER_NEAR_FIRST, ORDER_REFERENCE = 0, 1
 FLAG_TIMING, FLAG_KEEP_UNSORTED = 1, 2
 (FETCH_RECORDS, FETCH_TILES_TOUCHED, FETCH_OFFSETS, FETCH_KEYS_UNSORTED, FETCH_VALS_UNSORTED,
- FETCH_KEYS_SORTED, FETCH_VALS_SORTED, FETCH_TILE_RANGES, FETCH_DIGIT_HISTOGRAMS) = range(9)
+ FETCH_KEYS_SORTED, FETCH_VALS_SORTED, FETCH_TILE_RANGES, FETCH_DIGIT_HISTOGRAMS, FETCH_INSTANCES,
+ FETCH_SH_REST) = range(11)
 
 RECORD_DTYPE = np.dtype([
     ("cx", "<f4"), ("cy", "<f4"), ("ux", "<f4"), ("uy", "<f4"), ("vx", "<f4"), ("vy", "<f4"),
@@ -26,7 +27,7 @@ RECORD_DTYPE = np.dtype([
 
 EXPORTS = [
     "splat_create", "splat_destroy", "splat_upload", "splat_upload_sh", "splat_render",
-    "splat_render_host", "splat_render_batch", "splat_render_batch_host", "splat_frame_status", "splat_debug_fetch",
+    "splat_render_host", "splat_render_batch", "splat_render_batch_host", "splat_pack_bgra8", "splat_upload_ply_rows", "splat_frame_status", "splat_debug_fetch",
     "splat_stage_times", "splat_sort_pairs_u64_u32", "splat_last_error_string", "splat_version",
 ]
 
@@ -65,6 +66,8 @@ def lib():
         L.splat_render_host.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.POINTER(SplatOpts)]
         L.splat_render_batch.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.POINTER(SplatOpts)]
         L.splat_render_batch_host.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.POINTER(SplatOpts)]
+        L.splat_upload_ply_rows.argtypes = [vp, vp, C.c_uint64, C.c_uint32, vp, C.c_float, C.c_int, C.POINTER(C.c_uint32)]
+        L.splat_pack_bgra8.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int]
         L.splat_frame_status.argtypes = [vp, C.POINTER(SplatStatus)]
         L.splat_debug_fetch.argtypes = [vp, C.c_int, vp, C.POINTER(C.c_size_t)]
         L.splat_stage_times.argtypes = [vp, C.POINTER(C.c_float)]
@@ -89,7 +92,7 @@ def make_opts(mode=MODE_TILE, max_fragments=0, order=ORDER_NEAR_FIRST, sh_degree
 _FETCH_DTYPE = {FETCH_RECORDS: RECORD_DTYPE, FETCH_TILES_TOUCHED: np.uint32, FETCH_OFFSETS: np.uint32,
                 FETCH_KEYS_UNSORTED: np.uint64, FETCH_VALS_UNSORTED: np.uint32, FETCH_KEYS_SORTED: np.uint64,
                 FETCH_VALS_SORTED: np.uint32, FETCH_TILE_RANGES: np.uint32,
-                FETCH_DIGIT_HISTOGRAMS: np.uint32}
+                FETCH_DIGIT_HISTOGRAMS: np.uint32, FETCH_INSTANCES: np.float32, FETCH_SH_REST: np.float32}
 
 
 class Context:
@@ -139,6 +142,20 @@ class Context:
         _check(lib().splat_render_batch(self._h, stream_ptr, arr, v.ctypes.data, p.ctypes.data, n, w, h,
                                         C.byref(opts) if opts is not None else None), "splat_render_batch")
 
+    def upload_ply_rows(self, rows: np.ndarray, slot_dst, crop: float = 5.0, sh_degree: int = 0) -> int:
+        """GPU-side PLY decode: rows float32 [n, stride] raw properties, slot_dst int32 [stride]. Returns splats kept."""
+        rows = np.ascontiguousarray(rows, np.float32)
+        slots = np.ascontiguousarray(slot_dst, np.int32)
+        n, stride = (rows.shape if rows.ndim == 2 else (0, slots.size))
+        kept = C.c_uint32(0)
+        _check(lib().splat_upload_ply_rows(self._h, rows.ctypes.data if n else None, n, stride, slots.ctypes.data, crop,
+                                           sh_degree, C.byref(kept)), "splat_upload_ply_rows")
+        return int(kept.value)
+
+    def pack_bgra8(self, stream_ptr: int, fb_dev_ptr: int, bgra_dev_ptr: int, w: int, h: int):
+        """RGBA16F framebuffer -> BGRA8Unorm (the reference drawable's format), on the device."""
+        _check(lib().splat_pack_bgra8(self._h, stream_ptr, fb_dev_ptr, bgra_dev_ptr, w, h), "splat_pack_bgra8")
+
     def render_batch_host(self, fb_host_ptrs, views, projs, w: int, h: int, opts=None):
         """n views end to end into host framebuffers (pinned for overlap), copies pipelined behind rendering."""
         n = len(fb_host_ptrs)
@@ -162,6 +179,10 @@ class Context:
             _check(lib().splat_debug_fetch(self._h, what, out.ctypes.data, C.byref(nbytes)), "splat_debug_fetch")
         if what == FETCH_DIGIT_HISTOGRAMS:
             return out.reshape(8, 256)
+        if what == FETCH_INSTANCES:
+            return out.reshape(-1, 14)
+        if what == FETCH_SH_REST:
+            return out.reshape(-1, 45)
         return out.reshape(-1, 2) if what == FETCH_TILE_RANGES else out
 
     def stage_times(self):

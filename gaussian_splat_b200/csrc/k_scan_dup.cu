@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
     __shared__ unsigned int s_rlo[SCAN_TILE_ITEMS], s_rhi[SCAN_TILE_ITEMS], s_df[SCAN_TILE_ITEMS];
     __shared__ unsigned int s_hist[FRAME_MAX_PASSES][256];
     __shared__ unsigned int s_warp[SCAN_THREADS / 32];
-    __shared__ unsigned int s_tile, s_prefix, s_total;
+    __shared__ unsigned int s_tile, s_prefix;
 
     const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) s_tile = atomicAdd(&ctl->scan_ticket, 1u);
@@ -95,7 +95,6 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
             const unsigned int inclusive = sat_add(prefix, btotal);
             if (tile != 0) lb_store(status + tile, lb_pack(epoch, LB_FLAG_INC, inclusive));
             s_prefix = prefix;
-            s_total = btotal;
             atomicAdd(&ctl->total_pairs, (unsigned long long)btotal);
             if (tile == n_tiles - 1) {
                 const bool over = (unsigned long long)inclusive > capacity;

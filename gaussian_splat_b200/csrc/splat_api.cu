@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <vector>
 
 static thread_local std::string g_err;
 
@@ -220,6 +221,33 @@ int splat_destroy(splat_ctx* c) {
     return SPLAT_OK;
 }
 
+// Installs n SplatInstance rows that already sit in device memory as the scene (planes + per-frame scratch).
+static int install_scene(splat_ctx* c, const float* aos_dev, uint32_t n) {
+    const size_t n_pad = ((size_t)n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS * SCAN_TILE_ITEMS;
+    CK(cudaMalloc(&c->rot, n_pad * 16)); CK(cudaMalloc(&c->pos_sx, n_pad * 16)); CK(cudaMalloc(&c->syz, n_pad * 16));
+    CK(cudaMalloc(&c->bq, n_pad * 2)); CK(cudaMalloc(&c->base_rgb, n_pad * 16));
+    { const int rc = alloc_scene_scratch(c, n_pad); if (rc) return rc; }
+    launch_upload_soa(aos_dev, n, c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, 0);
+    CK(cudaGetLastError());
+    CK(cudaDeviceSynchronize());
+    c->n = n; c->n_pad = n_pad;
+    // vals hold splat indices; stale ones from a larger scene must not survive
+    for (int k = 0; k < 2; ++k) if (c->vals[k]) CK(cudaMemset(c->vals[k], 0, c->capacity * 4));
+    unsigned long long want = (unsigned long long)n * 12ull;
+    if (want < (1ull << 20)) want = 1ull << 20;
+    if (want > 0xC0000000ull) want = 0xC0000000ull;
+    return ensure_pairs_all(c, want);
+}
+
+static int install_sh(splat_ctx* c, const float* sh_dev, uint32_t n, int degree) {
+    CK(cudaMalloc(&c->sh, c->n_pad * 12 * 16));
+    launch_upload_sh(sh_dev, n, c->n_pad, c->sh, 0);
+    CK(cudaGetLastError());
+    CK(cudaDeviceSynchronize());
+    c->sh_degree = degree;
+    return SPLAT_OK;
+}
+
 int splat_upload(splat_ctx* c, const void* aos_host, uint32_t n) {
     if (!c) ARG_FAIL("splat_upload: ctx is NULL");
     if (n && !aos_host) ARG_FAIL("splat_upload: aos_host is NULL");
@@ -228,24 +256,64 @@ int splat_upload(splat_ctx* c, const void* aos_host, uint32_t n) {
     free_scene(c);
     c->have_frame = false;
     if (n == 0) return SPLAT_OK;
-    const size_t n_pad = ((size_t)n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS * SCAN_TILE_ITEMS;
-    CK(cudaMalloc(&c->rot, n_pad * 16)); CK(cudaMalloc(&c->pos_sx, n_pad * 16)); CK(cudaMalloc(&c->syz, n_pad * 16));
-    CK(cudaMalloc(&c->bq, n_pad * 2)); CK(cudaMalloc(&c->base_rgb, n_pad * 16));
-    { const int rc = alloc_scene_scratch(c, n_pad); if (rc) return rc; }
     float* aos_dev = nullptr;
     CK(cudaMalloc(&aos_dev, (size_t)n * 56));
-    CK(cudaMemcpy(aos_dev, aos_host, (size_t)n * 56, cudaMemcpyHostToDevice));
-    launch_upload_soa(aos_dev, n, c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, 0);
-    CK(cudaGetLastError());
-    CK(cudaDeviceSynchronize());
+    int rc = cudaMemcpy(aos_dev, aos_host, (size_t)n * 56, cudaMemcpyHostToDevice) == cudaSuccess ? SPLAT_OK : SPLAT_ERR_CUDA;
+    if (rc) g_err = "splat_upload: host to device copy failed";
+    else rc = install_scene(c, aos_dev, n);
     cudaFree(aos_dev);
-    c->n = n; c->n_pad = n_pad;
-    // vals hold splat indices; stale ones from a larger scene must not survive
-    for (int k = 0; k < 2; ++k) if (c->vals[k]) CK(cudaMemset(c->vals[k], 0, c->capacity * 4));
-    unsigned long long want = (unsigned long long)n * 12ull;
-    if (want < (1ull << 20)) want = 1ull << 20;
-    if (want > 0xC0000000ull) want = 0xC0000000ull;
-    return ensure_pairs_all(c, want);
+    return rc;
+}
+
+int splat_upload_ply_rows(splat_ctx* c, const void* rows_host, uint64_t n_rows, uint32_t stride, const int32_t* slot_dst,
+                          float crop, int sh_degree, uint32_t* n_kept) {
+    if (!c) ARG_FAIL("splat_upload_ply_rows: ctx is NULL");
+    if (n_kept) *n_kept = 0;
+    if (n_rows && (!rows_host || !slot_dst)) ARG_FAIL("splat_upload_ply_rows: NULL rows or slot table");
+    if (n_rows >= 0xFFFF0000ull) ARG_FAIL("splat_upload_ply_rows: too many rows");
+    if (n_rows && (stride == 0 || stride > 512)) ARG_FAIL("splat_upload_ply_rows: stride must be 1..512 floats");
+    if (sh_degree < 0 || sh_degree > 3) ARG_FAIL("splat_upload_ply_rows: sh_degree must be 0..3");
+    int jx = -1, jy = -1, jz = -1;                       // a later property of the same name overrides an earlier one
+    for (uint32_t j = 0; j < stride && n_rows; ++j) {
+        if (slot_dst[j] < -1 || slot_dst[j] > 61) ARG_FAIL("splat_upload_ply_rows: slot index outside -1..61");
+        if (slot_dst[j] == 0) jx = (int)j; else if (slot_dst[j] == 1) jy = (int)j; else if (slot_dst[j] == 2) jz = (int)j;
+    }
+    CK(cudaSetDevice(c->device));
+    CK(cudaDeviceSynchronize());
+    free_scene(c);
+    c->have_frame = false;
+    if (n_rows == 0) return SPLAT_OK;
+
+    const uint32_t chunk_rows = 1u << 18;                // 65 MB of a 62-float file per chunk
+    const uint32_t max_blocks = (chunk_rows + 127) / 128;
+    float *rows_dev = nullptr, *aos_dev = nullptr, *sh_dev = nullptr;
+    int* slots_dev = nullptr; unsigned int *counts = nullptr, *running = nullptr;
+    int rc = SPLAT_OK;
+    auto fail = [&](const char* what) { g_err = std::string("splat_upload_ply_rows: ") + what; rc = SPLAT_ERR_CUDA; };
+    const size_t chunk_bytes = (size_t)(n_rows < chunk_rows ? n_rows : chunk_rows) * stride * 4;
+    if (cudaMalloc(&rows_dev, chunk_bytes) != cudaSuccess || cudaMalloc(&aos_dev, (size_t)n_rows * 56) != cudaSuccess ||
+        (sh_degree > 0 && cudaMalloc(&sh_dev, (size_t)n_rows * 45 * 4) != cudaSuccess) ||
+        cudaMalloc(&slots_dev, stride * 4) != cudaSuccess || cudaMalloc(&counts, max_blocks * 4) != cudaSuccess ||
+        cudaMalloc(&running, 4) != cudaSuccess) fail("device allocation failed");
+    if (!rc && (cudaMemcpy(slots_dev, slot_dst, stride * 4, cudaMemcpyHostToDevice) != cudaSuccess ||
+                cudaMemset(running, 0, 4) != cudaSuccess)) fail("slot table copy failed");
+    for (uint64_t r0 = 0; !rc && r0 < n_rows; r0 += chunk_rows) {
+        const uint32_t nr = (uint32_t)(n_rows - r0 < chunk_rows ? n_rows - r0 : chunk_rows);
+        if (cudaMemcpyAsync(rows_dev, (const char*)rows_host + r0 * stride * 4, (size_t)nr * stride * 4, cudaMemcpyHostToDevice,
+                            c->own_stream) != cudaSuccess) { fail("host to device copy failed"); break; }
+        if (launch_ply_decode_chunk(rows_dev, nr, stride, slots_dev, jx, jy, jz, crop, counts, running, aos_dev, sh_dev,
+                                    c->own_stream) != cudaSuccess) { fail(cudaGetErrorString(cudaGetLastError())); break; }
+    }
+    unsigned int kept = 0;
+    if (!rc && (cudaStreamSynchronize(c->own_stream) != cudaSuccess ||
+                cudaMemcpy(&kept, running, 4, cudaMemcpyDeviceToHost) != cudaSuccess)) fail(cudaGetErrorString(cudaGetLastError()));
+    if (!rc && kept) {
+        rc = install_scene(c, aos_dev, kept);
+        if (!rc && sh_degree > 0) rc = install_sh(c, sh_dev, kept, sh_degree);
+    }
+    cudaFree(rows_dev); cudaFree(aos_dev); cudaFree(sh_dev); cudaFree(slots_dev); cudaFree(counts); cudaFree(running);
+    if (!rc && n_kept) *n_kept = kept;
+    return rc;
 }
 
 int splat_upload_sh(splat_ctx* c, const float* sh_host, uint32_t n, int degree) {
@@ -259,14 +327,11 @@ int splat_upload_sh(splat_ctx* c, const float* sh_host, uint32_t n, int degree) 
     if (!sh_host) ARG_FAIL("splat_upload_sh: sh_rest45_host is NULL");
     float* staging = nullptr;
     CK(cudaMalloc(&staging, (size_t)n * 45 * 4));
-    CK(cudaMemcpy(staging, sh_host, (size_t)n * 45 * 4, cudaMemcpyHostToDevice));
-    CK(cudaMalloc(&c->sh, c->n_pad * 12 * 16));
-    launch_upload_sh(staging, n, c->n_pad, c->sh, 0);
-    CK(cudaGetLastError());
-    CK(cudaDeviceSynchronize());
+    int rc = cudaMemcpy(staging, sh_host, (size_t)n * 45 * 4, cudaMemcpyHostToDevice) == cudaSuccess ? SPLAT_OK : SPLAT_ERR_CUDA;
+    if (rc) g_err = "splat_upload_sh: host to device copy failed";
+    else rc = install_sh(c, staging, n, degree);
     cudaFree(staging);
-    c->sh_degree = degree;
-    return SPLAT_OK;
+    return rc;
 }
 
 }  // extern "C"
@@ -599,6 +664,39 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
         *bytes = need;
         return SPLAT_OK;
     }
+    if (what == SPLAT_FETCH_INSTANCES || what == SPLAT_FETCH_SH_REST) {
+        const bool sh = what == SPLAT_FETCH_SH_REST;
+        if (sh && c->n && !c->sh) { g_err = "splat_debug_fetch: no SH coefficients uploaded"; return SPLAT_ERR_STATE; }
+        const size_t need = (size_t)c->n * (sh ? 45 : 14) * 4;
+        if (!dst) { *bytes = need; return SPLAT_OK; }
+        if (*bytes < need) { *bytes = need; ARG_FAIL("splat_debug_fetch: destination too small"); }
+        float* o = (float*)dst;
+        if (!sh && c->n) {
+            std::vector<float> rot((size_t)c->n * 4), pos((size_t)c->n * 4), syz((size_t)c->n * 4), rgb((size_t)c->n * 4);
+            CK(cudaMemcpy(rot.data(), c->rot, rot.size() * 4, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(pos.data(), c->pos_sx, pos.size() * 4, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(syz.data(), c->syz, syz.size() * 4, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(rgb.data(), c->base_rgb, rgb.size() * 4, cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < c->n; ++i) {
+                float* a = o + i * 14;
+                for (int k = 0; k < 4; ++k) a[k] = rot[i * 4 + k];
+                a[4] = pos[i * 4 + 3]; a[5] = syz[i * 4 + 0]; a[6] = syz[i * 4 + 1];
+                a[7] = pos[i * 4 + 0]; a[8] = pos[i * 4 + 1]; a[9] = pos[i * 4 + 2];
+                a[10] = rgb[i * 4 + 0]; a[11] = rgb[i * 4 + 1]; a[12] = rgb[i * 4 + 2]; a[13] = syz[i * 4 + 2];
+            }
+        } else if (c->n) {
+            // planes: float4[12][n_pad], coefficient-major; float index f of plane j = channel (4j+f)/15, coefficient (4j+f)%15
+            std::vector<float> pl(c->n_pad * 48);
+            CK(cudaMemcpy(pl.data(), c->sh, pl.size() * 4, cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < c->n; ++i)
+                for (int q = 0; q < 45; ++q) {
+                    const int coef = q / 3, ch = q % 3;                   // plane order: coefficient-major, rgb interleaved
+                    o[i * 45 + ch * 15 + coef] = pl[((size_t)(q / 4) * c->n_pad + i) * 4 + (q % 4)];
+                }
+        }
+        *bytes = need;
+        return SPLAT_OK;
+    }
     if (!c->have_frame) { g_err = "splat_debug_fetch: no frame rendered"; return SPLAT_ERR_STATE; }
     CK(cudaMemcpy(c->ctl_host, c->ctl, 64, cudaMemcpyDeviceToHost));
     if (c->ctl_host->overflow) { g_err = "splat_debug_fetch: last frame overflowed the pair buffers"; return SPLAT_ERR_OVERFLOW; }
@@ -644,6 +742,16 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
         CK(e);
     }
     *bytes = need;
+    return SPLAT_OK;
+}
+
+int splat_pack_bgra8(splat_ctx* c, void* stream, const void* fb_half4, void* bgra8, int w, int h) {
+    if (!c) ARG_FAIL("splat_pack_bgra8: ctx is NULL");
+    if (w < 0 || h < 0 || ((w && h) && (!fb_half4 || !bgra8))) ARG_FAIL("splat_pack_bgra8: bad arguments");
+    if (((uintptr_t)fb_half4 & 15u) || ((uintptr_t)bgra8 & 7u)) ARG_FAIL("splat_pack_bgra8: buffers must be 16- / 8-byte aligned");
+    CK(cudaSetDevice(c->device));
+    launch_pack_bgra8(fb_half4, bgra8, (size_t)w * h, (cudaStream_t)stream);
+    CK(cudaGetLastError());
     return SPLAT_OK;
 }
 

@@ -103,5 +103,9 @@ void launch_radix_sort(unsigned long long* keys, unsigned int* vals, unsigned lo
 // bounds[t] = first sorted pair of tile t (t = 0..n_tiles); tile t owns [bounds[t], bounds[t+1]).
 void launch_tile_bounds(const unsigned long long* keys_sorted, const FrameCtl* ctl, unsigned int n_tiles,
                         unsigned int* bounds, cudaStream_t s);
+void launch_pack_bgra8(const void* fb_half4, void* bgra8, size_t n_pixels, cudaStream_t s);
+cudaError_t launch_ply_decode_chunk(const float* rows_dev, unsigned int n_rows, unsigned int stride, const int* slot_dst_dev,
+                                    int jx, int jy, int jz, float crop, unsigned int* block_counts, unsigned int* running,
+                                    float* aos_out, float* sh_out, cudaStream_t s);
 void launch_blend(const FrameUniforms& U, const splat_record* rec, const unsigned int* vals_sorted,
                   const unsigned int* vals_depth_sorted, const unsigned int* bounds, void* fb_half4, cudaStream_t s);

@@ -36,6 +36,7 @@ void host_cam_target(void* c, float o[3]) { const simd_float3 p = static_cast<Tr
 
 // ---- InstancedSplatRenderer
 void* host_renderer_create(const char* ply_path) { return new InstancedSplatRenderer(ply_path); }
+void* host_renderer_create_device_decode(const char* ply_path) { return new InstancedSplatRenderer(ply_path, SplatDecode::Device); }
 void host_renderer_destroy(void* r) { delete static_cast<InstancedSplatRenderer*>(r); }
 int host_renderer_initialize(void* r, int cuda_device) { SplatDevice d{cuda_device}; return static_cast<InstancedSplatRenderer*>(r)->initialize(&d) ? 1 : 0; }
 int host_renderer_point_count(void* r) { return static_cast<InstancedSplatRenderer*>(r)->getPointCount(); }

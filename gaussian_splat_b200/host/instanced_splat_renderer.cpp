@@ -15,9 +15,20 @@ public:
     splat_opts opts{};
     std::vector<float> sh_rest;   // [n][45], kept only so a later setOptions(sh_degree > 0) can upload it
     bool sh_uploaded = false;
+    bool device_decode = false;
+    PLYLoader::Rows raw;          // undecoded vertex table (SplatDecode::Device), released after initialize()
 };
 
-InstancedSplatRenderer::InstancedSplatRenderer(std::string filepath) : impl(new Impl()) {
+InstancedSplatRenderer::InstancedSplatRenderer(std::string filepath, SplatDecode where) : impl(new Impl()) {
+    if (where == SplatDecode::Host) { decodeOnHost(filepath); return; }
+    impl->device_decode = true;
+    if (!PLYLoader::loadRows(filepath, impl->raw))
+        std::cerr << "Failed to load Gaussian splat from: " << filepath << std::endl;
+}
+
+InstancedSplatRenderer::InstancedSplatRenderer(std::string filepath) : impl(new Impl()) { decodeOnHost(filepath); }
+
+void InstancedSplatRenderer::decodeOnHost(const std::string& filepath) {
     std::vector<PointData> points;
     if (!PLYLoader::load(filepath, points)) {
         std::cerr << "Failed to load Gaussian splat from: " << filepath << std::endl;
@@ -36,6 +47,7 @@ InstancedSplatRenderer::InstancedSplatRenderer(std::string filepath) : impl(new 
         _instances.push_back(s);
         impl->sh_rest.insert(impl->sh_rest.end(), p.sh_rest, p.sh_rest + 45);
     }
+    _count = _instances.size();
 }
 
 InstancedSplatRenderer::~InstancedSplatRenderer() {
@@ -50,6 +62,19 @@ bool InstancedSplatRenderer::initialize(void* device) {
         std::cerr << "InstancedSplatRenderer: " << splat_last_error_string() << std::endl;
         return false;
     }
+    if (impl->device_decode) {
+        uint32_t kept = 0;
+        const float crop = 5.0f;                           // src/instanced_splat_renderer.mm:360
+        if (impl->raw.n && splat_upload_ply_rows(impl->ctx, impl->raw.rows.data(), impl->raw.n, impl->raw.stride,
+                                                 impl->raw.slot_dst.data(), crop, 3, &kept) != SPLAT_OK) {
+            std::cerr << "InstancedSplatRenderer: " << splat_last_error_string() << std::endl;
+            return false;
+        }
+        _count = kept;
+        _instances.clear();
+        impl->sh_uploaded = true;                          // f_rest went up with the decode
+        return true;
+    }
     if (!_instances.empty() && splat_upload(impl->ctx, _instances.data(), (uint32_t)_instances.size()) != SPLAT_OK) {
         std::cerr << "InstancedSplatRenderer: " << splat_last_error_string() << std::endl;
         return false;
@@ -61,11 +86,20 @@ bool InstancedSplatRenderer::initialize(void* device) {
 void InstancedSplatRenderer::setOptions(const splat_opts& o) { impl->opts = o; }
 splat_ctx* InstancedSplatRenderer::context() { return impl->ctx; }
 
+const std::vector<SplatInstance>& InstancedSplatRenderer::instances() {
+    if (_instances.empty() && _count && impl->device_decode && impl->ctx) {
+        _instances.resize(_count);
+        size_t bytes = _count * sizeof(SplatInstance);
+        if (splat_debug_fetch(impl->ctx, SPLAT_FETCH_INSTANCES, _instances.data(), &bytes) != SPLAT_OK) _instances.clear();
+    }
+    return _instances;
+}
+
 bool InstancedSplatRenderer::stageTimes(float ms[8]) { return impl->ctx && splat_stage_times(impl->ctx, ms) == SPLAT_OK; }
 
 void InstancedSplatRenderer::render(void* commandBuffer, void* drawableTexture, const simd_float4x4& view,
                                     const simd_float4x4& proj, float viewportWidth, float viewportHeight) {
-    if (!impl->ctx || !drawableTexture || _instances.empty()) return;   // src/instanced_splat_renderer.mm:434-440
+    if (!impl->ctx || !drawableTexture || _count == 0) return;   // src/instanced_splat_renderer.mm:434-440
     if (impl->opts.sh_degree > 0 && !impl->sh_uploaded) {
         if (splat_upload_sh(impl->ctx, impl->sh_rest.data(), (uint32_t)_instances.size(), 3) != SPLAT_OK) {
             std::cerr << "InstancedSplatRenderer: " << splat_last_error_string() << std::endl;

@@ -22,10 +22,15 @@ struct SplatInstance {
 static_assert(sizeof(SplatInstance) == 56, "SplatInstance is 56 packed bytes (src/instanced_splat_renderer.h:6-11)");
 
 struct SplatDevice { int cuda_device; };
+// Where the PLY vertex table is decoded (activations, DC -> colour, crop): on the host as the reference
+// does (src/ply_loader.cpp:91-146 + src/instanced_splat_renderer.mm:360-388), or by the device kernel behind
+// splat_upload_ply_rows during initialize() (same results, bit for bit).
+enum class SplatDecode { Host, Device };
 
 class InstancedSplatRenderer {
 public:
     InstancedSplatRenderer(std::string filepath);
+    InstancedSplatRenderer(std::string filepath, SplatDecode where);     // addition: Device defers the decode to initialize()
     ~InstancedSplatRenderer();
 
     bool initialize(void* device);
@@ -33,18 +38,23 @@ public:
     void render(void* commandBuffer, void* drawableTexture, const simd_float4x4& viewMatrix,
                 const simd_float4x4& projectionMatrix, float viewportWidth, float viewportHeight);
 
-    int getPointCount() const { return (int)_instances.size(); }
+    int getPointCount() const { return (int)_count; }
 
     // --- additions (no counterpart in the reference) ---
     // mode / K / depth order / SH degree / tile-row band; defaults = TILE, K 32, near-first, degree 0.
     void setOptions(const splat_opts& opts);
     // Per-stage ms of the last frame rendered with SPLAT_FLAG_TIMING (synchronises).
     bool stageTimes(float ms[8]);
-    const std::vector<SplatInstance>& instances() const { return _instances; }
+    // Host copy of the instances; with SplatDecode::Device it is read back from the device on first use.
+    const std::vector<SplatInstance>& instances();
     splat_ctx* context();
 
 private:
     std::vector<SplatInstance> _instances;
+    size_t _count = 0;
+    void decodeOnHost(const std::string& filepath);
+    InstancedSplatRenderer(const InstancedSplatRenderer&) = delete;
+    InstancedSplatRenderer& operator=(const InstancedSplatRenderer&) = delete;
     class Impl;
     Impl* impl;
 };

@@ -106,3 +106,29 @@ bool PLYLoader::load(const std::string& filepath, std::vector<PointData>& points
     }
     return !points.empty();
 }
+
+bool PLYLoader::loadRows(const std::string& filepath, Rows& out) {
+    std::ifstream in(filepath, std::ios::binary);
+    if (!in.is_open()) { std::cerr << "Failed to open PLY file: " << filepath << std::endl; return false; }
+    Header h;
+    if (!read_header(in, h)) { std::cerr << "Failed to parse PLY header" << std::endl; return false; }
+    out = Rows{};
+    out.stride = (unsigned)h.slots.size();
+    for (const Slot& s : h.slots) out.slot_dst.push_back(s.dst);
+    const size_t stride = h.slots.size();
+    if (h.binary) {
+        out.n = (size_t)h.vertices;
+        out.rows.assign(out.n * stride, 0.0f);             // a short file leaves a zero-fed tail, as in load()
+        in.read(reinterpret_cast<char*>(out.rows.data()), (std::streamsize)(out.rows.size() * sizeof(float)));
+    } else {
+        std::string line;
+        for (long i = 0; i < h.vertices && std::getline(in, line); ++i) {
+            std::istringstream ss(line);
+            const size_t at = out.rows.size();
+            out.rows.resize(at + stride, 0.0f);
+            for (size_t j = 0; j < stride; ++j) { float v = 0.0f; ss >> v; out.rows[at + j] = v; }
+            ++out.n;
+        }
+    }
+    return out.n > 0;
+}

@@ -25,4 +25,16 @@ public:
     //  * ASCII files yield exactly `element vertex` points (the reference yields 2x: a resize
     //    followed by push_back, src/ply_loader.cpp:52,199 — deliberately not reproduced).
     static bool load(const std::string& filepath, std::vector<PointData>& points);
+
+    // --- addition (no counterpart in the reference): the file's vertex table left UNDECODED, for the GPU
+    // decode entry splat_upload_ply_rows (include/splat_cuda.h). rows = n * stride floats exactly as load()
+    // would feed them to its per-row decode (binary body, or the parsed numbers of an ASCII file);
+    // slot_dst[j] = PointData float index of the j-th property, -1 = ignored.
+    struct Rows {
+        std::vector<float> rows;
+        size_t n = 0;
+        unsigned stride = 0;
+        std::vector<int> slot_dst;
+    };
+    static bool loadRows(const std::string& filepath, Rows& out);
 };

@@ -4,7 +4,7 @@
 // last one as a binary PPM.
 //
 //   splat_headless scene.ply [--width 1920] [--height 1080] [--frames 64] [--mode tile|layer50|mlab]
-//                  [--k N] [--order near|reference] [--sh 0..3] [--device 0] [--out frame.ppm]
+//                  [--k N] [--order near|reference] [--sh 0..3] [--device 0] [--out frame.ppm] [--decode host|device]
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -18,17 +18,17 @@
 #include "instanced_splat_renderer.h"
 #include "trackball_camera.h"
 
-static bool write_ppm(const char* path, const std::vector<_Float16>& px, int w, int h) {
+// P6 from the BGRA8 drawable image produced by splat_pack_bgra8.
+static bool write_ppm(const char* path, const std::vector<unsigned char>& bgra, int w, int h) {
     FILE* f = std::fopen(path, "wb");
     if (!f) return false;
     std::fprintf(f, "P6\n%d %d\n255\n", w, h);
     std::vector<unsigned char> row((size_t)w * 3);
     for (int j = 0; j < h; ++j) {
-        for (int i = 0; i < w; ++i)
-            for (int c = 0; c < 3; ++c) {
-                const float v = (float)px[((size_t)j * w + i) * 4 + c];
-                row[(size_t)i * 3 + c] = (unsigned char)std::lround(std::min(1.0f, std::max(0.0f, v)) * 255.0f);
-            }
+        for (int i = 0; i < w; ++i) {
+            const unsigned char* p = &bgra[((size_t)j * w + i) * 4];
+            row[(size_t)i * 3 + 0] = p[2]; row[(size_t)i * 3 + 1] = p[1]; row[(size_t)i * 3 + 2] = p[0];
+        }
         std::fwrite(row.data(), 1, row.size(), f);
     }
     std::fclose(f);
@@ -39,6 +39,7 @@ int main(int argc, char** argv) {
     if (argc < 2) { std::fprintf(stderr, "usage: %s scene.ply [options]\n", argv[0]); return 2; }
     int w = 1920, h = 1080, frames = 64, device = 0;
     const char* out = nullptr;
+    SplatDecode decode = SplatDecode::Host;
     splat_opts opts{};
     opts.flags = SPLAT_FLAG_TIMING;
     for (int a = 2; a + 1 < argc; a += 2) {
@@ -47,6 +48,7 @@ int main(int argc, char** argv) {
         else if (k == "--height") h = std::atoi(v);
         else if (k == "--frames") frames = std::atoi(v);
         else if (k == "--device") device = std::atoi(v);
+        else if (k == "--decode") decode = std::strcmp(v, "device") == 0 ? SplatDecode::Device : SplatDecode::Host;
         else if (k == "--k") opts.max_fragments = std::atoi(v);
         else if (k == "--sh") opts.sh_degree = std::atoi(v);
         else if (k == "--out") out = v;
@@ -55,7 +57,7 @@ int main(int argc, char** argv) {
         else { std::fprintf(stderr, "unknown option %s\n", k.c_str()); return 2; }
     }
 
-    InstancedSplatRenderer renderer(argv[1]);
+    InstancedSplatRenderer renderer(argv[1], decode);
     SplatDevice dev{device};
     if (!renderer.initialize(&dev)) return 1;
     renderer.setOptions(opts);
@@ -85,8 +87,14 @@ int main(int argc, char** argv) {
     const int timed = frames > 1 ? frames - 1 : frames;
     if (timed > 0) std::printf("%d frames, %.3f ms/frame, %.1f frames/s\n", timed, total_ms / timed, 1e3 * timed / total_ms);
     if (out) {
-        std::vector<_Float16> host((size_t)w * h * 4);
-        cudaMemcpy(host.data(), fb, host.size() * 2, cudaMemcpyDeviceToHost);
+        // the reference presents a BGRA8Unorm drawable (src/metal_renderer.mm:58): pack on the device, copy 4 B/pixel
+        void* bgra = nullptr;
+        std::vector<unsigned char> host((size_t)w * h * 4);
+        if (cudaMalloc(&bgra, host.size()) != cudaSuccess ||
+            splat_pack_bgra8(renderer.context(), stream, fb, bgra, w, h) != SPLAT_OK ||
+            cudaMemcpyAsync(host.data(), bgra, host.size(), cudaMemcpyDeviceToHost, stream) != cudaSuccess ||
+            cudaStreamSynchronize(stream) != cudaSuccess) { std::fprintf(stderr, "BGRA8 pack failed\n"); return 1; }
+        cudaFree(bgra);
         if (!write_ppm(out, host, w, h)) { std::fprintf(stderr, "cannot write %s\n", out); return 1; }
         std::printf("wrote %s\n", out);
     }

@@ -37,6 +37,7 @@ def lib():
         for n in ("view", "proj", "position", "target"):
             getattr(L, "host_cam_" + n).argtypes = [vp, vp]
         L.host_renderer_create.restype = vp; L.host_renderer_create.argtypes = [C.c_char_p]
+        L.host_renderer_create_device_decode.restype = vp; L.host_renderer_create_device_decode.argtypes = [C.c_char_p]
         L.host_renderer_destroy.argtypes = [vp]
         L.host_renderer_initialize.argtypes = [vp, C.c_int]
         L.host_renderer_point_count.argtypes = [vp]
@@ -90,8 +91,10 @@ class TrackballCamera:
 class InstancedSplatRenderer:
     """The C++ class with the reference's constructor / initialize / render / getPointCount."""
 
-    def __init__(self, ply_path: str):
-        self.L = lib(); self.h = self.L.host_renderer_create(os.fsencode(ply_path))
+    def __init__(self, ply_path: str, device_decode: bool = False):
+        self.L = lib()
+        make = self.L.host_renderer_create_device_decode if device_decode else self.L.host_renderer_create
+        self.h = make(os.fsencode(ply_path))
 
     def __del__(self):
         if getattr(self, "h", None):

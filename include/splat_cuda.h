@@ -131,7 +131,9 @@ enum {
     SPLAT_FETCH_KEYS_SORTED,     /* uint64[D]                                 */
     SPLAT_FETCH_VALS_SORTED,     /* uint32[D]                                 */
     SPLAT_FETCH_TILE_RANGES,     /* uint32[T][2]                              */
-    SPLAT_FETCH_DIGIT_HISTOGRAMS /* uint32[8][256]: per-pass digit counts of the last frame or stand-alone sort */
+    SPLAT_FETCH_DIGIT_HISTOGRAMS,/* uint32[8][256]: per-pass digit counts of the last frame or stand-alone sort */
+    SPLAT_FETCH_INSTANCES,       /* SplatInstancePOD[n]: the uploaded scene rebuilt from the device planes (no frame needed) */
+    SPLAT_FETCH_SH_REST          /* float[n][45]: uploaded f_rest rows rebuilt from the SH planes (no frame needed)        */
 };
 int splat_debug_fetch(splat_ctx* ctx, int what, void* host_dst, size_t* bytes);
 
@@ -146,6 +148,25 @@ int splat_stage_times(splat_ctx* ctx, float ms[8]);
 int splat_sort_pairs_u64_u32(splat_ctx* ctx, void* stream, uint64_t* keys, uint32_t* vals,
                              uint64_t* keys_alt, uint32_t* vals_alt, uint64_t n,
                              int begin_bit, int end_bit, int* result_in_alt);
+
+/* GPU-side PLY vertex decode (the step before the path): `rows_host` is the binary body of a PLY vertex
+ * element, n_rows rows of stride_floats 4-byte little-endian floats (the reference reads every property as
+ * a float, src/ply_loader.cpp:104-110). slot_dst[j] says where the j-th property goes in the reference's
+ * PointData (src/ply_loader.h:7-17): 0-2 x y z, 3-5 normals, 6-8 f_dc, 9 opacity, 10-12 scale, 13-16 rot,
+ * 17-61 f_rest_0..44, or -1 = ignored (src/ply_loader.cpp:59-81). The kernel applies sigmoid / exp / DC ->
+ * colour exactly as src/ply_loader.cpp:112-139 does (bit-identical to the host C library's expf; a NaN stays a
+ * NaN but loses its payload), drops rows
+ * outside |x|,|y|,|z| < crop_half_extent (src/instanced_splat_renderer.mm:360-366; <= 0 keeps all), keeps
+ * file order, and installs the result as the scene (as splat_upload would), with the f_rest coefficients
+ * as by splat_upload_sh when sh_degree is 1..3. *n_kept receives the number of splats kept. Synchronous. */
+int splat_upload_ply_rows(splat_ctx* ctx, const void* rows_host, uint64_t n_rows, uint32_t stride_floats,
+                          const int32_t* slot_dst, float crop_half_extent, int sh_degree, uint32_t* n_kept);
+
+/* Presentation step after the path: RGBA16F framebuffer -> BGRA8Unorm, the format of the reference's
+ * drawable (src/metal_renderer.mm:58; blit / resolve at src/instanced_splat_renderer.mm:513-527,557-576).
+ * byte = rint(clamp(x, 0, 1) * 255), NaN -> 0; bytes in memory B G R A. Device pointers (16- and 8-byte
+ * aligned); enqueues on stream. */
+int splat_pack_bgra8(splat_ctx* ctx, void* stream, const void* fb_half4, void* bgra8, int w, int h);
 
 const char* splat_last_error_string(void);
 int splat_version(void);

@@ -266,3 +266,21 @@ def test_committed_golden_fixture(gpu_ctx, name, mode, order):
     assert np.array_equal(gpu_ctx.fetch(capi.FETCH_VALS_SORTED), g[name + "_vals"])
     assert np.array_equal(gpu_ctx.fetch(capi.FETCH_TILE_RANGES), g[name + "_ranges"])
     assert np.array_equal(got, g[name + "_image"])
+
+
+def test_pack_bgra8_matches_unorm_conversion(gpu_ctx):
+    """Presentation step: RGBA16F -> BGRA8Unorm, byte-exact against
+    rint(clamp(x,0,1)*255) on every finite half, the infinities, NaN and negative zero; odd pixel count."""
+    import torch
+    w, h = 257, 255                                               # odd pixel count: exercises the tail pixel
+    bits = (np.arange(w * h * 4, dtype=np.uint32) * 2654435761 >> 16).astype(np.uint16)   # all 65536 patterns occur
+    bits[:65536] = np.arange(65536, dtype=np.uint16)
+    x = bits.view(np.float16).astype(np.float32)
+    with np.errstate(invalid="ignore"):
+        u = np.rint(np.clip(np.nan_to_num(x, nan=0.0, posinf=1.0, neginf=0.0), 0.0, 1.0) * np.float32(255.0)).astype(np.uint8)
+    want = u.reshape(h, w, 4)[..., [2, 1, 0, 3]]
+    fb = torch.from_numpy(bits.view(np.int16).reshape(h, w, 4)).cuda()
+    out = torch.zeros((h, w, 4), dtype=torch.uint8, device="cuda")
+    gpu_ctx.pack_bgra8(torch.cuda.current_stream().cuda_stream, fb.data_ptr(), out.data_ptr(), w, h)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy(), want)
