@@ -7,7 +7,7 @@
 __global__ void __launch_bounds__(256) upload_soa_kernel(const float* __restrict__ aos, unsigned int n,
                                                          float4* __restrict__ rot, float4* __restrict__ pos_sx,
                                                          float4* __restrict__ syz_op_rg, uint16_t* __restrict__ bq,
-                                                         float4* __restrict__ base_rgb)
+                                                         float4* __restrict__ base_rgb, float4* __restrict__ scr)
 {
     // Stage 256 rows (256*14 floats) through shared memory so the AoS read is coalesced.
     __shared__ float s[256 * 14];
@@ -26,6 +26,7 @@ __global__ void __launch_bounds__(256) upload_soa_kernel(const float* __restrict
     syz_op_rg[i] = make_float4(r[5], r[6], r[13], __uint_as_float(rg));
     bq[i] = __half_as_ushort(__float2half_rn(r[12]));
     base_rgb[i] = make_float4(r[10], r[11], r[12], 0.0f);
+    scr[i] = make_float4(r[7], r[8], r[9], fmaxf(r[4], fmaxf(r[5], r[6])));     // all the screening kernel reads: 16 B / splat
 }
 
 // f_rest rows (45 floats, channel-major as src/ply_loader.cpp:76-81 stores them) -> 12 float4 planes,
@@ -60,14 +61,13 @@ void launch_upload_sh(const float* sh_rest45_dev, unsigned int n, size_t n_pad, 
 }
 
 void launch_upload_soa(const float* aos_dev, unsigned int n, float4* rot, float4* pos_sx, float4* syz_op_rg,
-                       uint16_t* b, float4* base_rgb, cudaStream_t s)
+                       uint16_t* b, float4* base_rgb, float4* scr, cudaStream_t s)
 {
     if (n == 0) return;
-    upload_soa_kernel<<<(n + 255) / 256, 256, 0, s>>>(aos_dev, n, rot, pos_sx, syz_op_rg, b, base_rgb);
+    upload_soa_kernel<<<(n + 255) / 256, 256, 0, s>>>(aos_dev, n, rot, pos_sx, syz_op_rg, b, base_rgb, scr);
 }
 
-#define K1_ITEMS 2     // splats per thread in the screening phase: all their plane loads are issued before any arithmetic
-#define K1_TILE (256 * K1_ITEMS)
+#define K1_TILE (SCAN_TILE_ITEMS / 2)      // splats per pair-count cell (two cells per duplication tile)
 
 // Screening: can this splat possibly produce a tile (in the viewport and, with tile-row bands, in the
 // band)? Fast approximate arithmetic (FMA, rcp.approx, sqrt.approx: ~70 instructions against ~600 for the
@@ -77,7 +77,7 @@ void launch_upload_soa(const float* aos_dev, unsigned int n, float4* rot, float4
 // bound to be trusted are kept. Results never depend on it; it exists so that the exact path runs on
 // warps full of survivors instead of on every warp that holds one (splat order is unrelated to screen
 // position: at 1M/1080p 46% of the splats are culled, with tile-row bands up to 97%).
-__device__ __forceinline__ bool may_be_visible(const float4 p, const float4 t, const FrameUniforms& U) {
+__device__ __forceinline__ bool may_be_visible(const float4 p, const FrameUniforms& U) {      // p = x y z max(scale)
     const float vx = fmaf(U.V[0], p.x, fmaf(U.V[4], p.y, fmaf(U.V[8], p.z, U.V[12])));
     const float vy = fmaf(U.V[1], p.x, fmaf(U.V[5], p.y, fmaf(U.V[9], p.z, U.V[13])));
     const float zf = -fmaf(U.V[2], p.x, fmaf(U.V[6], p.y, fmaf(U.V[10], p.z, U.V[14])));
@@ -90,7 +90,7 @@ __device__ __forceinline__ bool may_be_visible(const float4 p, const float4 t, c
     const float cy = fmaf(fmaf(U.VP[1], p.x, fmaf(U.VP[5], p.y, fmaf(U.VP[9], p.z, U.VP[13]))) * rw, -0.5f, 0.5f) * U.H;
     const float iz = __fdividef(1.0f, zf), fx = U.P[0] * (U.W * 0.5f) * iz, fy = U.P[5] * (U.H * 0.5f) * iz;
     const float jx = fx * vx * iz, jy = fy * vy * iz;
-    const float smax = fmaxf(p.w, fmaxf(t.x, t.y));
+    const float smax = p.w;
     const float tr = fmaf(fmaf(fx, fx, fmaf(fy, fy, fmaf(jx, jx, jy * jy))) * U.band_bound, smax * smax, 2e-4f);
     float root;
     asm("sqrt.approx.f32 %0, %1;" : "=f"(root) : "f"(tr));
@@ -99,28 +99,50 @@ __device__ __forceinline__ bool may_be_visible(const float4 p, const float4 t, c
            cy - hb <= fminf((float)(U.row_end * 16), U.H);
 }
 
+// K1 = preprocess_kernel + tile_scan_kernel.
+// preprocess_kernel: a CTA owns 2048 splats. (1) Screening from the 16-byte screening plane, 8 splats per
+// thread with all loads issued first; culled splats get tiles_touched = 0. (2) The survivors' local indices
+// are compacted in shared memory. (3) The exactly rounded ~600-instruction pipeline runs on dense warps of
+// survivors, gathering their other planes. With 512-splat CTAs a tile-row band left ~37 survivors per CTA:
+// two warps worked while six waited at the barrier (ncu: 9.7 barrier-stalled warps per issue); a split into
+// separate screening / exact kernels was tried and lost more to the extra launch and the list round trip
+// than it won. The CTA also leaves the pair count of each of its four 512-splat cells for tile_scan_kernel,
+// so K2 needs neither tickets nor a lookback chain.
+// Two shapes. Tile-row bands (few survivors): K1_ITEMS = 8 (2048 splats per CTA), screening reads only the
+// 16-byte screening plane and the survivors gather their other planes (6M-splat band: 115 -> 85 us). Whole
+// frames (a CTA is half full of survivors): K1_ITEMS = 2, the position / scale planes are read coalesced in
+// phase 1 and staged through shared memory for phase 2 (the gather shape costs 45 instead of 35 us at 1M).
+template <int K1_ITEMS, bool GATHER>
 __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const __grid_constant__ FrameUniforms U,
-                                                         splat_record* __restrict__ rec,
-                                                         unsigned int* __restrict__ touched)
+                                                         splat_record* __restrict__ rec, unsigned int* __restrict__ touched,
+                                                         unsigned int* __restrict__ tile_sums)
 {
-    __shared__ float4 s_p[K1_TILE], s_t[K1_TILE];
-    __shared__ unsigned short s_list[K1_TILE];
-    __shared__ unsigned int s_count;
+    constexpr int K1_CTA_SPLATS = 256 * K1_ITEMS;
+    static_assert(K1_CTA_SPLATS % K1_TILE == 0, "a CTA covers whole pair-count cells");
+    __shared__ unsigned short s_list[K1_CTA_SPLATS];
+    __shared__ unsigned int s_count, s_sum[K1_CTA_SPLATS / K1_TILE];
+    __shared__ float4 s_p[GATHER ? 1 : K1_CTA_SPLATS], s_t[GATHER ? 1 : K1_CTA_SPLATS];
     const unsigned int tid = threadIdx.x, lane = tid & 31;
-    const unsigned int base = blockIdx.x * (unsigned int)K1_TILE;
+    const unsigned int base = blockIdx.x * (unsigned int)K1_CTA_SPLATS;
     if (tid == 0) s_count = 0;
-    float4 p[K1_ITEMS], t[K1_ITEMS];
+    if (tid < K1_CTA_SPLATS / K1_TILE) s_sum[tid] = 0;
+    float4 p[K1_ITEMS], t[GATHER ? 1 : K1_ITEMS];
 #pragma unroll
     for (int k = 0; k < K1_ITEMS; ++k) {
         const unsigned int i = base + k * 256u + tid;
-        if (i < U.n) { p[k] = __ldg(sp.pos_sx + i); t[k] = __ldg(sp.syz_op_rg + i); }
+        if (i < U.n) {
+            if (GATHER) p[k] = __ldg(sp.scr + i);
+            else { p[k] = __ldg(sp.pos_sx + i); t[k] = __ldg(sp.syz_op_rg + i); }
+        }
     }
     __syncthreads();
     // ---- phase 1: screen, compact the survivors' local indices
 #pragma unroll
     for (int k = 0; k < K1_ITEMS; ++k) {
         const unsigned int li = k * 256u + tid, i = base + li;
-        const bool keep = i < U.n && may_be_visible(p[k], t[k], U);
+        float4 ps = p[k];
+        if (!GATHER) ps.w = fmaxf(p[k].w, fmaxf(t[k].x, t[k].y));      // x y z max(scale), what the screening plane holds
+        const bool keep = i < U.n && may_be_visible(ps, U);
         if (i < U.n && !keep) touched[i] = 0;
         const unsigned int m = __ballot_sync(0xFFFFFFFFu, keep);
         unsigned int wbase = 0;
@@ -128,7 +150,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
         wbase = __shfl_sync(0xFFFFFFFFu, wbase, 0);
         if (keep) {
             s_list[wbase + __popc(m & ((1u << lane) - 1u))] = (unsigned short)li;
-            s_p[li] = p[k]; s_t[li] = t[k];
+            if (!GATHER) { s_p[li] = p[k]; s_t[li] = t[k]; }
         }
     }
     __syncthreads();
@@ -136,14 +158,16 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
     const unsigned int n_keep = s_count;
     for (unsigned int j = tid; j < n_keep; j += 256u) {
         const unsigned int li = s_list[j], i = base + li;
-        const float4 pp = s_p[li], tt = s_t[li];
+        const float4 pp = GATHER ? __ldg(sp.pos_sx + i) : s_p[li], tt = GATHER ? __ldg(sp.syz_op_rg + i) : s_t[li];
         const float4 q = __ldg(sp.rot + i);
         const unsigned int bh = __ldg(sp.b + i);
         splat_record r;
         const unsigned int cnt = preprocess_one(q.x, q.y, q.z, q.w, pp.w, tt.x, tt.y, pp.x, pp.y, pp.z,
                                                 __float_as_uint(tt.w), bh, tt.z, U, r);
         touched[i] = cnt;
-        if (cnt && U.sh_degree > 0) {
+        if (cnt == 0) continue;
+        atomicAdd(&s_sum[li / K1_TILE], cnt);       // fits: 512 splats x at most 65536 tiles each < 2^32
+        if (U.sh_degree > 0) {
             // D11: colour = max(0, loader colour + sum_{k>=1} basis_k(dir) * f_rest[k][channel]), then half
             const float dx = pp.x - U.cam[0], dy = pp.y - U.cam[1], dz = pp.z - U.cam[2];
             const float dl = sqrtf((dx * dx + dy * dy) + dz * dz);
@@ -166,18 +190,55 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
                    ((unsigned int)__half_as_ushort(__float2half_rn(fmaxf(col[1], 0.0f))) << 16);
             r.bd = (r.bd & 0xFFFF0000u) | (unsigned int)__half_as_ushort(__float2half_rn(fmaxf(col[2], 0.0f)));
         }
-        if (cnt) {
-            float4* dst = reinterpret_cast<float4*>(rec + i);
-            dst[0] = make_float4(r.cx, r.cy, r.ux, r.uy);
-            dst[1] = make_float4(r.vx, r.vy, r.opacity, __uint_as_float(r.rg));
-            dst[2] = make_float4(__uint_as_float(r.bd), r.z_front, __uint_as_float(r.rect_lo), __uint_as_float(r.rect_hi));
-        }
+        float4* dst = reinterpret_cast<float4*>(rec + i);
+        dst[0] = make_float4(r.cx, r.cy, r.ux, r.uy);
+        dst[1] = make_float4(r.vx, r.vy, r.opacity, __uint_as_float(r.rg));
+        dst[2] = make_float4(__uint_as_float(r.bd), r.z_front, __uint_as_float(r.rect_lo), __uint_as_float(r.rect_hi));
+    }
+    __syncthreads();
+    if (tid < K1_CTA_SPLATS / K1_TILE && base + tid * K1_TILE < U.n) tile_sums[blockIdx.x * (K1_CTA_SPLATS / K1_TILE) + tid] = s_sum[tid];
+}
+
+__global__ void __launch_bounds__(1024) tile_scan_kernel(const unsigned int* __restrict__ tile_sums, unsigned int* __restrict__ scan_prefix,
+                                                         unsigned int n, unsigned long long capacity, FrameCtl* ctl)
+{
+    __shared__ unsigned long long s_wsum[32];
+    const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned int n_cells = (n + K1_TILE - 1) / K1_TILE;
+    const unsigned int n_scan = (n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS;
+    const unsigned int per = (n_scan + 1023u) / 1024u;          // contiguous chunk per thread: all its loads in flight at once
+    const unsigned int j0 = min(tid * per, n_scan), j1 = min(j0 + per, n_scan);
+    unsigned long long part = 0;
+    for (unsigned int j = j0; j < j1; ++j) {
+        part += tile_sums[2 * j];
+        if (2 * j + 1 < n_cells) part += tile_sums[2 * j + 1];
+    }
+    unsigned long long incl = part;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const unsigned long long x = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= (unsigned)d) incl += x; }
+    if (lane == 31) s_wsum[warp] = incl;
+    __syncthreads();
+    unsigned long long run = incl - part, total = 0;
+    for (int k = 0; k < 32; ++k) { const unsigned long long x = s_wsum[k]; if (k < (int)warp) run += x; total += x; }
+    for (unsigned int j = j0; j < j1; ++j) {
+        scan_prefix[j] = run > 0xFFFFFFFFull ? 0xFFFFFFFFu : (unsigned int)run;     // saturating, as the offsets are
+        run += tile_sums[2 * j];
+        if (2 * j + 1 < n_cells) run += tile_sums[2 * j + 1];
+    }
+    if (tid == 0) {
+        const bool over = total > capacity;
+        ctl->total_pairs = total;
+        ctl->n_sort = over ? (unsigned int)capacity : (unsigned int)total;
+        ctl->overflow = over ? 1u : 0u;
     }
 }
 
 void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record* rec, unsigned int* touched,
+                       unsigned int* tile_sums, unsigned int* scan_prefix, unsigned long long capacity, FrameCtl* ctl,
                        cudaStream_t s)
 {
     if (U.n == 0) return;
-    preprocess_kernel<<<(U.n + K1_TILE - 1) / K1_TILE, 256, 0, s>>>(sp, U, rec, touched);
+    if ((U.row_end - U.row_begin) * 2 <= U.tiles_y) preprocess_kernel<8, true><<<(U.n + 2047u) / 2048u, 256, 0, s>>>(sp, U, rec, touched, tile_sums);
+    else preprocess_kernel<2, false><<<(U.n + 511u) / 512u, 256, 0, s>>>(sp, U, rec, touched, tile_sums);
+    tile_scan_kernel<<<1, 1024, 0, s>>>(tile_sums, scan_prefix, U.n, capacity, ctl);
 }

@@ -33,7 +33,8 @@ struct FrameSet {
     // LAYER50 only: the same pairs in tile | depth order (allocated on the first LAYER50 frame)
     unsigned long long* keys_d[2] = {nullptr, nullptr}; uint32_t* vals_d[2] = {nullptr, nullptr}; unsigned long long capacity_d = 0;
     FrameCtl* ctl = nullptr;
-    unsigned long long *scan_status = nullptr, *sort_status = nullptr; size_t sort_status_tiles = 0;
+    unsigned int* tile_sums = nullptr;      // K1 pair counts per 512 splats, then K2's tile prefixes
+    unsigned long long* sort_status = nullptr; size_t sort_status_tiles = 0;
     uint32_t* bounds = nullptr; uint32_t ranges_cap = 0;   // [T+1] first sorted pair of every tile
     cudaStream_t own_stream = nullptr;
 };
@@ -42,7 +43,7 @@ struct splat_ctx : FrameSet {
     FrameSet alt; bool alt_ready = false; int cur_set = 0;
     int device = 0, sm_count = 148;
     uint32_t n = 0; size_t n_pad = 0;
-    float4 *rot = nullptr, *pos_sx = nullptr, *syz = nullptr, *base_rgb = nullptr, *sh = nullptr; uint16_t* bq = nullptr;
+    float4 *rot = nullptr, *pos_sx = nullptr, *syz = nullptr, *base_rgb = nullptr, *sh = nullptr, *scr = nullptr; uint16_t* bq = nullptr;
     int sh_degree = 0;
     unsigned long long* dbg_keys = nullptr; uint32_t* dbg_vals = nullptr; unsigned long long dbg_cap = 0;
     FrameCtl* ctl_host = nullptr;
@@ -147,17 +148,17 @@ int splat_create(int device, splat_ctx** out) {
 
 // Per-splat scratch of the CURRENT frame set (records, counts, offsets, scan lookback words).
 static void free_scene_scratch(splat_ctx* c) {
-    cudaFree(c->rec); cudaFree(c->touched); cudaFree(c->offsets); cudaFree(c->scan_status);
-    c->rec = nullptr; c->touched = c->offsets = nullptr; c->scan_status = nullptr;
+    cudaFree(c->rec); cudaFree(c->touched); cudaFree(c->offsets); cudaFree(c->tile_sums);
+    c->rec = nullptr; c->touched = c->offsets = nullptr; c->tile_sums = nullptr;
 }
 static int alloc_scene_scratch(splat_ctx* c, size_t n_pad) {
     CK(cudaMalloc(&c->rec, n_pad * sizeof(splat_record)));
     CK(cudaMalloc(&c->touched, n_pad * 4)); CK(cudaMalloc(&c->offsets, n_pad * 4));
     CK(cudaMemset(c->touched, 0, n_pad * 4));
     CK(cudaMemset(c->rec, 0, n_pad * sizeof(splat_record)));
-    const size_t scan_tiles = n_pad / SCAN_TILE_ITEMS + 1;
-    CK(cudaMalloc(&c->scan_status, scan_tiles * 8));
-    CK(cudaMemset(c->scan_status, 0, scan_tiles * 8));
+    const size_t sums = n_pad / (SCAN_TILE_ITEMS / 2) + n_pad / SCAN_TILE_ITEMS + 2;   // [n/512] sums, then [n/1024] prefixes
+    CK(cudaMalloc(&c->tile_sums, sums * 4));
+    CK(cudaMemset(c->tile_sums, 0, sums * 4));
     return SPLAT_OK;
 }
 // Releases the second frame set completely (it is rebuilt by the next camera-batch call).
@@ -198,9 +199,9 @@ static int ensure_pairs_all(splat_ctx* c, unsigned long long cap) {
 
 static void free_scene(splat_ctx* c) {
     drop_alt(c);
-    cudaFree(c->rot); cudaFree(c->pos_sx); cudaFree(c->syz); cudaFree(c->bq); cudaFree(c->sh); cudaFree(c->base_rgb);
+    cudaFree(c->rot); cudaFree(c->pos_sx); cudaFree(c->syz); cudaFree(c->bq); cudaFree(c->sh); cudaFree(c->base_rgb); cudaFree(c->scr);
     free_scene_scratch(c);
-    c->rot = c->pos_sx = c->syz = c->base_rgb = c->sh = nullptr; c->bq = nullptr;
+    c->rot = c->pos_sx = c->syz = c->base_rgb = c->sh = c->scr = nullptr; c->bq = nullptr;
     c->n = 0; c->n_pad = 0; c->sh_degree = 0;
 }
 
@@ -225,9 +226,9 @@ int splat_destroy(splat_ctx* c) {
 static int install_scene(splat_ctx* c, const float* aos_dev, uint32_t n) {
     const size_t n_pad = ((size_t)n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS * SCAN_TILE_ITEMS;
     CK(cudaMalloc(&c->rot, n_pad * 16)); CK(cudaMalloc(&c->pos_sx, n_pad * 16)); CK(cudaMalloc(&c->syz, n_pad * 16));
-    CK(cudaMalloc(&c->bq, n_pad * 2)); CK(cudaMalloc(&c->base_rgb, n_pad * 16));
+    CK(cudaMalloc(&c->bq, n_pad * 2)); CK(cudaMalloc(&c->base_rgb, n_pad * 16)); CK(cudaMalloc(&c->scr, n_pad * 16));
     { const int rc = alloc_scene_scratch(c, n_pad); if (rc) return rc; }
-    launch_upload_soa(aos_dev, n, c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, 0);
+    launch_upload_soa(aos_dev, n, c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->scr, 0);
     CK(cudaGetLastError());
     CK(cudaDeviceSynchronize());
     c->n = n; c->n_pad = n_pad;
@@ -440,11 +441,12 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
     if (timed) CK(cudaEventRecord(c->ev[0], s));
     CK(cudaMemsetAsync(c->ctl, 0, sizeof(FrameCtl), s));
     if (c->n) {
-        ScenePlanes sp{c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->sh, c->n_pad};
-        launch_preprocess(sp, U, c->rec, c->touched, s);
+        ScenePlanes sp{c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->scr, c->sh, c->n_pad};
+        unsigned int* scan_prefix = c->tile_sums + c->n_pad / (SCAN_TILE_ITEMS / 2);
+        launch_preprocess(sp, U, c->rec, c->touched, c->tile_sums, scan_prefix, c->capacity, c->ctl, s);
         if (timed) CK(cudaEventRecord(c->ev[1], s));
         launch_scan_duplicate(U, c->rec, c->touched, c->offsets, c->keys[0], c->vals[0], layer ? c->keys_d[0] : nullptr,
-                              layer ? c->vals_d[0] : nullptr, c->capacity, c->ctl, c->scan_status, epoch, plan, s);
+                              layer ? c->vals_d[0] : nullptr, c->capacity, c->ctl, c->tile_sums, scan_prefix, plan, c->sm_count, s);
         if (keep) {
             CK(cudaMemcpyAsync(c->dbg_keys, c->keys[0], c->capacity * 8, cudaMemcpyDeviceToDevice, s));
             CK(cudaMemcpyAsync(c->dbg_vals, c->vals[0], c->capacity * 4, cudaMemcpyDeviceToDevice, s));

@@ -33,9 +33,9 @@ struct FrameUniforms {
 struct FrameCtl {
     unsigned long long total_pairs;   // D (exact even when it exceeds capacity)
     unsigned int overflow;
-    unsigned int scan_ticket;
+    unsigned int reserved0;
     unsigned int sort_ticket[SPLAT_MAX_SORT_PASSES];
-    unsigned int n_sort;              // min(D, capacity), written by the scan kernel's last tile
+    unsigned int n_sort;              // min(D, capacity), written by the tile-sum scan
     unsigned int pad[5];
     unsigned int hist[SPLAT_MAX_SORT_PASSES][256];
 };
@@ -47,6 +47,7 @@ struct ScenePlanes {
     const float4* syz_op_rg;  // scale.y, scale.z, opacity, bits(half r | half g << 16)
     const uint16_t* b;        // half(b)
     const float4* base_rgb;   // fp32 r g b (loader colour) for the SH extension; .w unused
+    const float4* scr;        // position.xyz, max(scale): the 16 bytes the screening kernel reads
     const float4* sh;         // SH planes [12][n_pad]: float4 j of splat i holds coefficients f' = 4j..4j+3,
                               // f' = 3*k + channel (coefficient-major, so degree L reads planes 0 .. 3*((L+1)^2-1)/4)
     size_t n_pad;
@@ -79,16 +80,17 @@ __device__ __forceinline__ void lb_store(unsigned long long* p, unsigned long lo
 
 // Launchers (each enqueues on `s` and returns).
 void launch_upload_soa(const float* aos_dev, unsigned int n, float4* rot, float4* pos_sx, float4* syz_op_rg,
-                       uint16_t* b, float4* base_rgb, cudaStream_t s);
+                       uint16_t* b, float4* base_rgb, float4* scr, cudaStream_t s);
 // sh_rest45_dev: [n][45] as the loader stores it (channel-major: f = channel*15 + k) -> coefficient-major planes
 void launch_upload_sh(const float* sh_rest45_dev, unsigned int n, size_t n_pad, float4* planes, cudaStream_t s);
 void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record* rec, unsigned int* touched,
+                       unsigned int* tile_sums, unsigned int* scan_prefix, unsigned long long capacity, FrameCtl* ctl,
                        cudaStream_t s);
 void launch_scan_duplicate(const FrameUniforms& U, const splat_record* rec, const unsigned int* touched,
                            unsigned int* offsets, unsigned long long* keys, unsigned int* vals,
                            unsigned long long* keys_depth, unsigned int* vals_depth,
-                           unsigned long long capacity, FrameCtl* ctl, unsigned long long* scan_status,
-                           unsigned int epoch, SortPlan plan, cudaStream_t s);
+                           unsigned long long capacity, FrameCtl* ctl, const unsigned int* tile_sums,
+                           const unsigned int* scan_prefix, SortPlan plan, int sm_count, cudaStream_t s);
 // LAYER50 keeps two orders of the same pairs: (keys, vals) = tile | instance index (arrival order, D3) and
 // (keys_depth, vals_depth) = tile | half-depth field (composite order). keys_depth may be NULL (TILE mode).
 // Per-pass digit histograms of keys[0..n) into ctl->hist (stand-alone sort only; frames get
