@@ -303,6 +303,28 @@ def main():
         r = ctx.fetch(capi.FETCH_TILE_RANGES).astype(np.int64)
         row_pairs = (r[:, 1] - r[:, 0]).reshape(tiles_y, tiles_x).sum(axis=1)
         band_list = multigpu.band_rows(tiles_y, world, None if args.even_bands else row_pairs)
+        if not args.even_bands:
+            # Measured-time balancing (untimed set-up, like the pair count above): pairs per row are not the cost
+            # (rows of large near splats blend slower per pair), so three rounds of "render the band, exchange
+            # the band-proportional stage times, move the boundaries" follow.
+            wts = row_pairs.astype(np.float64)
+            for _ in range(3):
+                a, b = band_list[rank]
+                o = capi.make_opts(mode=mode, sh_degree=args.sh_degree, tile_row_begin=a, tile_row_end=b, flags=capi.FLAG_TIMING)
+                acc = []
+                for it in range(6):
+                    var = 0.0
+                    if b > a:
+                        ctx.render(stream, fb.data_ptr(), *cam(0), w, h, o); torch.cuda.synchronize()
+                        st_ = ctx.stage_times()
+                        var = st_["sort"] + st_["ranges"] + st_["blend"] + 0.5 * st_["scan_duplicate"]
+                    if it >= 2:
+                        acc.append(var)
+                tt = torch.tensor([float(np.median(acc))], dtype=torch.float64, device=dev)
+                allt = [torch.zeros_like(tt) for _ in range(world)]
+                dist.all_gather(allt, tt)
+                wts = multigpu.reweight_rows(wts, band_list, [float(x.item()) for x in allt])
+                band_list = multigpu.band_rows(tiles_y, world, wts)
         row0, row1 = band_list[rank]
     rows_px = multigpu.bands_to_pixel_rows(band_list, h) if bands else [(0, h)]
     have_rows = row1 > row0

@@ -92,7 +92,7 @@ struct KBuffer {
 
 struct PixelState {
     __half2 accRG, accBA;     // (aR, aG) and (aB, accumAlpha | accumVis): every op an _rn intrinsic (D7)
-    int cnt;                  // kept fragments; cnt >= K doubles as "this pixel is finished"
+    int rem;                  // fragments the pixel can still take; <= 0 doubles as "this pixel is finished"
     unsigned int cutoff;      // LAYER50: instance index of the K-th arrival (fragments after it were dropped)
 };
 
@@ -110,7 +110,7 @@ __device__ __forceinline__ void walk_list(const splat_record* __restrict__ rec, 
     const unsigned int a_ab = smem_addr(s_ab), a_cm = smem_addr(s_cm);
     const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const __half h_one = __ushort_as_half(0x3C00);
-#define done (px.cnt >= K)
+#define done (px.rem <= 0)
     for (unsigned int b0 = range.x; b0 < range.y; b0 += BLEND_BATCH) {
         const unsigned int nb = min((unsigned int)BLEND_BATCH, range.y - b0);
         unsigned int wmask = 0;
@@ -120,7 +120,11 @@ __device__ __forceinline__ void walk_list(const splat_record* __restrict__ rec, 
             const float4 A = __ldg(r), B = __ldg(r + 1);
             s_a[tid] = A;
             s_b[tid] = B;
-            if (WALK != WALK_COUNT) s_c[tid] = __float_as_uint(__ldg(reinterpret_cast<const float*>(r + 2)));
+            if (WALK != WALK_COUNT) {
+                // TILE: (b, 1.0h) so that one half2 multiply gives (b * src, src); UNDER: (b, 0); MLAB: (b, depth) as stored
+                const unsigned int bd = __float_as_uint(__ldg(reinterpret_cast<const float*>(r + 2)));
+                s_c[tid] = WALK == WALK_TILE ? ((bd & 0xFFFFu) | 0x3C000000u) : WALK == WALK_UNDER ? (bd & 0xFFFFu) : bd;
+            }
             const bool too_near = WALK == WALK_MLAB && __ldg(reinterpret_cast<const float*>(r + 2) + 1) < 0.001f;   // gaussian_splat.metal:209
             if (WALK != WALK_TILE) s_i[tid] = si;
             // Conservative pixel AABB of {q <= 9.2103404}: d = Winv (u,v), Winv = [vy -uy; -vx ux] / det.
@@ -148,12 +152,17 @@ __device__ __forceinline__ void walk_list(const splat_record* __restrict__ rec, 
         __syncthreads();
         if (!__all_sync(0xFFFFFFFFu, done)) {
             for (unsigned int c0 = 0; c0 < nb; c0 += 32) {
-                unsigned int bits = __ballot_sync(0xFFFFFFFFu, (s_m[c0 + lane] >> warp) & 1u);
+                // candidates of this warp; lane j looks at entry c0 + 31 - j, so the FIRST entry is the HIGHEST
+                // set bit: one bfind per step instead of the brev + bfind of a find-first-set
+                unsigned int bits = __ballot_sync(0xFFFFFFFFu, (s_m[c0 + 31u - lane] >> warp) & 1u);
+                const unsigned int a_top = a_ab + (c0 + 31u) * 16u, c_top = a_cm + (c0 + 31u) * 4u;
                 while (bits) {
-                    const unsigned int e = c0 + __ffs(bits) - 1;
-                    bits &= bits - 1;
-                    const float4 A = lds128<0>(a_ab + e * 16u);
-                    const float4 B = lds128<BLEND_BATCH * 16>(a_ab + e * 16u);
+                    unsigned int j;
+                    asm("bfind.u32 %0, %1;" : "=r"(j) : "r"(bits));
+                    bits ^= 1u << j;
+                    const unsigned int a_e = a_top - j * 16u, c_e = c_top - j * 4u;
+                    const float4 A = lds128<0>(a_e);
+                    const float4 B = lds128<BLEND_BATCH * 16>(a_e);
                     const float dx = pxc - A.x, dy = pyc - A.y;
                     const float u = fmaf(dx, A.z, dy * A.w);
                     const float v = fmaf(dx, B.x, dy * B.y);
@@ -161,12 +170,12 @@ __device__ __forceinline__ void walk_list(const splat_record* __restrict__ rec, 
                     if (done || !(q <= 9.2103404f) || !(fabsf(u) <= 3.0f) || !(fabsf(v) <= 3.0f)) continue;
                     if (WALK == WALK_COUNT) {
                         // arrival number cnt+1; the K-th closes the pixel's list
-                        if (++px.cnt >= K) px.cutoff = lds32<2 * BLEND_BATCH * 4>(a_cm + e * 4u);
+                        if (--px.rem <= 0) px.cutoff = lds32<2 * BLEND_BATCH * 4>(c_e);
                         continue;
                     }
-                    if (WALK == WALK_UNDER && lds32<2 * BLEND_BATCH * 4>(a_cm + e * 4u) > px.cutoff) continue;   // arrived after the cap
+                    if (WALK == WALK_UNDER && lds32<2 * BLEND_BATCH * 4>(c_e) > px.cutoff) continue;   // arrived after the cap
                     const float alpha = exp_neg_half(q) * B.z;
-                    const unsigned int rg = __float_as_uint(B.w), bd = lds32<0>(a_cm + e * 4u);
+                    const unsigned int rg = __float_as_uint(B.w), bd = lds32<0>(c_e);
                     if (WALK == WALK_MLAB) {
                         // newLayer = half4(half3(color) * half(alpha), 1h - half(alpha)); newDepth = half(depth)
                         const __half ah = __float2half_rn(alpha);
@@ -195,21 +204,21 @@ __device__ __forceinline__ void walk_list(const splat_record* __restrict__ rec, 
                         const __half ah = __float2half_rn(alpha);
                         const __half src = __hmul_rn(ah, __hsub_rn(h_one, __high2half(px.accBA)));
                         const __half2 src2 = __half2half2(src);
-                        const unsigned int b1 = (bd & 0xFFFFu) | 0x3C000000u;      // (b, 1.0h): 1.0h * src == src
+                        const unsigned int b1 = bd;                                // staged as (b, 1.0h): 1.0h * src == src
                         px.accRG = __hadd2_rn(px.accRG, __hmul2_rn(*reinterpret_cast<const __half2*>(&rg), src2));
                         px.accBA = __hadd2_rn(px.accBA, __hmul2_rn(*reinterpret_cast<const __half2*>(&b1), src2));
-                        px.cnt = __hge(__high2half(px.accBA), __ushort_as_half(0x3BEC)) ? K : px.cnt + 1;
+                        px.rem = __hge(__high2half(px.accBA), __ushort_as_half(0x3BEC)) ? 0 : px.rem - 1;
                     } else {
                         // accumColor += color * accumVis; accumVis *= visibility; stop below 0.01h.
                         // visibility = half(1 - alpha), float subtract then round (50layer.metal:174).
                         const __half vis = __high2half(px.accBA);
                         const __half2 vis2 = __half2half2(vis);
-                        const unsigned int b0h = bd & 0xFFFFu;                    // (b, 0): the alpha lane is replaced below
+                        const unsigned int b0h = bd;                              // staged as (b, 0): the alpha lane is replaced below
                         px.accRG = __hadd2_rn(px.accRG, __hmul2_rn(*reinterpret_cast<const __half2*>(&rg), vis2));
                         const __half2 bsum = __hadd2_rn(px.accBA, __hmul2_rn(*reinterpret_cast<const __half2*>(&b0h), vis2));
                         const __half nvis = __hmul_rn(vis, __float2half_rn(1.0f - alpha));
                         px.accBA = __halves2half2(__low2half(bsum), nvis);
-                        if (__hlt(nvis, __ushort_as_half(0x211F))) px.cnt = K;
+                        if (__hlt(nvis, __ushort_as_half(0x211F))) px.rem = 0;
                     }
                 }
                 if (__all_sync(0xFFFFFFFFu, done)) break;
@@ -245,14 +254,14 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
     px.cutoff = 0xFFFFFFFFu;
     if (MODE == SPLAT_MODE_TILE) {
         px.accBA = px.accRG;
-        px.cnt = inside ? 0 : K;
+        px.rem = inside ? K : 0;
         walk_list<WALK_TILE>(rec, vals, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
     } else if (MODE == SPLAT_MODE_MLAB) {
         const __half h0 = __ushort_as_half(0), h1 = __ushort_as_half(0x3C00);
 #pragma unroll
         for (int k = 0; k < 6; ++k) { kb.rg[k] = __halves2half2(h0, h0); kb.ba[k] = __halves2half2(h0, h1); kb.d[k] = k == 3 ? h1 : h0; }
         px.accBA = px.accRG;
-        px.cnt = inside ? 0 : K;                       // K = INT_MAX: a pixel never closes
+        px.rem = inside ? K : 0;                       // K = INT_MAX: a pixel never closes
         walk_list<WALK_MLAB>(rec, vals, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
         // resolve_main: composite the six layers front to back
         __half2 crg = __halves2half2(h0, h0); __half cb = h0, at = h1;
@@ -270,12 +279,12 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
         // composite the kept arrivals front to back with the shader's early exit. The per-pixel lists of
         // the reference (504 B/pixel in device memory) are never materialised.
         if (range.y - range.x > (unsigned int)K) {
-            px.cnt = inside ? 0 : K;
+            px.rem = inside ? K : 0;
             walk_list<WALK_COUNT>(rec, vals, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
             __syncthreads();
         }
         px.accBA = __halves2half2(__ushort_as_half(0), __ushort_as_half(0x3C00));   // accumVis = 1
-        px.cnt = inside ? 0 : K;
+        px.rem = inside ? K : 0;
         walk_list<WALK_UNDER>(rec, vals_depth, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
     }
     if (!inside) return;

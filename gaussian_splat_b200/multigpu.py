@@ -57,6 +57,27 @@ def band_rows(tiles_y: int, world: int, weights: Sequence[float] | None = None) 
     return sorted(bands)
 
 
+def reweight_rows(weights: Sequence[float], bands: Sequence[Tuple[int, int]], band_times: Sequence[float],
+                  damping: float = 0.7) -> np.ndarray:
+    """One step of measured-time balancing: rows keep their relative weights inside a band, and each band's
+    rows are rescaled so the band's weight moves towards the time that band actually took (the part of the
+    frame that scales with the band: sort, ranges, blend). Pairs per row are a good first guess but not the
+    cost: rows of large, near splats blend slower per pair. Feed the result to band_rows() again."""
+    wt = np.asarray(weights, np.float64).copy()
+    t = np.asarray(band_times, np.float64)
+    if len(bands) != t.shape[0] or np.any(t < 0):
+        raise ValueError("one non-negative time per band")
+    total_w, total_t = wt.sum(), t.sum()
+    if total_w <= 0 or total_t <= 0:
+        return wt
+    for (b, e), tb in zip(bands, t):
+        wb = wt[b:e].sum()
+        if e > b and wb > 0:
+            target = tb / total_t * total_w                       # the band's share of the frame, in weight units
+            wt[b:e] *= (1.0 - damping) + damping * target / wb
+    return wt
+
+
 def bands_to_pixel_rows(bands: Sequence[Tuple[int, int]], height: int, tile: int = 16) -> List[Tuple[int, int]]:
     return [(min(b * tile, height), min(e * tile, height)) for b, e in bands]
 

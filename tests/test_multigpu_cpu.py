@@ -78,3 +78,26 @@ def test_weighted_bands_compose_to_full_frame(small_scene):
         Fb = O.Frame(small_scene, V, P, w, h, tile_row_begin=b, tile_row_end=e)
         Fb.blend(fb=fb); total += Fb.D
     assert np.array_equal(fb, full) and total == F.D
+
+
+def test_measured_time_rebalancing_converges():
+    """reweight_rows + band_rows on a synthetic cost model (cost per row != pairs per row): the heaviest band
+    approaches the ideal share within a few iterations and never gets worse than the pair-balanced start."""
+    from gaussian_splat_b200 import multigpu
+    rng = np.random.default_rng(3)
+    rows, world = 135, 8
+    pairs = rng.uniform(0.5, 1.5, rows) * np.linspace(0.6, 1.4, rows)
+    true_cost = pairs * np.linspace(1.6, 0.7, rows)              # upper rows cost more per pair
+    w = pairs.copy()
+    bands = multigpu.band_rows(rows, world, w)
+    worst0 = max(true_cost[b:e].sum() for b, e in bands)
+    worst = worst0
+    for _ in range(5):
+        times = [true_cost[b:e].sum() for b, e in bands]
+        w = multigpu.reweight_rows(w, bands, times)
+        bands = multigpu.band_rows(rows, world, w)
+        assert bands[0][0] == 0 and bands[-1][1] == rows and all(bands[k][1] == bands[k + 1][0] for k in range(world - 1))
+        worst = max(true_cost[b:e].sum() for b, e in bands)
+    ideal = true_cost.sum() / world
+    assert worst <= worst0 + 1e-9
+    assert worst <= 1.08 * ideal, (worst, ideal, worst0)
