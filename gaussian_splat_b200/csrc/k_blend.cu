@@ -14,11 +14,11 @@
 // One warp per boundary, 32 probes per round (5 dependent L2 round trips for D < 32M instead of
 // the 21+ of a scalar binary search; the kernel is pure latency).
 __global__ void __launch_bounds__(256) tile_bounds_kernel(const unsigned long long* __restrict__ keys,
-                                                          const FrameCtl* __restrict__ ctl, unsigned int n_bounds,
-                                                          unsigned int* __restrict__ bounds)
+                                                          const FrameCtl* __restrict__ ctl, unsigned int first,
+                                                          unsigned int n_bounds, unsigned int* __restrict__ bounds)
 {
-    const unsigned int t = blockIdx.x * 8u + (threadIdx.x >> 5), lane = threadIdx.x & 31u;
-    if (t >= n_bounds) return;
+    const unsigned int t = first + blockIdx.x * 8u + (threadIdx.x >> 5), lane = threadIdx.x & 31u;
+    if (t >= first + n_bounds) return;
     const unsigned int n = ctl->overflow ? 0u : ctl->n_sort;
     const unsigned long long x = (unsigned long long)t << 32;
     unsigned int lo = 0, hi = n;
@@ -33,10 +33,12 @@ __global__ void __launch_bounds__(256) tile_bounds_kernel(const unsigned long lo
     if (lane == 0) bounds[t] = lo;
 }
 
-void launch_tile_bounds(const unsigned long long* keys_sorted, const FrameCtl* ctl, unsigned int n_tiles,
-                        unsigned int* bounds, cudaStream_t s)
+// Only tiles [first_tile, first_tile + n_tiles] get a boundary: with a tile-row band that is the band (the blend
+// reads nothing else), which keeps this latency-bound kernel to one wave of CTAs.
+void launch_tile_bounds(const unsigned long long* keys_sorted, const FrameCtl* ctl, unsigned int first_tile,
+                        unsigned int n_tiles, unsigned int* bounds, cudaStream_t s)
 {
-    tile_bounds_kernel<<<(n_tiles + 1 + 7) / 8, 256, 0, s>>>(keys_sorted, ctl, n_tiles + 1, bounds);
+    tile_bounds_kernel<<<(n_tiles + 1 + 7) / 8, 256, 0, s>>>(keys_sorted, ctl, first_tile, n_tiles + 1, bounds);
 }
 
 // ------------------------------------------------------------------ K5
@@ -110,6 +112,8 @@ __device__ __forceinline__ void walk_list(const splat_record* __restrict__ rec, 
     const unsigned int a_ab = smem_addr(s_ab), a_cm = smem_addr(s_cm);
     const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const __half h_one = __ushort_as_half(0x3C00);
+    float exp_c5;
+    asm volatile("mov.f32 %0, 0f3AADDD2A;" : "=f"(exp_c5));      // EXP_NEG_HALF_C5, pinned to a register
 #define done (px.rem <= 0)
     for (unsigned int b0 = range.x; b0 < range.y; b0 += BLEND_BATCH) {
         const unsigned int nb = min((unsigned int)BLEND_BATCH, range.y - b0);
@@ -159,7 +163,11 @@ __device__ __forceinline__ void walk_list(const splat_record* __restrict__ rec, 
                 while (bits) {
                     unsigned int j;
                     asm("bfind.u32 %0, %1;" : "=r"(j) : "r"(bits));
-                    bits ^= 1u << j;
+                    {   // clear the top bit: keep bits [0, j)
+                        unsigned int below;
+                        asm("bmsk.clamp.b32 %0, %1, %2;" : "=r"(below) : "r"(0), "r"(j));
+                        bits &= below;
+                    }
                     const unsigned int a_e = a_top - j * 16u, c_e = c_top - j * 4u;
                     const float4 A = lds128<0>(a_e);
                     const float4 B = lds128<BLEND_BATCH * 16>(a_e);
@@ -174,7 +182,7 @@ __device__ __forceinline__ void walk_list(const splat_record* __restrict__ rec, 
                         continue;
                     }
                     if (WALK == WALK_UNDER && lds32<2 * BLEND_BATCH * 4>(c_e) > px.cutoff) continue;   // arrived after the cap
-                    const float alpha = exp_neg_half(q) * B.z;
+                    const float alpha = exp_neg_half(q, exp_c5) * B.z;
                     const unsigned int rg = __float_as_uint(B.w), bd = lds32<0>(c_e);
                     if (WALK == WALK_MLAB) {
                         // newLayer = half4(half3(color) * half(alpha), 1h - half(alpha)); newDepth = half(depth)

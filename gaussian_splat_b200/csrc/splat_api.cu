@@ -465,7 +465,8 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
     if (timed) CK(cudaEventRecord(c->ev[3], s));
     const int sb = (layer ? layer_plan(plan).n_pass : plan.n_pass) & 1;    // arrival-ordered (LAYER50) or the only (TILE) list
     const int sd = plan.n_pass & 1;
-    launch_tile_bounds(c->keys[sb], c->ctl, T, c->bounds, s);
+    launch_tile_bounds(c->keys[sb], c->ctl, (unsigned int)(U.row_begin * U.tiles_x),
+                       (unsigned int)((U.row_end - U.row_begin) * U.tiles_x), c->bounds, s);
     if (timed) CK(cudaEventRecord(c->ev[4], s));
     launch_blend(U, c->rec, c->vals[sb], layer ? c->vals_d[sd] : nullptr, c->bounds, fb, s);
     if (timed) CK(cudaEventRecord(c->ev[5], s));
@@ -725,8 +726,9 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
         uint32_t* b = new uint32_t[T + 1];
         cudaError_t e = cudaMemcpy(b, c->bounds, (T + 1) * 4, cudaMemcpyDeviceToHost);
         uint32_t* r = (uint32_t*)dst;
+        const size_t t_lo = (size_t)c->lastU.row_begin * c->lastU.tiles_x, t_hi = (size_t)c->lastU.row_end * c->lastU.tiles_x;
         for (size_t t = 0; t < T && e == cudaSuccess; ++t) {
-            const bool any = b[t] < b[t + 1];
+            const bool any = t >= t_lo && t < t_hi && b[t] < b[t + 1];      // only the band's boundaries were computed
             r[2 * t] = any ? b[t] : 0u; r[2 * t + 1] = any ? b[t + 1] : 0u;
         }
         delete[] b;

@@ -103,8 +103,8 @@ void launch_radix_sort(unsigned long long* keys, unsigned int* vals, unsigned lo
                        unsigned int* vals_alt, FrameCtl* ctl, unsigned long long* sort_status,
                        unsigned int epoch_base, SortPlan plan, int sm_count, bool small_tiles, cudaStream_t s);
 // bounds[t] = first sorted pair of tile t (t = 0..n_tiles); tile t owns [bounds[t], bounds[t+1]).
-void launch_tile_bounds(const unsigned long long* keys_sorted, const FrameCtl* ctl, unsigned int n_tiles,
-                        unsigned int* bounds, cudaStream_t s);
+void launch_tile_bounds(const unsigned long long* keys_sorted, const FrameCtl* ctl, unsigned int first_tile,
+                        unsigned int n_tiles, unsigned int* bounds, cudaStream_t s);
 void launch_pack_bgra8(const void* fb_half4, void* bgra8, size_t n_pixels, cudaStream_t s);
 cudaError_t launch_ply_decode_chunk(const float* rows_dev, unsigned int n_rows, unsigned int stride, const int* slot_dst_dev,
                                     int jx, int jy, int jz, float crop, unsigned int* block_counts, unsigned int* running,

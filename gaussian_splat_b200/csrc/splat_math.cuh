@@ -9,12 +9,15 @@
 // exp(-0.5*q), q in [0, ~9.3], as 2^t with t = q * (-0.5*log2 e): magic-add rounding (no cvt
 // instructions), f = t - n exact, degree-5 minimax 2^f in explicit fmaf, exponent added as an
 // integer. 10 instructions; max rel. error 9e-8 + 4e-7 from the rounding of t.
-__device__ __forceinline__ float exp_neg_half(float q) {
+// c5 = the leading coefficient 0.0013264764565974474f (0x3AADDD2A), passed in so that a caller's hot loop can
+// keep it in a register (an FFMA takes one immediate; the compiler otherwise re-materialises it per call).
+#define EXP_NEG_HALF_C5 0.0013264764565974474f
+__device__ __forceinline__ float exp_neg_half(float q, float c5 = EXP_NEG_HALF_C5) {
     const float t = q * -0.72134752044448170368f;
     const float s = t + 12582912.0f;
     const float n = s - 12582912.0f;
     const float f = t - n;
-    float p = 0.0013264764565974474f;
+    float p = c5;
     p = fmaf(p, f, 0.009671512991189957f);
     p = fmaf(p, f, 0.05550733581185341f);
     p = fmaf(p, f, 0.24022242426872253f);
