@@ -16,27 +16,34 @@ __device__ __forceinline__ void warp_hist_inc(unsigned int* hist, unsigned int d
     if ((peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0) atomicAdd(hist + digit, __popc(peers));
 }
 
+// What K2 needs of the sort plan: where the two depth digits (bits 0-7, 8-15 of the depth field; absent in MLAB
+// frames) and the one or two tile digits (bits 32-39, 40-47 of the key) are counted.
+struct DupPlan { int d0, d1, t0, t1; unsigned int tmask0, tmask1; };
+
 // Persistent grid: a CTA walks duplication tiles (1024 splats) with a fixed stride and keeps ONE digit
-// histogram for all of them, flushed once at the end. With one CTA per tile, a 6M-splat band frame issued
-// 5860 x up to 1024 same-address global atomics (a band has 2-3 distinct high tile digits); now at most
-// grid x 1024. Tiles that produced no pair (K1 left their pair count) only write their offsets.
+// histogram for all of them, flushed once at the end (with one CTA per tile, a 6M-splat band frame issued
+// 5860 x up to 1024 same-address global atomics). Tiles that produced no pair only write their offsets.
+// Per tile: one block scan gives every splat its first pair slot AND the visible splats their rank, so the
+// visible ones are compacted into shared memory (first slot, rect, depth field, index). The expansion then
+// works warp by warp on 32 consecutive pair slots: one binary search for the owner of the first slot, and
+// because every visible splat owns at least one slot the other 31 owners lie within the next 32 compact
+// entries - each lane finds its own with five shuffles instead of a ten-step search in shared memory.
 __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
     const __grid_constant__ FrameUniforms U, const splat_record* __restrict__ rec,
     const unsigned int* __restrict__ touched, unsigned int* __restrict__ offsets,
     unsigned long long* __restrict__ keys, unsigned int* __restrict__ vals,
     unsigned long long* __restrict__ keys_depth, unsigned int* __restrict__ vals_depth, unsigned long long capacity,
     FrameCtl* ctl, const unsigned int* __restrict__ tile_sums, const unsigned int* __restrict__ scan_prefix,
-    const __grid_constant__ SortPlan plan, unsigned int n_tiles, unsigned int n_k1_tiles)
+    const DupPlan plan, unsigned int n_tiles, unsigned int n_k1_tiles)
 {
-    __shared__ unsigned int s_scan[SCAN_TILE_ITEMS];
-    __shared__ unsigned int s_rlo[SCAN_TILE_ITEMS], s_rhi[SCAN_TILE_ITEMS], s_df[SCAN_TILE_ITEMS];
+    __shared__ unsigned int s_start[SCAN_TILE_ITEMS + 1];      // first pair slot of the v-th visible splat (+ sentinel)
+    __shared__ unsigned int s_rlo[SCAN_TILE_ITEMS], s_rhi[SCAN_TILE_ITEMS];
+    __shared__ unsigned int s_dfi[SCAN_TILE_ITEMS];            // depth field << 16 | splat index within the tile
     __shared__ unsigned int s_hist[FRAME_MAX_PASSES][256];
-    __shared__ unsigned int s_warp[SCAN_THREADS / 32];
+    __shared__ unsigned int s_warp[SCAN_THREADS / 32], s_wvis[SCAN_THREADS / 32];
 
     const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int p = 0; p < FRAME_MAX_PASSES; ++p) s_hist[p][tid] = 0;
-    int tile_pass[2], n_tile_pass = 0;
-    for (int p = 0; p < plan.n_pass; ++p) if (plan.shift[p] >= 32 && n_tile_pass < 2) tile_pass[n_tile_pass++] = p;
     const bool layer = U.mode == SPLAT_MODE_LAYER50;        // second, depth-ordered list
     const bool arrival = U.mode != SPLAT_MODE_TILE;         // LAYER50 / MLAB: the list the pixels walk is in instance order
     __syncthreads();
@@ -49,71 +56,96 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
             *reinterpret_cast<uint4*>(offsets + base + tid * SCAN_ITEMS) = make_uint4(prefix, prefix, prefix, prefix);
             continue;
         }
-        // ---- load 4 consecutive counts per thread (buffers are padded to the tile size)
+        // ---- 4 consecutive counts per thread; scan of (pairs, visible splats) packed in one 64-bit word
         const uint4 c4 = *reinterpret_cast<const uint4*>(touched + base + tid * SCAN_ITEMS);
-        unsigned int cnt[SCAN_ITEMS] = {c4.x, c4.y, c4.z, c4.w};
-        unsigned int tsum = 0;
+        const unsigned int cnt[SCAN_ITEMS] = {c4.x, c4.y, c4.z, c4.w};
+        unsigned int tsum = 0, tvis = 0;
 #pragma unroll
-        for (int k = 0; k < SCAN_ITEMS; ++k) tsum += cnt[k];
-        unsigned int incl = tsum;
+        for (int k = 0; k < SCAN_ITEMS; ++k) { tsum += cnt[k]; tvis += cnt[k] ? 1u : 0u; }
+        unsigned int incl = tsum, ivis = tvis;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { unsigned int v = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += v; }
-        if (lane == 31) s_warp[warp] = incl;
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned int a = __shfl_up_sync(0xFFFFFFFFu, incl, d), b = __shfl_up_sync(0xFFFFFFFFu, ivis, d);
+            if (lane >= d) { incl += a; ivis += b; }
+        }
+        if (lane == 31) { s_warp[warp] = incl; s_wvis[warp] = ivis; }
         __syncthreads();
-        unsigned int wbase = 0;
+        unsigned int wbase = 0, vbase = 0, n_vis = 0;
 #pragma unroll
-        for (int k = 0; k < SCAN_THREADS / 32; ++k) { unsigned int v = s_warp[k]; if (k < (int)warp) wbase += v; }
-        unsigned int excl = wbase + incl - tsum;   // thread-exclusive, block-local
+        for (int k = 0; k < SCAN_THREADS / 32; ++k) {
+            const unsigned int a = s_warp[k], b = s_wvis[k];
+            if (k < (int)warp) { wbase += a; vbase += b; }
+            n_vis += b;
+        }
+        unsigned int excl = wbase + incl - tsum;   // first pair slot of this thread's first splat, block-local
+        unsigned int v = vbase + ivis - tvis;      // rank of this thread's first visible splat
 
-        // ---- stage per-splat rect / depth field; per-splat (depth-digit) histograms; offsets
+        // ---- offsets; visible splats compacted with their rect / depth field; depth-digit histograms
         uint4 o;
         unsigned int* ov = &o.x;
 #pragma unroll
         for (int k = 0; k < SCAN_ITEMS; ++k) {
             const unsigned int li = tid * SCAN_ITEMS + k;
-            s_scan[li] = excl;
             ov[k] = sat_add(prefix, excl);
-            excl += cnt[k];
             if (cnt[k]) {
                 const float4 tail = __ldg(reinterpret_cast<const float4*>(rec + base + li) + 2);  // bd, z, rect_lo, rect_hi
                 const unsigned int h = __float_as_uint(tail.x) >> 16;
                 const unsigned int df = U.order == SPLAT_ORDER_REFERENCE ? (0xFFFFu - h) : h;   // half-depth field (D3)
-                s_df[li] = df;
-                s_rlo[li] = __float_as_uint(tail.z);
-                s_rhi[li] = __float_as_uint(tail.w);
-                for (int p = 0; p < plan.n_pass; ++p)
-                    if (plan.shift[p] < 32) atomicAdd(&s_hist[plan.slot[p]][(df >> plan.shift[p]) & plan.mask[p]], cnt[k]);
+                s_start[v] = excl;
+                s_dfi[v] = (df << 16) | li;                  // li < 1024 fits beside the 16-bit depth field
+                s_rlo[v] = __float_as_uint(tail.z);
+                s_rhi[v] = __float_as_uint(tail.w);
+                if (plan.d0 >= 0) {
+                    atomicAdd(&s_hist[plan.d0][df & 0xFFu], cnt[k]);
+                    atomicAdd(&s_hist[plan.d1][df >> 8], cnt[k]);
+                }
+                ++v;
             }
+            excl += cnt[k];
         }
         *reinterpret_cast<uint4*>(offsets + base + tid * SCAN_ITEMS) = o;
+        if (tid == 0) s_start[n_vis] = btotal;              // sentinel: end of the last owner
         __syncthreads();
 
-        // ---- cooperative expansion: output slot j -> (splat, k-th tile of its rectangle)
-        for (unsigned int j = tid; j < btotal; j += SCAN_THREADS) {
-            unsigned int lo = 0, hi = SCAN_TILE_ITEMS;
-            while (lo < hi) { const unsigned int mid = (lo + hi) >> 1; if (s_scan[mid] <= j) lo = mid + 1; else hi = mid; }
-            const unsigned int sidx = lo - 1;
-            const unsigned int k = j - s_scan[sidx];
-            const unsigned int rlo = s_rlo[sidx], rhi = s_rhi[sidx];
-            const unsigned int tx0 = rlo & 0xFFFFu, ty0 = rlo >> 16, tx1 = rhi & 0xFFFFu;
-            const unsigned int wdt = tx1 - tx0 + 1;
-            const unsigned int ry = k / wdt, rx = k - ry * wdt;
-            const unsigned int t = (ty0 + ry) * (unsigned int)U.tiles_x + (tx0 + rx);
-            for (int q = 0; q < n_tile_pass; ++q)
-                warp_hist_inc(s_hist[plan.slot[tile_pass[q]]], (t >> (plan.shift[tile_pass[q]] - 32)) & plan.mask[tile_pass[q]]);
-            const unsigned long long g = (unsigned long long)prefix + j;
-            if (g < capacity) {
-                // TILE: tile | depth. LAYER50 / MLAB: tile | instance index (arrival order made explicit); LAYER50
-                // adds a second copy in tile | depth order for the composite.
-                keys[g] = ((unsigned long long)t << 32) | (arrival ? base + sidx : s_df[sidx]);
-                vals[g] = base + sidx;
-                if (layer) {
-                    keys_depth[g] = ((unsigned long long)t << 32) | s_df[sidx];
-                    vals_depth[g] = base + sidx;
+        // ---- expansion: a warp takes 32 consecutive pair slots at a time
+        for (unsigned int j0 = warp * 32u; j0 < btotal; j0 += SCAN_THREADS) {
+            const unsigned int j = j0 + lane;
+            // owner of slot j0: last compact entry whose first slot is <= j0 (uniform across the warp)
+            unsigned int lo = 0, hi = n_vis;
+            while (hi - lo > 1) { const unsigned int mid = (lo + hi) >> 1; if (s_start[mid] <= j0) lo = mid; else hi = mid; }
+            // ends of the 32 owners from there on; lane's owner = lo + #{ends <= j}
+            const unsigned int end_l = s_start[min(lo + lane + 1u, n_vis)];
+            unsigned int c = 0;
+#pragma unroll
+            for (int st = 16; st > 0; st >>= 1) {
+                const unsigned int e = __shfl_sync(0xFFFFFFFFu, end_l, c + st - 1);
+                if (e <= j) c += st;
+            }
+            if (j < btotal) {
+                const unsigned int vi = lo + c;
+                const unsigned int k = j - s_start[vi];
+                const unsigned int rlo = s_rlo[vi], rhi = s_rhi[vi], dfi = s_dfi[vi];
+                const unsigned int tx0 = rlo & 0xFFFFu, ty0 = rlo >> 16, tx1 = rhi & 0xFFFFu;
+                const unsigned int wdt = tx1 - tx0 + 1;
+                const unsigned int ry = k / wdt, rx = k - ry * wdt;
+                const unsigned int t = (ty0 + ry) * (unsigned int)U.tiles_x + (tx0 + rx);
+                const unsigned int splat = base + (dfi & 0xFFFFu), df = dfi >> 16;
+                warp_hist_inc(s_hist[plan.t0], t & plan.tmask0);
+                if (plan.t1 >= 0) warp_hist_inc(s_hist[plan.t1], (t >> 8) & plan.tmask1);
+                const unsigned long long g = (unsigned long long)prefix + j;
+                if (g < capacity) {
+                    // TILE: tile | depth. LAYER50 / MLAB: tile | instance index (arrival order made explicit); LAYER50
+                    // adds a second copy in tile | depth order for the composite.
+                    keys[g] = ((unsigned long long)t << 32) | (arrival ? splat : df);
+                    vals[g] = splat;
+                    if (layer) {
+                        keys_depth[g] = ((unsigned long long)t << 32) | df;
+                        vals_depth[g] = splat;
+                    }
                 }
             }
         }
-        __syncthreads();            // s_scan / s_rlo / s_rhi / s_df / s_warp are reused by the next tile
+        __syncthreads();            // the compact arrays are reused by the next tile
     }
     __syncthreads();
     for (int p = 0; p < FRAME_MAX_PASSES; ++p) {
@@ -129,9 +161,17 @@ void launch_scan_duplicate(const FrameUniforms& U, const splat_record* rec, cons
                            const unsigned int* scan_prefix, SortPlan plan, int sm_count, cudaStream_t s)
 {
     if (U.n == 0) return;
+    DupPlan dp{-1, -1, -1, -1, 0u, 0u};
+    for (int p = 0; p < plan.n_pass; ++p) {
+        if (plan.shift[p] == 0) dp.d0 = plan.slot[p];
+        else if (plan.shift[p] == 8) dp.d1 = plan.slot[p];
+        else if (plan.shift[p] == 32) { dp.t0 = plan.slot[p]; dp.tmask0 = plan.mask[p]; }
+        else if (plan.shift[p] == 40) { dp.t1 = plan.slot[p]; dp.tmask1 = plan.mask[p]; }
+    }
+    if (dp.t0 < 0) { dp.t0 = FRAME_MAX_PASSES - 1; dp.tmask0 = 0; }      // single-tile frame: no tile digit is sorted; count into an unused row
     const unsigned int n_tiles = (U.n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS;
     const unsigned int n_k1 = (U.n + SCAN_TILE_ITEMS / 2 - 1) / (SCAN_TILE_ITEMS / 2);
     const unsigned int grid = n_tiles < (unsigned int)sm_count * 8u ? n_tiles : (unsigned int)sm_count * 8u;
     scan_duplicate_kernel<<<grid, SCAN_THREADS, 0, s>>>(U, rec, touched, offsets, keys, vals, keys_depth, vals_depth, capacity, ctl,
-                                                        tile_sums, scan_prefix, plan, n_tiles, n_k1);
+                                                        tile_sums, scan_prefix, dp, n_tiles, n_k1);
 }
