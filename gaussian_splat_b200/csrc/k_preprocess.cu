@@ -101,7 +101,7 @@ __device__ __forceinline__ bool may_be_visible(const float4 p, const FrameUnifor
 
 // K1 = preprocess_kernel + tile_scan_kernel.
 // preprocess_kernel: a CTA owns 2048 splats. (1) Screening from the 16-byte screening plane, 8 splats per
-// thread with all loads issued first; culled splats get tiles_touched = 0. (2) The survivors' local indices
+// thread with all loads issued first; culled splats get a zero bin word. (2) The survivors' local indices
 // are compacted in shared memory. (3) The exactly rounded ~600-instruction pipeline runs on dense warps of
 // survivors, gathering their other planes. With 512-splat CTAs a tile-row band left ~37 survivors per CTA:
 // two warps worked while six waited at the barrier (ncu: 9.7 barrier-stalled warps per issue); a split into
@@ -114,7 +114,7 @@ __device__ __forceinline__ bool may_be_visible(const float4 p, const FrameUnifor
 // phase 1 and staged through shared memory for phase 2 (the gather shape costs 45 instead of 35 us at 1M).
 template <int K1_ITEMS, bool GATHER>
 __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const __grid_constant__ FrameUniforms U,
-                                                         splat_record* __restrict__ rec, unsigned int* __restrict__ touched,
+                                                         splat_record* __restrict__ rec, unsigned long long* __restrict__ binw,
                                                          unsigned int* __restrict__ tile_sums)
 {
     constexpr int K1_CTA_SPLATS = 256 * K1_ITEMS;
@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
         float4 ps = p[k];
         if (!GATHER) ps.w = fmaxf(p[k].w, fmaxf(t[k].x, t[k].y));      // x y z max(scale), what the screening plane holds
         const bool keep = i < U.n && may_be_visible(ps, U);
-        if (i < U.n && !keep) touched[i] = 0;
+        if (i < U.n && !keep) binw[i] = 0ull;
         const unsigned int m = __ballot_sync(0xFFFFFFFFu, keep);
         unsigned int wbase = 0;
         if (lane == 0 && m) wbase = atomicAdd(&s_count, __popc(m));
@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
         splat_record r;
         const unsigned int cnt = preprocess_one(q.x, q.y, q.z, q.w, pp.w, tt.x, tt.y, pp.x, pp.y, pp.z,
                                                 __float_as_uint(tt.w), bh, tt.z, U, r);
-        touched[i] = cnt;
+        binw[i] = cnt ? binw_pack(r.rect_lo, r.rect_hi, r.bd >> 16) : 0ull;
         if (cnt == 0) continue;
         atomicAdd(&s_sum[li / K1_TILE], cnt);       // fits: 512 splats x at most 65536 tiles each < 2^32
         if (U.sh_degree > 0) {
@@ -233,12 +233,12 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(const unsigned int* __r
     }
 }
 
-void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record* rec, unsigned int* touched,
+void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record* rec, unsigned long long* binw,
                        unsigned int* tile_sums, unsigned int* scan_prefix, unsigned long long capacity, FrameCtl* ctl,
                        cudaStream_t s)
 {
     if (U.n == 0) return;
-    if ((U.row_end - U.row_begin) * 2 <= U.tiles_y) preprocess_kernel<8, true><<<(U.n + 2047u) / 2048u, 256, 0, s>>>(sp, U, rec, touched, tile_sums);
-    else preprocess_kernel<2, false><<<(U.n + 511u) / 512u, 256, 0, s>>>(sp, U, rec, touched, tile_sums);
+    if ((U.row_end - U.row_begin) * 2 <= U.tiles_y) preprocess_kernel<8, true><<<(U.n + 2047u) / 2048u, 256, 0, s>>>(sp, U, rec, binw, tile_sums);
+    else preprocess_kernel<2, false><<<(U.n + 511u) / 512u, 256, 0, s>>>(sp, U, rec, binw, tile_sums);
     tile_scan_kernel<<<1, 1024, 0, s>>>(tile_sums, scan_prefix, U.n, capacity, ctl);
 }

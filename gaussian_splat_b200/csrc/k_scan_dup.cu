@@ -24,20 +24,21 @@ struct DupPlan { int d0, d1, t0, t1; unsigned int tmask0, tmask1; };
 // histogram for all of them, flushed once at the end (with one CTA per tile, a 6M-splat band frame issued
 // 5860 x up to 1024 same-address global atomics). Tiles that produced no pair only write their offsets.
 // Per tile: one block scan gives every splat its first pair slot AND the visible splats their rank, so the
-// visible ones are compacted into shared memory (first slot, rect, depth field, index). The expansion then
+// visible ones are compacted into shared memory (first slot, rect, depth field, index) straight from K1's
+// 8-byte bin words: no gather from the 48-byte records. The expansion then
 // works warp by warp on 32 consecutive pair slots: one binary search for the owner of the first slot, and
 // because every visible splat owns at least one slot the other 31 owners lie within the next 32 compact
 // entries - each lane finds its own with five shuffles instead of a ten-step search in shared memory.
 __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
-    const __grid_constant__ FrameUniforms U, const splat_record* __restrict__ rec,
-    const unsigned int* __restrict__ touched, unsigned int* __restrict__ offsets,
+    const __grid_constant__ FrameUniforms U, const unsigned long long* __restrict__ binw,
+    unsigned int* __restrict__ offsets,
     unsigned long long* __restrict__ keys, unsigned int* __restrict__ vals,
     unsigned long long* __restrict__ keys_depth, unsigned int* __restrict__ vals_depth, unsigned long long capacity,
     FrameCtl* ctl, const unsigned int* __restrict__ tile_sums, const unsigned int* __restrict__ scan_prefix,
     const DupPlan plan, unsigned int n_tiles, unsigned int n_k1_tiles)
 {
     __shared__ unsigned int s_start[SCAN_TILE_ITEMS + 1];      // first pair slot of the v-th visible splat (+ sentinel)
-    __shared__ unsigned int s_rlo[SCAN_TILE_ITEMS], s_rhi[SCAN_TILE_ITEMS];
+    __shared__ unsigned int s_rect[SCAN_TILE_ITEMS], s_wdt[SCAN_TILE_ITEMS];   // tx0 | ty0 << 12, rectangle width in tiles
     __shared__ unsigned int s_dfi[SCAN_TILE_ITEMS];            // depth field << 16 | splat index within the tile
     __shared__ unsigned int s_hist[FRAME_MAX_PASSES][256];
     __shared__ unsigned int s_warp[SCAN_THREADS / 32], s_wvis[SCAN_THREADS / 32];
@@ -56,9 +57,13 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
             *reinterpret_cast<uint4*>(offsets + base + tid * SCAN_ITEMS) = make_uint4(prefix, prefix, prefix, prefix);
             continue;
         }
-        // ---- 4 consecutive counts per thread; scan of (pairs, visible splats) packed in one 64-bit word
-        const uint4 c4 = *reinterpret_cast<const uint4*>(touched + base + tid * SCAN_ITEMS);
-        const unsigned int cnt[SCAN_ITEMS] = {c4.x, c4.y, c4.z, c4.w};
+        // ---- 4 consecutive bin words per thread (buffers are padded to the tile size); scan of pairs and of visible splats
+        const ulonglong2 w01 = *reinterpret_cast<const ulonglong2*>(binw + base + tid * SCAN_ITEMS);
+        const ulonglong2 w23 = *reinterpret_cast<const ulonglong2*>(binw + base + tid * SCAN_ITEMS + 2);
+        const unsigned long long bw[SCAN_ITEMS] = {w01.x, w01.y, w23.x, w23.y};
+        unsigned int cnt[SCAN_ITEMS];
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS; ++k) cnt[k] = binw_count(bw[k]);
         unsigned int tsum = 0, tvis = 0;
 #pragma unroll
         for (int k = 0; k < SCAN_ITEMS; ++k) { tsum += cnt[k]; tvis += cnt[k] ? 1u : 0u; }
@@ -88,13 +93,12 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
             const unsigned int li = tid * SCAN_ITEMS + k;
             ov[k] = sat_add(prefix, excl);
             if (cnt[k]) {
-                const float4 tail = __ldg(reinterpret_cast<const float4*>(rec + base + li) + 2);  // bd, z, rect_lo, rect_hi
-                const unsigned int h = __float_as_uint(tail.x) >> 16;
+                const unsigned int h = (unsigned int)(bw[k] >> 48);
                 const unsigned int df = U.order == SPLAT_ORDER_REFERENCE ? (0xFFFFu - h) : h;   // half-depth field (D3)
                 s_start[v] = excl;
                 s_dfi[v] = (df << 16) | li;                  // li < 1024 fits beside the 16-bit depth field
-                s_rlo[v] = __float_as_uint(tail.z);
-                s_rhi[v] = __float_as_uint(tail.w);
+                s_rect[v] = (unsigned int)bw[k] & 0xFFFFFFu;              // tx0 | ty0 << 12
+                s_wdt[v] = ((unsigned int)(bw[k] >> 24) & 0xFFFu) - ((unsigned int)bw[k] & 0xFFFu) + 1u;
                 if (plan.d0 >= 0) {
                     atomicAdd(&s_hist[plan.d0][df & 0xFFu], cnt[k]);
                     atomicAdd(&s_hist[plan.d1][df >> 8], cnt[k]);
@@ -124,9 +128,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
             if (j < btotal) {
                 const unsigned int vi = lo + c;
                 const unsigned int k = j - s_start[vi];
-                const unsigned int rlo = s_rlo[vi], rhi = s_rhi[vi], dfi = s_dfi[vi];
-                const unsigned int tx0 = rlo & 0xFFFFu, ty0 = rlo >> 16, tx1 = rhi & 0xFFFFu;
-                const unsigned int wdt = tx1 - tx0 + 1;
+                const unsigned int rect = s_rect[vi], wdt = s_wdt[vi], dfi = s_dfi[vi];
+                const unsigned int tx0 = rect & 0xFFFu, ty0 = rect >> 12;
                 const unsigned int ry = k / wdt, rx = k - ry * wdt;
                 const unsigned int t = (ty0 + ry) * (unsigned int)U.tiles_x + (tx0 + rx);
                 const unsigned int splat = base + (dfi & 0xFFFFu), df = dfi >> 16;
@@ -154,7 +157,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
     }
 }
 
-void launch_scan_duplicate(const FrameUniforms& U, const splat_record* rec, const unsigned int* touched,
+void launch_scan_duplicate(const FrameUniforms& U, const unsigned long long* binw,
                            unsigned int* offsets, unsigned long long* keys, unsigned int* vals,
                            unsigned long long* keys_depth, unsigned int* vals_depth,
                            unsigned long long capacity, FrameCtl* ctl, const unsigned int* tile_sums,
@@ -172,6 +175,6 @@ void launch_scan_duplicate(const FrameUniforms& U, const splat_record* rec, cons
     const unsigned int n_tiles = (U.n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS;
     const unsigned int n_k1 = (U.n + SCAN_TILE_ITEMS / 2 - 1) / (SCAN_TILE_ITEMS / 2);
     const unsigned int grid = n_tiles < (unsigned int)sm_count * 8u ? n_tiles : (unsigned int)sm_count * 8u;
-    scan_duplicate_kernel<<<grid, SCAN_THREADS, 0, s>>>(U, rec, touched, offsets, keys, vals, keys_depth, vals_depth, capacity, ctl,
+    scan_duplicate_kernel<<<grid, SCAN_THREADS, 0, s>>>(U, binw, offsets, keys, vals, keys_depth, vals_depth, capacity, ctl,
                                                         tile_sums, scan_prefix, dp, n_tiles, n_k1);
 }

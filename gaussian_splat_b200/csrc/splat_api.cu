@@ -27,7 +27,7 @@ __global__ void set_n_sort_kernel(FrameCtl* ctl, unsigned int n) { ctl->n_sort =
 // in flight on two streams (at frame sizes K2-K4 are latency-bound and leave most SMs idle). The single
 // frame entry points use set 0 only; the second set is allocated on the first batch call.
 struct FrameSet {
-    splat_record* rec = nullptr; uint32_t *touched = nullptr, *offsets = nullptr;
+    splat_record* rec = nullptr; unsigned long long* binw = nullptr; uint32_t* offsets = nullptr;
     unsigned long long* keys[2] = {nullptr, nullptr}; uint32_t* vals[2] = {nullptr, nullptr};
     unsigned long long capacity = 0;
     // LAYER50 only: the same pairs in tile | depth order (allocated on the first LAYER50 frame)
@@ -148,13 +148,13 @@ int splat_create(int device, splat_ctx** out) {
 
 // Per-splat scratch of the CURRENT frame set (records, counts, offsets, scan lookback words).
 static void free_scene_scratch(splat_ctx* c) {
-    cudaFree(c->rec); cudaFree(c->touched); cudaFree(c->offsets); cudaFree(c->tile_sums);
-    c->rec = nullptr; c->touched = c->offsets = nullptr; c->tile_sums = nullptr;
+    cudaFree(c->rec); cudaFree(c->binw); cudaFree(c->offsets); cudaFree(c->tile_sums);
+    c->rec = nullptr; c->binw = nullptr; c->offsets = nullptr; c->tile_sums = nullptr;
 }
 static int alloc_scene_scratch(splat_ctx* c, size_t n_pad) {
     CK(cudaMalloc(&c->rec, n_pad * sizeof(splat_record)));
-    CK(cudaMalloc(&c->touched, n_pad * 4)); CK(cudaMalloc(&c->offsets, n_pad * 4));
-    CK(cudaMemset(c->touched, 0, n_pad * 4));
+    CK(cudaMalloc(&c->binw, n_pad * 8)); CK(cudaMalloc(&c->offsets, n_pad * 4));
+    CK(cudaMemset(c->binw, 0, n_pad * 8));
     CK(cudaMemset(c->rec, 0, n_pad * sizeof(splat_record)));
     const size_t sums = n_pad / (SCAN_TILE_ITEMS / 2) + n_pad / SCAN_TILE_ITEMS + 2;   // [n/512] sums, then [n/1024] prefixes
     CK(cudaMalloc(&c->tile_sums, sums * 4));
@@ -378,6 +378,7 @@ static int build_frame(splat_ctx* c, const float* view, const float* proj, int w
     const unsigned int T = (unsigned int)(U.tiles_x * U.tiles_y);
     const int tb = tile_bits(T);
     if (tb > 16) ARG_FAIL("splat_render: more than 65536 tiles");
+    if (U.tiles_x > 4096 || U.tiles_y > 4096) ARG_FAIL("splat_render: viewport wider or taller than 65536 pixels");
     // Digit passes of the (tile | half-depth) order: 15 significant depth bits (the sign bit is 0) then the
     // tile bits. TILE sorts its pairs with all of them. LAYER50 sorts the depth-ordered copy the same way and
     // the arrival-ordered list by the tile digits only (pairs are emitted in instance order and the sort is
@@ -443,9 +444,9 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
     if (c->n) {
         ScenePlanes sp{c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->scr, c->sh, c->n_pad};
         unsigned int* scan_prefix = c->tile_sums + c->n_pad / (SCAN_TILE_ITEMS / 2);
-        launch_preprocess(sp, U, c->rec, c->touched, c->tile_sums, scan_prefix, c->capacity, c->ctl, s);
+        launch_preprocess(sp, U, c->rec, c->binw, c->tile_sums, scan_prefix, c->capacity, c->ctl, s);
         if (timed) CK(cudaEventRecord(c->ev[1], s));
-        launch_scan_duplicate(U, c->rec, c->touched, c->offsets, c->keys[0], c->vals[0], layer ? c->keys_d[0] : nullptr,
+        launch_scan_duplicate(U, c->binw, c->offsets, c->keys[0], c->vals[0], layer ? c->keys_d[0] : nullptr,
                               layer ? c->vals_d[0] : nullptr, c->capacity, c->ctl, c->tile_sums, scan_prefix, plan, c->sm_count, s);
         if (keep) {
             CK(cudaMemcpyAsync(c->dbg_keys, c->keys[0], c->capacity * 8, cudaMemcpyDeviceToDevice, s));
@@ -708,7 +709,7 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
     const void* src = nullptr; size_t need = 0;
     switch (what) {
         case SPLAT_FETCH_RECORDS:       src = c->rec;      need = (size_t)c->n * sizeof(splat_record); break;
-        case SPLAT_FETCH_TILES_TOUCHED: src = c->touched;  need = (size_t)c->n * 4; break;
+        case SPLAT_FETCH_TILES_TOUCHED: src = nullptr;     need = (size_t)c->n * 4; break;   // derived from the bin words below
         case SPLAT_FETCH_OFFSETS:       src = c->offsets;  need = (size_t)c->n * 4; break;
         case SPLAT_FETCH_KEYS_UNSORTED: src = c->dbg_keys; need = D * 8; break;
         case SPLAT_FETCH_VALS_UNSORTED: src = c->dbg_vals; need = D * 4; break;
@@ -733,11 +734,15 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
         }
         delete[] b;
         CK(e);
+    } else if (what == SPLAT_FETCH_TILES_TOUCHED) {
+        std::vector<unsigned long long> w(c->n);
+        if (c->n) CK(cudaMemcpy(w.data(), c->binw, (size_t)c->n * 8, cudaMemcpyDeviceToHost));
+        for (uint32_t i = 0; i < c->n; ++i) ((uint32_t*)dst)[i] = binw_count(w[i]);
     } else if (need) CK(cudaMemcpy(dst, src, need, cudaMemcpyDeviceToHost));
     if (what == SPLAT_FETCH_RECORDS && c->n) {
         // culled splats have no record written: present them zeroed
-        uint32_t* t = new uint32_t[c->n];
-        cudaError_t e = cudaMemcpy(t, c->touched, (size_t)c->n * 4, cudaMemcpyDeviceToHost);
+        unsigned long long* t = new unsigned long long[c->n];
+        cudaError_t e = cudaMemcpy(t, c->binw, (size_t)c->n * 8, cudaMemcpyDeviceToHost);
         if (e == cudaSuccess) {
             splat_record* r = (splat_record*)dst;
             for (uint32_t i = 0; i < c->n; ++i) if (!t[i]) std::memset(r + i, 0, sizeof(splat_record));

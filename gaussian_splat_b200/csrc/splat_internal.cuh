@@ -83,10 +83,25 @@ void launch_upload_soa(const float* aos_dev, unsigned int n, float4* rot, float4
                        uint16_t* b, float4* base_rgb, float4* scr, cudaStream_t s);
 // sh_rest45_dev: [n][45] as the loader stores it (channel-major: f = channel*15 + k) -> coefficient-major planes
 void launch_upload_sh(const float* sh_rest45_dev, unsigned int n, size_t n_pad, float4* planes, cudaStream_t s);
-void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record* rec, unsigned int* touched,
+// Per-splat "bin word" written by K1 and read by K2 (8 bytes, 0 = culled): the tile rectangle and the half depth,
+// everything K2 needs, so it never gathers from the 48-byte records.
+//   bits  0-11 tx0 | 12-23 ty0 | 24-35 tx1 | 36-47 ty1 (inclusive, < 4096 each) | 48-63 bits of half(zFront)
+__host__ __device__ __forceinline__ unsigned long long binw_pack(unsigned int rect_lo, unsigned int rect_hi, unsigned int half_depth) {
+    return (unsigned long long)(rect_lo & 0xFFFu) | ((unsigned long long)(rect_lo >> 16) << 12) |
+           ((unsigned long long)(rect_hi & 0xFFFu) << 24) | ((unsigned long long)(rect_hi >> 16) << 36) |
+           ((unsigned long long)half_depth << 48);
+}
+__host__ __device__ __forceinline__ unsigned int binw_count(unsigned long long w) {
+    if (w == 0) return 0u;
+    const unsigned int tx0 = (unsigned int)w & 0xFFFu, ty0 = (unsigned int)(w >> 12) & 0xFFFu;
+    const unsigned int tx1 = (unsigned int)(w >> 24) & 0xFFFu, ty1 = (unsigned int)(w >> 36) & 0xFFFu;
+    return (tx1 - tx0 + 1u) * (ty1 - ty0 + 1u);
+}
+
+void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record* rec, unsigned long long* binw,
                        unsigned int* tile_sums, unsigned int* scan_prefix, unsigned long long capacity, FrameCtl* ctl,
                        cudaStream_t s);
-void launch_scan_duplicate(const FrameUniforms& U, const splat_record* rec, const unsigned int* touched,
+void launch_scan_duplicate(const FrameUniforms& U, const unsigned long long* binw,
                            unsigned int* offsets, unsigned long long* keys, unsigned int* vals,
                            unsigned long long* keys_depth, unsigned int* vals_depth,
                            unsigned long long capacity, FrameCtl* ctl, const unsigned int* tile_sums,
