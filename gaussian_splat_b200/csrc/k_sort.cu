@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 3) onesweep_pa
     constexpr int TILE_KEYS = SORT_THREADS * ITEMS;
     extern __shared__ unsigned long long s_keys[];                 // [TILE_KEYS] keys, then values
     __shared__ unsigned int s_gexcl[256], s_off[256], s_w[SORT_WARPS];
-    __shared__ unsigned int s_tile;
+    __shared__ unsigned int s_tile[2];
     unsigned int* s_vals = reinterpret_cast<unsigned int*>(s_keys + TILE_KEYS);
     // per set, warp, digit: peer bitmap of the current round / keys of that digit seen so far (later: tile-local offsets)
     unsigned int (*s_bm)[SORT_WARPS][256] = reinterpret_cast<unsigned int (*)[SORT_WARPS][256]>(s_vals + TILE_KEYS);
@@ -100,12 +100,15 @@ __global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 3) onesweep_pa
     // on in the lookback is owned by a running CTA: no deadlock.
     unsigned int next_ticket = 0;
     if (tid == 0) next_ticket = atomicAdd(&ctl->sort_ticket[tix], 1u);
+    unsigned int parity = 0;
     while (true) {
-        __syncthreads();
+        // one barrier per tile: the ticket slot is double-buffered, so thread 0 may publish the next tile's
+        // number while slower warps still read the current one (it is rewritten two barriers later)
+        if (tid == 0) s_tile[parity] = next_ticket;
         PROF(6);
-        if (tid == 0) s_tile = next_ticket;
         __syncthreads();
-        const unsigned int tile = s_tile;
+        const unsigned int tile = s_tile[parity];
+        parity ^= 1u;
         PROF(0);
         if (tile >= n_tiles) break;
         const unsigned int tbase = tile * TILE_KEYS;
