@@ -414,12 +414,17 @@ def main():
         t_wall = time.perf_counter() - t_wall0
         sampler.stop_flag = True
         sampler.join()
-        total_ms = sum(a.elapsed_time(b) for a, b in ev)
+        per_step = [a.elapsed_time(b) for a, b in ev]
+        total_ms = sum(per_step)
     if world > 1:
         t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         total_ms = float(t.item())
     ms_per_step = total_ms / args.steps
+    step_pct = None
+    if not bands:      # this rank's per-step distribution (median and p10 / p90)
+        q = np.percentile(np.asarray(per_step), [10, 50, 90])
+        step_pct = {"p10": float(q[0]), "p50": float(q[1]), "p90": float(q[2])}
     frames_per_step = 1 if bands else world
     fps = frames_per_step * 1e3 / ms_per_step
     st = ctx.status()
@@ -502,7 +507,8 @@ def main():
         roof = {"kernel": {"blend": "blend_kernel", "sort": "onesweep_pass_kernel", "preprocess": "preprocess_kernel",
                            "scan_duplicate": "scan_duplicate_kernel", "ranges": "tile_bounds_kernel"}[dom],
                 "bound": "hbm", "achieved": stages[dom]["gb_per_s"], "peak": hbm_peak, "unit": "GB/s",
-                "frac": stages[dom]["frac_of_hbm_peak"], "traffic": measured_traffic(wl, dom), "peak_kind": peak_kind,
+                "frac": stages[dom]["frac_of_hbm_peak"], "frac_of_8TBs_nominal": stages[dom]["gb_per_s"] / 8000.0,
+                "traffic": measured_traffic(wl, dom), "peak_kind": peak_kind,
                 "alg_bytes_per_launch": ab[dom], "ms_per_launch": stage_ms.get(dom),
                 "share_of_step": stage_ms.get(dom, 0.0) / max(1e-9, stage_ms.get("total", 0.0)),
                 "note": ("the blend is bound by SM instruction issue, not HBM (ncu: issue slots ~89% busy, DRAM ~2%); "
@@ -520,7 +526,7 @@ def main():
             "metric": "frames_per_s", "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "strong" if bands else "weak", "vs_baseline": None, "dtype": "f32+f16", "data": "synthetic",
-            "mgaussians_per_s": n * fps / 1e6,
+            "mgaussians_per_s": n * fps / 1e6, "ms_per_step_percentiles": step_pct,
             "config": {"workload": name, "n_gaussians": n, "width": w, "height": h,
                        "mode": "LAYER50" if mode else "TILE", "order": "near_first", "sh_degree": args.sh_degree,
                        "pairs_D": D, "visible": visible, "sort_passes": n_pass,
@@ -532,7 +538,7 @@ def main():
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": 128, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps, "single_frame_ms": lat_ms, "note": e2e_note},
             "camera_batch_device": inflight,
-            "gpu_launches": args.steps * (4 + n_pass),      # K1, K2, K3 x n_pass, K4, K5 (+1 memset node, not counted)
+            "gpu_launches": args.steps * (5 + n_pass),      # K1 (preprocess + tile scan), K2, K3 x n_pass, K4, K5 (+1 memset node, not counted)
             "clocks": clocks, "wall_s": t_wall,
         }
         if world == 1 and not args.no_sort_bench:
