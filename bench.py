@@ -466,6 +466,17 @@ def main():
         t0 = time.perf_counter()
         ctx.render_batch_host(ptrs, views, projs, w, h, eopts)
         e2e_s = time.perf_counter() - t0
+        # the same, delivered in the reference drawable's format (BGRA8Unorm, 4 B / pixel, packed on the device)
+        bgra_fbs = torch.empty((e2e_steps, h, w, 4), dtype=torch.uint8).pin_memory()
+        bptrs = [bgra_fbs[k].data_ptr() for k in range(e2e_steps)]
+        bopts = opts_for(capi.FLAG_HOST_BGRA8)
+        ctx.render_batch_host(bptrs[:4], views[:4], projs[:4], w, h, bopts)
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        ctx.render_batch_host(bptrs, views, projs, w, h, bopts)
+        e2e_bgra_s = time.perf_counter() - t0
+        del bgra_fbs
         d2h = w * h * 8 + 16
         e2e_note = ("splat_render_batch_host: %d frames, each frame's matrices from host and its framebuffer to pinned "
                     "host memory, copies pipelined behind the next frame's kernels" % e2e_steps)
@@ -474,6 +485,13 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
     e2e_fps = frames_per_step * e2e_steps / e2e_s
+    e2e_bgra_fps = None
+    if not bands:
+        if world > 1:
+            t = torch.tensor([e2e_bgra_s], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_bgra_s = float(t.item())
+        e2e_bgra_fps = frames_per_step * e2e_steps / e2e_bgra_s
 
     # ---- device-resident camera batch (splat_render_batch: two frames in flight on two internal streams)
     inflight = None
@@ -487,7 +505,8 @@ def main():
         b0.record()
         ctx.render_batch(stream, dptrs, views, projs, w, h, eopts)
         b1.record(); torch.cuda.synchronize()
-        inflight = {"frames_per_s": e2e_steps * 1e3 / b0.elapsed_time(b1), "frames": e2e_steps, "frames_in_flight": 2,
+        two = (not mode) and n <= 2_500_000 and w * h <= 2_400_000      # the library's own rule (splat_api.cu: two_frames_in_flight)
+        inflight = {"frames_per_s": e2e_steps * 1e3 / b0.elapsed_time(b1), "frames": e2e_steps, "frames_in_flight": 2 if two else 1,
                     "note": "splat_render_batch, framebuffers stay on the device; no L2 flush (a frame touches ~2x the L2)"}
         del dfb
 
@@ -536,7 +555,9 @@ def main():
                               "overlapped with frame i+1") if bands else "flushed between timed steps (256 MiB write, untimed)"},
             "roofline": roof, "stages": stages,
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": 128, "d2h_bytes_per_step": d2h,
-                    "steps": e2e_steps, "single_frame_ms": lat_ms, "note": e2e_note},
+                    "steps": e2e_steps, "single_frame_ms": lat_ms, "note": e2e_note,
+                    "bgra8": {"value": e2e_bgra_fps, "d2h_bytes_per_step": w * h * 4 + 16,
+                              "note": "same call with SPLAT_FLAG_HOST_BGRA8: frames delivered as the reference drawable's BGRA8Unorm"}},
             "camera_batch_device": inflight,
             "gpu_launches": args.steps * (5 + n_pass),      # K1 (preprocess + tile scan), K2, K3 x n_pass, K4, K5 (+1 memset node, not counted)
             "clocks": clocks, "wall_s": t_wall,

@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libsplat_cuda.so")
 
 MODE_TILE, MODE_LAYER50, MODE_MLAB = 0, 1, 2
 ORDER_NEAR_FIRST, ORDER_REFERENCE = 0, 1
-FLAG_TIMING, FLAG_KEEP_UNSORTED = 1, 2
+FLAG_TIMING, FLAG_KEEP_UNSORTED, FLAG_HOST_BGRA8 = 1, 2, 4
 (FETCH_RECORDS, FETCH_TILES_TOUCHED, FETCH_OFFSETS, FETCH_KEYS_UNSORTED, FETCH_VALS_UNSORTED,
  FETCH_KEYS_SORTED, FETCH_VALS_SORTED, FETCH_TILE_RANGES, FETCH_DIGIT_HISTOGRAMS, FETCH_INSTANCES,
  FETCH_SH_REST) = range(11)

@@ -53,6 +53,7 @@ struct splat_ctx : FrameSet {
     void* fb_scratch = nullptr; size_t fb_scratch_bytes = 0;
     // camera-batch pipeline (splat_render_batch_host): second framebuffer, copy stream, per-buffer events
     cudaStream_t copy_stream = nullptr; void* fb_scratch2 = nullptr; size_t fb_scratch2_bytes = 0;
+    void* bgra_scratch[2] = {nullptr, nullptr}; size_t bgra_bytes = 0;      // SPLAT_FLAG_HOST_BGRA8 staging
     cudaEvent_t ev_rendered[2] = {}, ev_copied[2] = {}, ev_fork = nullptr;
     unsigned int* batch_flags = nullptr; int batch_flags_cap = 0;   // pinned: overflow word + D of every view
 };
@@ -217,7 +218,7 @@ int splat_destroy(splat_ctx* c) {
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     for (int k = 0; k < 2; ++k) { if (c->ev_rendered[k]) cudaEventDestroy(c->ev_rendered[k]); if (c->ev_copied[k]) cudaEventDestroy(c->ev_copied[k]); }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
-    cudaFree(c->fb_scratch2); cudaFreeHost(c->batch_flags);
+    cudaFree(c->fb_scratch2); cudaFree(c->bgra_scratch[0]); cudaFree(c->bgra_scratch[1]); cudaFreeHost(c->batch_flags);
     delete c;
     return SPLAT_OK;
 }
@@ -491,6 +492,14 @@ int splat_render(splat_ctx* c, void* stream, void* fb, const float* view, const 
     return enqueue_frame(c, (cudaStream_t)stream, fb, U, plan, o ? o->flags : 0);
 }
 
+// Two frames in flight only pay while one frame leaves SMs idle in its latency-bound stages. Measured on B200:
+// 1M / 1080p TILE +11% end to end; 2M LAYER50 -14% and 6M / 4K -48% (two sets of persistent sort CTAs and two
+// 16 MB+ working sets fight over shared memory and L2), so large frames and LAYER50 stay serial.
+static bool two_frames_in_flight(const splat_ctx* c, int w, int h, const splat_opts* o) {
+    if (o && o->mode == SPLAT_MODE_LAYER50) return false;
+    return c->n <= 2500000u && (long long)w * h <= 2400000ll;
+}
+
 // Camera batches keep two frames in flight: view v runs on frame set v & 1 (own scratch, own stream), so the
 // latency-bound stages of one frame (K2-K4) fill the SMs the other frame's tails leave idle.
 int splat_render_batch(splat_ctx* c, void* stream, void* const* fbs, const float* views, const float* projs,
@@ -499,9 +508,7 @@ int splat_render_batch(splat_ctx* c, void* stream, void* const* fbs, const float
     if (n_views < 0 || (n_views && (!fbs || !views || !projs))) ARG_FAIL("splat_render_batch: bad arguments");
     if (n_views == 0) return SPLAT_OK;
     CK(cudaSetDevice(c->device));
-    // LAYER50 frames are dominated by a blend that already fills the machine twice over; measured on B200,
-    // overlapping two of them loses 14% (L2 contention), so that mode stays serial on the caller's stream.
-    if (n_views == 1 || (o && o->mode == SPLAT_MODE_LAYER50)) {
+    if (n_views == 1 || !two_frames_in_flight(c, w, h, o)) {
         for (int v = 0; v < n_views; ++v) {
             const int rc = splat_render(c, stream, fbs[v], views + 16 * v, projs + 16 * v, w, h, o);
             if (rc) return rc;
@@ -567,13 +574,23 @@ int splat_render_host(splat_ctx* c, void* fb_host, const float* view, const floa
         c->fb_scratch_bytes = bytes;
     }
     if (c->capacity == 0) { rc = ensure_pairs(c, 1ull << 20); if (rc) return rc; }
+    const bool bgra = o && (o->flags & SPLAT_FLAG_HOST_BGRA8);
+    if (bgra && (size_t)w * h * 4 > c->bgra_bytes) {
+        CK(cudaDeviceSynchronize());
+        for (int k = 0; k < 2; ++k) { cudaFree(c->bgra_scratch[k]); c->bgra_scratch[k] = nullptr; CK(cudaMalloc(&c->bgra_scratch[k], (size_t)w * h * 4)); }
+        c->bgra_bytes = (size_t)w * h * 4;
+    }
     // rows outside the band are not rendered: only the band is copied back
     const size_t row0 = (size_t)U.row_begin * SPLAT_TILE, row1 = (size_t)U.row_end * SPLAT_TILE < (size_t)h ? (size_t)U.row_end * SPLAT_TILE : (size_t)h;
     for (int attempt = 0; attempt < 4; ++attempt) {
         rc = enqueue_frame(c, c->own_stream, c->fb_scratch, U, plan, o ? o->flags : 0);
         if (rc) return rc;
         CK(cudaMemcpyAsync(c->ctl_host, c->ctl, 64, cudaMemcpyDeviceToHost, c->own_stream));
-        if (row1 > row0)
+        if (row1 > row0 && bgra) {
+            launch_pack_bgra8((char*)c->fb_scratch + row0 * w * 8, (char*)c->bgra_scratch[0] + row0 * w * 4, (row1 - row0) * w, c->own_stream);
+            CK(cudaMemcpyAsync((char*)fb_host + row0 * w * 4, (char*)c->bgra_scratch[0] + row0 * w * 4, (row1 - row0) * w * 4,
+                               cudaMemcpyDeviceToHost, c->own_stream));
+        } else if (row1 > row0)
             CK(cudaMemcpyAsync((char*)fb_host + row0 * w * 8, (char*)c->fb_scratch + row0 * w * 8, (row1 - row0) * w * 8,
                                cudaMemcpyDeviceToHost, c->own_stream));
         CK(cudaStreamSynchronize(c->own_stream));
@@ -611,14 +628,22 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
     }
     use_set(c, 0);
     if (c->capacity == 0) { const int rc = ensure_pairs(c, 1ull << 20); if (rc) return rc; }
-    if (n_views > 1) { const int rc = ensure_alt(c); if (rc) return rc; }
+    const bool bgra = o && (o->flags & SPLAT_FLAG_HOST_BGRA8);
+    if (bgra && (size_t)w * h * 4 > c->bgra_bytes) {
+        CK(cudaDeviceSynchronize());
+        for (int k = 0; k < 2; ++k) { cudaFree(c->bgra_scratch[k]); c->bgra_scratch[k] = nullptr; CK(cudaMalloc(&c->bgra_scratch[k], (size_t)w * h * 4)); }
+        c->bgra_bytes = (size_t)w * h * 4;
+    }
+    const size_t px_bytes = bgra ? 4 : 8;
+    const bool two = n_views > 1 && two_frames_in_flight(c, w, h, o);
+    if (two) { const int rc = ensure_alt(c); if (rc) return rc; }
     const int flags = o ? (o->flags & ~(SPLAT_FLAG_TIMING | SPLAT_FLAG_KEEP_UNSORTED)) : 0;
     void* buf[2] = {c->fb_scratch, c->fb_scratch2};
     for (int attempt = 0; attempt < 4; ++attempt) {
         for (int v = 0; v < n_views; ++v) {
             if (!fb_host[v]) ARG_FAIL("splat_render_batch_host: NULL framebuffer");
             const int b = v & 1;
-            use_set(c, b);                                  // frame set, stream and framebuffer b
+            use_set(c, two ? b : 0);                        // frame set and stream (two in flight), framebuffer b
             FrameUniforms U; SortPlan plan;
             int rc = build_frame(c, views + 16 * v, projs + 16 * v, w, h, o, U, plan);
             if (rc) return rc;
@@ -626,12 +651,15 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
             rc = enqueue_frame(c, c->own_stream, buf[b], U, plan, flags);
             if (rc) return rc;
             CK(cudaMemcpyAsync(c->batch_flags + 4 * v, c->ctl, 16, cudaMemcpyDeviceToHost, c->own_stream));   // D, overflow
-            CK(cudaEventRecord(c->ev_rendered[b], c->own_stream));
-            CK(cudaStreamWaitEvent(c->copy_stream, c->ev_rendered[b], 0));
             const size_t row0 = (size_t)U.row_begin * SPLAT_TILE;
             const size_t row1 = (size_t)U.row_end * SPLAT_TILE < (size_t)h ? (size_t)U.row_end * SPLAT_TILE : (size_t)h;
+            if (bgra && row1 > row0)
+                launch_pack_bgra8((char*)buf[b] + row0 * w * 8, (char*)c->bgra_scratch[b] + row0 * w * 4, (row1 - row0) * w, c->own_stream);
+            CK(cudaEventRecord(c->ev_rendered[b], c->own_stream));
+            CK(cudaStreamWaitEvent(c->copy_stream, c->ev_rendered[b], 0));
+            const char* src = bgra ? (const char*)c->bgra_scratch[b] : (const char*)buf[b];
             if (row1 > row0)
-                CK(cudaMemcpyAsync((char*)fb_host[v] + row0 * w * 8, (char*)buf[b] + row0 * w * 8, (row1 - row0) * w * 8,
+                CK(cudaMemcpyAsync((char*)fb_host[v] + row0 * w * px_bytes, src + row0 * w * px_bytes, (row1 - row0) * w * px_bytes,
                                    cudaMemcpyDeviceToHost, c->copy_stream));
             CK(cudaEventRecord(c->ev_copied[b], c->copy_stream));
         }

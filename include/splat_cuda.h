@@ -37,7 +37,10 @@ enum {
 };
 enum {
     SPLAT_FLAG_TIMING = 1,        /* record per-stage CUDA events (adds event overhead)          */
-    SPLAT_FLAG_KEEP_UNSORTED = 2  /* keep a copy of the unsorted pairs for splat_debug_fetch      */
+    SPLAT_FLAG_KEEP_UNSORTED = 2, /* keep a copy of the unsorted pairs for splat_debug_fetch      */
+    SPLAT_FLAG_HOST_BGRA8 = 4     /* splat_render_host / splat_render_batch_host deliver the frame as the
+                                     reference's drawable format, BGRA8Unorm (4 B / pixel, packed on the
+                                     device by the splat_pack_bgra8 kernel) instead of half4 (8 B / pixel) */
 };
 
 /* Mirrors src/instanced_splat_renderer.h:6-11 (56 bytes, no padding). */

@@ -284,3 +284,24 @@ def test_pack_bgra8_matches_unorm_conversion(gpu_ctx):
     gpu_ctx.pack_bgra8(torch.cuda.current_stream().cuda_stream, fb.data_ptr(), out.data_ptr(), w, h)
     torch.cuda.synchronize()
     assert np.array_equal(out.cpu().numpy(), want)
+
+
+def test_host_delivery_as_bgra8(gpu_ctx, small_scene):
+    """SPLAT_FLAG_HOST_BGRA8: host frames arrive in the reference drawable's format, equal to packing the half4 frame."""
+    import torch
+    from gaussian_splat_b200 import capi
+    from oracle import oracle as O
+    w, h, n = 400, 240, 3
+    gpu_ctx.upload(small_scene)
+    cams = [O.app_camera(w, h, eye=(1.0 + k, 2.0, 5.0)) for k in range(n)]
+    views = np.stack([c[0] for c in cams]); projs = np.stack([c[1] for c in cams])
+    half = torch.zeros((n, h, w, 4), dtype=torch.float16).pin_memory()
+    gpu_ctx.render_batch_host([half[k].data_ptr() for k in range(n)], views, projs, w, h, capi.make_opts())
+    out = torch.zeros((n, h, w, 4), dtype=torch.uint8).pin_memory()
+    gpu_ctx.render_batch_host([out[k].data_ptr() for k in range(n)], views, projs, w, h, capi.make_opts(flags=capi.FLAG_HOST_BGRA8))
+    x = half.numpy().astype(np.float32)
+    want = np.rint(np.clip(x, 0.0, 1.0) * np.float32(255.0)).astype(np.uint8)[..., [2, 1, 0, 3]]
+    assert np.array_equal(out.numpy(), want) and want.any()
+    one = np.zeros((h, w, 4), np.uint8)
+    gpu_ctx.render_host(one.ctypes.data, views[1], projs[1], w, h, capi.make_opts(flags=capi.FLAG_HOST_BGRA8))
+    assert np.array_equal(one, want[1])
