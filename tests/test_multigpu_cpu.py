@@ -101,3 +101,33 @@ def test_measured_time_rebalancing_converges():
     ideal = true_cost.sum() / world
     assert worst <= worst0 + 1e-9
     assert worst <= 1.08 * ideal, (worst, ideal, worst0)
+
+
+def _shared_worker(rank, world, port, h, w, bands, name, out_path):
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    rows = M.bands_to_pixel_rows(bands, h)
+    frame = M.SharedHostFrame(name, h, w, rank, world, register=False)      # no CUDA here: plain shared mapping
+    fb = torch.full((h, w, 4), float(rank + 1), dtype=torch.float16)        # this rank's "device" framebuffer
+    frame.deliver(fb, rows[rank])
+    dist.barrier()
+    if rank == world - 1:                                                   # any rank sees the whole frame
+        np.save(out_path, frame.tensor.numpy().copy())
+    dist.barrier()
+    frame.close()
+    dist.destroy_process_group()
+
+
+def test_shared_host_frame_composes_bands_without_a_collective(tmp_path):
+    """World-size-2 host delivery: every rank writes its band straight into one shared host frame."""
+    import torch.multiprocessing as mp
+    h, w, world = 100, 48, 2
+    bands = M.band_rows((h + 15) // 16, world, np.arange(1, (h + 15) // 16 + 1))
+    out = str(tmp_path / "frame.npy"); name = "splat_test_frame_%d" % os.getpid()
+    mp.spawn(_shared_worker, args=(world, _free_port(), h, w, bands, name, out), nprocs=world, join=True)
+    fr = np.load(out)
+    for r, (a, b) in enumerate(M.bands_to_pixel_rows(bands, h)):
+        assert np.all(fr[a:b] == r + 1)
+    assert not os.path.exists(os.path.join("/dev/shm", name))
