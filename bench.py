@@ -268,6 +268,7 @@ def main():
         raise SystemExit("bench.py: no CUDA device (there is no CPU fallback; use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = multigpu.bind_to_gpu_numa_node(local) if world > 1 else None      # host buffers land next to this rank's GPU
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -586,7 +587,7 @@ def main():
                         "note": "same call with SPLAT_FLAG_HOST_BGRA8: frames delivered as the reference drawable's BGRA8Unorm"}},
             "camera_batch_device": inflight,
             "gpu_launches": args.steps * (5 + n_pass),      # K1 (preprocess + tile scan), K2, K3 x n_pass, K4, K5 (+1 memset node, not counted)
-            "clocks": clocks, "wall_s": t_wall,
+            "clocks": clocks, "wall_s": t_wall, "numa": numa,
         }
         if world == 1 and not args.no_sort_bench:
             sb = sort_bench(ctx, torch)

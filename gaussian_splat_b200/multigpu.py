@@ -158,3 +158,36 @@ class SharedHostFrame:
         self._map = None
         if self.rank == 0 and os.path.exists(self.path):
             os.unlink(self.path)
+
+
+def bind_to_gpu_numa_node(device_index: int) -> dict:
+    """Pin this process to the CPU cores of the NUMA node its GPU hangs off, BEFORE any page-locked host buffer is
+    allocated (first-touch places the pages on that node). With one process per GPU and framebuffers streaming
+    to host memory, buffers on the far socket put every copy on the inter-socket link. Best effort: returns what
+    it found and did; never raises (containers may hide sysfs)."""
+    info = {"device": device_index, "bound": False}
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(device_index)
+        bus = "%04x:%02x:%02x.0" % (getattr(pr, "pci_domain_id", 0), pr.pci_bus_id, pr.pci_device_id)
+        info["pci"] = bus
+        with open("/sys/bus/pci/devices/%s/numa_node" % bus) as f:
+            node = int(f.read().strip())
+        info["numa_node"] = node
+        if node < 0:
+            return info
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
+            spec = f.read().strip()
+        cpus = set()
+        for part in spec.split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        allowed = os.sched_getaffinity(0)
+        use = cpus & allowed
+        if use:
+            os.sched_setaffinity(0, use)
+            info["bound"] = True
+            info["cpus"] = len(use)
+    except Exception as e:      # noqa: BLE001 - diagnostic only
+        info["error"] = repr(e)
+    return info
