@@ -5,6 +5,9 @@
 //
 //   splat_headless scene.ply [--width 1920] [--height 1080] [--frames 64] [--mode tile|layer50|mlab]
 //                  [--k N] [--order near|reference] [--sh 0..3] [--device 0] [--out frame.ppm] [--decode host|device]
+//                  [--trace events.txt]   replay an interaction trace through the reference's camera handlers
+//                                         (src/trackball_camera.mm:39-105, driven as src/main.mm:104-141 drives them): lines
+//                                         `down x y button` | `move x y` | `up` | `scroll delta` | `frame`
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -39,6 +42,7 @@ int main(int argc, char** argv) {
     if (argc < 2) { std::fprintf(stderr, "usage: %s scene.ply [options]\n", argv[0]); return 2; }
     int w = 1920, h = 1080, frames = 64, device = 0;
     const char* out = nullptr;
+    const char* trace = nullptr;
     SplatDecode decode = SplatDecode::Host;
     splat_opts opts{};
     opts.flags = SPLAT_FLAG_TIMING;
@@ -52,6 +56,7 @@ int main(int argc, char** argv) {
         else if (k == "--k") opts.max_fragments = std::atoi(v);
         else if (k == "--sh") opts.sh_degree = std::atoi(v);
         else if (k == "--out") out = v;
+        else if (k == "--trace") trace = v;
         else if (k == "--mode") opts.mode = std::strcmp(v, "layer50") == 0 ? SPLAT_MODE_LAYER50 : std::strcmp(v, "mlab") == 0 ? SPLAT_MODE_MLAB : SPLAT_MODE_TILE;
         else if (k == "--order") opts.order = std::strcmp(v, "reference") == 0 ? SPLAT_ORDER_REFERENCE : SPLAT_ORDER_NEAR_FIRST;
         else { std::fprintf(stderr, "unknown option %s\n", k.c_str()); return 2; }
@@ -72,17 +77,43 @@ int main(int argc, char** argv) {
     if (cudaMalloc(&fb, (size_t)w * h * 8) != cudaSuccess) { std::fprintf(stderr, "cudaMalloc failed\n"); return 1; }
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     double total_ms = 0;
-    for (int f = 0; f < frames; ++f) {
-        const float t = 6.28318530718f * (float)f / (float)std::max(frames, 1);
-        camera.setPosition(simd_make_float3(5.0f * std::sin(t), 2.0f, 5.0f * std::cos(t)));
-        cudaEventRecord(e0, stream);
-        renderer.render(stream, fb, camera.getViewMatrix(), camera.getProjectionMatrix(), (float)w, (float)h);
-        cudaEventRecord(e1, stream);
-        cudaEventSynchronize(e1);
-        float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
-        if (f > 0 || frames == 1) total_ms += ms;
-        splat_status st;
-        if (splat_frame_status(renderer.context(), &st) == SPLAT_OK && st.overflow) { --f; continue; }   // buffers grown: redo
+    auto render_frame = [&](bool count) {
+        for (int attempt = 0; attempt < 4; ++attempt) {
+            cudaEventRecord(e0, stream);
+            renderer.render(stream, fb, camera.getViewMatrix(), camera.getProjectionMatrix(), (float)w, (float)h);
+            cudaEventRecord(e1, stream);
+            cudaEventSynchronize(e1);
+            splat_status st;
+            if (splat_frame_status(renderer.context(), &st) == SPLAT_OK && st.overflow) continue;   // buffers grown: redo
+            float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+            if (count) total_ms += ms;
+            return;
+        }
+    };
+    if (trace) {
+        // the app's start pose (src/main.mm:55-58), then the recorded events; every `frame` line renders one
+        camera.setPosition(simd_make_float3(0, 2, 5));
+        FILE* tf = std::fopen(trace, "r");
+        if (!tf) { std::fprintf(stderr, "cannot open %s\n", trace); return 1; }
+        char word[32]; frames = 0;
+        while (std::fscanf(tf, "%31s", word) == 1) {
+            float a = 0, b = 0; int btn = 0;
+            if (!std::strcmp(word, "down") && std::fscanf(tf, "%f %f %d", &a, &b, &btn) == 3) camera.handleMouseDown(a, b, btn);
+            else if (!std::strcmp(word, "move") && std::fscanf(tf, "%f %f", &a, &b) == 2) camera.handleMouseMove(a, b);
+            else if (!std::strcmp(word, "up")) camera.handleMouseUp();
+            else if (!std::strcmp(word, "scroll") && std::fscanf(tf, "%f", &a) == 1) camera.handleScroll(a);
+            else if (!std::strcmp(word, "frame")) { render_frame(frames > 0); ++frames; }
+            else { std::fprintf(stderr, "bad trace line at '%s'\n", word); return 2; }
+        }
+        std::fclose(tf);
+        const simd_float3 p = camera.getPosition();
+        std::printf("trace: %d frames, camera at %.9g %.9g %.9g\n", frames, p.x, p.y, p.z);
+    } else {
+        for (int f = 0; f < frames; ++f) {
+            const float t = 6.28318530718f * (float)f / (float)std::max(frames, 1);
+            camera.setPosition(simd_make_float3(5.0f * std::sin(t), 2.0f, 5.0f * std::cos(t)));
+            render_frame(f > 0 || frames == 1);
+        }
     }
     const int timed = frames > 1 ? frames - 1 : frames;
     if (timed > 0) std::printf("%d frames, %.3f ms/frame, %.1f frames/s\n", timed, total_ms / timed, 1e3 * timed / total_ms);

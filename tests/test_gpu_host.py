@@ -44,3 +44,32 @@ def test_headless_driver_runs_and_writes_a_frame(tmp_path):
     raw = open(out, "rb").read()
     assert raw.startswith(b"P6\n320 200\n255\n") and len(raw) == 15 + 320 * 200 * 3
     assert np.frombuffer(raw[15:], np.uint8).max() > 100           # something was drawn
+
+
+def test_headless_driver_replays_an_interaction_trace(tmp_path):
+    """SURVEY 8(f) rank 4: mouse / scroll events through the reference's camera handlers, a frame per `frame` line;
+    the final camera pose equals the one the same events give the host camera class directly."""
+    from gaussian_splat_b200 import host_api as H, scene
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "gaussian_splat_b200", "splat_headless")
+    p = str(tmp_path / "s.ply"); out = str(tmp_path / "t.ppm"); tr = str(tmp_path / "trace.txt")
+    scene.write_ply(p, 20000, 0x5EED0001)
+    events = [("frame",), ("down", 100.0, 80.0, 0), ("move", 140.0, 95.0), ("frame",), ("move", 180.0, 60.0), ("up",),
+              ("scroll", 1.5), ("frame",), ("down", 50.0, 50.0, 1), ("move", 70.0, 90.0), ("up",), ("scroll", -0.5), ("frame",)]
+    with open(tr, "w") as f:
+        for e in events:
+            f.write(" ".join(str(x) for x in e) + "\n")
+    res = subprocess.run([exe, p, "--width", "320", "--height", "200", "--trace", tr, "--out", out],
+                         capture_output=True, text=True, timeout=120)
+    assert res.returncode == 0, res.stderr
+    cam = H.TrackballCamera(); cam.set_viewport(320, 200); cam.set_target(0, 0, 0); cam.set_position(0, 2, 5)
+    for e in events:
+        if e[0] == "down": cam.mouse_down(e[1], e[2], e[3])
+        elif e[0] == "move": cam.mouse_move(e[1], e[2])
+        elif e[0] == "up": cam.mouse_up()
+        elif e[0] == "scroll": cam.scroll(e[1])
+    line = [ln for ln in res.stdout.splitlines() if ln.startswith("trace:")][0]
+    assert line.startswith("trace: 4 frames")
+    got = np.array([float(x) for x in line.split("camera at")[1].split()], np.float32)
+    assert np.array_equal(got, np.asarray(cam.position(), np.float32))
+    assert open(out, "rb").read().startswith(b"P6\n320 200\n255\n")
