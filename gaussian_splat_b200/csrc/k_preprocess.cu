@@ -239,6 +239,6 @@ void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_reco
 {
     if (U.n == 0) return;
     if ((U.row_end - U.row_begin) * 2 <= U.tiles_y) preprocess_kernel<8, true><<<(U.n + 2047u) / 2048u, 256, 0, s>>>(sp, U, rec, binw, tile_sums);
-    else preprocess_kernel<2, false><<<(U.n + 511u) / 512u, 256, 0, s>>>(sp, U, rec, binw, tile_sums);
+    else preprocess_kernel<4, false><<<(U.n + 1023u) / 1024u, 256, 0, s>>>(sp, U, rec, binw, tile_sums);
     tile_scan_kernel<<<1, 1024, 0, s>>>(tile_sums, scan_prefix, U.n, capacity, ctl);
 }
