@@ -111,9 +111,9 @@ def algorithmic_bytes(n, visible, D, n_pass, P, sh_degree=0, layer=False):
     lists = 2 if layer else 1
     return {
         "preprocess": n * (56 + 4) + visible * (48 + sh),
-        "scan_duplicate": n * 8 + n * 4 + visible * 12 + D * 12 * lists,
-        "sort": D * (8 * lists + n_pass * 24),
-        "ranges": D * 8,
+        "scan_duplicate": n * 8 + n * 4 + D * 8 * lists,            # bin words in, offsets out, (u32 key, u32 value) pairs out
+        "sort": D * n_pass * 16,                                    # every pass reads and writes 4 + 4 B per pair
+        "ranges": D * 4,
         "blend": D * (4 + 48) * lists + P * 8,
     }
 
@@ -210,7 +210,7 @@ def cpu_baseline_leg(inst, V, P, w, h, mode, name):
 
 
 def sort_bench(ctx, torch, n=1 << 26, reps=5):
-    """Stand-alone 'sort HBM GB/s': full-entropy 64-bit keys, 8 passes, D*(8+8*24) bytes."""
+    """Stand-alone 'sort HBM GB/s' of the 64-bit entry point: full-entropy keys, 8 passes, D*(8+8*24) bytes."""
     g = torch.Generator(device="cuda"); g.manual_seed(1)
     hi = torch.randint(-2 ** 31, 2 ** 31, (n,), generator=g, dtype=torch.int64, device="cuda")
     lo = torch.randint(0, 2 ** 32, (n,), generator=g, dtype=torch.int64, device="cuda")

@@ -28,7 +28,7 @@ RECORD_DTYPE = np.dtype([
 EXPORTS = [
     "splat_create", "splat_destroy", "splat_upload", "splat_upload_sh", "splat_render",
     "splat_render_host", "splat_render_batch", "splat_render_batch_host", "splat_pack_bgra8", "splat_upload_ply_rows", "splat_frame_status", "splat_debug_fetch",
-    "splat_stage_times", "splat_sort_pairs_u64_u32", "splat_last_error_string", "splat_version",
+    "splat_stage_times", "splat_sort_pairs_u64_u32", "splat_sort_pairs_u32_u32", "splat_last_error_string", "splat_version",
 ]
 
 
@@ -73,6 +73,7 @@ def lib():
         L.splat_stage_times.argtypes = [vp, C.POINTER(C.c_float)]
         L.splat_sort_pairs_u64_u32.argtypes = [vp, vp, vp, vp, vp, vp, C.c_uint64, C.c_int, C.c_int,
                                                C.POINTER(C.c_int)]
+        L.splat_sort_pairs_u32_u32.argtypes = L.splat_sort_pairs_u64_u32.argtypes
         L.splat_last_error_string.restype = C.c_char_p
         L.splat_version.restype = C.c_int
         _LIB = L
@@ -190,8 +191,11 @@ class Context:
         _check(lib().splat_stage_times(self._h, ms), "splat_stage_times")
         return dict(zip(("preprocess", "scan_duplicate", "sort", "ranges", "blend", "total"), list(ms)[:6]))
 
-    def sort_pairs(self, stream_ptr, keys_ptr, vals_ptr, keys_alt_ptr, vals_alt_ptr, n, begin_bit=0, end_bit=64):
+    def sort_pairs(self, stream_ptr, keys_ptr, vals_ptr, keys_alt_ptr, vals_alt_ptr, n, begin_bit=0, end_bit=64,
+                   key_bits=64):
+        """Stand-alone pair sort; key_bits = 64 or 32 (the width frames sort). Returns 1 if the result is in *_alt."""
         res = C.c_int(0)
-        _check(lib().splat_sort_pairs_u64_u32(self._h, stream_ptr, keys_ptr, vals_ptr, keys_alt_ptr, vals_alt_ptr,
-                                              n, begin_bit, end_bit, C.byref(res)), "splat_sort_pairs_u64_u32")
+        fn = lib().splat_sort_pairs_u64_u32 if key_bits == 64 else lib().splat_sort_pairs_u32_u32
+        _check(fn(self._h, stream_ptr, keys_ptr, vals_ptr, keys_alt_ptr, vals_alt_ptr,
+                  n, begin_bit, min(end_bit, key_bits), C.byref(res)), "splat_sort_pairs")
         return res.value

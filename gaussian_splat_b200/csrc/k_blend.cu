@@ -10,22 +10,22 @@
 #include "splat_math.cuh"
 
 // ------------------------------------------------------------------ K4
-// bounds[t] = lower_bound(keys, t << 32) for t = 0..T; tile t owns [bounds[t], bounds[t+1]).
+// bounds[t] = lower_bound(keys, t << 16) for t = 0..T; tile t owns [bounds[t], bounds[t+1]).
 // One warp per boundary, 32 probes per round (5 dependent L2 round trips for D < 32M instead of
 // the 21+ of a scalar binary search; the kernel is pure latency).
-__global__ void __launch_bounds__(256) tile_bounds_kernel(const unsigned long long* __restrict__ keys,
+__global__ void __launch_bounds__(256) tile_bounds_kernel(const unsigned int* __restrict__ keys,
                                                           const FrameCtl* __restrict__ ctl, unsigned int first,
                                                           unsigned int n_bounds, unsigned int* __restrict__ bounds)
 {
     const unsigned int t = first + blockIdx.x * 8u + (threadIdx.x >> 5), lane = threadIdx.x & 31u;
     if (t >= first + n_bounds) return;
     const unsigned int n = ctl->overflow ? 0u : ctl->n_sort;
-    const unsigned long long x = (unsigned long long)t << 32;
+    const unsigned long long x = (unsigned long long)t << 16;      // 64-bit: t == 65536 is past every key
     unsigned int lo = 0, hi = n;
     while (lo < hi) {
         const unsigned int span = hi - lo;
         const unsigned int pos = lo + (unsigned int)(((unsigned long long)(lane + 1) * span) / 33u);
-        const unsigned int c = __popc(__ballot_sync(0xFFFFFFFFu, __ldg(keys + pos) < x));
+        const unsigned int c = __popc(__ballot_sync(0xFFFFFFFFu, (unsigned long long)__ldg(keys + pos) < x));
         const unsigned int new_lo = c == 0 ? lo : lo + (unsigned int)(((unsigned long long)c * span) / 33u) + 1u;
         const unsigned int new_hi = c == 32 ? hi : lo + (unsigned int)(((unsigned long long)(c + 1) * span) / 33u);
         lo = new_lo; hi = new_hi;
@@ -35,7 +35,7 @@ __global__ void __launch_bounds__(256) tile_bounds_kernel(const unsigned long lo
 
 // Only tiles [first_tile, first_tile + n_tiles] get a boundary: with a tile-row band that is the band (the blend
 // reads nothing else), which keeps this latency-bound kernel to one wave of CTAs.
-void launch_tile_bounds(const unsigned long long* keys_sorted, const FrameCtl* ctl, unsigned int first_tile,
+void launch_tile_bounds(const unsigned int* keys_sorted, const FrameCtl* ctl, unsigned int first_tile,
                         unsigned int n_tiles, unsigned int* bounds, cudaStream_t s)
 {
     tile_bounds_kernel<<<(n_tiles + 1 + 7) / 8, 256, 0, s>>>(keys_sorted, ctl, first_tile, n_tiles + 1, bounds);

@@ -32,8 +32,8 @@ struct DupPlan { int d0, d1, t0, t1; unsigned int tmask0, tmask1; };
 __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
     const __grid_constant__ FrameUniforms U, const unsigned long long* __restrict__ binw,
     unsigned int* __restrict__ offsets,
-    unsigned long long* __restrict__ keys, unsigned int* __restrict__ vals,
-    unsigned long long* __restrict__ keys_depth, unsigned int* __restrict__ vals_depth, unsigned long long capacity,
+    unsigned int* __restrict__ keys, unsigned int* __restrict__ vals,
+    unsigned int* __restrict__ keys_depth, unsigned int* __restrict__ vals_depth, unsigned long long capacity,
     FrameCtl* ctl, const unsigned int* __restrict__ tile_sums, const unsigned int* __restrict__ scan_prefix,
     const DupPlan plan, unsigned int n_tiles, unsigned int n_k1_tiles)
 {
@@ -137,12 +137,12 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
                 if (plan.t1 >= 0) warp_hist_inc(s_hist[plan.t1], (t >> 8) & plan.tmask1);
                 const unsigned long long g = (unsigned long long)prefix + j;
                 if (g < capacity) {
-                    // TILE: tile | depth. LAYER50 / MLAB: tile | instance index (arrival order made explicit); LAYER50
-                    // adds a second copy in tile | depth order for the composite.
-                    keys[g] = ((unsigned long long)t << 32) | (arrival ? splat : df);
+                    // TILE: tile | depth. LAYER50 / MLAB: tile alone (slots are in instance order and the sort is
+                    // stable); LAYER50 adds a second copy in tile | depth order for the composite.
+                    keys[g] = (t << 16) | (arrival ? 0u : df);
                     vals[g] = splat;
                     if (layer) {
-                        keys_depth[g] = ((unsigned long long)t << 32) | df;
+                        keys_depth[g] = (t << 16) | df;
                         vals_depth[g] = splat;
                     }
                 }
@@ -158,8 +158,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
 }
 
 void launch_scan_duplicate(const FrameUniforms& U, const unsigned long long* binw,
-                           unsigned int* offsets, unsigned long long* keys, unsigned int* vals,
-                           unsigned long long* keys_depth, unsigned int* vals_depth,
+                           unsigned int* offsets, unsigned int* keys, unsigned int* vals,
+                           unsigned int* keys_depth, unsigned int* vals_depth,
                            unsigned long long capacity, FrameCtl* ctl, const unsigned int* tile_sums,
                            const unsigned int* scan_prefix, SortPlan plan, int sm_count, cudaStream_t s)
 {
@@ -168,8 +168,8 @@ void launch_scan_duplicate(const FrameUniforms& U, const unsigned long long* bin
     for (int p = 0; p < plan.n_pass; ++p) {
         if (plan.shift[p] == 0) dp.d0 = plan.slot[p];
         else if (plan.shift[p] == 8) dp.d1 = plan.slot[p];
-        else if (plan.shift[p] == 32) { dp.t0 = plan.slot[p]; dp.tmask0 = plan.mask[p]; }
-        else if (plan.shift[p] == 40) { dp.t1 = plan.slot[p]; dp.tmask1 = plan.mask[p]; }
+        else if (plan.shift[p] == 16) { dp.t0 = plan.slot[p]; dp.tmask0 = plan.mask[p]; }
+        else if (plan.shift[p] == 24) { dp.t1 = plan.slot[p]; dp.tmask1 = plan.mask[p]; }
     }
     if (dp.t0 < 0) { dp.t0 = FRAME_MAX_PASSES - 1; dp.tmask0 = 0; }      // single-tile frame: no tile digit is sorted; count into an unused row
     const unsigned int n_tiles = (U.n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS;

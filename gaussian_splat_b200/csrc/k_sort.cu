@@ -1,6 +1,6 @@
-// K3: stable LSD "onesweep" radix sort of (uint64 key, uint32 value) pairs, 8-bit digits.
-// One kernel per digit pass; each pass reads and writes every pair exactly once
-// (24 B per pair). Per-warp digit ranks come from __match_any_sync, tile prefixes from an
+// K3: stable LSD "onesweep" radix sort of (key, uint32 value) pairs, 8-bit digits. Keys are 32 bits wide in
+// frames (tile << 16 | half depth: 16 B per pair and pass) and 64 bits wide in the stand-alone entry point
+// (24 B per pair and pass). One kernel per digit pass; each pass reads and writes every pair exactly once. Per-warp digit ranks come from __match_any_sync, tile prefixes from an
 // epoch-tagged decoupled lookback per digit. Replaces the per-pixel insertion sorts of
 // shaders/gaussian_splat_tile.metal:240-249 / gaussian_splat_50layer.metal:198-206 with
 // one global (tile | depth) sort.
@@ -8,9 +8,8 @@
 #include <cstdlib>
 
 #define SORT_WARPS (SORT_THREADS / 32)
+#ifndef LB_DEPTH
 #define LB_DEPTH 8
-#ifndef RANK_SETS
-#define RANK_SETS 4
 #endif
 // -DSORT_PROFILE: thread 0 of every CTA accumulates clock64() per phase into ctl->hist[7][0..7] (tuning aid).
 #ifdef SORT_PROFILE
@@ -19,7 +18,8 @@
 #define PROF(k) do {} while (0)
 #endif
 
-__global__ void __launch_bounds__(256) sort_histogram_kernel(const unsigned long long* __restrict__ keys,
+template <typename KeyT>
+__global__ void __launch_bounds__(256) sort_histogram_kernel(const KeyT* __restrict__ keys,
                                                              unsigned long long n, FrameCtl* ctl,
                                                              const __grid_constant__ SortPlan plan)
 {
@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(256) sort_histogram_kernel(const unsigned long
     __syncthreads();
     const unsigned long long stride = (unsigned long long)gridDim.x * 256ull;
     for (unsigned long long i = (unsigned long long)blockIdx.x * 256ull + threadIdx.x; i < n; i += stride) {
-        const unsigned long long k = __ldg(keys + i);
+        const KeyT k = __ldg(keys + i);
         for (int p = 0; p < plan.n_pass; ++p) atomicAdd(&h[plan.slot[p]][(unsigned int)(k >> plan.shift[p]) & plan.mask[p]], 1u);
     }
     __syncthreads();
@@ -38,13 +38,14 @@ __global__ void __launch_bounds__(256) sort_histogram_kernel(const unsigned long
     }
 }
 
-void launch_sort_histogram(const unsigned long long* keys, unsigned long long n, FrameCtl* ctl, SortPlan plan,
+void launch_sort_histogram(const void* keys, int key_bytes, unsigned long long n, FrameCtl* ctl, SortPlan plan,
                            int sm_count, cudaStream_t s)
 {
     if (n == 0) return;
     unsigned long long blocks = (n + 256ull * 16 - 1) / (256ull * 16);
     if (blocks > (unsigned long long)sm_count * 8) blocks = (unsigned long long)sm_count * 8;
-    sort_histogram_kernel<<<(unsigned int)blocks, 256, 0, s>>>(keys, n, ctl, plan);
+    if (key_bytes == 4) sort_histogram_kernel<unsigned int><<<(unsigned int)blocks, 256, 0, s>>>((const unsigned int*)keys, n, ctl, plan);
+    else sort_histogram_kernel<unsigned long long><<<(unsigned int)blocks, 256, 0, s>>>((const unsigned long long*)keys, n, ctl, plan);
 }
 
 __device__ __forceinline__ void bulk_prefetch_l2(const void* gptr, unsigned int bytes) {   // bytes % 16 == 0
@@ -66,16 +67,19 @@ __device__ __forceinline__ unsigned int block_excl_scan_256(unsigned int v, unsi
     return base + incl - v;
 }
 
-template <int ITEMS>
-__global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 3) onesweep_pass_kernel(
-    const unsigned long long* __restrict__ keys_in, const unsigned int* __restrict__ vals_in,
-    unsigned long long* __restrict__ keys_out, unsigned int* __restrict__ vals_out,
-    FrameCtl* ctl, unsigned long long* status, unsigned int epoch, int pass, int tix, int shift, unsigned int mask)
+struct SortShared { unsigned int gexcl[256], off[256], w[SORT_WARPS], tile[2]; };
+
+template <int ITEMS, typename KeyT, int RANK_SETS>
+__device__ __forceinline__ void onesweep_pass_body(
+    const KeyT* __restrict__ keys_in, const unsigned int* __restrict__ vals_in,
+    KeyT* __restrict__ keys_out, unsigned int* __restrict__ vals_out,
+    FrameCtl* ctl, unsigned long long* status, unsigned int epoch, int pass, int tix, int shift, unsigned int mask,
+    unsigned long long* s_raw, SortShared& sh)
 {
     constexpr int TILE_KEYS = SORT_THREADS * ITEMS;
-    extern __shared__ unsigned long long s_keys[];                 // [TILE_KEYS] keys, then values
-    __shared__ unsigned int s_gexcl[256], s_off[256], s_w[SORT_WARPS];
-    __shared__ unsigned int s_tile[2];
+    KeyT* s_keys = reinterpret_cast<KeyT*>(s_raw);                 // [TILE_KEYS] keys, then values
+    unsigned int* const s_gexcl = sh.gexcl; unsigned int* const s_off = sh.off; unsigned int* const s_w = sh.w;
+    unsigned int* const s_tile = sh.tile;
     unsigned int* s_vals = reinterpret_cast<unsigned int*>(s_keys + TILE_KEYS);
     // per set, warp, digit: peer bitmap of the current round / keys of that digit seen so far (later: tile-local offsets)
     unsigned int (*s_bm)[SORT_WARPS][256] = reinterpret_cast<unsigned int (*)[SORT_WARPS][256]>(s_vals + TILE_KEYS);
@@ -115,13 +119,13 @@ __global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 3) onesweep_pa
         const unsigned int tcount = min((unsigned int)TILE_KEYS, n - tbase);
 
         // ---- load (warp-striped: order (warp, item, lane) == memory order)
-        unsigned long long key[ITEMS];
+        KeyT key[ITEMS];
         unsigned int val[ITEMS];
         const unsigned int wofs = warp * (32 * ITEMS) + lane;
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) {
             const unsigned int li = wofs + i * 32;
-            key[i] = li < tcount ? keys_in[tbase + li] : ~0ull;
+            key[i] = li < tcount ? keys_in[tbase + li] : ~(KeyT)0;
         }
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) {
@@ -136,7 +140,7 @@ __global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 3) onesweep_pa
                 const unsigned int nb = next_ticket * TILE_KEYS;
                 const unsigned int nc = min((unsigned int)TILE_KEYS, n - nb) & ~3u;
                 if (nc) {
-                    bulk_prefetch_l2(keys_in + nb, nc * 8u);
+                    bulk_prefetch_l2(keys_in + nb, nc * (unsigned int)sizeof(KeyT));
                     bulk_prefetch_l2(vals_in + nb, nc * 4u);
                 }
             }
@@ -253,7 +257,7 @@ __global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 3) onesweep_pa
         for (int i = 0; i < ITEMS; ++i) {
             const unsigned int j = tid + i * SORT_THREADS;
             if (j < tcount) {
-                const unsigned long long k = s_keys[j];
+                const KeyT k = s_keys[j];
                 const unsigned int g = s_off[(unsigned int)(k >> shift) & mask] + j;
                 keys_out[g] = k;
                 vals_out[g] = s_vals[j];
@@ -265,21 +269,39 @@ __global__ void __launch_bounds__(SORT_THREADS, ITEMS >= 16 ? 2 : 3) onesweep_pa
 #endif
 }
 
-template <int ITEMS>
-static void run_passes(unsigned long long* ki, unsigned int* vi, unsigned long long* ko, unsigned int* vo, FrameCtl* ctl,
+// SETS / SETS_LONG rank-counter sets: with different values, sorts of more than SORT_LONG pairs would take the
+// SETS_LONG instantiation on the device's own count. Measured 6% slower on long sorts than a kernel with the one
+// body (more spills), so the callers below pass SETS == SETS_LONG and choose on the host's estimate of n.
+#define SORT_LONG 8000000u
+template <int ITEMS, typename KeyT, int SETS, int SETS_LONG, int MIN_CTAS>
+__global__ void __launch_bounds__(SORT_THREADS, MIN_CTAS) onesweep_pass_kernel(
+    const KeyT* __restrict__ keys_in, const unsigned int* __restrict__ vals_in,
+    KeyT* __restrict__ keys_out, unsigned int* __restrict__ vals_out,
+    FrameCtl* ctl, unsigned long long* status, unsigned int epoch, int pass, int tix, int shift, unsigned int mask)
+{
+    extern __shared__ unsigned long long s_raw[];
+    __shared__ SortShared sh;
+    if (SETS_LONG != SETS && ctl->n_sort > SORT_LONG)
+        onesweep_pass_body<ITEMS, KeyT, SETS_LONG>(keys_in, vals_in, keys_out, vals_out, ctl, status, epoch, pass, tix, shift, mask, s_raw, sh);
+    else
+        onesweep_pass_body<ITEMS, KeyT, SETS>(keys_in, vals_in, keys_out, vals_out, ctl, status, epoch, pass, tix, shift, mask, s_raw, sh);
+}
+
+template <int ITEMS, typename KeyT, int SETS, int SETS_LONG, int MIN_CTAS>
+static void run_passes(KeyT* ki, unsigned int* vi, KeyT* ko, unsigned int* vo, FrameCtl* ctl,
                        unsigned long long* sort_status, unsigned int epoch_base, const SortPlan& plan, int grid,
                        cudaStream_t s)
 {
-    constexpr int smem = SORT_THREADS * ITEMS * 12 + RANK_SETS * SORT_WARPS * 256 * 6;
+    constexpr int smem = SORT_THREADS * ITEMS * ((int)sizeof(KeyT) + 4) + (SETS > SETS_LONG ? SETS : SETS_LONG) * SORT_WARPS * 256 * 6;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(onesweep_pass_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaFuncSetAttribute(onesweep_pass_kernel<ITEMS, KeyT, SETS, SETS_LONG, MIN_CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         attr_set = true;
     }
     for (int p = 0; p < plan.n_pass; ++p) {
-        onesweep_pass_kernel<ITEMS><<<grid, SORT_THREADS, smem, s>>>(ki, vi, ko, vo, ctl, sort_status, epoch_base + p,
+        onesweep_pass_kernel<ITEMS, KeyT, SETS, SETS_LONG, MIN_CTAS><<<grid, SORT_THREADS, smem, s>>>(ki, vi, ko, vo, ctl, sort_status, epoch_base + p,
                                                                     plan.slot[p], plan.ticket[p], plan.shift[p], plan.mask[p]);
-        unsigned long long* tk = ki; ki = ko; ko = tk;
+        KeyT* tk = ki; ki = ko; ko = tk;
         unsigned int* tv = vi; vi = vo; vo = tv;
     }
 }
@@ -287,13 +309,23 @@ static void run_passes(unsigned long long* ki, unsigned int* vi, unsigned long l
 // small_tiles: 2048-pair tiles, 3 CTAs per SM. Measured slower than 4096-pair tiles at every size tried
 // (1.6M, 12M, 64M pairs: the per-tile fixed costs dominate), so callers pass false; kept as a tuning
 // knob (SPLAT_SORT_TILE=small|large).
-void launch_radix_sort(unsigned long long* keys, unsigned int* vals, unsigned long long* keys_alt,
-                       unsigned int* vals_alt, FrameCtl* ctl, unsigned long long* sort_status,
+void launch_radix_sort(void* keys, unsigned int* vals, void* keys_alt, unsigned int* vals_alt, int key_bytes,
+                       unsigned long long n_hint, FrameCtl* ctl, unsigned long long* sort_status,
                        unsigned int epoch_base, SortPlan plan, int sm_count, bool small_tiles, cudaStream_t s)
 {
+    if (key_bytes == 4) {
+        // 6144-pair tiles (24 per thread; measured best of 2048 .. 8192: the per-tile fixed costs - counter
+        // clearing, digit scans, lookback - amortise, beyond that registers spill). Four rank-counter sets are
+        // quicker when the sort is one or two waves of tiles, two sets (half the clearing) on long sorts.
+        unsigned int* k0 = (unsigned int*)keys; unsigned int* k1 = (unsigned int*)keys_alt;
+        if (n_hint > SORT_LONG) run_passes<SORT_ITEMS_NARROW, unsigned int, 2, 2, 2>(k0, vals, k1, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * 2, s);
+        else run_passes<SORT_ITEMS_NARROW, unsigned int, 4, 4, 2>(k0, vals, k1, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * 2, s);
+        return;
+    }
     static const char* force = getenv("SPLAT_SORT_TILE");    // tuning knob: "small" | "large"
     if (force && force[0] == 's') small_tiles = true;
     if (force && force[0] == 'l') small_tiles = false;
-    if (small_tiles) run_passes<SORT_ITEMS_SMALL>(keys, vals, keys_alt, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * 3, s);
-    else run_passes<SORT_ITEMS>(keys, vals, keys_alt, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * 2, s);
+    unsigned long long* k0 = (unsigned long long*)keys; unsigned long long* k1 = (unsigned long long*)keys_alt;
+    if (small_tiles) run_passes<SORT_ITEMS_SMALL, unsigned long long, 4, 4, 3>(k0, vals, k1, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * 3, s);
+    else run_passes<SORT_ITEMS, unsigned long long, 4, 4, 2>(k0, vals, k1, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * 2, s);
 }

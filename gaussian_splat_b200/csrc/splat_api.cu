@@ -28,10 +28,10 @@ __global__ void set_n_sort_kernel(FrameCtl* ctl, unsigned int n) { ctl->n_sort =
 // frame entry points use set 0 only; the second set is allocated on the first batch call.
 struct FrameSet {
     splat_record* rec = nullptr; unsigned long long* binw = nullptr; uint32_t* offsets = nullptr;
-    unsigned long long* keys[2] = {nullptr, nullptr}; uint32_t* vals[2] = {nullptr, nullptr};
+    uint32_t* keys[2] = {nullptr, nullptr}; uint32_t* vals[2] = {nullptr, nullptr};
     unsigned long long capacity = 0;
     // LAYER50 only: the same pairs in tile | depth order (allocated on the first LAYER50 frame)
-    unsigned long long* keys_d[2] = {nullptr, nullptr}; uint32_t* vals_d[2] = {nullptr, nullptr}; unsigned long long capacity_d = 0;
+    uint32_t* keys_d[2] = {nullptr, nullptr}; uint32_t* vals_d[2] = {nullptr, nullptr}; unsigned long long capacity_d = 0;
     FrameCtl* ctl = nullptr;
     unsigned int* tile_sums = nullptr;      // K1 pair counts per 512 splats, then K2's tile prefixes
     unsigned long long* sort_status = nullptr; size_t sort_status_tiles = 0;
@@ -45,7 +45,7 @@ struct splat_ctx : FrameSet {
     uint32_t n = 0; size_t n_pad = 0;
     float4 *rot = nullptr, *pos_sx = nullptr, *syz = nullptr, *base_rgb = nullptr, *sh = nullptr, *scr = nullptr; uint16_t* bq = nullptr;
     int sh_degree = 0;
-    unsigned long long* dbg_keys = nullptr; uint32_t* dbg_vals = nullptr; unsigned long long dbg_cap = 0;
+    uint32_t* dbg_keys = nullptr; uint32_t* dbg_vals = nullptr; unsigned long long dbg_cap = 0;
     FrameCtl* ctl_host = nullptr;
     uint32_t frame_no = 0;
     FrameUniforms lastU{}; SortPlan lastPlan{}; int sorted_buf = 0; bool have_frame = false, kept_unsorted = false;
@@ -107,10 +107,10 @@ static int ensure_pairs(splat_ctx* c, unsigned long long cap) {
     free_pairs(c);
     cap = (cap + SORT_TILE_KEYS - 1) / SORT_TILE_KEYS * SORT_TILE_KEYS;
     for (int k = 0; k < 2; ++k) {
-        CK(cudaMalloc(&c->keys[k], cap * 8));
+        CK(cudaMalloc(&c->keys[k], cap * 4));
         CK(cudaMalloc(&c->vals[k], cap * 4));
         CK(cudaMemset(c->vals[k], 0, cap * 4));   // stale slots must stay valid splat indices
-        CK(cudaMemset(c->keys[k], 0, cap * 8));
+        CK(cudaMemset(c->keys[k], 0, cap * 4));
     }
     c->capacity = cap;
     return ensure_sort_status(c, cap);
@@ -380,8 +380,8 @@ static int build_frame(splat_ctx* c, const float* view, const float* proj, int w
     const int tb = tile_bits(T);
     if (tb > 16) ARG_FAIL("splat_render: more than 65536 tiles");
     if (U.tiles_x > 4096 || U.tiles_y > 4096) ARG_FAIL("splat_render: viewport wider or taller than 65536 pixels");
-    // Digit passes of the (tile | half-depth) order: 15 significant depth bits (the sign bit is 0) then the
-    // tile bits. TILE sorts its pairs with all of them. LAYER50 sorts the depth-ordered copy the same way and
+    // Digit passes of the 32-bit (tile << 16 | half-depth) keys: 15 significant depth bits (the sign bit is 0)
+    // then the tile bits. TILE sorts its pairs with all of them. LAYER50 sorts the depth-ordered copy the same way and
     // the arrival-ordered list by the tile digits only (pairs are emitted in instance order and the sort is
     // stable); see layer_plan().
     // MLAB walks its pairs in instance order only: tile-digit passes alone (as layer_plan()).
@@ -391,8 +391,8 @@ static int build_frame(splat_ctx* c, const float* view, const float* proj, int w
         plan.shift[p] = 0; plan.mask[p++] = 0xFF;
         plan.shift[p] = 8; plan.mask[p++] = 0xFF;
     }
-    if (tb > 0) { plan.shift[p] = 32; plan.mask[p++] = tb >= 8 ? 0xFFu : ((1u << tb) - 1u); }
-    if (tb > 8) { plan.shift[p] = 40; plan.mask[p++] = (1u << (tb - 8)) - 1u; }
+    if (tb > 0) { plan.shift[p] = 16; plan.mask[p++] = tb >= 8 ? 0xFFu : ((1u << tb) - 1u); }
+    if (tb > 8) { plan.shift[p] = 24; plan.mask[p++] = (1u << (tb - 8)) - 1u; }
     for (int k = 0; k < SPLAT_MAX_SORT_PASSES; ++k) { plan.slot[k] = k; plan.ticket[k] = k; }
     plan.n_pass = p;
     return SPLAT_OK;
@@ -403,7 +403,7 @@ static int build_frame(splat_ctx* c, const float* view, const float* proj, int w
 static SortPlan layer_plan(const SortPlan& full) {
     SortPlan a{};
     for (int p = 0; p < full.n_pass; ++p)
-        if (full.shift[p] >= 32) {
+        if (full.shift[p] >= 16) {
             a.shift[a.n_pass] = full.shift[p]; a.mask[a.n_pass] = full.mask[p];
             a.slot[a.n_pass] = full.slot[p]; a.ticket[a.n_pass] = 4 + a.n_pass;
             ++a.n_pass;
@@ -424,16 +424,17 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
     if (keep && c->dbg_cap < c->capacity) {
         CK(cudaDeviceSynchronize());
         cudaFree(c->dbg_keys); cudaFree(c->dbg_vals); c->dbg_keys = nullptr; c->dbg_vals = nullptr;
-        CK(cudaMalloc(&c->dbg_keys, c->capacity * 8)); CK(cudaMalloc(&c->dbg_vals, c->capacity * 4));
+        CK(cudaMalloc(&c->dbg_keys, c->capacity * 4)); CK(cudaMalloc(&c->dbg_vals, c->capacity * 4));
         c->dbg_cap = c->capacity;
     }
     const bool layer = U.mode == SPLAT_MODE_LAYER50;
+    const unsigned long long pairs_hint = c->ctl_host->total_pairs;     // of the last frame whose status was read back; shapes the sort
     if (layer && c->capacity_d < c->capacity) {
         CK(cudaDeviceSynchronize());
         for (int k = 0; k < 2; ++k) {
             cudaFree(c->keys_d[k]); cudaFree(c->vals_d[k]); c->keys_d[k] = nullptr; c->vals_d[k] = nullptr;
-            CK(cudaMalloc(&c->keys_d[k], c->capacity * 8)); CK(cudaMalloc(&c->vals_d[k], c->capacity * 4));
-            CK(cudaMemset(c->vals_d[k], 0, c->capacity * 4)); CK(cudaMemset(c->keys_d[k], 0, c->capacity * 8));
+            CK(cudaMalloc(&c->keys_d[k], c->capacity * 4)); CK(cudaMalloc(&c->vals_d[k], c->capacity * 4));
+            CK(cudaMemset(c->vals_d[k], 0, c->capacity * 4)); CK(cudaMemset(c->keys_d[k], 0, c->capacity * 4));
         }
         c->capacity_d = c->capacity;
     }
@@ -450,17 +451,17 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
         launch_scan_duplicate(U, c->binw, c->offsets, c->keys[0], c->vals[0], layer ? c->keys_d[0] : nullptr,
                               layer ? c->vals_d[0] : nullptr, c->capacity, c->ctl, c->tile_sums, scan_prefix, plan, c->sm_count, s);
         if (keep) {
-            CK(cudaMemcpyAsync(c->dbg_keys, c->keys[0], c->capacity * 8, cudaMemcpyDeviceToDevice, s));
+            CK(cudaMemcpyAsync(c->dbg_keys, c->keys[0], c->capacity * 4, cudaMemcpyDeviceToDevice, s));
             CK(cudaMemcpyAsync(c->dbg_vals, c->vals[0], c->capacity * 4, cudaMemcpyDeviceToDevice, s));
         }
         if (timed) CK(cudaEventRecord(c->ev[2], s));
         if (layer) {
-            launch_radix_sort(c->keys_d[0], c->vals_d[0], c->keys_d[1], c->vals_d[1], c->ctl, c->sort_status, epoch + 1, plan,
+            launch_radix_sort(c->keys_d[0], c->vals_d[0], c->keys_d[1], c->vals_d[1], 4, pairs_hint, c->ctl, c->sort_status, epoch + 1, plan,
                               c->sm_count, false, s);
-            launch_radix_sort(c->keys[0], c->vals[0], c->keys[1], c->vals[1], c->ctl, c->sort_status, epoch + 1 + plan.n_pass,
+            launch_radix_sort(c->keys[0], c->vals[0], c->keys[1], c->vals[1], 4, pairs_hint, c->ctl, c->sort_status, epoch + 1 + plan.n_pass,
                               layer_plan(plan), c->sm_count, false, s);
         } else {
-            launch_radix_sort(c->keys[0], c->vals[0], c->keys[1], c->vals[1], c->ctl, c->sort_status, epoch + 1, plan,
+            launch_radix_sort(c->keys[0], c->vals[0], c->keys[1], c->vals[1], 4, pairs_hint, c->ctl, c->sort_status, epoch + 1, plan,
                               c->sm_count, false, s);
         }
     } else if (timed) { CK(cudaEventRecord(c->ev[1], s)); CK(cudaEventRecord(c->ev[2], s)); }
@@ -766,6 +767,16 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
         std::vector<unsigned long long> w(c->n);
         if (c->n) CK(cudaMemcpy(w.data(), c->binw, (size_t)c->n * 8, cudaMemcpyDeviceToHost));
         for (uint32_t i = 0; i < c->n; ++i) ((uint32_t*)dst)[i] = binw_count(w[i]);
+    } else if (what == SPLAT_FETCH_KEYS_UNSORTED || what == SPLAT_FETCH_KEYS_SORTED) {
+        // presented in the documented 64-bit form, tile << 32 | half-depth field (TILE) or | instance index (lists kept
+        // in instance order); the device holds tile << 16 | depth, and the instance index is the pair's value
+        const bool sorted = what == SPLAT_FETCH_KEYS_SORTED;
+        const bool by_instance = c->lastU.mode != SPLAT_MODE_TILE;
+        std::vector<uint32_t> k32(D), v32(by_instance ? D : 0);
+        if (D) CK(cudaMemcpy(k32.data(), src, D * 4, cudaMemcpyDeviceToHost));
+        if (D && by_instance) CK(cudaMemcpy(v32.data(), sorted ? c->vals[c->sorted_buf] : c->dbg_vals, D * 4, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < D; ++i)
+            ((uint64_t*)dst)[i] = ((uint64_t)(k32[i] >> 16) << 32) | (by_instance ? v32[i] : (k32[i] & 0xFFFFu));
     } else if (need) CK(cudaMemcpy(dst, src, need, cudaMemcpyDeviceToHost));
     if (what == SPLAT_FETCH_RECORDS && c->n) {
         // culled splats have no record written: present them zeroed
@@ -803,11 +814,11 @@ int splat_stage_times(splat_ctx* c, float ms[8]) {
     return SPLAT_OK;
 }
 
-int splat_sort_pairs_u64_u32(splat_ctx* c, void* stream, uint64_t* keys, uint32_t* vals, uint64_t* keys_alt,
-                             uint32_t* vals_alt, uint64_t n, int begin_bit, int end_bit, int* result_in_alt) {
+static int sort_pairs_impl(splat_ctx* c, void* stream, void* keys, uint32_t* vals, void* keys_alt, uint32_t* vals_alt,
+                           uint64_t n, int begin_bit, int end_bit, int key_bytes, int* result_in_alt) {
     if (!c) ARG_FAIL("splat_sort_pairs: ctx is NULL");
     if (n && (!keys || !vals || !keys_alt || !vals_alt)) ARG_FAIL("splat_sort_pairs: NULL buffer");
-    if (begin_bit < 0 || end_bit > 64 || begin_bit > end_bit) ARG_FAIL("splat_sort_pairs: bad bit range");
+    if (begin_bit < 0 || end_bit > key_bytes * 8 || begin_bit > end_bit) ARG_FAIL("splat_sort_pairs: bad bit range");
     if (n >= 0xFFFF0000ull) ARG_FAIL("splat_sort_pairs: n must be below 2^32");
     CK(cudaSetDevice(c->device));
     SortPlan plan{};
@@ -825,12 +836,22 @@ int splat_sort_pairs_u64_u32(splat_ctx* c, void* stream, uint64_t* keys, uint32_
     if (c->frame_no >= (1u << 25)) c->frame_no = 1;
     CK(cudaMemsetAsync(c->ctl, 0, sizeof(FrameCtl), s));
     set_n_sort_kernel<<<1, 1, 0, s>>>(c->ctl, (unsigned int)n);
-    launch_sort_histogram((const unsigned long long*)keys, n, c->ctl, plan, c->sm_count, s);
-    launch_radix_sort((unsigned long long*)keys, vals, (unsigned long long*)keys_alt, vals_alt, c->ctl, c->sort_status,
+    launch_sort_histogram(keys, key_bytes, n, c->ctl, plan, c->sm_count, s);
+    launch_radix_sort(keys, vals, keys_alt, vals_alt, key_bytes, n, c->ctl, c->sort_status,
                       c->frame_no * 16u + 1, plan, c->sm_count, false, s);
     CK(cudaGetLastError());
     c->have_frame = false;
     return SPLAT_OK;
+}
+
+int splat_sort_pairs_u64_u32(splat_ctx* c, void* stream, uint64_t* keys, uint32_t* vals, uint64_t* keys_alt,
+                             uint32_t* vals_alt, uint64_t n, int begin_bit, int end_bit, int* result_in_alt) {
+    return sort_pairs_impl(c, stream, keys, vals, keys_alt, vals_alt, n, begin_bit, end_bit, 8, result_in_alt);
+}
+
+int splat_sort_pairs_u32_u32(splat_ctx* c, void* stream, uint32_t* keys, uint32_t* vals, uint32_t* keys_alt,
+                             uint32_t* vals_alt, uint64_t n, int begin_bit, int end_bit, int* result_in_alt) {
+    return sort_pairs_impl(c, stream, keys, vals, keys_alt, vals_alt, n, begin_bit, end_bit, 4, result_in_alt);
 }
 
 }  // extern "C"

@@ -9,6 +9,7 @@
 #define SORT_THREADS 256
 #define SORT_ITEMS 16
 #define SORT_ITEMS_SMALL 8
+#define SORT_ITEMS_NARROW 24                         // 32-bit keys: 6144 pairs per tile
 #define SORT_TILE_KEYS (SORT_THREADS * SORT_ITEMS)   // keys per onesweep tile (large sorts)
 #define SORT_TILE_KEYS_SMALL (SORT_THREADS * SORT_ITEMS_SMALL)  // frame-sized sorts
 #define SCAN_THREADS 256
@@ -102,23 +103,27 @@ void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_reco
                        unsigned int* tile_sums, unsigned int* scan_prefix, unsigned long long capacity, FrameCtl* ctl,
                        cudaStream_t s);
 void launch_scan_duplicate(const FrameUniforms& U, const unsigned long long* binw,
-                           unsigned int* offsets, unsigned long long* keys, unsigned int* vals,
-                           unsigned long long* keys_depth, unsigned int* vals_depth,
+                           unsigned int* offsets, unsigned int* keys, unsigned int* vals,
+                           unsigned int* keys_depth, unsigned int* vals_depth,
                            unsigned long long capacity, FrameCtl* ctl, const unsigned int* tile_sums,
                            const unsigned int* scan_prefix, SortPlan plan, int sm_count, cudaStream_t s);
-// LAYER50 keeps two orders of the same pairs: (keys, vals) = tile | instance index (arrival order, D3) and
-// (keys_depth, vals_depth) = tile | half-depth field (composite order). keys_depth may be NULL (TILE mode).
+// Frame keys are 32 bits: tile << 16 | half-depth field (TILE), or tile << 16 alone for a list kept in instance
+// order (pairs are emitted in instance order and the sort is stable, so only the tile digits are sorted).
+// LAYER50 keeps two orders of the same pairs: (keys, vals) in arrival order (D3) and (keys_depth, vals_depth) in
+// tile | depth order for the composite. keys_depth may be NULL (TILE, MLAB).
 // Per-pass digit histograms of keys[0..n) into ctl->hist (stand-alone sort only; frames get
 // them from the duplication kernel).
-void launch_sort_histogram(const unsigned long long* keys, unsigned long long n, FrameCtl* ctl, SortPlan plan,
+void launch_sort_histogram(const void* keys, int key_bytes, unsigned long long n, FrameCtl* ctl, SortPlan plan,
                            int sm_count, cudaStream_t s);
 // Sorts n pairs, n read from ctl->n_sort on the device. Result lands in (keys, vals) when
 // plan.n_pass is even, in (keys_alt, vals_alt) when odd. Uses epochs epoch_base .. +n_pass-1.
-void launch_radix_sort(unsigned long long* keys, unsigned int* vals, unsigned long long* keys_alt,
-                       unsigned int* vals_alt, FrameCtl* ctl, unsigned long long* sort_status,
+// key_bytes: 4 (frame keys, tile << 16 | half depth) or 8 (stand-alone entry point). n_hint: the host's estimate of n
+// (the pair count it last read back; 0 = unknown), used only to pick a kernel shape.
+void launch_radix_sort(void* keys, unsigned int* vals, void* keys_alt, unsigned int* vals_alt, int key_bytes,
+                       unsigned long long n_hint, FrameCtl* ctl, unsigned long long* sort_status,
                        unsigned int epoch_base, SortPlan plan, int sm_count, bool small_tiles, cudaStream_t s);
 // bounds[t] = first sorted pair of tile t (t = 0..n_tiles); tile t owns [bounds[t], bounds[t+1]).
-void launch_tile_bounds(const unsigned long long* keys_sorted, const FrameCtl* ctl, unsigned int first_tile,
+void launch_tile_bounds(const unsigned int* keys_sorted, const FrameCtl* ctl, unsigned int first_tile,
                         unsigned int n_tiles, unsigned int* bounds, cudaStream_t s);
 void launch_pack_bgra8(const void* fb_half4, void* bgra8, size_t n_pixels, cudaStream_t s);
 cudaError_t launch_ply_decode_chunk(const float* rows_dev, unsigned int n_rows, unsigned int stride, const int* slot_dst_dev,

@@ -151,6 +151,11 @@ int splat_stage_times(splat_ctx* ctx, float ms[8]);
 int splat_sort_pairs_u64_u32(splat_ctx* ctx, void* stream, uint64_t* keys, uint32_t* vals,
                              uint64_t* keys_alt, uint32_t* vals_alt, uint64_t n,
                              int begin_bit, int end_bit, int* result_in_alt);
+/* The same sort on 32-bit keys, the width the frame pipeline itself sorts (tile << 16 | half depth):
+ * 16 B per pair and pass instead of 24. end_bit <= 32. */
+int splat_sort_pairs_u32_u32(splat_ctx* ctx, void* stream, uint32_t* keys, uint32_t* vals,
+                             uint32_t* keys_alt, uint32_t* vals_alt, uint64_t n,
+                             int begin_bit, int end_bit, int* result_in_alt);
 
 /* GPU-side PLY vertex decode (the step before the path): `rows_host` is the binary body of a PLY vertex
  * element, n_rows rows of stride_floats 4-byte little-endian floats (the reference reads every property as

@@ -161,6 +161,28 @@ def test_sort_standalone(gpu_ctx):
         assert np.array_equal(rv.cpu().numpy().view(np.uint32), ev)
 
 
+def test_sort_standalone_32bit_keys(gpu_ctx):
+    """The key width frames sort (tile << 16 | half depth). Sizes straddle the pair-tile size; duplicates test stability."""
+    import torch
+    from oracle import oracle as O
+    rng = np.random.default_rng(9)
+    for n, bits, dup in ((1, 32, False), (6143, 32, False), (6145, 32, True), (300001, 32, False), (200000, 29, True), (50000, 9, False)):
+        k = rng.integers(0, 2 ** 32, n, dtype=np.uint64)
+        if dup:
+            k = ((k & 0x3FF) << 16) | ((k >> 40) & 3)      # few distinct keys, long runs of equal ones
+        k = (k & ((1 << bits) - 1)).astype(np.uint32)
+        v = np.arange(n, dtype=np.uint32)
+        kd, vd = torch.from_numpy(k.view(np.int32)).cuda(), torch.from_numpy(v.view(np.int32)).cuda()
+        ka, va = torch.empty_like(kd), torch.empty_like(vd)
+        alt = gpu_ctx.sort_pairs(torch.cuda.current_stream().cuda_stream, kd.data_ptr(), vd.data_ptr(),
+                                 ka.data_ptr(), va.data_ptr(), n, 0, bits, key_bits=32)
+        torch.cuda.synchronize()
+        rk, rv = (ka, va) if alt else (kd, vd)
+        ek, ev = O.sort_pairs(k.astype(np.uint64), v)
+        assert np.array_equal(rk.cpu().numpy().view(np.uint32).astype(np.uint64), ek)
+        assert np.array_equal(rv.cpu().numpy().view(np.uint32), ev)
+
+
 def test_render_host_matches_device(gpu_ctx, small_scene):
     from gaussian_splat_b200 import capi
     from oracle import oracle as O
