@@ -11,7 +11,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsplat_cuda.so")
+# SPLAT_CUDA_LIB: another build of the same library (tuning variants, `make -C csrc variant NAME=...`)
+LIB_PATH = os.environ.get("SPLAT_CUDA_LIB") or os.path.join(_HERE, "libsplat_cuda.so")
 
 MODE_TILE, MODE_LAYER50, MODE_MLAB = 0, 1, 2
 ORDER_NEAR_FIRST, ORDER_REFERENCE = 0, 1

@@ -1,7 +1,7 @@
 // K3: stable LSD "onesweep" radix sort of (key, uint32 value) pairs, 8-bit digits. Keys are 32 bits wide in
 // frames (tile << 16 | half depth: 16 B per pair and pass) and 64 bits wide in the stand-alone entry point
-// (24 B per pair and pass). One kernel per digit pass; each pass reads and writes every pair exactly once. Per-warp digit ranks come from __match_any_sync, tile prefixes from an
-// epoch-tagged decoupled lookback per digit. Replaces the per-pixel insertion sorts of
+// (24 B per pair and pass). One kernel per digit pass; each pass reads and writes every pair exactly once. Per-warp
+// digit ranks come from eight ballots per key, tile prefixes from an epoch-tagged decoupled lookback per digit. Replaces the per-pixel insertion sorts of
 // shaders/gaussian_splat_tile.metal:240-249 / gaussian_splat_50layer.metal:198-206 with
 // one global (tile | depth) sort.
 #include "splat_internal.cuh"
@@ -52,6 +52,18 @@ __device__ __forceinline__ void bulk_prefetch_l2(const void* gptr, unsigned int 
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gptr), "r"(bytes) : "memory");
 }
 
+// peers &= lanes whose digit agrees with mine in the bit `bitmask`: test, vote, select, one three-input logic op
+// (ptxas sets the eight predicates of a digit with one R2P).
+__device__ __forceinline__ unsigned int ballot_match_step(unsigned int peers, unsigned int d, unsigned int bitmask) {
+    asm("{\n\t.reg .pred q;\n\t.reg .b32 t, m, nb;\n\t"
+        "and.b32 t, %1, %2;\n\tsetp.ne.u32 q, t, 0;\n\t"
+        "vote.sync.ballot.b32 m, q, 0xffffffff;\n\t"
+        "selp.b32 nb, 0, 0xffffffff, q;\n\t"
+        "lop3.b32 %0, %0, m, nb, 0x60;\n\t}"          // peers & (m ^ nb)
+        : "+r"(peers) : "r"(d), "r"(bitmask));
+    return peers;
+}
+
 // Exclusive scan of one value per thread over a 256-thread block. s_w: SORT_WARPS words.
 __device__ __forceinline__ unsigned int block_excl_scan_256(unsigned int v, unsigned int* s_w, unsigned int& total) {
     const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -81,9 +93,8 @@ __device__ __forceinline__ void onesweep_pass_body(
     unsigned int* const s_gexcl = sh.gexcl; unsigned int* const s_off = sh.off; unsigned int* const s_w = sh.w;
     unsigned int* const s_tile = sh.tile;
     unsigned int* s_vals = reinterpret_cast<unsigned int*>(s_keys + TILE_KEYS);
-    // per set, warp, digit: peer bitmap of the current round / keys of that digit seen so far (later: tile-local offsets)
-    unsigned int (*s_bm)[SORT_WARPS][256] = reinterpret_cast<unsigned int (*)[SORT_WARPS][256]>(s_vals + TILE_KEYS);
-    unsigned short (*s_wh)[SORT_WARPS][256] = reinterpret_cast<unsigned short (*)[SORT_WARPS][256]>(s_bm + RANK_SETS);
+    // per set, warp, digit: keys of that digit seen so far in the warp (later: tile-local offsets)
+    unsigned short (*s_wh)[SORT_WARPS][256] = reinterpret_cast<unsigned short (*)[SORT_WARPS][256]>(s_vals + TILE_KEYS);
 
     if (ctl->overflow) return;
     const unsigned int n = ctl->n_sort;
@@ -146,9 +157,9 @@ __device__ __forceinline__ void onesweep_pass_body(
             }
         }
 #pragma unroll
-        for (int k = 0; k < 8; ++k)
+        for (int k = 0; k < 4; ++k)     // 256 16-bit counters per (set, warp) = 128 words
 #pragma unroll
-            for (int c = 0; c < RANK_SETS; ++c) { s_wh[c][warp][lane + k * 32] = 0; s_bm[c][warp][lane + k * 32] = 0; }
+            for (int c = 0; c < RANK_SETS; ++c) reinterpret_cast<unsigned int*>(&s_wh[c][warp][0])[lane + k * 32] = 0u;
         __syncwarp();
 #ifdef SORT_PROFILE
         { unsigned long long x_ = 0;
@@ -158,14 +169,16 @@ __device__ __forceinline__ void onesweep_pass_body(
         PROF(1);
 #endif
 
-        // ---- per-warp ranks through a shared-memory "match": every lane ORs its lane bit into the
-        // word of its digit, reads back the peer mask together with the running count of that digit
-        // (one 64-bit word: lo = peers of this round, hi = keys of this digit in earlier rounds), and
-        // the lowest peer folds the round into the count. 3 shared-memory instructions per key instead
-        // of a hardware match.any (ADU-bound: 70% of that pipe at 64M pairs) or 8 ballots + 8 logic ops.
-        // RANK_SETS independent counter sets (items [c*ITEMS/SETS, (c+1)*ITEMS/SETS) use set c) give
-        // that many independent shared-memory chains per warp and share the three warp barriers
-        // (measured at 64M pairs: 11.9K -> 6.8K cycles per tile going from 1 to 2 sets).
+        // ---- per-warp ranks. Peer mask of a key = AND over the digit's eight bits of (ballot of that bit,
+        // complemented where the key's bit is clear): registers and the vote unit only. The running count of
+        // the digit in this warp lives in a 16-bit shared counter: every lane reads it, the lowest peer adds
+        // the round's peers. History at 64M pairs: hardware match.any saturated the ADU pipe (70%, about 64
+        // cycles per MATCH); a shared-memory bitmap match (atomicOr, load, clearing store per key, 4 counter
+        // sets) held the LSU pipe 81% busy, an ATOMS costing about two LSU cycles per lane; the ballots need no
+        // bitmap, so the LSU pipe drops to 61% and one counter set (least clearing) is the quickest:
+        // 2.92 -> 3.19 TB/s, and the frame's four passes 77 -> 73 us.
+        // RANK_SETS independent counter sets (items [c*ITEMS/SETS, (c+1)*ITEMS/SETS) use set c) share the two
+        // warp barriers of a round.
         unsigned int rank[ITEMS];
         constexpr int PER_SET = ITEMS / RANK_SETS;
 #pragma unroll
@@ -174,22 +187,18 @@ __device__ __forceinline__ void onesweep_pass_body(
 #pragma unroll
             for (int c = 0; c < RANK_SETS; ++c) {
                 dd[c] = (unsigned int)(key[c * PER_SET + i] >> shift) & mask;
-                atomicOr(&s_bm[c][warp][dd[c]], 1u << lane);
-            }
-            __syncwarp();
-#pragma unroll
-            for (int c = 0; c < RANK_SETS; ++c) {
-                peers[c] = *reinterpret_cast<volatile unsigned int*>(&s_bm[c][warp][dd[c]]);
                 before[c] = *reinterpret_cast<volatile unsigned short*>(&s_wh[c][warp][dd[c]]);
-                rank[c * PER_SET + i] = before[c] + __popc(peers[c] & lt_mask);
+                unsigned int p = 0xFFFFFFFFu;
+#pragma unroll
+                for (int b = 0; b < 8; ++b) p = ballot_match_step(p, dd[c], 1u << b);
+                peers[c] = p;
+                rank[c * PER_SET + i] = before[c] + __popc(p & lt_mask);
             }
             __syncwarp();
 #pragma unroll
             for (int c = 0; c < RANK_SETS; ++c)
-                if ((peers[c] & lt_mask) == 0) {
-                    *reinterpret_cast<volatile unsigned int*>(&s_bm[c][warp][dd[c]]) = 0u;
+                if ((peers[c] & lt_mask) == 0)
                     *reinterpret_cast<volatile unsigned short*>(&s_wh[c][warp][dd[c]]) = (unsigned short)(before[c] + __popc(peers[c]));
-                }
             __syncwarp();
         }
         __syncthreads();
@@ -273,6 +282,27 @@ __device__ __forceinline__ void onesweep_pass_body(
 // SETS_LONG instantiation on the device's own count. Measured 6% slower on long sorts than a kernel with the one
 // body (more spills), so the callers below pass SETS == SETS_LONG and choose on the host's estimate of n.
 #define SORT_LONG 8000000u
+#ifndef K_ITEMS_WIDE
+#define K_ITEMS_WIDE SORT_ITEMS
+#endif
+#ifndef K_CTAS_WIDE
+#define K_CTAS_WIDE 2
+#endif
+#ifndef K_CTAS_NARROW
+#define K_CTAS_NARROW 2
+#endif
+#ifndef K_ITEMS_NARROW
+#define K_ITEMS_NARROW SORT_ITEMS_NARROW
+#endif
+#ifndef SORT_SETS
+#define SORT_SETS 1          // 32-bit keys, frame-sized sorts
+#endif
+#ifndef SORT_SETS_LONG
+#define SORT_SETS_LONG 1     // 32-bit keys, more than SORT_LONG pairs
+#endif
+#ifndef SORT_SETS_WIDE
+#define SORT_SETS_WIDE 1     // 64-bit keys
+#endif
 template <int ITEMS, typename KeyT, int SETS, int SETS_LONG, int MIN_CTAS>
 __global__ void __launch_bounds__(SORT_THREADS, MIN_CTAS) onesweep_pass_kernel(
     const KeyT* __restrict__ keys_in, const unsigned int* __restrict__ vals_in,
@@ -292,7 +322,7 @@ static void run_passes(KeyT* ki, unsigned int* vi, KeyT* ko, unsigned int* vo, F
                        unsigned long long* sort_status, unsigned int epoch_base, const SortPlan& plan, int grid,
                        cudaStream_t s)
 {
-    constexpr int smem = SORT_THREADS * ITEMS * ((int)sizeof(KeyT) + 4) + (SETS > SETS_LONG ? SETS : SETS_LONG) * SORT_WARPS * 256 * 6;
+    constexpr int smem = SORT_THREADS * ITEMS * ((int)sizeof(KeyT) + 4) + (SETS > SETS_LONG ? SETS : SETS_LONG) * SORT_WARPS * 256 * 2;
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(onesweep_pass_kernel<ITEMS, KeyT, SETS, SETS_LONG, MIN_CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -315,11 +345,10 @@ void launch_radix_sort(void* keys, unsigned int* vals, void* keys_alt, unsigned 
 {
     if (key_bytes == 4) {
         // 6144-pair tiles (24 per thread; measured best of 2048 .. 8192: the per-tile fixed costs - counter
-        // clearing, digit scans, lookback - amortise, beyond that registers spill). Four rank-counter sets are
-        // quicker when the sort is one or two waves of tiles, two sets (half the clearing) on long sorts.
+        // clearing, digit scans, lookback - amortise, beyond that registers spill).
         unsigned int* k0 = (unsigned int*)keys; unsigned int* k1 = (unsigned int*)keys_alt;
-        if (n_hint > SORT_LONG) run_passes<SORT_ITEMS_NARROW, unsigned int, 2, 2, 2>(k0, vals, k1, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * 2, s);
-        else run_passes<SORT_ITEMS_NARROW, unsigned int, 4, 4, 2>(k0, vals, k1, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * 2, s);
+        if (n_hint > SORT_LONG) run_passes<K_ITEMS_NARROW, unsigned int, SORT_SETS_LONG, SORT_SETS_LONG, K_CTAS_NARROW>(k0, vals, k1, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * K_CTAS_NARROW, s);
+        else run_passes<K_ITEMS_NARROW, unsigned int, SORT_SETS, SORT_SETS, K_CTAS_NARROW>(k0, vals, k1, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * K_CTAS_NARROW, s);
         return;
     }
     static const char* force = getenv("SPLAT_SORT_TILE");    // tuning knob: "small" | "large"
@@ -327,5 +356,5 @@ void launch_radix_sort(void* keys, unsigned int* vals, void* keys_alt, unsigned 
     if (force && force[0] == 'l') small_tiles = false;
     unsigned long long* k0 = (unsigned long long*)keys; unsigned long long* k1 = (unsigned long long*)keys_alt;
     if (small_tiles) run_passes<SORT_ITEMS_SMALL, unsigned long long, 4, 4, 3>(k0, vals, k1, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * 3, s);
-    else run_passes<SORT_ITEMS, unsigned long long, 4, 4, 2>(k0, vals, k1, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * 2, s);
+    else run_passes<K_ITEMS_WIDE, unsigned long long, SORT_SETS_WIDE, SORT_SETS_WIDE, K_CTAS_WIDE>(k0, vals, k1, vals_alt, ctl, sort_status, epoch_base, plan, sm_count * K_CTAS_WIDE, s);
 }
