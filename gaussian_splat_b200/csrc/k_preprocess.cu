@@ -7,7 +7,8 @@
 __global__ void __launch_bounds__(256) upload_soa_kernel(const float* __restrict__ aos, unsigned int n,
                                                          float4* __restrict__ rot, float4* __restrict__ pos_sx,
                                                          float4* __restrict__ syz_op_rg, uint16_t* __restrict__ bq,
-                                                         float4* __restrict__ base_rgb, float4* __restrict__ scr)
+                                                         float4* __restrict__ base_rgb, float4* __restrict__ scr,
+                                                         float4* __restrict__ row)
 {
     // Stage 256 rows (256*14 floats) through shared memory so the AoS read is coalesced.
     __shared__ float s[256 * 14];
@@ -19,14 +20,19 @@ __global__ void __launch_bounds__(256) upload_soa_kernel(const float* __restrict
     if (threadIdx.x >= rows) return;
     const float* r = s + threadIdx.x * 14;   // stride 14 words: conflict-free enough (gcd(14,32)=2)
     const unsigned int i = base + threadIdx.x;
-    rot[i] = make_float4(r[0], r[1], r[2], r[3]);
-    pos_sx[i] = make_float4(r[7], r[8], r[9], r[4]);
+    const float4 v_rot = make_float4(r[0], r[1], r[2], r[3]), v_pos = make_float4(r[7], r[8], r[9], r[4]);
     const unsigned int rg = (unsigned int)__half_as_ushort(__float2half_rn(r[10])) |
                             ((unsigned int)__half_as_ushort(__float2half_rn(r[11])) << 16);
-    syz_op_rg[i] = make_float4(r[5], r[6], r[13], __uint_as_float(rg));
-    bq[i] = __half_as_ushort(__float2half_rn(r[12]));
+    const float4 v_syz = make_float4(r[5], r[6], r[13], __uint_as_float(rg));
+    const unsigned int v_b = __half_as_ushort(__float2half_rn(r[12]));
+    rot[i] = v_rot; pos_sx[i] = v_pos; syz_op_rg[i] = v_syz; bq[i] = (uint16_t)v_b;
     base_rgb[i] = make_float4(r[10], r[11], r[12], 0.0f);
     scr[i] = make_float4(r[7], r[8], r[9], fmaxf(r[4], fmaxf(r[5], r[6])));     // all the screening kernel reads: 16 B / splat
+    // the same attributes once more as one aligned 64-byte row: what a band frame's survivors gather (one DRAM
+    // burst instead of four 32-byte sectors of four planes)
+    float4* rw = row + (size_t)i * 4;
+    rw[0] = v_rot; rw[1] = v_pos; rw[2] = v_syz;
+    rw[3] = make_float4(__uint_as_float(v_b), 0.0f, 0.0f, 0.0f);
 }
 
 // f_rest rows (45 floats, channel-major as src/ply_loader.cpp:76-81 stores them) -> 12 float4 planes,
@@ -61,10 +67,10 @@ void launch_upload_sh(const float* sh_rest45_dev, unsigned int n, size_t n_pad, 
 }
 
 void launch_upload_soa(const float* aos_dev, unsigned int n, float4* rot, float4* pos_sx, float4* syz_op_rg,
-                       uint16_t* b, float4* base_rgb, float4* scr, cudaStream_t s)
+                       uint16_t* b, float4* base_rgb, float4* scr, float4* row, cudaStream_t s)
 {
     if (n == 0) return;
-    upload_soa_kernel<<<(n + 255) / 256, 256, 0, s>>>(aos_dev, n, rot, pos_sx, syz_op_rg, b, base_rgb, scr);
+    upload_soa_kernel<<<(n + 255) / 256, 256, 0, s>>>(aos_dev, n, rot, pos_sx, syz_op_rg, b, base_rgb, scr, row);
 }
 
 #define K1_TILE (SCAN_TILE_ITEMS / 2)      // splats per pair-count cell (two cells per duplication tile)
@@ -72,8 +78,9 @@ void launch_upload_soa(const float* aos_dev, unsigned int n, float4* rot, float4
 // Screening: can this splat possibly produce a tile (in the viewport and, with tile-row bands, in the
 // band)? Fast approximate arithmetic (FMA, rcp.approx, sqrt.approx: ~70 instructions against ~600 for the
 // exactly rounded pipeline) with 5% + 2 px slack, so it only ever says "no" when the exact path would too:
-// the quad's pixel half-extent is at most 3*sqrt(trace(Cov2D)) and trace(J C J^T) <= ||J||_F^2 *
-// ||V3x3||_F^2 * max(scale)^2 (+2e-4 for the two epsilons). Splats too close to the eye plane for the
+// the quad's pixel half-extent is at most 3*sqrt(trace(Cov2D)) and trace(J W S W^T J^T) <= ||J||_F^2 *
+// lambda_max(W^T W) * max(scale)^2 (+2e-4 for the two epsilons), W the view matrix's 3x3 block; the host
+// passes a Gershgorin bound on lambda_max (1 for a rigid view, where the Frobenius norm it replaced gave 3). Splats too close to the eye plane for the
 // bound to be trusted are kept. Results never depend on it; it exists so that the exact path runs on
 // warps full of survivors instead of on every warp that holds one (splat order is unrelated to screen
 // position: at 1M/1080p 46% of the splats are culled, with tile-row bands up to 97%).
@@ -158,9 +165,10 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
     const unsigned int n_keep = s_count;
     for (unsigned int j = tid; j < n_keep; j += 256u) {
         const unsigned int li = s_list[j], i = base + li;
-        const float4 pp = GATHER ? __ldg(sp.pos_sx + i) : s_p[li], tt = GATHER ? __ldg(sp.syz_op_rg + i) : s_t[li];
-        const float4 q = __ldg(sp.rot + i);
-        const unsigned int bh = __ldg(sp.b + i);
+        const float4* rw = sp.row + (size_t)i * 4;
+        const float4 pp = GATHER ? __ldg(rw + 1) : s_p[li], tt = GATHER ? __ldg(rw + 2) : s_t[li];
+        const float4 q = GATHER ? __ldg(rw) : __ldg(sp.rot + i);
+        const unsigned int bh = GATHER ? __ldg(reinterpret_cast<const unsigned int*>(rw + 3)) : (unsigned int)__ldg(sp.b + i);
         splat_record r;
         const unsigned int cnt = preprocess_one(q.x, q.y, q.z, q.w, pp.w, tt.x, tt.y, pp.x, pp.y, pp.z,
                                                 __float_as_uint(tt.w), bh, tt.z, U, r);

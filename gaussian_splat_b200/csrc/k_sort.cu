@@ -9,7 +9,7 @@
 
 #define SORT_WARPS (SORT_THREADS / 32)
 #ifndef LB_DEPTH
-#define LB_DEPTH 8
+#define LB_DEPTH 4
 #endif
 // -DSORT_PROFILE: thread 0 of every CTA accumulates clock64() per phase into ctl->hist[7][0..7] (tuning aid).
 #ifdef SORT_PROFILE

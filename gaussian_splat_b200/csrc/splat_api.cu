@@ -43,7 +43,7 @@ struct splat_ctx : FrameSet {
     FrameSet alt; bool alt_ready = false; int cur_set = 0;
     int device = 0, sm_count = 148;
     uint32_t n = 0; size_t n_pad = 0;
-    float4 *rot = nullptr, *pos_sx = nullptr, *syz = nullptr, *base_rgb = nullptr, *sh = nullptr, *scr = nullptr; uint16_t* bq = nullptr;
+    float4 *rot = nullptr, *pos_sx = nullptr, *syz = nullptr, *base_rgb = nullptr, *sh = nullptr, *scr = nullptr, *row = nullptr; uint16_t* bq = nullptr;
     int sh_degree = 0;
     uint32_t* dbg_keys = nullptr; uint32_t* dbg_vals = nullptr; unsigned long long dbg_cap = 0;
     FrameCtl* ctl_host = nullptr;
@@ -200,9 +200,9 @@ static int ensure_pairs_all(splat_ctx* c, unsigned long long cap) {
 
 static void free_scene(splat_ctx* c) {
     drop_alt(c);
-    cudaFree(c->rot); cudaFree(c->pos_sx); cudaFree(c->syz); cudaFree(c->bq); cudaFree(c->sh); cudaFree(c->base_rgb); cudaFree(c->scr);
+    cudaFree(c->rot); cudaFree(c->pos_sx); cudaFree(c->syz); cudaFree(c->bq); cudaFree(c->sh); cudaFree(c->base_rgb); cudaFree(c->scr); cudaFree(c->row);
     free_scene_scratch(c);
-    c->rot = c->pos_sx = c->syz = c->base_rgb = c->sh = c->scr = nullptr; c->bq = nullptr;
+    c->rot = c->pos_sx = c->syz = c->base_rgb = c->sh = c->scr = c->row = nullptr; c->bq = nullptr;
     c->n = 0; c->n_pad = 0; c->sh_degree = 0;
 }
 
@@ -228,8 +228,9 @@ static int install_scene(splat_ctx* c, const float* aos_dev, uint32_t n) {
     const size_t n_pad = ((size_t)n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS * SCAN_TILE_ITEMS;
     CK(cudaMalloc(&c->rot, n_pad * 16)); CK(cudaMalloc(&c->pos_sx, n_pad * 16)); CK(cudaMalloc(&c->syz, n_pad * 16));
     CK(cudaMalloc(&c->bq, n_pad * 2)); CK(cudaMalloc(&c->base_rgb, n_pad * 16)); CK(cudaMalloc(&c->scr, n_pad * 16));
+    CK(cudaMalloc(&c->row, n_pad * 64));
     { const int rc = alloc_scene_scratch(c, n_pad); if (rc) return rc; }
-    launch_upload_soa(aos_dev, n, c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->scr, 0);
+    launch_upload_soa(aos_dev, n, c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->scr, c->row, 0);
     CK(cudaGetLastError());
     CK(cudaDeviceSynchronize());
     c->n = n; c->n_pad = n_pad;
@@ -371,10 +372,19 @@ static int build_frame(splat_ctx* c, const float* view, const float* proj, int w
         U.cam[j] = -acc;
     }
     U.n = c->n;
-    {   // ||V3x3||_F^2 with slack, for K1's conservative screening bound
-        float f2 = 0.0f;
-        for (int cc = 0; cc < 3; ++cc) for (int r = 0; r < 3; ++r) f2 += view[cc * 4 + r] * view[cc * 4 + r];
-        U.band_bound = f2 * 1.02f;
+    {   // K1's conservative screening bound: lambda_max(W^T W) <= the largest absolute row sum of W^T W
+        // (Gershgorin), W = the view matrix's 3x3 block; 1 for a rigid view. 2% slack for the rounding here.
+        float g = 0.0f;
+        for (int a = 0; a < 3; ++a) {
+            float rs = 0.0f;
+            for (int b = 0; b < 3; ++b) {
+                float d = 0.0f;
+                for (int r = 0; r < 3; ++r) d += view[a * 4 + r] * view[b * 4 + r];
+                rs += fabsf(d);
+            }
+            g = fmaxf(g, rs);
+        }
+        U.band_bound = g * 1.02f;
     }
     const unsigned int T = (unsigned int)(U.tiles_x * U.tiles_y);
     const int tb = tile_bits(T);
@@ -444,7 +454,7 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
     if (timed) CK(cudaEventRecord(c->ev[0], s));
     CK(cudaMemsetAsync(c->ctl, 0, sizeof(FrameCtl), s));
     if (c->n) {
-        ScenePlanes sp{c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->scr, c->sh, c->n_pad};
+        ScenePlanes sp{c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->scr, c->row, c->sh, c->n_pad};
         unsigned int* scan_prefix = c->tile_sums + c->n_pad / (SCAN_TILE_ITEMS / 2);
         launch_preprocess(sp, U, c->rec, c->binw, c->tile_sums, scan_prefix, c->capacity, c->ctl, s);
         if (timed) CK(cudaEventRecord(c->ev[1], s));

@@ -49,6 +49,7 @@ struct ScenePlanes {
     const uint16_t* b;        // half(b)
     const float4* base_rgb;   // fp32 r g b (loader colour) for the SH extension; .w unused
     const float4* scr;        // position.xyz, max(scale): the 16 bytes the screening kernel reads
+    const float4* row;        // [n][4]: rot, pos_sx, syz_op_rg, (half b bits, -, -, -): one 64-byte row per splat for gathers
     const float4* sh;         // SH planes [12][n_pad]: float4 j of splat i holds coefficients f' = 4j..4j+3,
                               // f' = 3*k + channel (coefficient-major, so degree L reads planes 0 .. 3*((L+1)^2-1)/4)
     size_t n_pad;
@@ -81,7 +82,7 @@ __device__ __forceinline__ void lb_store(unsigned long long* p, unsigned long lo
 
 // Launchers (each enqueues on `s` and returns).
 void launch_upload_soa(const float* aos_dev, unsigned int n, float4* rot, float4* pos_sx, float4* syz_op_rg,
-                       uint16_t* b, float4* base_rgb, float4* scr, cudaStream_t s);
+                       uint16_t* b, float4* base_rgb, float4* scr, float4* row, cudaStream_t s);
 // sh_rest45_dev: [n][45] as the loader stores it (channel-major: f = channel*15 + k) -> coefficient-major planes
 void launch_upload_sh(const float* sh_rest45_dev, unsigned int n, size_t n_pad, float4* planes, cudaStream_t s);
 // Per-splat "bin word" written by K1 and read by K2 (8 bytes, 0 = culled): the tile rectangle and the half depth,
