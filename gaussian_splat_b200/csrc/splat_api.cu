@@ -39,6 +39,7 @@ struct FrameSet {
     cudaStream_t own_stream = nullptr;
 };
 
+#define FB_RING 4
 struct splat_ctx : FrameSet {
     FrameSet alt; bool alt_ready = false; int cur_set = 0;
     int device = 0, sm_count = 148;
@@ -52,9 +53,11 @@ struct splat_ctx : FrameSet {
     cudaEvent_t ev[6] = {}; bool timed = false;
     void* fb_scratch = nullptr; size_t fb_scratch_bytes = 0;
     // camera-batch pipeline (splat_render_batch_host): second framebuffer, copy stream, per-buffer events
-    cudaStream_t copy_stream = nullptr; void* fb_scratch2 = nullptr; size_t fb_scratch2_bytes = 0;
-    void* bgra_scratch[2] = {nullptr, nullptr}; size_t bgra_bytes = 0;      // SPLAT_FLAG_HOST_BGRA8 staging
-    cudaEvent_t ev_rendered[2] = {}, ev_copied[2] = {}, ev_fork = nullptr;
+    // splat_render_batch_host: a ring of FB_RING device framebuffers, so rendering runs
+    // ahead of the device-to-host copies instead of waiting for the copy two frames back
+    cudaStream_t copy_stream = nullptr; void* fb_ring[FB_RING] = {}; size_t fb_ring_bytes = 0;
+    void* bgra_scratch[FB_RING] = {}; size_t bgra_bytes = 0;      // SPLAT_FLAG_HOST_BGRA8 staging
+    cudaEvent_t ev_rendered[FB_RING] = {}, ev_copied[FB_RING] = {}, ev_fork = nullptr;
     unsigned int* batch_flags = nullptr; int batch_flags_cap = 0;   // pinned: overflow word + D of every view
 };
 
@@ -139,7 +142,7 @@ int splat_create(int device, splat_ctx** out) {
     CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
-    for (int k = 0; k < 2; ++k) {
+    for (int k = 0; k < FB_RING; ++k) {
         CK(cudaEventCreateWithFlags(&c->ev_rendered[k], cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&c->ev_copied[k], cudaEventDisableTiming));
     }
@@ -216,9 +219,10 @@ int splat_destroy(splat_ctx* c) {
     for (int k = 0; k < 6; ++k) if (c->ev[k]) cudaEventDestroy(c->ev[k]);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
-    for (int k = 0; k < 2; ++k) { if (c->ev_rendered[k]) cudaEventDestroy(c->ev_rendered[k]); if (c->ev_copied[k]) cudaEventDestroy(c->ev_copied[k]); }
+    for (int k = 0; k < FB_RING; ++k) { if (c->ev_rendered[k]) cudaEventDestroy(c->ev_rendered[k]); if (c->ev_copied[k]) cudaEventDestroy(c->ev_copied[k]); }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
-    cudaFree(c->fb_scratch2); cudaFree(c->bgra_scratch[0]); cudaFree(c->bgra_scratch[1]); cudaFreeHost(c->batch_flags);
+    for (int k = 0; k < FB_RING; ++k) { cudaFree(c->fb_ring[k]); cudaFree(c->bgra_scratch[k]); }
+    cudaFreeHost(c->batch_flags);
     delete c;
     return SPLAT_OK;
 }
@@ -588,7 +592,7 @@ int splat_render_host(splat_ctx* c, void* fb_host, const float* view, const floa
     const bool bgra = o && (o->flags & SPLAT_FLAG_HOST_BGRA8);
     if (bgra && (size_t)w * h * 4 > c->bgra_bytes) {
         CK(cudaDeviceSynchronize());
-        for (int k = 0; k < 2; ++k) { cudaFree(c->bgra_scratch[k]); c->bgra_scratch[k] = nullptr; CK(cudaMalloc(&c->bgra_scratch[k], (size_t)w * h * 4)); }
+        for (int k = 0; k < FB_RING; ++k) { cudaFree(c->bgra_scratch[k]); c->bgra_scratch[k] = nullptr; CK(cudaMalloc(&c->bgra_scratch[k], (size_t)w * h * 4)); }
         c->bgra_bytes = (size_t)w * h * 4;
     }
     // rows outside the band are not rendered: only the band is copied back
@@ -622,15 +626,10 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
     CK(cudaSetDevice(c->device));
     const size_t bytes = (size_t)w * h * 8;
     if (w <= 0 || h <= 0) ARG_FAIL("splat_render: bad viewport");
-    if (bytes > c->fb_scratch_bytes) {
+    if (bytes > c->fb_ring_bytes) {
         CK(cudaDeviceSynchronize());
-        cudaFree(c->fb_scratch); c->fb_scratch = nullptr;
-        CK(cudaMalloc(&c->fb_scratch, bytes)); c->fb_scratch_bytes = bytes;
-    }
-    if (bytes > c->fb_scratch2_bytes) {
-        CK(cudaDeviceSynchronize());
-        cudaFree(c->fb_scratch2); c->fb_scratch2 = nullptr;
-        CK(cudaMalloc(&c->fb_scratch2, bytes)); c->fb_scratch2_bytes = bytes;
+        for (int k = 0; k < FB_RING; ++k) { cudaFree(c->fb_ring[k]); c->fb_ring[k] = nullptr; CK(cudaMalloc(&c->fb_ring[k], bytes)); }
+        c->fb_ring_bytes = bytes;
     }
     if (n_views > c->batch_flags_cap) {
         cudaFreeHost(c->batch_flags); c->batch_flags = nullptr;
@@ -642,23 +641,23 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
     const bool bgra = o && (o->flags & SPLAT_FLAG_HOST_BGRA8);
     if (bgra && (size_t)w * h * 4 > c->bgra_bytes) {
         CK(cudaDeviceSynchronize());
-        for (int k = 0; k < 2; ++k) { cudaFree(c->bgra_scratch[k]); c->bgra_scratch[k] = nullptr; CK(cudaMalloc(&c->bgra_scratch[k], (size_t)w * h * 4)); }
+        for (int k = 0; k < FB_RING; ++k) { cudaFree(c->bgra_scratch[k]); c->bgra_scratch[k] = nullptr; CK(cudaMalloc(&c->bgra_scratch[k], (size_t)w * h * 4)); }
         c->bgra_bytes = (size_t)w * h * 4;
     }
     const size_t px_bytes = bgra ? 4 : 8;
     const bool two = n_views > 1 && two_frames_in_flight(c, w, h, o);
     if (two) { const int rc = ensure_alt(c); if (rc) return rc; }
     const int flags = o ? (o->flags & ~(SPLAT_FLAG_TIMING | SPLAT_FLAG_KEEP_UNSORTED)) : 0;
-    void* buf[2] = {c->fb_scratch, c->fb_scratch2};
+    void* const* buf = c->fb_ring;
     for (int attempt = 0; attempt < 4; ++attempt) {
         for (int v = 0; v < n_views; ++v) {
             if (!fb_host[v]) ARG_FAIL("splat_render_batch_host: NULL framebuffer");
-            const int b = v & 1;
-            use_set(c, two ? b : 0);                        // frame set and stream (two in flight), framebuffer b
+            const int b = v % FB_RING;
+            use_set(c, two ? (v & 1) : 0);                  // frame set and stream (two in flight); framebuffer ring slot b
             FrameUniforms U; SortPlan plan;
             int rc = build_frame(c, views + 16 * v, projs + 16 * v, w, h, o, U, plan);
             if (rc) return rc;
-            if (v >= 2) CK(cudaStreamWaitEvent(c->own_stream, c->ev_copied[b], 0));     // buffer b is free again
+            if (v >= FB_RING) CK(cudaStreamWaitEvent(c->own_stream, c->ev_copied[b], 0));     // slot b is free again
             rc = enqueue_frame(c, c->own_stream, buf[b], U, plan, flags);
             if (rc) return rc;
             CK(cudaMemcpyAsync(c->batch_flags + 4 * v, c->ctl, 16, cudaMemcpyDeviceToHost, c->own_stream));   // D, overflow
