@@ -17,6 +17,7 @@ __global__ void __launch_bounds__(256) tile_bounds_kernel(const unsigned int* __
                                                           const FrameCtl* __restrict__ ctl, unsigned int first,
                                                           unsigned int n_bounds, unsigned int* __restrict__ bounds)
 {
+    pdl_prologue();
     const unsigned int t = first + blockIdx.x * 8u + (threadIdx.x >> 5), lane = threadIdx.x & 31u;
     if (t >= first + n_bounds) return;
     const unsigned int n = ctl->overflow ? 0u : ctl->n_sort;
@@ -38,7 +39,7 @@ __global__ void __launch_bounds__(256) tile_bounds_kernel(const unsigned int* __
 void launch_tile_bounds(const unsigned int* keys_sorted, const FrameCtl* ctl, unsigned int first_tile,
                         unsigned int n_tiles, unsigned int* bounds, cudaStream_t s)
 {
-    tile_bounds_kernel<<<(n_tiles + 1 + 7) / 8, 256, 0, s>>>(keys_sorted, ctl, first_tile, n_tiles + 1, bounds);
+    launch_pdl(tile_bounds_kernel, dim3((n_tiles + 1 + 7) / 8), dim3(256), 0, s, keys_sorted, ctl, first_tile, n_tiles + 1, bounds);
 }
 
 // ------------------------------------------------------------------ K5
@@ -245,6 +246,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
 {
     __shared__ float4 s_ab[2 * BLEND_BATCH];        // [0..B): cx cy ux uy   [B..2B): vx vy opacity rg
     __shared__ unsigned int s_cm[3 * BLEND_BATCH];  // [0..B): bd   [B..2B): 8x4-block mask   [2B..3B): instance index
+    pdl_prologue();
 
     const int tx = blockIdx.x, ty = U.row_begin + blockIdx.y;
     const unsigned int tile = (unsigned int)(ty * U.tiles_x + tx);
@@ -315,12 +317,9 @@ void launch_blend(const FrameUniforms& U, const splat_record* rec, const unsigne
     if (rows <= 0 || U.tiles_x <= 0) return;
     const dim3 grid(U.tiles_x, rows);
     if (U.mode == SPLAT_MODE_MLAB)
-        blend_kernel<SPLAT_MODE_MLAB><<<grid, BLEND_THREADS, 0, s>>>(U, rec, vals_sorted, vals_sorted, bounds,
-                                                                    reinterpret_cast<uint2*>(fb_half4));
+        launch_pdl(blend_kernel<SPLAT_MODE_MLAB>, grid, dim3(BLEND_THREADS), 0, s, U, rec, vals_sorted, vals_sorted, bounds, reinterpret_cast<uint2*>(fb_half4));
     else if (U.mode == SPLAT_MODE_LAYER50)
-        blend_kernel<SPLAT_MODE_LAYER50><<<grid, BLEND_THREADS, 0, s>>>(U, rec, vals_sorted, vals_depth_sorted, bounds,
-                                                                       reinterpret_cast<uint2*>(fb_half4));
+        launch_pdl(blend_kernel<SPLAT_MODE_LAYER50>, grid, dim3(BLEND_THREADS), 0, s, U, rec, vals_sorted, vals_depth_sorted, bounds, reinterpret_cast<uint2*>(fb_half4));
     else
-        blend_kernel<SPLAT_MODE_TILE><<<grid, BLEND_THREADS, 0, s>>>(U, rec, vals_sorted, vals_sorted, bounds,
-                                                                    reinterpret_cast<uint2*>(fb_half4));
+        launch_pdl(blend_kernel<SPLAT_MODE_TILE>, grid, dim3(BLEND_THREADS), 0, s, U, rec, vals_sorted, vals_sorted, bounds, reinterpret_cast<uint2*>(fb_half4));
 }

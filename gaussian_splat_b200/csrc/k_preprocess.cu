@@ -131,6 +131,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
     __shared__ float4 s_p[GATHER ? 1 : K1_CTA_SPLATS], s_t[GATHER ? 1 : K1_CTA_SPLATS];
     const unsigned int tid = threadIdx.x, lane = tid & 31;
     const unsigned int base = blockIdx.x * (unsigned int)K1_CTA_SPLATS;
+    pdl_prologue();
     if (tid == 0) s_count = 0;
     if (tid < K1_CTA_SPLATS / K1_TILE) s_sum[tid] = 0;
     float4 p[K1_ITEMS], t[GATHER ? 1 : K1_ITEMS];
@@ -211,6 +212,7 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(const unsigned int* __r
                                                          unsigned int n, unsigned long long capacity, FrameCtl* ctl)
 {
     __shared__ unsigned long long s_wsum[32];
+    pdl_prologue();
     const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned int n_cells = (n + K1_TILE - 1) / K1_TILE;
     const unsigned int n_scan = (n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS;
@@ -246,7 +248,7 @@ void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_reco
                        cudaStream_t s)
 {
     if (U.n == 0) return;
-    if ((U.row_end - U.row_begin) * 2 <= U.tiles_y) preprocess_kernel<8, true><<<(U.n + 2047u) / 2048u, 256, 0, s>>>(sp, U, rec, binw, tile_sums);
-    else preprocess_kernel<4, false><<<(U.n + 1023u) / 1024u, 256, 0, s>>>(sp, U, rec, binw, tile_sums);
-    tile_scan_kernel<<<1, 1024, 0, s>>>(tile_sums, scan_prefix, U.n, capacity, ctl);
+    if ((U.row_end - U.row_begin) * 2 <= U.tiles_y) launch_pdl(preprocess_kernel<8, true>, dim3((U.n + 2047u) / 2048u), dim3(256), 0, s, sp, U, rec, binw, tile_sums);
+    else launch_pdl(preprocess_kernel<4, false>, dim3((U.n + 1023u) / 1024u), dim3(256), 0, s, sp, U, rec, binw, tile_sums);
+    launch_pdl(tile_scan_kernel, dim3(1), dim3(1024), 0, s, (const unsigned int*)tile_sums, scan_prefix, U.n, capacity, ctl);
 }

@@ -44,6 +44,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_duplicate_kernel(
     __shared__ unsigned int s_warp[SCAN_THREADS / 32], s_wvis[SCAN_THREADS / 32];
 
     const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    pdl_prologue();
     for (int p = 0; p < FRAME_MAX_PASSES; ++p) s_hist[p][tid] = 0;
     const bool layer = U.mode == SPLAT_MODE_LAYER50;        // second, depth-ordered list
     const bool arrival = U.mode != SPLAT_MODE_TILE;         // LAYER50 / MLAB: the list the pixels walk is in instance order
@@ -175,6 +176,6 @@ void launch_scan_duplicate(const FrameUniforms& U, const unsigned long long* bin
     const unsigned int n_tiles = (U.n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS;
     const unsigned int n_k1 = (U.n + SCAN_TILE_ITEMS / 2 - 1) / (SCAN_TILE_ITEMS / 2);
     const unsigned int grid = n_tiles < (unsigned int)sm_count * 8u ? n_tiles : (unsigned int)sm_count * 8u;
-    scan_duplicate_kernel<<<grid, SCAN_THREADS, 0, s>>>(U, binw, offsets, keys, vals, keys_depth, vals_depth, capacity, ctl,
-                                                        tile_sums, scan_prefix, dp, n_tiles, n_k1);
+    launch_pdl(scan_duplicate_kernel, dim3(grid), dim3(SCAN_THREADS), 0, s, U, binw, offsets, keys, vals, keys_depth, vals_depth, capacity, ctl,
+               tile_sums, scan_prefix, dp, n_tiles, n_k1);
 }

@@ -311,6 +311,7 @@ __global__ void __launch_bounds__(SORT_THREADS, MIN_CTAS) onesweep_pass_kernel(
 {
     extern __shared__ unsigned long long s_raw[];
     __shared__ SortShared sh;
+    pdl_prologue();
     if (SETS_LONG != SETS && ctl->n_sort > SORT_LONG)
         onesweep_pass_body<ITEMS, KeyT, SETS_LONG>(keys_in, vals_in, keys_out, vals_out, ctl, status, epoch, pass, tix, shift, mask, s_raw, sh);
     else
@@ -329,8 +330,9 @@ static void run_passes(KeyT* ki, unsigned int* vi, KeyT* ko, unsigned int* vo, F
         attr_set = true;
     }
     for (int p = 0; p < plan.n_pass; ++p) {
-        onesweep_pass_kernel<ITEMS, KeyT, SETS, SETS_LONG, MIN_CTAS><<<grid, SORT_THREADS, smem, s>>>(ki, vi, ko, vo, ctl, sort_status, epoch_base + p,
-                                                                    plan.slot[p], plan.ticket[p], plan.shift[p], plan.mask[p]);
+        launch_pdl(onesweep_pass_kernel<ITEMS, KeyT, SETS, SETS_LONG, MIN_CTAS>, dim3(grid), dim3(SORT_THREADS), smem, s,
+                   (const KeyT*)ki, (const unsigned int*)vi, ko, vo, ctl, sort_status, epoch_base + p,
+                   plan.slot[p], plan.ticket[p], plan.shift[p], plan.mask[p]);
         KeyT* tk = ki; ki = ko; ko = tk;
         unsigned int* tv = vi; vi = vo; vo = tv;
     }

@@ -425,7 +425,11 @@ static SortPlan layer_plan(const SortPlan& full) {
     return a;
 }
 
+thread_local bool g_pdl_frame = true;
+// Internal flag (not a splat_opts flag): launch this frame's kernels without programmatic dependent launch.
+#define FRAME_NO_PDL (1 << 30)
 static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUniforms& U, const SortPlan& plan, int flags) {
+    g_pdl_frame = (flags & FRAME_NO_PDL) == 0;
     const unsigned int T = (unsigned int)(U.tiles_x * U.tiles_y);
     if (T > c->ranges_cap) {
         CK(cudaDeviceSynchronize());
@@ -543,7 +547,7 @@ int splat_render_batch(splat_ctx* c, void* stream, void* const* fbs, const float
         FrameUniforms U; SortPlan plan;
         int rc = build_frame(c, views + 16 * v, projs + 16 * v, w, h, o, U, plan);
         if (rc) return rc;
-        rc = enqueue_frame(c, c->own_stream, fbs[v], U, plan, flags);
+        rc = enqueue_frame(c, c->own_stream, fbs[v], U, plan, flags | FRAME_NO_PDL);
         if (rc) return rc;
         if (v >= n_views - 2) {                      // join: the caller's stream continues after both sets drain
             CK(cudaEventRecord(c->ev_rendered[v & 1], c->own_stream));
@@ -846,6 +850,7 @@ static int sort_pairs_impl(splat_ctx* c, void* stream, void* keys, uint32_t* val
     CK(cudaMemsetAsync(c->ctl, 0, sizeof(FrameCtl), s));
     set_n_sort_kernel<<<1, 1, 0, s>>>(c->ctl, (unsigned int)n);
     launch_sort_histogram(keys, key_bytes, n, c->ctl, plan, c->sm_count, s);
+    g_pdl_frame = true;
     launch_radix_sort(keys, vals, keys_alt, vals_alt, key_bytes, n, c->ctl, c->sort_status,
                       c->frame_no * 16u + 1, plan, c->sm_count, false, s);
     CK(cudaGetLastError());
