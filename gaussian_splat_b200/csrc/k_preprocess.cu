@@ -122,18 +122,20 @@ __device__ __forceinline__ bool may_be_visible(const float4 p, const FrameUnifor
 template <int K1_ITEMS, bool GATHER>
 __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const __grid_constant__ FrameUniforms U,
                                                          splat_record* __restrict__ rec, unsigned long long* __restrict__ binw,
-                                                         unsigned int* __restrict__ tile_sums)
+                                                         unsigned int* __restrict__ tile_sums, unsigned int* __restrict__ visbits)
 {
     constexpr int K1_CTA_SPLATS = 256 * K1_ITEMS;
     static_assert(K1_CTA_SPLATS % K1_TILE == 0, "a CTA covers whole pair-count cells");
     __shared__ unsigned short s_list[K1_CTA_SPLATS];
     __shared__ unsigned int s_count, s_sum[K1_CTA_SPLATS / K1_TILE];
+    __shared__ unsigned int s_vis[GATHER ? K1_CTA_SPLATS / 32 : 1];     // band shape: which of the CTA's splats produced pairs
     __shared__ float4 s_p[GATHER ? 1 : K1_CTA_SPLATS], s_t[GATHER ? 1 : K1_CTA_SPLATS];
     const unsigned int tid = threadIdx.x, lane = tid & 31;
     const unsigned int base = blockIdx.x * (unsigned int)K1_CTA_SPLATS;
     pdl_prologue();
     if (tid == 0) s_count = 0;
     if (tid < K1_CTA_SPLATS / K1_TILE) s_sum[tid] = 0;
+    if (GATHER && tid < K1_CTA_SPLATS / 32) s_vis[tid] = 0;
     float4 p[K1_ITEMS], t[GATHER ? 1 : K1_ITEMS];
 #pragma unroll
     for (int k = 0; k < K1_ITEMS; ++k) {
@@ -151,7 +153,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
         float4 ps = p[k];
         if (!GATHER) ps.w = fmaxf(p[k].w, fmaxf(t[k].x, t[k].y));      // x y z max(scale), what the screening plane holds
         const bool keep = i < U.n && may_be_visible(ps, U);
-        if (i < U.n && !keep) binw[i] = 0ull;
+        if (!GATHER && i < U.n && !keep) binw[i] = 0ull;      // band shape: the visibility bitmap says which bin words are live
         const unsigned int m = __ballot_sync(0xFFFFFFFFu, keep);
         unsigned int wbase = 0;
         if (lane == 0 && m) wbase = atomicAdd(&s_count, __popc(m));
@@ -173,8 +175,9 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
         splat_record r;
         const unsigned int cnt = preprocess_one(q.x, q.y, q.z, q.w, pp.w, tt.x, tt.y, pp.x, pp.y, pp.z,
                                                 __float_as_uint(tt.w), bh, tt.z, U, r);
-        binw[i] = cnt ? binw_pack(r.rect_lo, r.rect_hi, r.bd >> 16) : 0ull;
+        if (!GATHER) binw[i] = cnt ? binw_pack(r.rect_lo, r.rect_hi, r.bd >> 16) : 0ull;
         if (cnt == 0) continue;
+        if (GATHER) { binw[i] = binw_pack(r.rect_lo, r.rect_hi, r.bd >> 16); atomicOr(&s_vis[li >> 5], 1u << (li & 31u)); }
         atomicAdd(&s_sum[li / K1_TILE], cnt);       // fits: 512 splats x at most 65536 tiles each < 2^32
         if (U.sh_degree > 0) {
             // D11: colour = max(0, loader colour + sum_{k>=1} basis_k(dir) * f_rest[k][channel]), then half
@@ -206,6 +209,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
     }
     __syncthreads();
     if (tid < K1_CTA_SPLATS / K1_TILE && base + tid * K1_TILE < U.n) tile_sums[blockIdx.x * (K1_CTA_SPLATS / K1_TILE) + tid] = s_sum[tid];
+    if (GATHER && tid < K1_CTA_SPLATS / 32) visbits[blockIdx.x * (K1_CTA_SPLATS / 32) + tid] = s_vis[tid];
 }
 
 __global__ void __launch_bounds__(1024) tile_scan_kernel(const unsigned int* __restrict__ tile_sums, unsigned int* __restrict__ scan_prefix,
@@ -244,11 +248,11 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(const unsigned int* __r
 }
 
 void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record* rec, unsigned long long* binw,
-                       unsigned int* tile_sums, unsigned int* scan_prefix, unsigned long long capacity, FrameCtl* ctl,
-                       cudaStream_t s)
+                       unsigned int* tile_sums, unsigned int* scan_prefix, unsigned int* visbits, unsigned long long capacity,
+                       FrameCtl* ctl, cudaStream_t s)
 {
     if (U.n == 0) return;
-    if ((U.row_end - U.row_begin) * 2 <= U.tiles_y) launch_pdl(preprocess_kernel<8, true>, dim3((U.n + 2047u) / 2048u), dim3(256), 0, s, sp, U, rec, binw, tile_sums);
-    else launch_pdl(preprocess_kernel<4, false>, dim3((U.n + 1023u) / 1024u), dim3(256), 0, s, sp, U, rec, binw, tile_sums);
+    if (frame_is_band(U)) launch_pdl(preprocess_kernel<BAND_TILE / 256, true>, dim3((U.n + BAND_TILE - 1u) / BAND_TILE), dim3(256), 0, s, sp, U, rec, binw, tile_sums, visbits);
+    else launch_pdl(preprocess_kernel<4, false>, dim3((U.n + 1023u) / 1024u), dim3(256), 0, s, sp, U, rec, binw, tile_sums, visbits);
     launch_pdl(tile_scan_kernel, dim3(1), dim3(1024), 0, s, (const unsigned int*)tile_sums, scan_prefix, U.n, capacity, ctl);
 }

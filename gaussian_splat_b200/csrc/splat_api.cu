@@ -34,6 +34,7 @@ struct FrameSet {
     uint32_t* keys_d[2] = {nullptr, nullptr}; uint32_t* vals_d[2] = {nullptr, nullptr}; unsigned long long capacity_d = 0;
     FrameCtl* ctl = nullptr;
     unsigned int* tile_sums = nullptr;      // K1 pair counts per 512 splats, then K2's tile prefixes
+    unsigned int* visbits = nullptr;        // band frames: one bit per splat that produced pairs (K1 -> K2)
     unsigned long long* sort_status = nullptr; size_t sort_status_tiles = 0;
     uint32_t* bounds = nullptr; uint32_t ranges_cap = 0;   // [T+1] first sorted pair of every tile
     cudaStream_t own_stream = nullptr;
@@ -152,8 +153,8 @@ int splat_create(int device, splat_ctx** out) {
 
 // Per-splat scratch of the CURRENT frame set (records, counts, offsets, scan lookback words).
 static void free_scene_scratch(splat_ctx* c) {
-    cudaFree(c->rec); cudaFree(c->binw); cudaFree(c->offsets); cudaFree(c->tile_sums);
-    c->rec = nullptr; c->binw = nullptr; c->offsets = nullptr; c->tile_sums = nullptr;
+    cudaFree(c->rec); cudaFree(c->binw); cudaFree(c->offsets); cudaFree(c->tile_sums); cudaFree(c->visbits);
+    c->rec = nullptr; c->binw = nullptr; c->offsets = nullptr; c->tile_sums = nullptr; c->visbits = nullptr;
 }
 static int alloc_scene_scratch(splat_ctx* c, size_t n_pad) {
     CK(cudaMalloc(&c->rec, n_pad * sizeof(splat_record)));
@@ -163,6 +164,9 @@ static int alloc_scene_scratch(splat_ctx* c, size_t n_pad) {
     const size_t sums = n_pad / (SCAN_TILE_ITEMS / 2) + n_pad / SCAN_TILE_ITEMS + 2;   // [n/512] sums, then [n/1024] prefixes
     CK(cudaMalloc(&c->tile_sums, sums * 4));
     CK(cudaMemset(c->tile_sums, 0, sums * 4));
+    const size_t vis_words = (n_pad / BAND_TILE + 1) * (BAND_TILE / 32);
+    CK(cudaMalloc(&c->visbits, vis_words * 4));
+    CK(cudaMemset(c->visbits, 0, vis_words * 4));
     return SPLAT_OK;
 }
 // Releases the second frame set completely (it is rebuilt by the next camera-batch call).
@@ -464,10 +468,10 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
     if (c->n) {
         ScenePlanes sp{c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->scr, c->row, c->sh, c->n_pad};
         unsigned int* scan_prefix = c->tile_sums + c->n_pad / (SCAN_TILE_ITEMS / 2);
-        launch_preprocess(sp, U, c->rec, c->binw, c->tile_sums, scan_prefix, c->capacity, c->ctl, s);
+        launch_preprocess(sp, U, c->rec, c->binw, c->tile_sums, scan_prefix, c->visbits, c->capacity, c->ctl, s);
         if (timed) CK(cudaEventRecord(c->ev[1], s));
         launch_scan_duplicate(U, c->binw, c->offsets, c->keys[0], c->vals[0], layer ? c->keys_d[0] : nullptr,
-                              layer ? c->vals_d[0] : nullptr, c->capacity, c->ctl, c->tile_sums, scan_prefix, plan, c->sm_count, s);
+                              layer ? c->vals_d[0] : nullptr, c->capacity, c->ctl, c->tile_sums, scan_prefix, c->visbits, plan, c->sm_count, s);
         if (keep) {
             CK(cudaMemcpyAsync(c->dbg_keys, c->keys[0], c->capacity * 4, cudaMemcpyDeviceToDevice, s));
             CK(cudaMemcpyAsync(c->dbg_vals, c->vals[0], c->capacity * 4, cudaMemcpyDeviceToDevice, s));
@@ -698,6 +702,20 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
 // ------------------------------------------------------ debug / timing / sort
 extern "C" {
 
+// Bin words of the last frame with the culled splats' entries zeroed. A band frame leaves stale words where its
+// visibility bitmap has no bit (K1 only writes the live ones).
+static cudaError_t fetch_binw(splat_ctx* c, std::vector<unsigned long long>& w) {
+    w.resize(c->n);
+    if (!c->n) return cudaSuccess;
+    cudaError_t e = cudaMemcpy(w.data(), c->binw, (size_t)c->n * 8, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess || !frame_is_band(c->lastU)) return e;
+    std::vector<uint32_t> bits(((size_t)c->n + 31) / 32);
+    e = cudaMemcpy(bits.data(), c->visbits, bits.size() * 4, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return e;
+    for (uint32_t i = 0; i < c->n; ++i) if (!((bits[i >> 5] >> (i & 31)) & 1u)) w[i] = 0;
+    return cudaSuccess;
+}
+
 int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
     if (!c || !bytes) ARG_FAIL("splat_debug_fetch: NULL argument");
     CK(cudaSetDevice(c->device));
@@ -777,9 +795,19 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
         delete[] b;
         CK(e);
     } else if (what == SPLAT_FETCH_TILES_TOUCHED) {
-        std::vector<unsigned long long> w(c->n);
-        if (c->n) CK(cudaMemcpy(w.data(), c->binw, (size_t)c->n * 8, cudaMemcpyDeviceToHost));
+        std::vector<unsigned long long> w;
+        CK(fetch_binw(c, w));
         for (uint32_t i = 0; i < c->n; ++i) ((uint32_t*)dst)[i] = binw_count(w[i]);
+    } else if (what == SPLAT_FETCH_OFFSETS && frame_is_band(c->lastU)) {
+        // a band frame's K2 walks only the visible splats and writes no per-splat offsets: the exclusive,
+        // saturating scan of the pair counts is rebuilt here from the bin words
+        std::vector<unsigned long long> w;
+        CK(fetch_binw(c, w));
+        unsigned long long run = 0;
+        for (uint32_t i = 0; i < c->n; ++i) {
+            ((uint32_t*)dst)[i] = run > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)run;
+            run += binw_count(w[i]);
+        }
     } else if (what == SPLAT_FETCH_KEYS_UNSORTED || what == SPLAT_FETCH_KEYS_SORTED) {
         // presented in the documented 64-bit form, tile << 32 | half-depth field (TILE) or | instance index (lists kept
         // in instance order); the device holds tile << 16 | depth, and the instance index is the pair's value
@@ -793,14 +821,10 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
     } else if (need) CK(cudaMemcpy(dst, src, need, cudaMemcpyDeviceToHost));
     if (what == SPLAT_FETCH_RECORDS && c->n) {
         // culled splats have no record written: present them zeroed
-        unsigned long long* t = new unsigned long long[c->n];
-        cudaError_t e = cudaMemcpy(t, c->binw, (size_t)c->n * 8, cudaMemcpyDeviceToHost);
-        if (e == cudaSuccess) {
-            splat_record* r = (splat_record*)dst;
-            for (uint32_t i = 0; i < c->n; ++i) if (!t[i]) std::memset(r + i, 0, sizeof(splat_record));
-        }
-        delete[] t;
-        CK(e);
+        std::vector<unsigned long long> t;
+        CK(fetch_binw(c, t));
+        splat_record* r = (splat_record*)dst;
+        for (uint32_t i = 0; i < c->n; ++i) if (!t[i]) std::memset(r + i, 0, sizeof(splat_record));
     }
     *bytes = need;
     return SPLAT_OK;

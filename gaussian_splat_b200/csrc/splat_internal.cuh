@@ -27,7 +27,7 @@ struct FrameUniforms {
     int mode, order, K, sh_degree;
     float cam[3];
     unsigned int n;
-    float band_bound;   // ||V3x3||_F^2 * 1.02 for K1's conservative screening bound
+    float band_bound;   // bound on lambda_max(W^T W) * 1.02, W = V's 3x3 block, for K1's conservative screening bound
 };
 
 // Device control block, zeroed by one memsetAsync at the start of every frame.
@@ -132,14 +132,19 @@ __host__ __device__ __forceinline__ unsigned int binw_count(unsigned long long w
     return (tx1 - tx0 + 1u) * (ty1 - ty0 + 1u);
 }
 
+// Band shape (a tile-row band of at most half the frame: most splats are culled): K1 owns BAND_TILE splats per CTA,
+// writes bin words only for the splats that produced pairs and says which in a bitmap (BAND_TILE / 32 words per
+// CTA); K2 walks those bitmaps instead of every bin word.
+#define BAND_TILE 2048u
+static inline bool frame_is_band(const FrameUniforms& U) { return (U.row_end - U.row_begin) * 2 <= U.tiles_y; }
 void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record* rec, unsigned long long* binw,
-                       unsigned int* tile_sums, unsigned int* scan_prefix, unsigned long long capacity, FrameCtl* ctl,
+                       unsigned int* tile_sums, unsigned int* scan_prefix, unsigned int* visbits, unsigned long long capacity, FrameCtl* ctl,
                        cudaStream_t s);
 void launch_scan_duplicate(const FrameUniforms& U, const unsigned long long* binw,
                            unsigned int* offsets, unsigned int* keys, unsigned int* vals,
                            unsigned int* keys_depth, unsigned int* vals_depth,
                            unsigned long long capacity, FrameCtl* ctl, const unsigned int* tile_sums,
-                           const unsigned int* scan_prefix, SortPlan plan, int sm_count, cudaStream_t s);
+                           const unsigned int* scan_prefix, const unsigned int* visbits, SortPlan plan, int sm_count, cudaStream_t s);
 // Frame keys are 32 bits: tile << 16 | half-depth field (TILE), or tile << 16 alone for a list kept in instance
 // order (pairs are emitted in instance order and the sort is stable, so only the tile digits are sorted).
 // LAYER50 keeps two orders of the same pairs: (keys, vals) in arrival order (D3) and (keys_depth, vals_depth) in
