@@ -9,16 +9,6 @@ __device__ __forceinline__ unsigned int sat_add(unsigned int a, unsigned int b) 
     return s > 0xFFFFFFFFull ? 0xFFFFFFFFu : (unsigned int)s;
 }
 
-// Adds 1 to hist[digit] for every active lane, one shared-memory atomic per distinct digit. (A warp expands 32
-// consecutive pair slots, which belong to about eight splats at unrelated screen positions. Tried instead of the
-// match: a plain atomic per lane, 40% slower - shared atomics cost two LSU cycles per lane and serialise on equal
-// addresses; a shuffle + ballot loop over the distinct values of the high tile digit, 60% slower.)
-__device__ __forceinline__ void warp_hist_inc(unsigned int* hist, unsigned int digit) {
-    const unsigned int act = __activemask();
-    const unsigned int peers = __match_any_sync(act, digit);
-    if ((peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0) atomicAdd(hist + digit, __popc(peers));
-}
-
 // What K2 needs of the sort plan: where the two depth digits (bits 0-7, 8-15 of the depth field; absent in MLAB
 // frames) and the one or two tile digits (bits 32-39, 40-47 of the key) are counted.
 struct DupPlan { int d0, d1, t0, t1; unsigned int tmask0, tmask1; };
@@ -186,8 +176,19 @@ __global__ void __launch_bounds__(SCAN_THREADS, 8) scan_duplicate_kernel(
                 const unsigned int ry = k / wdt, rx = k - ry * wdt;
                 const unsigned int t = (ty0 + ry) * (unsigned int)U.tiles_x + (tx0 + rx);
                 const unsigned int splat = base + (dfi & 0xFFFFu), df = dfi >> 16;
-                warp_hist_inc(s_hist[plan.t0], t & plan.tmask0);
-                if (plan.t1 >= 0) warp_hist_inc(s_hist[plan.t1], (t >> 8) & plan.tmask1);
+{   // tile-digit histograms: ONE match on the whole tile id serves both digits, the lowest peer adds the
+                    // group's size to each (a match per digit cost twice the ADU time: K2 187 -> 152 us at 6M / 4K).
+                    // A warp's 32 consecutive slots belong to about eight splats at unrelated screen positions;
+                    // tried instead of the match: a plain shared atomic per lane (40% slower: two LSU cycles per
+                    // lane, serialised on equal addresses) and a shuffle + ballot loop over the distinct values
+                    // of the high digit (60% slower)
+                    const unsigned int peers = __match_any_sync(__activemask(), t);
+                    if ((peers & ((1u << lane) - 1u)) == 0) {
+                        const unsigned int c = __popc(peers);
+                        atomicAdd(&s_hist[plan.t0][t & plan.tmask0], c);
+                        if (plan.t1 >= 0) atomicAdd(&s_hist[plan.t1][(t >> 8) & plan.tmask1], c);
+                    }
+                }
                 const unsigned long long g = (unsigned long long)prefix + carry + j;
                 if (g < capacity) {
                     // TILE: tile | depth. LAYER50 / MLAB: tile alone (slots are in instance order and the sort is

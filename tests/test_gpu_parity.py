@@ -104,6 +104,27 @@ def test_ragged_viewport_and_band(gpu_ctx, small_scene):
     _check_all(gpu_ctx, small_scene, V, P, w, h, 1, 0, rows=(5, 14))
 
 
+def test_band_shape_dense_tiles_and_stale_bin_words(gpu_ctx):
+    """The band shape of K1 / K2 (a band of at most half the tile rows): K1 leaves bin words only for splats that
+    produced pairs plus a visibility bitmap, K2 walks the bitmaps 1024 visible splats at a time. A scene packed
+    around the view axis puts far more than 1024 visible splats into every 2048-splat tile (the chunk loop), and
+    band / whole frame / other band in turn leave stale bin words behind that the bitmaps must mask. All three
+    modes; stages bit-exact as everywhere."""
+    from gaussian_splat_b200 import scene
+    from oracle import oracle as O
+    w, h = 320, 256                                  # 20 x 16 tiles
+    V, P = O.app_camera(w, h)
+    inst, _ = scene.make_instances(5000, 0x5EED00B1)
+    inst[:, 7:10] *= 0.12                            # every splat near the target: all visible, all in the middle rows
+    for rows in ((4, 12), (0, 0), (6, 10), (0, 8)):
+        F = _check_all(gpu_ctx, inst, V, P, w, h, 0, 0, rows=rows)
+        if rows == (4, 12):
+            vis = (F.tiles_touched.reshape(-1)[:4096].reshape(2, 2048) > 0).sum(axis=1)
+            assert vis.min() > 1024, vis              # the case the chunk loop exists for
+    _check_all(gpu_ctx, inst, V, P, w, h, 1, 0, K=50, rows=(4, 12))
+    _check_all(gpu_ctx, inst, V, P, w, h, 2, 0, rows=(4, 12))
+
+
 def test_empty_and_tiny_scenes(gpu_ctx):
     import torch
     from gaussian_splat_b200 import capi, scene
