@@ -84,26 +84,28 @@ void launch_upload_soa(const float* aos_dev, unsigned int n, float4* rot, float4
 // bound to be trusted are kept. Results never depend on it; it exists so that the exact path runs on
 // warps full of survivors instead of on every warp that holds one (splat order is unrelated to screen
 // position: at 1M/1080p 46% of the splats are culled, with tile-row bands up to 97%).
+__device__ __forceinline__ float rcp_ftz(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float sqrt_ftz(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 __device__ __forceinline__ bool may_be_visible(const float4 p, const FrameUniforms& U) {      // p = x y z max(scale)
+    // straight-line: lanes that fail the depth guard compute garbage (inf / nan) that the final select discards;
+    // single-instruction reciprocal and square root (flush-to-zero: the guard keeps their arguments above 1e-3 / 2e-4)
     const float vx = fmaf(U.V[0], p.x, fmaf(U.V[4], p.y, fmaf(U.V[8], p.z, U.V[12])));
     const float vy = fmaf(U.V[1], p.x, fmaf(U.V[5], p.y, fmaf(U.V[9], p.z, U.V[13])));
     const float zf = -fmaf(U.V[2], p.x, fmaf(U.V[6], p.y, fmaf(U.V[10], p.z, U.V[14])));
     const float cw = fmaf(U.VP[3], p.x, fmaf(U.VP[7], p.y, fmaf(U.VP[11], p.z, U.VP[15])));
-    if (!(zf > 1e-3f && cw > 1e-3f)) return !(zf < 0.0f && cw < 0.0f && zf < -1e-3f);   // clearly behind the eye: culled by zFront < 1e-4
-    const float rw = __fdividef(1.0f, cw);
+    const bool trusted = zf > 1e-3f && cw > 1e-3f;
+    const bool behind = zf < -1e-3f && cw < 0.0f;            // clearly behind the eye: culled by zFront < 1e-4
+    const float rw = rcp_ftz(cw), iz = rcp_ftz(zf);
     const float ndcz = fmaf(U.VP[2], p.x, fmaf(U.VP[6], p.y, fmaf(U.VP[10], p.z, U.VP[14]))) * rw;
-    if (ndcz < -2e-3f || ndcz > 1.002f) return false;
-    const float cx = fmaf(fmaf(U.VP[0], p.x, fmaf(U.VP[4], p.y, fmaf(U.VP[8], p.z, U.VP[12]))) * rw, 0.5f, 0.5f) * U.W;
-    const float cy = fmaf(fmaf(U.VP[1], p.x, fmaf(U.VP[5], p.y, fmaf(U.VP[9], p.z, U.VP[13]))) * rw, -0.5f, 0.5f) * U.H;
-    const float iz = __fdividef(1.0f, zf), fx = U.P[0] * (U.W * 0.5f) * iz, fy = U.P[5] * (U.H * 0.5f) * iz;
-    const float jx = fx * vx * iz, jy = fy * vy * iz;
-    const float smax = p.w;
-    const float tr = fmaf(fmaf(fx, fx, fmaf(fy, fy, fmaf(jx, jx, jy * jy))) * U.band_bound, smax * smax, 2e-4f);
-    float root;
-    asm("sqrt.approx.f32 %0, %1;" : "=f"(root) : "f"(tr));
-    const float hb = fmaf(3.15f, root, 2.0f);
-    return cx + hb >= 0.0f && cx - hb <= U.W && cy + hb >= (float)(U.row_begin * 16) &&
-           cy - hb <= fminf((float)(U.row_end * 16), U.H);
+    const float cx = fmaf(fmaf(U.VP[0], p.x, fmaf(U.VP[4], p.y, fmaf(U.VP[8], p.z, U.VP[12]))) * rw, U.scr_hw, U.scr_hw);
+    const float cy = fmaf(fmaf(U.VP[1], p.x, fmaf(U.VP[5], p.y, fmaf(U.VP[9], p.z, U.VP[13]))) * rw, -U.scr_hh, U.scr_hh);
+    // trace bound = iz^2 smax^2 B (Fx^2 (1 + (vx iz)^2) + Fy^2 (1 + (vy iz)^2)); Fx^2 B and Fy^2 B come from the host
+    const float ax = vx * iz, ay = vy * iz, si = p.w * iz;
+    const float g = fmaf(U.scr_fx2b, fmaf(ax, ax, 1.0f), U.scr_fy2b * fmaf(ay, ay, 1.0f));
+    const float hb = fmaf(3.15f, sqrt_ftz(fmaf(g, si * si, 2e-4f)), 2.0f);
+    const bool in_view = ndcz >= -2e-3f && ndcz <= 1.002f && cx + hb >= 0.0f && cx - hb <= U.W &&
+                         cy + hb >= U.scr_ylo && cy - hb <= U.scr_yhi;
+    return trusted ? in_view : !behind;
 }
 
 // K1 = preprocess_kernel + tile_scan_kernel.
@@ -146,7 +148,8 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
         }
     }
     __syncthreads();
-    // ---- phase 1: screen, compact the survivors' local indices
+    // ---- phase 1: screen, compact the survivors' local indices (one shared atomic per warp for all its items)
+    unsigned int wm[K1_ITEMS], wtotal = 0;
 #pragma unroll
     for (int k = 0; k < K1_ITEMS; ++k) {
         const unsigned int li = k * 256u + tid, i = base + li;
@@ -154,14 +157,20 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
         if (!GATHER) ps.w = fmaxf(p[k].w, fmaxf(t[k].x, t[k].y));      // x y z max(scale), what the screening plane holds
         const bool keep = i < U.n && may_be_visible(ps, U);
         if (!GATHER && i < U.n && !keep) binw[i] = 0ull;      // band shape: the visibility bitmap says which bin words are live
-        const unsigned int m = __ballot_sync(0xFFFFFFFFu, keep);
-        unsigned int wbase = 0;
-        if (lane == 0 && m) wbase = atomicAdd(&s_count, __popc(m));
-        wbase = __shfl_sync(0xFFFFFFFFu, wbase, 0);
-        if (keep) {
-            s_list[wbase + __popc(m & ((1u << lane) - 1u))] = (unsigned short)li;
+        wm[k] = __ballot_sync(0xFFFFFFFFu, keep);
+        wtotal += __popc(wm[k]);
+    }
+    unsigned int wbase = 0;
+    if (lane == 0 && wtotal) wbase = atomicAdd(&s_count, wtotal);
+    wbase = __shfl_sync(0xFFFFFFFFu, wbase, 0);
+#pragma unroll
+    for (int k = 0; k < K1_ITEMS; ++k) {
+        const unsigned int li = k * 256u + tid;
+        if ((wm[k] >> lane) & 1u) {
+            s_list[wbase + __popc(wm[k] & ((1u << lane) - 1u))] = (unsigned short)li;
             if (!GATHER) { s_p[li] = p[k]; s_t[li] = t[k]; }
         }
+        wbase += __popc(wm[k]);
     }
     __syncthreads();
     // ---- phase 2: the exactly rounded pipeline on dense warps of survivors

@@ -392,7 +392,11 @@ static int build_frame(splat_ctx* c, const float* view, const float* proj, int w
             }
             g = fmaxf(g, rs);
         }
-        U.band_bound = g * 1.02f;
+        const float B = g * 1.02f, Fx = proj[0] * (U.W * 0.5f), Fy = proj[5] * (U.H * 0.5f);
+        U.scr_hw = 0.5f * U.W; U.scr_hh = 0.5f * U.H;
+        U.scr_fx2b = Fx * Fx * B * 1.0001f; U.scr_fy2b = Fy * Fy * B * 1.0001f;
+        U.scr_ylo = (float)(U.row_begin * 16);
+        U.scr_yhi = fminf((float)(U.row_end * 16), U.H);
     }
     const unsigned int T = (unsigned int)(U.tiles_x * U.tiles_y);
     const int tb = tile_bits(T);

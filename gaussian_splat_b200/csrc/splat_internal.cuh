@@ -27,7 +27,10 @@ struct FrameUniforms {
     int mode, order, K, sh_degree;
     float cam[3];
     unsigned int n;
-    float band_bound;   // bound on lambda_max(W^T W) * 1.02, W = V's 3x3 block, for K1's conservative screening bound
+    // K1's screening, precomputed on the host (conservative: each carries its own slack): 0.5 W, 0.5 H,
+    // (P00 W/2)^2 * B and (P11 H/2)^2 * B with B = 1.02 * a bound on lambda_max(W^T W), W = V's 3x3 block,
+    // and the band's pixel rows [scr_ylo, scr_yhi]
+    float scr_hw, scr_hh, scr_fx2b, scr_fy2b, scr_ylo, scr_yhi;
 };
 
 // Device control block, zeroed by one memsetAsync at the start of every frame.
