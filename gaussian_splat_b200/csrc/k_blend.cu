@@ -104,7 +104,7 @@ struct PixelState {
 // of the 8x4-pixel warp blocks it can touch; each warp ballots the masks and visits only its own
 // candidates. Returns when every pixel of the tile is finished or the list ends.
 template <int WALK>
-__device__ __forceinline__ void walk_list(const splat_record* __restrict__ rec, const unsigned int* __restrict__ vals,
+__device__ __forceinline__ void walk_list(const splat_record_row* __restrict__ rec, const unsigned int* __restrict__ vals,
                                           uint2 range, int K, float pxc, float pyc, float tox, float toy,
                                           float4* s_ab, unsigned int* s_cm, PixelState& px, KBuffer& kb)
 {
@@ -240,7 +240,7 @@ __device__ __forceinline__ void walk_list(const splat_record* __restrict__ rec, 
 
 template <int MODE>
 __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
-    const __grid_constant__ FrameUniforms U, const splat_record* __restrict__ rec,
+    const __grid_constant__ FrameUniforms U, const splat_record_row* __restrict__ rec,
     const unsigned int* __restrict__ vals, const unsigned int* __restrict__ vals_depth,
     const unsigned int* __restrict__ bounds, uint2* __restrict__ fb)
 {
@@ -310,7 +310,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
     fb[(size_t)pj * U.w + pi] = out;
 }
 
-void launch_blend(const FrameUniforms& U, const splat_record* rec, const unsigned int* vals_sorted,
+void launch_blend(const FrameUniforms& U, const splat_record_row* rec, const unsigned int* vals_sorted,
                   const unsigned int* vals_depth_sorted, const unsigned int* bounds, void* fb_half4, cudaStream_t s)
 {
     const int rows = U.row_end - U.row_begin;

@@ -123,7 +123,7 @@ __device__ __forceinline__ bool may_be_visible(const float4 p, const FrameUnifor
 // phase 1 and staged through shared memory for phase 2 (the gather shape costs 45 instead of 35 us at 1M).
 template <int K1_ITEMS, bool GATHER>
 __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const __grid_constant__ FrameUniforms U,
-                                                         splat_record* __restrict__ rec, unsigned long long* __restrict__ binw,
+                                                         splat_record_row* __restrict__ rec, unsigned long long* __restrict__ binw,
                                                          unsigned int* __restrict__ tile_sums, unsigned int* __restrict__ visbits)
 {
     constexpr int K1_CTA_SPLATS = 256 * K1_ITEMS;
@@ -215,6 +215,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
         dst[0] = make_float4(r.cx, r.cy, r.ux, r.uy);
         dst[1] = make_float4(r.vx, r.vy, r.opacity, __uint_as_float(r.rg));
         dst[2] = make_float4(__uint_as_float(r.bd), r.z_front, __uint_as_float(r.rect_lo), __uint_as_float(r.rect_hi));
+        dst[3] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);       // the row's padding: both 32-byte sectors written whole
     }
     __syncthreads();
     if (tid < K1_CTA_SPLATS / K1_TILE && base + tid * K1_TILE < U.n) tile_sums[blockIdx.x * (K1_CTA_SPLATS / K1_TILE) + tid] = s_sum[tid];
@@ -256,7 +257,7 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(const unsigned int* __r
     }
 }
 
-void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record* rec, unsigned long long* binw,
+void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record_row* rec, unsigned long long* binw,
                        unsigned int* tile_sums, unsigned int* scan_prefix, unsigned int* visbits, unsigned long long capacity,
                        FrameCtl* ctl, cudaStream_t s)
 {

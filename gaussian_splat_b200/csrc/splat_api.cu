@@ -27,7 +27,7 @@ __global__ void set_n_sort_kernel(FrameCtl* ctl, unsigned int n) { ctl->n_sort =
 // in flight on two streams (at frame sizes K2-K4 are latency-bound and leave most SMs idle). The single
 // frame entry points use set 0 only; the second set is allocated on the first batch call.
 struct FrameSet {
-    splat_record* rec = nullptr; unsigned long long* binw = nullptr; uint32_t* offsets = nullptr;
+    splat_record_row* rec = nullptr; unsigned long long* binw = nullptr; uint32_t* offsets = nullptr;
     uint32_t* keys[2] = {nullptr, nullptr}; uint32_t* vals[2] = {nullptr, nullptr};
     unsigned long long capacity = 0;
     // LAYER50 only: the same pairs in tile | depth order (allocated on the first LAYER50 frame)
@@ -157,10 +157,10 @@ static void free_scene_scratch(splat_ctx* c) {
     c->rec = nullptr; c->binw = nullptr; c->offsets = nullptr; c->tile_sums = nullptr; c->visbits = nullptr;
 }
 static int alloc_scene_scratch(splat_ctx* c, size_t n_pad) {
-    CK(cudaMalloc(&c->rec, n_pad * sizeof(splat_record)));
+    CK(cudaMalloc(&c->rec, n_pad * sizeof(splat_record_row)));
     CK(cudaMalloc(&c->binw, n_pad * 8)); CK(cudaMalloc(&c->offsets, n_pad * 4));
     CK(cudaMemset(c->binw, 0, n_pad * 8));
-    CK(cudaMemset(c->rec, 0, n_pad * sizeof(splat_record)));
+    CK(cudaMemset(c->rec, 0, n_pad * sizeof(splat_record_row)));
     const size_t sums = n_pad / (SCAN_TILE_ITEMS / 2) + n_pad / SCAN_TILE_ITEMS + 2;   // [n/512] sums, then [n/1024] prefixes
     CK(cudaMalloc(&c->tile_sums, sums * 4));
     CK(cudaMemset(c->tile_sums, 0, sums * 4));
@@ -772,7 +772,7 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
     const size_t T = (size_t)c->lastU.tiles_x * c->lastU.tiles_y;
     const void* src = nullptr; size_t need = 0;
     switch (what) {
-        case SPLAT_FETCH_RECORDS:       src = c->rec;      need = (size_t)c->n * sizeof(splat_record); break;
+        case SPLAT_FETCH_RECORDS:       src = nullptr;     need = (size_t)c->n * sizeof(splat_record); break;
         case SPLAT_FETCH_TILES_TOUCHED: src = nullptr;     need = (size_t)c->n * 4; break;   // derived from the bin words below
         case SPLAT_FETCH_OFFSETS:       src = c->offsets;  need = (size_t)c->n * 4; break;
         case SPLAT_FETCH_KEYS_UNSORTED: src = c->dbg_keys; need = D * 8; break;
@@ -822,8 +822,13 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
         if (D && by_instance) CK(cudaMemcpy(v32.data(), sorted ? c->vals[c->sorted_buf] : c->dbg_vals, D * 4, cudaMemcpyDeviceToHost));
         for (size_t i = 0; i < D; ++i)
             ((uint64_t*)dst)[i] = ((uint64_t)(k32[i] >> 16) << 32) | (by_instance ? v32[i] : (k32[i] & 0xFFFFu));
-    } else if (need) CK(cudaMemcpy(dst, src, need, cudaMemcpyDeviceToHost));
+    } else if (need && src) CK(cudaMemcpy(dst, src, need, cudaMemcpyDeviceToHost));
     if (what == SPLAT_FETCH_RECORDS && c->n) {
+        {   // device rows are 64 bytes (splat_record_row): present the 48-byte records
+            std::vector<splat_record_row> rows(c->n);
+            CK(cudaMemcpy(rows.data(), c->rec, (size_t)c->n * sizeof(splat_record_row), cudaMemcpyDeviceToHost));
+            for (uint32_t i = 0; i < c->n; ++i) ((splat_record*)dst)[i] = rows[i].r;
+        }
         // culled splats have no record written: present them zeroed
         std::vector<unsigned long long> t;
         CK(fetch_binw(c, t));

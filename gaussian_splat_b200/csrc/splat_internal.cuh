@@ -33,6 +33,11 @@ struct FrameUniforms {
     float scr_hw, scr_hh, scr_fx2b, scr_fy2b, scr_ylo, scr_yhi;
 };
 
+// Device layout of the records: the 48-byte splat_record padded to one aligned 64-byte row, so K1's scattered record
+// writes fill whole 32-byte sectors (a 48-byte stride left partial sectors: read-modify-write in L2 / DRAM, ncu had
+// 182 MB of DRAM reads on a band frame whose inputs are 125 MB) and the blend's gathers touch exactly two sectors.
+struct alignas(64) splat_record_row { splat_record r; unsigned int pad[4]; };
+
 // Device control block, zeroed by one memsetAsync at the start of every frame.
 struct FrameCtl {
     unsigned long long total_pairs;   // D (exact even when it exceeds capacity)
@@ -140,7 +145,7 @@ __host__ __device__ __forceinline__ unsigned int binw_count(unsigned long long w
 // CTA); K2 walks those bitmaps instead of every bin word.
 #define BAND_TILE 2048u
 static inline bool frame_is_band(const FrameUniforms& U) { return (U.row_end - U.row_begin) * 2 <= U.tiles_y; }
-void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record* rec, unsigned long long* binw,
+void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record_row* rec, unsigned long long* binw,
                        unsigned int* tile_sums, unsigned int* scan_prefix, unsigned int* visbits, unsigned long long capacity, FrameCtl* ctl,
                        cudaStream_t s);
 void launch_scan_duplicate(const FrameUniforms& U, const unsigned long long* binw,
@@ -170,5 +175,5 @@ void launch_pack_bgra8(const void* fb_half4, void* bgra8, size_t n_pixels, cudaS
 cudaError_t launch_ply_decode_chunk(const float* rows_dev, unsigned int n_rows, unsigned int stride, const int* slot_dst_dev,
                                     int jx, int jy, int jz, float crop, unsigned int* block_counts, unsigned int* running,
                                     float* aos_out, float* sh_out, cudaStream_t s);
-void launch_blend(const FrameUniforms& U, const splat_record* rec, const unsigned int* vals_sorted,
+void launch_blend(const FrameUniforms& U, const splat_record_row* rec, const unsigned int* vals_sorted,
                   const unsigned int* vals_depth_sorted, const unsigned int* bounds, void* fb_half4, cudaStream_t s);
