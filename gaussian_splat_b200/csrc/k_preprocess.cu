@@ -119,7 +119,7 @@ __device__ __forceinline__ bool may_be_visible(const float4 p, const FrameUnifor
 // so K2 needs neither tickets nor a lookback chain.
 // Two shapes. Tile-row bands (few survivors): K1_ITEMS = 8 (2048 splats per CTA), screening reads only the
 // 16-byte screening plane and the survivors gather their other planes (6M-splat band: 115 -> 85 us). Whole
-// frames (a CTA is half full of survivors): K1_ITEMS = 2, the position / scale planes are read coalesced in
+// frames (a CTA is half full of survivors): K1_ITEMS = 4, the position / scale planes are read coalesced in
 // phase 1 and staged through shared memory for phase 2 (the gather shape costs 45 instead of 35 us at 1M).
 template <int K1_ITEMS, bool GATHER>
 __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const __grid_constant__ FrameUniforms U,

@@ -1,4 +1,4 @@
-// K2: exclusive scan of tiles_touched (tile prefixes come from K1's last CTA, so there is no ticket and
+// K2: exclusive scan of tiles_touched (tile prefixes come from tile_scan_kernel, so there is no ticket and
 // no lookback chain here) fused with (tile | depth) key / value duplication and the radix-sort digit histograms.
 // Replaces the hardware tiler's binning of the instanced quads
 // (src/instanced_splat_renderer.mm:496-499 draw call).
