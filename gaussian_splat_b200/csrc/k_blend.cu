@@ -1,4 +1,4 @@
-// K4 tile ranges and K5 per-16x16-tile blend.
+// K5: per-16x16-tile blend (the tile lists and their bounds come from k_bin.cu).
 // K5 folds the reference's fragment stage and per-pixel sort+composite into one kernel:
 //   TILE    fragment_main + tile_sort_composite   shaders/gaussian_splat_tile.metal:178-267
 //   LAYER50 fragment_accumulate + compute_sort_composite
@@ -8,39 +8,6 @@
 // Per-pixel fragment lists never touch HBM (the reference keeps 504 B/pixel there and
 // clears it every frame, src/instanced_splat_renderer.mm:256-262,475-477).
 #include "splat_math.cuh"
-
-// ------------------------------------------------------------------ K4
-// bounds[t] = lower_bound(keys, t << 16) for t = 0..T; tile t owns [bounds[t], bounds[t+1]).
-// One warp per boundary, 32 probes per round (5 dependent L2 round trips for D < 32M instead of
-// the 21+ of a scalar binary search; the kernel is pure latency).
-__global__ void __launch_bounds__(256) tile_bounds_kernel(const unsigned int* __restrict__ keys,
-                                                          const FrameCtl* __restrict__ ctl, unsigned int first,
-                                                          unsigned int n_bounds, unsigned int* __restrict__ bounds)
-{
-    pdl_prologue();
-    const unsigned int t = first + blockIdx.x * 8u + (threadIdx.x >> 5), lane = threadIdx.x & 31u;
-    if (t >= first + n_bounds) return;
-    const unsigned int n = ctl->overflow ? 0u : ctl->n_sort;
-    const unsigned long long x = (unsigned long long)t << 16;      // 64-bit: t == 65536 is past every key
-    unsigned int lo = 0, hi = n;
-    while (lo < hi) {
-        const unsigned int span = hi - lo;
-        const unsigned int pos = lo + (unsigned int)(((unsigned long long)(lane + 1) * span) / 33u);
-        const unsigned int c = __popc(__ballot_sync(0xFFFFFFFFu, (unsigned long long)__ldg(keys + pos) < x));
-        const unsigned int new_lo = c == 0 ? lo : lo + (unsigned int)(((unsigned long long)c * span) / 33u) + 1u;
-        const unsigned int new_hi = c == 32 ? hi : lo + (unsigned int)(((unsigned long long)(c + 1) * span) / 33u);
-        lo = new_lo; hi = new_hi;
-    }
-    if (lane == 0) bounds[t] = lo;
-}
-
-// Only tiles [first_tile, first_tile + n_tiles] get a boundary: with a tile-row band that is the band (the blend
-// reads nothing else), which keeps this latency-bound kernel to one wave of CTAs.
-void launch_tile_bounds(const unsigned int* keys_sorted, const FrameCtl* ctl, unsigned int first_tile,
-                        unsigned int n_tiles, unsigned int* bounds, cudaStream_t s)
-{
-    launch_pdl(tile_bounds_kernel, dim3((n_tiles + 1 + 7) / 8), dim3(256), 0, s, keys_sorted, ctl, first_tile, n_tiles + 1, bounds);
-}
 
 // ------------------------------------------------------------------ K5
 #define BLEND_THREADS 256
@@ -103,8 +70,11 @@ struct PixelState {
 // memory. Each staging thread also derives a conservative pixel AABB of its splat and an 8-bit mask
 // of the 8x4-pixel warp blocks it can touch; each warp ballots the masks and visits only its own
 // candidates. Returns when every pixel of the tile is finished or the list ends.
-template <int WALK>
-__device__ __forceinline__ void walk_list(const splat_record_row* __restrict__ rec, const unsigned int* __restrict__ vals,
+// vals[VSTRIDE * e] = instance index of list entry e (VSTRIDE 2: the low words of the 64-bit pairs, 1: LAYER50's arrival list).
+// rec / vals are written earlier in the same frame by kernels this one is linked to by programmatic dependent launch:
+// they are read through L2 (ld.global.cg), not through the non-coherent path.
+template <int WALK, int VSTRIDE>
+__device__ __forceinline__ void walk_list(const splat_record_row* rec, const unsigned int* vals,
                                           uint2 range, int K, float pxc, float pyc, float tox, float toy,
                                           float4* s_ab, unsigned int* s_cm, PixelState& px, KBuffer& kb)
 {
@@ -120,17 +90,17 @@ __device__ __forceinline__ void walk_list(const splat_record_row* __restrict__ r
         const unsigned int nb = min((unsigned int)BLEND_BATCH, range.y - b0);
         unsigned int wmask = 0;
         if (tid < nb) {
-            const unsigned int si = __ldg(vals + b0 + tid);
+            const unsigned int si = __ldcg(vals + (size_t)(b0 + tid) * VSTRIDE);
             const float4* r = reinterpret_cast<const float4*>(rec + si);
-            const float4 A = __ldg(r), B = __ldg(r + 1);
+            const float4 A = __ldcg(r), B = __ldcg(r + 1);
             s_a[tid] = A;
             s_b[tid] = B;
             if (WALK != WALK_COUNT) {
                 // TILE: (b, 1.0h) so that one half2 multiply gives (b * src, src); UNDER: (b, 0); MLAB: (b, depth) as stored
-                const unsigned int bd = __float_as_uint(__ldg(reinterpret_cast<const float*>(r + 2)));
+                const unsigned int bd = __float_as_uint(__ldcg(reinterpret_cast<const float*>(r + 2)));
                 s_c[tid] = WALK == WALK_TILE ? ((bd & 0xFFFFu) | 0x3C000000u) : WALK == WALK_UNDER ? (bd & 0xFFFFu) : bd;
             }
-            const bool too_near = WALK == WALK_MLAB && __ldg(reinterpret_cast<const float*>(r + 2) + 1) < 0.001f;   // gaussian_splat.metal:209
+            const bool too_near = WALK == WALK_MLAB && __ldcg(reinterpret_cast<const float*>(r + 2) + 1) < 0.001f;   // gaussian_splat.metal:209
             if (WALK != WALK_TILE) s_i[tid] = si;
             // Conservative pixel AABB of {q <= 9.2103404}: d = Winv (u,v), Winv = [vy -uy; -vx ux] / det.
             // Only used to skip 8x4 pixel blocks the splat cannot touch; never changes a result.
@@ -240,9 +210,9 @@ __device__ __forceinline__ void walk_list(const splat_record_row* __restrict__ r
 
 template <int MODE>
 __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
-    const __grid_constant__ FrameUniforms U, const splat_record_row* __restrict__ rec,
-    const unsigned int* __restrict__ vals, const unsigned int* __restrict__ vals_depth,
-    const unsigned int* __restrict__ bounds, uint2* __restrict__ fb)
+    const __grid_constant__ FrameUniforms U, const splat_record_row* rec,
+    const unsigned int* pairs_lo, const unsigned int* arrival,
+    const unsigned int* bounds, uint2* __restrict__ fb)
 {
     __shared__ float4 s_ab[2 * BLEND_BATCH];        // [0..B): cx cy ux uy   [B..2B): vx vy opacity rg
     __shared__ unsigned int s_cm[3 * BLEND_BATCH];  // [0..B): bd   [B..2B): 8x4-block mask   [2B..3B): instance index
@@ -255,7 +225,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
     const bool inside = pi < U.w && pj < U.h;
     const float pxc = (float)pi + 0.5f, pyc = (float)pj + 0.5f;
     const float tox = (float)(tx * 16), toy = (float)(ty * 16);
-    const uint2 range = make_uint2(__ldg(bounds + tile), __ldg(bounds + tile + 1));
+    const uint2 range = make_uint2(__ldcg(bounds + tile), __ldcg(bounds + tile + 1));
     const int K = U.K;
 
     PixelState px;
@@ -265,14 +235,14 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
     if (MODE == SPLAT_MODE_TILE) {
         px.accBA = px.accRG;
         px.rem = inside ? K : 0;
-        walk_list<WALK_TILE>(rec, vals, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
+        walk_list<WALK_TILE, 2>(rec, pairs_lo, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
     } else if (MODE == SPLAT_MODE_MLAB) {
         const __half h0 = __ushort_as_half(0), h1 = __ushort_as_half(0x3C00);
 #pragma unroll
         for (int k = 0; k < 6; ++k) { kb.rg[k] = __halves2half2(h0, h0); kb.ba[k] = __halves2half2(h0, h1); kb.d[k] = k == 3 ? h1 : h0; }
         px.accBA = px.accRG;
         px.rem = inside ? K : 0;                       // K = INT_MAX: a pixel never closes
-        walk_list<WALK_MLAB>(rec, vals, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
+        walk_list<WALK_MLAB, 2>(rec, pairs_lo, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
         // resolve_main: composite the six layers front to back
         __half2 crg = __halves2half2(h0, h0); __half cb = h0, at = h1;
 #pragma unroll
@@ -290,12 +260,12 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
         // the reference (504 B/pixel in device memory) are never materialised.
         if (range.y - range.x > (unsigned int)K) {
             px.rem = inside ? K : 0;
-            walk_list<WALK_COUNT>(rec, vals, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
+            walk_list<WALK_COUNT, 1>(rec, arrival, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
             __syncthreads();
         }
         px.accBA = __halves2half2(__ushort_as_half(0), __ushort_as_half(0x3C00));   // accumVis = 1
         px.rem = inside ? K : 0;
-        walk_list<WALK_UNDER>(rec, vals_depth, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
+        walk_list<WALK_UNDER, 2>(rec, pairs_lo, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
     }
     if (!inside) return;
     uint2 out;
@@ -310,16 +280,17 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
     fb[(size_t)pj * U.w + pi] = out;
 }
 
-void launch_blend(const FrameUniforms& U, const splat_record_row* rec, const unsigned int* vals_sorted,
-                  const unsigned int* vals_depth_sorted, const unsigned int* bounds, void* fb_half4, cudaStream_t s)
+void launch_blend(const FrameUniforms& U, const splat_record_row* rec, const unsigned long long* pairs,
+                  const unsigned int* arrival, const unsigned int* bounds, void* fb_half4, cudaStream_t s)
 {
     const int rows = U.row_end - U.row_begin;
     if (rows <= 0 || U.tiles_x <= 0) return;
     const dim3 grid(U.tiles_x, rows);
+    const unsigned int* lo = reinterpret_cast<const unsigned int*>(pairs);      // little endian: the instance index is word 0 of a pair
     if (U.mode == SPLAT_MODE_MLAB)
-        launch_pdl(blend_kernel<SPLAT_MODE_MLAB>, grid, dim3(BLEND_THREADS), 0, s, U, rec, vals_sorted, vals_sorted, bounds, reinterpret_cast<uint2*>(fb_half4));
+        launch_pdl(blend_kernel<SPLAT_MODE_MLAB>, grid, dim3(BLEND_THREADS), 0, s, U, rec, lo, arrival, bounds, reinterpret_cast<uint2*>(fb_half4));
     else if (U.mode == SPLAT_MODE_LAYER50)
-        launch_pdl(blend_kernel<SPLAT_MODE_LAYER50>, grid, dim3(BLEND_THREADS), 0, s, U, rec, vals_sorted, vals_depth_sorted, bounds, reinterpret_cast<uint2*>(fb_half4));
+        launch_pdl(blend_kernel<SPLAT_MODE_LAYER50>, grid, dim3(BLEND_THREADS), 0, s, U, rec, lo, arrival, bounds, reinterpret_cast<uint2*>(fb_half4));
     else
-        launch_pdl(blend_kernel<SPLAT_MODE_TILE>, grid, dim3(BLEND_THREADS), 0, s, U, rec, vals_sorted, vals_sorted, bounds, reinterpret_cast<uint2*>(fb_half4));
+        launch_pdl(blend_kernel<SPLAT_MODE_TILE>, grid, dim3(BLEND_THREADS), 0, s, U, rec, lo, arrival, bounds, reinterpret_cast<uint2*>(fb_half4));
 }

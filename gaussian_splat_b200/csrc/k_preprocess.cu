@@ -7,8 +7,7 @@
 __global__ void __launch_bounds__(256) upload_soa_kernel(const float* __restrict__ aos, unsigned int n,
                                                          float4* __restrict__ rot, float4* __restrict__ pos_sx,
                                                          float4* __restrict__ syz_op_rg, uint16_t* __restrict__ bq,
-                                                         float4* __restrict__ base_rgb, float4* __restrict__ scr,
-                                                         float4* __restrict__ row)
+                                                         float4* __restrict__ base_rgb)
 {
     // Stage 256 rows (256*14 floats) through shared memory so the AoS read is coalesced.
     __shared__ float s[256 * 14];
@@ -27,12 +26,6 @@ __global__ void __launch_bounds__(256) upload_soa_kernel(const float* __restrict
     const unsigned int v_b = __half_as_ushort(__float2half_rn(r[12]));
     rot[i] = v_rot; pos_sx[i] = v_pos; syz_op_rg[i] = v_syz; bq[i] = (uint16_t)v_b;
     base_rgb[i] = make_float4(r[10], r[11], r[12], 0.0f);
-    scr[i] = make_float4(r[7], r[8], r[9], fmaxf(r[4], fmaxf(r[5], r[6])));     // all the screening kernel reads: 16 B / splat
-    // the same attributes once more as one aligned 64-byte row: what a band frame's survivors gather (one DRAM
-    // burst instead of four 32-byte sectors of four planes)
-    float4* rw = row + (size_t)i * 4;
-    rw[0] = v_rot; rw[1] = v_pos; rw[2] = v_syz;
-    rw[3] = make_float4(__uint_as_float(v_b), 0.0f, 0.0f, 0.0f);
 }
 
 // f_rest rows (45 floats, channel-major as src/ply_loader.cpp:76-81 stores them) -> 12 float4 planes,
@@ -67,10 +60,10 @@ void launch_upload_sh(const float* sh_rest45_dev, unsigned int n, size_t n_pad, 
 }
 
 void launch_upload_soa(const float* aos_dev, unsigned int n, float4* rot, float4* pos_sx, float4* syz_op_rg,
-                       uint16_t* b, float4* base_rgb, float4* scr, float4* row, cudaStream_t s)
+                       uint16_t* b, float4* base_rgb, cudaStream_t s)
 {
     if (n == 0) return;
-    upload_soa_kernel<<<(n + 255) / 256, 256, 0, s>>>(aos_dev, n, rot, pos_sx, syz_op_rg, b, base_rgb, scr, row);
+    upload_soa_kernel<<<(n + 255) / 256, 256, 0, s>>>(aos_dev, n, rot, pos_sx, syz_op_rg, b, base_rgb);
 }
 
 #define K1_TILE (SCAN_TILE_ITEMS / 2)      // splats per pair-count cell (two cells per duplication tile)
@@ -109,43 +102,33 @@ __device__ __forceinline__ bool may_be_visible(const float4 p, const FrameUnifor
 }
 
 // K1 = preprocess_kernel + tile_scan_kernel.
-// preprocess_kernel: a CTA owns 2048 splats. (1) Screening from the 16-byte screening plane, 8 splats per
-// thread with all loads issued first; culled splats get a zero bin word. (2) The survivors' local indices
-// are compacted in shared memory. (3) The exactly rounded ~600-instruction pipeline runs on dense warps of
-// survivors, gathering their other planes. With 512-splat CTAs a tile-row band left ~37 survivors per CTA:
-// two warps worked while six waited at the barrier (ncu: 9.7 barrier-stalled warps per issue); a split into
-// separate screening / exact kernels was tried and lost more to the extra launch and the list round trip
-// than it won. The CTA also leaves the pair count of each of its four 512-splat cells for tile_scan_kernel,
-// so K2 needs neither tickets nor a lookback chain.
-// Two shapes. Tile-row bands (few survivors): K1_ITEMS = 8 (2048 splats per CTA), screening reads only the
-// 16-byte screening plane and the survivors gather their other planes (6M-splat band: 115 -> 85 us). Whole
-// frames (a CTA is half full of survivors): K1_ITEMS = 4, the position / scale planes are read coalesced in
-// phase 1 and staged through shared memory for phase 2 (the gather shape costs 45 instead of 35 us at 1M).
-template <int K1_ITEMS, bool GATHER>
+// preprocess_kernel: a CTA owns 1024 splats. (1) Screening, 4 splats per thread with all loads issued first (position /
+// scale planes read coalesced and kept in shared memory for phase 3); culled splats get a zero bin word. (2) The
+// survivors' local indices are compacted in shared memory. (3) The exactly rounded ~600-instruction pipeline runs on
+// dense warps of survivors. The CTA also leaves the candidate count (tile-rectangle area) of each of its two 512-splat
+// cells for tile_scan_kernel, so K2 needs neither tickets nor a lookback chain. History: 512-splat CTAs left two warps
+// working while six waited at the barrier; separate screening / exact kernels lost more to the extra launch and the
+// list round trip than they won.
+#define K1_ITEMS 4
 __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const __grid_constant__ FrameUniforms U,
                                                          splat_record_row* __restrict__ rec, unsigned long long* __restrict__ binw,
-                                                         unsigned int* __restrict__ tile_sums, unsigned int* __restrict__ visbits)
+                                                         unsigned int* __restrict__ tile_sums)
 {
     constexpr int K1_CTA_SPLATS = 256 * K1_ITEMS;
-    static_assert(K1_CTA_SPLATS % K1_TILE == 0, "a CTA covers whole pair-count cells");
+    static_assert(K1_CTA_SPLATS % K1_TILE == 0, "a CTA covers whole candidate-count cells");
     __shared__ unsigned short s_list[K1_CTA_SPLATS];
     __shared__ unsigned int s_count, s_sum[K1_CTA_SPLATS / K1_TILE];
-    __shared__ unsigned int s_vis[GATHER ? K1_CTA_SPLATS / 32 : 1];     // band shape: which of the CTA's splats produced pairs
-    __shared__ float4 s_p[GATHER ? 1 : K1_CTA_SPLATS], s_t[GATHER ? 1 : K1_CTA_SPLATS];
+    __shared__ float4 s_p[K1_CTA_SPLATS], s_t[K1_CTA_SPLATS];
     const unsigned int tid = threadIdx.x, lane = tid & 31;
     const unsigned int base = blockIdx.x * (unsigned int)K1_CTA_SPLATS;
     pdl_prologue();
     if (tid == 0) s_count = 0;
     if (tid < K1_CTA_SPLATS / K1_TILE) s_sum[tid] = 0;
-    if (GATHER && tid < K1_CTA_SPLATS / 32) s_vis[tid] = 0;
-    float4 p[K1_ITEMS], t[GATHER ? 1 : K1_ITEMS];
+    float4 p[K1_ITEMS], t[K1_ITEMS];
 #pragma unroll
     for (int k = 0; k < K1_ITEMS; ++k) {
         const unsigned int i = base + k * 256u + tid;
-        if (i < U.n) {
-            if (GATHER) p[k] = __ldg(sp.scr + i);
-            else { p[k] = __ldg(sp.pos_sx + i); t[k] = __ldg(sp.syz_op_rg + i); }
-        }
+        if (i < U.n) { p[k] = __ldg(sp.pos_sx + i); t[k] = __ldg(sp.syz_op_rg + i); }
     }
     __syncthreads();
     // ---- phase 1: screen, compact the survivors' local indices (one shared atomic per warp for all its items)
@@ -154,9 +137,9 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
     for (int k = 0; k < K1_ITEMS; ++k) {
         const unsigned int li = k * 256u + tid, i = base + li;
         float4 ps = p[k];
-        if (!GATHER) ps.w = fmaxf(p[k].w, fmaxf(t[k].x, t[k].y));      // x y z max(scale), what the screening plane holds
+        ps.w = fmaxf(p[k].w, fmaxf(t[k].x, t[k].y));      // x y z max(scale)
         const bool keep = i < U.n && may_be_visible(ps, U);
-        if (!GATHER && i < U.n && !keep) binw[i] = 0ull;      // band shape: the visibility bitmap says which bin words are live
+        if (i < U.n && !keep) binw[i] = 0ull;
         wm[k] = __ballot_sync(0xFFFFFFFFu, keep);
         wtotal += __popc(wm[k]);
     }
@@ -168,7 +151,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
         const unsigned int li = k * 256u + tid;
         if ((wm[k] >> lane) & 1u) {
             s_list[wbase + __popc(wm[k] & ((1u << lane) - 1u))] = (unsigned short)li;
-            if (!GATHER) { s_p[li] = p[k]; s_t[li] = t[k]; }
+            s_p[li] = p[k]; s_t[li] = t[k];
         }
         wbase += __popc(wm[k]);
     }
@@ -177,16 +160,14 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
     const unsigned int n_keep = s_count;
     for (unsigned int j = tid; j < n_keep; j += 256u) {
         const unsigned int li = s_list[j], i = base + li;
-        const float4* rw = sp.row + (size_t)i * 4;
-        const float4 pp = GATHER ? __ldg(rw + 1) : s_p[li], tt = GATHER ? __ldg(rw + 2) : s_t[li];
-        const float4 q = GATHER ? __ldg(rw) : __ldg(sp.rot + i);
-        const unsigned int bh = GATHER ? __ldg(reinterpret_cast<const unsigned int*>(rw + 3)) : (unsigned int)__ldg(sp.b + i);
+        const float4 pp = s_p[li], tt = s_t[li];
+        const float4 q = __ldg(sp.rot + i);
+        const unsigned int bh = (unsigned int)__ldg(sp.b + i);
         splat_record r;
         const unsigned int cnt = preprocess_one(q.x, q.y, q.z, q.w, pp.w, tt.x, tt.y, pp.x, pp.y, pp.z,
                                                 __float_as_uint(tt.w), bh, tt.z, U, r);
-        if (!GATHER) binw[i] = cnt ? binw_pack(r.rect_lo, r.rect_hi, r.bd >> 16) : 0ull;
+        binw[i] = cnt ? binw_pack(r.rect_lo, r.rect_hi, r.bd >> 16) : 0ull;
         if (cnt == 0) continue;
-        if (GATHER) { binw[i] = binw_pack(r.rect_lo, r.rect_hi, r.bd >> 16); atomicOr(&s_vis[li >> 5], 1u << (li & 31u)); }
         atomicAdd(&s_sum[li / K1_TILE], cnt);       // fits: 512 splats x at most 65536 tiles each < 2^32
         if (U.sh_degree > 0) {
             // D11: colour = max(0, loader colour + sum_{k>=1} basis_k(dir) * f_rest[k][channel]), then half
@@ -211,15 +192,16 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
                    ((unsigned int)__half_as_ushort(__float2half_rn(fmaxf(col[1], 0.0f))) << 16);
             r.bd = (r.bd & 0xFFFF0000u) | (unsigned int)__half_as_ushort(__float2half_rn(fmaxf(col[2], 0.0f)));
         }
+        float kx, ky;
+        tile_ratios(r.ux, r.uy, r.vx, r.vy, kx, ky);         // what K2's per-tile test needs beside the record: the row's padding
         float4* dst = reinterpret_cast<float4*>(rec + i);
         dst[0] = make_float4(r.cx, r.cy, r.ux, r.uy);
         dst[1] = make_float4(r.vx, r.vy, r.opacity, __uint_as_float(r.rg));
         dst[2] = make_float4(__uint_as_float(r.bd), r.z_front, __uint_as_float(r.rect_lo), __uint_as_float(r.rect_hi));
-        dst[3] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);       // the row's padding: both 32-byte sectors written whole
+        dst[3] = make_float4(kx, ky, 0.0f, 0.0f);           // both 32-byte sectors of the row written whole
     }
     __syncthreads();
     if (tid < K1_CTA_SPLATS / K1_TILE && base + tid * K1_TILE < U.n) tile_sums[blockIdx.x * (K1_CTA_SPLATS / K1_TILE) + tid] = s_sum[tid];
-    if (GATHER && tid < K1_CTA_SPLATS / 32) visbits[blockIdx.x * (K1_CTA_SPLATS / 32) + tid] = s_vis[tid];
 }
 
 __global__ void __launch_bounds__(1024) tile_scan_kernel(const unsigned int* __restrict__ tile_sums, unsigned int* __restrict__ scan_prefix,
@@ -251,18 +233,16 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(const unsigned int* __r
     }
     if (tid == 0) {
         const bool over = total > capacity;
-        ctl->total_pairs = total;
-        ctl->n_sort = over ? (unsigned int)capacity : (unsigned int)total;
+        ctl->total_cand = total;
+        ctl->n_cand = over ? (unsigned int)capacity : (unsigned int)total;
         ctl->overflow = over ? 1u : 0u;
     }
 }
 
 void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record_row* rec, unsigned long long* binw,
-                       unsigned int* tile_sums, unsigned int* scan_prefix, unsigned int* visbits, unsigned long long capacity,
-                       FrameCtl* ctl, cudaStream_t s)
+                       unsigned int* tile_sums, unsigned int* scan_prefix, unsigned long long capacity, FrameCtl* ctl, cudaStream_t s)
 {
     if (U.n == 0) return;
-    if (frame_is_band(U)) launch_pdl(preprocess_kernel<BAND_TILE / 256, true>, dim3((U.n + BAND_TILE - 1u) / BAND_TILE), dim3(256), 0, s, sp, U, rec, binw, tile_sums, visbits);
-    else launch_pdl(preprocess_kernel<4, false>, dim3((U.n + 1023u) / 1024u), dim3(256), 0, s, sp, U, rec, binw, tile_sums, visbits);
+    launch_pdl(preprocess_kernel, dim3((U.n + 1023u) / 1024u), dim3(256), 0, s, sp, U, rec, binw, tile_sums);
     launch_pdl(tile_scan_kernel, dim3(1), dim3(1024), 0, s, (const unsigned int*)tile_sums, scan_prefix, U.n, capacity, ctl);
 }

@@ -1,6 +1,6 @@
-// K3: stable LSD "onesweep" radix sort of (key, uint32 value) pairs, 8-bit digits. Keys are 32 bits wide in
-// frames (tile << 16 | half depth: 16 B per pair and pass) and 64 bits wide in the stand-alone entry point
-// (24 B per pair and pass). One kernel per digit pass; each pass reads and writes every pair exactly once. Per-warp
+// Stable LSD "onesweep" radix sort of (key, uint32 value) pairs, 8-bit digits: the stand-alone sort entry points
+// (splat_sort_pairs_u64_u32 / _u32_u32: 24 / 16 B per pair and pass) and the Morton ordering of the scene at upload.
+// Frames no longer sort their pairs globally (k_bin.cu: per-tile lists sorted in shared memory). One kernel per digit pass; each pass reads and writes every pair exactly once. Per-warp
 // digit ranks come from eight ballots per key, tile prefixes from an epoch-tagged decoupled lookback per digit. Replaces the per-pixel insertion sorts of
 // shaders/gaussian_splat_tile.metal:240-249 / gaussian_splat_50layer.metal:198-206 with
 // one global (tile | depth) sort.
@@ -20,7 +20,7 @@
 
 template <typename KeyT>
 __global__ void __launch_bounds__(256) sort_histogram_kernel(const KeyT* __restrict__ keys,
-                                                             unsigned long long n, FrameCtl* ctl,
+                                                             unsigned long long n, SortCtl* ctl,
                                                              const __grid_constant__ SortPlan plan)
 {
     __shared__ unsigned int h[SPLAT_MAX_SORT_PASSES][256];
@@ -38,7 +38,7 @@ __global__ void __launch_bounds__(256) sort_histogram_kernel(const KeyT* __restr
     }
 }
 
-void launch_sort_histogram(const void* keys, int key_bytes, unsigned long long n, FrameCtl* ctl, SortPlan plan,
+void launch_sort_histogram(const void* keys, int key_bytes, unsigned long long n, SortCtl* ctl, SortPlan plan,
                            int sm_count, cudaStream_t s)
 {
     if (n == 0) return;
@@ -85,7 +85,7 @@ template <int ITEMS, typename KeyT, int RANK_SETS>
 __device__ __forceinline__ void onesweep_pass_body(
     const KeyT* __restrict__ keys_in, const unsigned int* __restrict__ vals_in,
     KeyT* __restrict__ keys_out, unsigned int* __restrict__ vals_out,
-    FrameCtl* ctl, unsigned long long* status, unsigned int epoch, int pass, int tix, int shift, unsigned int mask,
+    SortCtl* ctl, unsigned long long* status, unsigned int epoch, int pass, int tix, int shift, unsigned int mask,
     unsigned long long* s_raw, SortShared& sh)
 {
     constexpr int TILE_KEYS = SORT_THREADS * ITEMS;
@@ -307,7 +307,7 @@ template <int ITEMS, typename KeyT, int SETS, int SETS_LONG, int MIN_CTAS>
 __global__ void __launch_bounds__(SORT_THREADS, MIN_CTAS) onesweep_pass_kernel(
     const KeyT* __restrict__ keys_in, const unsigned int* __restrict__ vals_in,
     KeyT* __restrict__ keys_out, unsigned int* __restrict__ vals_out,
-    FrameCtl* ctl, unsigned long long* status, unsigned int epoch, int pass, int tix, int shift, unsigned int mask)
+    SortCtl* ctl, unsigned long long* status, unsigned int epoch, int pass, int tix, int shift, unsigned int mask)
 {
     extern __shared__ unsigned long long s_raw[];
     __shared__ SortShared sh;
@@ -319,16 +319,13 @@ __global__ void __launch_bounds__(SORT_THREADS, MIN_CTAS) onesweep_pass_kernel(
 }
 
 template <int ITEMS, typename KeyT, int SETS, int SETS_LONG, int MIN_CTAS>
-static void run_passes(KeyT* ki, unsigned int* vi, KeyT* ko, unsigned int* vo, FrameCtl* ctl,
+static void run_passes(KeyT* ki, unsigned int* vi, KeyT* ko, unsigned int* vo, SortCtl* ctl,
                        unsigned long long* sort_status, unsigned int epoch_base, const SortPlan& plan, int grid,
                        cudaStream_t s)
 {
     constexpr int smem = SORT_THREADS * ITEMS * ((int)sizeof(KeyT) + 4) + (SETS > SETS_LONG ? SETS : SETS_LONG) * SORT_WARPS * 256 * 2;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(onesweep_pass_kernel<ITEMS, KeyT, SETS, SETS_LONG, MIN_CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        attr_set = true;
-    }
+    // function attributes are per device: set on every call (cheap), so a second context on another device works
+    cudaFuncSetAttribute(onesweep_pass_kernel<ITEMS, KeyT, SETS, SETS_LONG, MIN_CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     for (int p = 0; p < plan.n_pass; ++p) {
         launch_pdl(onesweep_pass_kernel<ITEMS, KeyT, SETS, SETS_LONG, MIN_CTAS>, dim3(grid), dim3(SORT_THREADS), smem, s,
                    (const KeyT*)ki, (const unsigned int*)vi, ko, vo, ctl, sort_status, epoch_base + p,
@@ -342,7 +339,7 @@ static void run_passes(KeyT* ki, unsigned int* vi, KeyT* ko, unsigned int* vo, F
 // (1.6M, 12M, 64M pairs: the per-tile fixed costs dominate), so callers pass false; kept as a tuning
 // knob (SPLAT_SORT_TILE=small|large).
 void launch_radix_sort(void* keys, unsigned int* vals, void* keys_alt, unsigned int* vals_alt, int key_bytes,
-                       unsigned long long n_hint, FrameCtl* ctl, unsigned long long* sort_status,
+                       unsigned long long n_hint, SortCtl* ctl, unsigned long long* sort_status,
                        unsigned int epoch_base, SortPlan plan, int sm_count, bool small_tiles, cudaStream_t s)
 {
     if (key_bytes == 4) {

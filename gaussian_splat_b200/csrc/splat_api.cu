@@ -21,39 +21,44 @@ static thread_local std::string g_err;
     } while (0)
 #define ARG_FAIL(msg) do { g_err = (msg); return SPLAT_ERR_ARG; } while (0)
 
-__global__ void set_n_sort_kernel(FrameCtl* ctl, unsigned int n) { ctl->n_sort = n; ctl->total_pairs = n; }
+__global__ void set_n_sort_kernel(SortCtl* ctl, unsigned int n) { ctl->n_sort = n; }
 
 // Everything one frame in flight writes: two such sets let the camera-batch entry points keep two frames
-// in flight on two streams (at frame sizes K2-K4 are latency-bound and leave most SMs idle). The single
+// in flight on two streams (at frame sizes the binning stages are latency-bound and leave most SMs idle). The single
 // frame entry points use set 0 only; the second set is allocated on the first batch call.
+#define CTL_BYTES (sizeof(FrameCtl) + (65536 + 8) * 4)      // control block + tile counters of the largest frame (65536 tiles)
 struct FrameSet {
-    splat_record_row* rec = nullptr; unsigned long long* binw = nullptr; uint32_t* offsets = nullptr;
-    uint32_t* keys[2] = {nullptr, nullptr}; uint32_t* vals[2] = {nullptr, nullptr};
-    unsigned long long capacity = 0;
-    // LAYER50 only: the same pairs in tile | depth order (allocated on the first LAYER50 frame)
-    uint32_t* keys_d[2] = {nullptr, nullptr}; uint32_t* vals_d[2] = {nullptr, nullptr}; unsigned long long capacity_d = 0;
-    FrameCtl* ctl = nullptr;
-    unsigned int* tile_sums = nullptr;      // K1 pair counts per 512 splats, then K2's tile prefixes
-    unsigned int* visbits = nullptr;        // band frames: one bit per splat that produced pairs (K1 -> K2)
-    unsigned long long* sort_status = nullptr; size_t sort_status_tiles = 0;
-    uint32_t* bounds = nullptr; uint32_t ranges_cap = 0;   // [T+1] first sorted pair of every tile
+    splat_record_row* rec = nullptr; unsigned long long* binw = nullptr;
+    // tile lists: pairs[cap] (depth field << 32 | instance index, sorted per tile), the candidates' parking arrays
+    // tmp_key / tmp_ts[cap], and LAYER50's instance-ordered copy arrival[cap_arr] (allocated on the first LAYER50 frame)
+    unsigned long long *pairs = nullptr, *tmp_key = nullptr, *tmp_ts = nullptr; unsigned long long capacity = 0;
+    uint32_t* arrival = nullptr; unsigned long long capacity_arr = 0;
+    FrameCtl* ctl = nullptr;                // + tile counters (CTL_BYTES)
+    unsigned int* tile_sums = nullptr;      // K1 candidate counts per 512 splats, then tile_scan's prefixes per 1024
+    uint32_t* bounds = nullptr; uint32_t ranges_cap = 0;   // [T+1] first pair of every tile's list
     cudaStream_t own_stream = nullptr;
 };
+
+// Status of frame `frame_no`, written by its tile_offsets_kernel straight into page-locked host memory (no copy is
+// enqueued): the next entry-point call sees an overflow without synchronising.
+struct FrameStatusSlot { unsigned long long total_pairs, total_cand; unsigned int overflow, max_tile_pairs, frame_no, pad; };
+#define STATUS_RING 64
 
 #define FB_RING 4
 struct splat_ctx : FrameSet {
     FrameSet alt; bool alt_ready = false; int cur_set = 0;
     int device = 0, sm_count = 148;
     uint32_t n = 0; size_t n_pad = 0;
-    float4 *rot = nullptr, *pos_sx = nullptr, *syz = nullptr, *base_rgb = nullptr, *sh = nullptr, *scr = nullptr, *row = nullptr; uint16_t* bq = nullptr;
+    float4 *rot = nullptr, *pos_sx = nullptr, *syz = nullptr, *base_rgb = nullptr, *sh = nullptr; uint16_t* bq = nullptr;
     int sh_degree = 0;
-    uint32_t* dbg_keys = nullptr; uint32_t* dbg_vals = nullptr; unsigned long long dbg_cap = 0;
     FrameCtl* ctl_host = nullptr;
-    uint32_t frame_no = 0;
-    FrameUniforms lastU{}; SortPlan lastPlan{}; int sorted_buf = 0; bool have_frame = false, kept_unsorted = false;
+    FrameStatusSlot* status_ring = nullptr;      // page-locked, mapped
+    uint32_t frame_no = 0, checked_frame = 0;    // frames enqueued / frames whose status has been looked at
+    // stand-alone sort
+    SortCtl* sort_ctl = nullptr; unsigned long long* sort_status = nullptr; size_t sort_status_tiles = 0; uint32_t sort_epoch = 0;
+    FrameUniforms lastU{}; bool have_frame = false;
     cudaEvent_t ev[6] = {}; bool timed = false;
     void* fb_scratch = nullptr; size_t fb_scratch_bytes = 0;
-    // camera-batch pipeline (splat_render_batch_host): second framebuffer, copy stream, per-buffer events
     // splat_render_batch_host: a ring of FB_RING device framebuffers, so rendering runs
     // ahead of the device-to-host copies instead of waiting for the copy two frames back
     cudaStream_t copy_stream = nullptr; void* fb_ring[FB_RING] = {}; size_t fb_ring_bytes = 0;
@@ -85,16 +90,15 @@ static void mat4_mul_host(const float* a, const float* b, float* o) {
 }
 
 static int free_pairs(splat_ctx* c) {
-    for (int k = 0; k < 2; ++k) { cudaFree(c->keys[k]); cudaFree(c->vals[k]); c->keys[k] = nullptr; c->vals[k] = nullptr; }
-    for (int k = 0; k < 2; ++k) { cudaFree(c->keys_d[k]); cudaFree(c->vals_d[k]); c->keys_d[k] = nullptr; c->vals_d[k] = nullptr; }
-    c->capacity_d = 0;
-    cudaFree(c->sort_status); c->sort_status = nullptr; c->sort_status_tiles = 0;
-    c->capacity = 0;
+    cudaFree(c->pairs); cudaFree(c->tmp_key); cudaFree(c->tmp_ts); cudaFree(c->arrival);
+    c->pairs = c->tmp_key = c->tmp_ts = nullptr; c->arrival = nullptr;
+    c->capacity = 0; c->capacity_arr = 0;
     return 0;
 }
 
 static int ensure_sort_status(splat_ctx* c, unsigned long long n_keys) {
     const size_t tiles = (size_t)((n_keys + SORT_TILE_KEYS_SMALL - 1) / SORT_TILE_KEYS_SMALL) + 1;
+    if (!c->sort_ctl) { CK(cudaMalloc(&c->sort_ctl, sizeof(SortCtl))); CK(cudaMemset(c->sort_ctl, 0, sizeof(SortCtl))); }
     if (tiles <= c->sort_status_tiles) return 0;
     CK(cudaDeviceSynchronize());
     cudaFree(c->sort_status); c->sort_status = nullptr;
@@ -104,20 +108,17 @@ static int ensure_sort_status(splat_ctx* c, unsigned long long n_keys) {
     return 0;
 }
 
+// Pair capacity = candidate slots (tile-rectangle areas; the pairs that pass the tile test are fewer). Nothing needs
+// clearing: every slot a kernel reads was written earlier in the same frame.
 static int ensure_pairs(splat_ctx* c, unsigned long long cap) {
     if (cap <= c->capacity) return 0;
     if (cap >= 0xFFFF0000ull) ARG_FAIL("pair capacity would exceed 2^32");
     CK(cudaDeviceSynchronize());
     free_pairs(c);
-    cap = (cap + SORT_TILE_KEYS - 1) / SORT_TILE_KEYS * SORT_TILE_KEYS;
-    for (int k = 0; k < 2; ++k) {
-        CK(cudaMalloc(&c->keys[k], cap * 4));
-        CK(cudaMalloc(&c->vals[k], cap * 4));
-        CK(cudaMemset(c->vals[k], 0, cap * 4));   // stale slots must stay valid splat indices
-        CK(cudaMemset(c->keys[k], 0, cap * 4));
-    }
+    cap = (cap + 4095) / 4096 * 4096;
+    CK(cudaMalloc(&c->pairs, cap * 8)); CK(cudaMalloc(&c->tmp_key, cap * 8)); CK(cudaMalloc(&c->tmp_ts, cap * 8));
     c->capacity = cap;
-    return ensure_sort_status(c, cap);
+    return 0;
 }
 
 extern "C" {
@@ -135,10 +136,12 @@ int splat_create(int device, splat_ctx** out) {
     splat_ctx* c = new splat_ctx();
     c->device = device;
     CK(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
-    CK(cudaMalloc(&c->ctl, sizeof(FrameCtl)));
-    CK(cudaMemset(c->ctl, 0, sizeof(FrameCtl)));
+    CK(cudaMalloc(&c->ctl, CTL_BYTES));
+    CK(cudaMemset(c->ctl, 0, CTL_BYTES));
     CK(cudaMallocHost(&c->ctl_host, sizeof(FrameCtl)));
     std::memset(c->ctl_host, 0, sizeof(FrameCtl));
+    CK(cudaHostAlloc(&c->status_ring, STATUS_RING * sizeof(FrameStatusSlot), cudaHostAllocMapped | cudaHostAllocPortable));
+    std::memset(c->status_ring, 0, STATUS_RING * sizeof(FrameStatusSlot));
     for (int k = 0; k < 6; ++k) CK(cudaEventCreate(&c->ev[k]));
     CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
@@ -151,22 +154,19 @@ int splat_create(int device, splat_ctx** out) {
     return SPLAT_OK;
 }
 
-// Per-splat scratch of the CURRENT frame set (records, counts, offsets, scan lookback words).
+// Per-splat scratch of the CURRENT frame set (records, bin words, candidate counts).
 static void free_scene_scratch(splat_ctx* c) {
-    cudaFree(c->rec); cudaFree(c->binw); cudaFree(c->offsets); cudaFree(c->tile_sums); cudaFree(c->visbits);
-    c->rec = nullptr; c->binw = nullptr; c->offsets = nullptr; c->tile_sums = nullptr; c->visbits = nullptr;
+    cudaFree(c->rec); cudaFree(c->binw); cudaFree(c->tile_sums);
+    c->rec = nullptr; c->binw = nullptr; c->tile_sums = nullptr;
 }
 static int alloc_scene_scratch(splat_ctx* c, size_t n_pad) {
     CK(cudaMalloc(&c->rec, n_pad * sizeof(splat_record_row)));
-    CK(cudaMalloc(&c->binw, n_pad * 8)); CK(cudaMalloc(&c->offsets, n_pad * 4));
+    CK(cudaMalloc(&c->binw, n_pad * 8));
     CK(cudaMemset(c->binw, 0, n_pad * 8));
     CK(cudaMemset(c->rec, 0, n_pad * sizeof(splat_record_row)));
     const size_t sums = n_pad / (SCAN_TILE_ITEMS / 2) + n_pad / SCAN_TILE_ITEMS + 2;   // [n/512] sums, then [n/1024] prefixes
     CK(cudaMalloc(&c->tile_sums, sums * 4));
     CK(cudaMemset(c->tile_sums, 0, sums * 4));
-    const size_t vis_words = (n_pad / BAND_TILE + 1) * (BAND_TILE / 32);
-    CK(cudaMalloc(&c->visbits, vis_words * 4));
-    CK(cudaMemset(c->visbits, 0, vis_words * 4));
     return SPLAT_OK;
 }
 // Releases the second frame set completely (it is rebuilt by the next camera-batch call).
@@ -188,7 +188,7 @@ static int ensure_alt(splat_ctx* c) {
     swap_sets(c);
     int rc = SPLAT_OK;
     do {
-        if (cudaMalloc(&c->ctl, sizeof(FrameCtl)) != cudaSuccess || cudaMemset(c->ctl, 0, sizeof(FrameCtl)) != cudaSuccess ||
+        if (cudaMalloc(&c->ctl, CTL_BYTES) != cudaSuccess || cudaMemset(c->ctl, 0, CTL_BYTES) != cudaSuccess ||
             cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) { g_err = "second frame set: allocation failed"; rc = SPLAT_ERR_CUDA; break; }
         if (c->n_pad) { rc = alloc_scene_scratch(c, c->n_pad); if (rc) break; }
         rc = ensure_pairs(c, cap ? cap : (1ull << 20));
@@ -207,9 +207,9 @@ static int ensure_pairs_all(splat_ctx* c, unsigned long long cap) {
 
 static void free_scene(splat_ctx* c) {
     drop_alt(c);
-    cudaFree(c->rot); cudaFree(c->pos_sx); cudaFree(c->syz); cudaFree(c->bq); cudaFree(c->sh); cudaFree(c->base_rgb); cudaFree(c->scr); cudaFree(c->row);
+    cudaFree(c->rot); cudaFree(c->pos_sx); cudaFree(c->syz); cudaFree(c->bq); cudaFree(c->sh); cudaFree(c->base_rgb);
     free_scene_scratch(c);
-    c->rot = c->pos_sx = c->syz = c->base_rgb = c->sh = c->scr = c->row = nullptr; c->bq = nullptr;
+    c->rot = c->pos_sx = c->syz = c->base_rgb = c->sh = nullptr; c->bq = nullptr;
     c->n = 0; c->n_pad = 0; c->sh_degree = 0;
 }
 
@@ -218,8 +218,8 @@ int splat_destroy(splat_ctx* c) {
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     free_scene(c); free_pairs(c);
-    cudaFree(c->dbg_keys); cudaFree(c->dbg_vals); cudaFree(c->bounds); cudaFree(c->ctl); cudaFree(c->fb_scratch);
-    cudaFreeHost(c->ctl_host);
+    cudaFree(c->bounds); cudaFree(c->ctl); cudaFree(c->fb_scratch); cudaFree(c->sort_ctl); cudaFree(c->sort_status);
+    cudaFreeHost(c->ctl_host); cudaFreeHost(c->status_ring);
     for (int k = 0; k < 6; ++k) if (c->ev[k]) cudaEventDestroy(c->ev[k]);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
@@ -235,15 +235,12 @@ int splat_destroy(splat_ctx* c) {
 static int install_scene(splat_ctx* c, const float* aos_dev, uint32_t n) {
     const size_t n_pad = ((size_t)n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS * SCAN_TILE_ITEMS;
     CK(cudaMalloc(&c->rot, n_pad * 16)); CK(cudaMalloc(&c->pos_sx, n_pad * 16)); CK(cudaMalloc(&c->syz, n_pad * 16));
-    CK(cudaMalloc(&c->bq, n_pad * 2)); CK(cudaMalloc(&c->base_rgb, n_pad * 16)); CK(cudaMalloc(&c->scr, n_pad * 16));
-    CK(cudaMalloc(&c->row, n_pad * 64));
+    CK(cudaMalloc(&c->bq, n_pad * 2)); CK(cudaMalloc(&c->base_rgb, n_pad * 16));
     { const int rc = alloc_scene_scratch(c, n_pad); if (rc) return rc; }
-    launch_upload_soa(aos_dev, n, c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->scr, c->row, 0);
+    launch_upload_soa(aos_dev, n, c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, 0);
     CK(cudaGetLastError());
     CK(cudaDeviceSynchronize());
     c->n = n; c->n_pad = n_pad;
-    // vals hold splat indices; stale ones from a larger scene must not survive
-    for (int k = 0; k < 2; ++k) if (c->vals[k]) CK(cudaMemset(c->vals[k], 0, c->capacity * 4));
     unsigned long long want = (unsigned long long)n * 12ull;
     if (want < (1ull << 20)) want = 1ull << 20;
     if (want > 0xC0000000ull) want = 0xC0000000ull;
@@ -348,10 +345,8 @@ int splat_upload_sh(splat_ctx* c, const float* sh_host, uint32_t n, int degree) 
 }  // extern "C"
 
 // --------------------------------------------------------------------- frames
-static int tile_bits(unsigned int T) { int b = 0; while ((1ull << b) < T) ++b; return b; }
-
 static int build_frame(splat_ctx* c, const float* view, const float* proj, int w, int h, const splat_opts* o,
-                       FrameUniforms& U, SortPlan& plan) {
+                       FrameUniforms& U) {
     if (!view || !proj) ARG_FAIL("splat_render: view/proj is NULL");
     if (w <= 0 || h <= 0 || w > 65536 || h > 65536) ARG_FAIL("splat_render: bad viewport");
     splat_opts d{}; if (o) d = *o;
@@ -398,45 +393,41 @@ static int build_frame(splat_ctx* c, const float* view, const float* proj, int w
         U.scr_ylo = (float)(U.row_begin * 16);
         U.scr_yhi = fminf((float)(U.row_end * 16), U.H);
     }
-    const unsigned int T = (unsigned int)(U.tiles_x * U.tiles_y);
-    const int tb = tile_bits(T);
-    if (tb > 16) ARG_FAIL("splat_render: more than 65536 tiles");
+    if ((long long)U.tiles_x * U.tiles_y > 65536) ARG_FAIL("splat_render: more than 65536 tiles");
     if (U.tiles_x > 4096 || U.tiles_y > 4096) ARG_FAIL("splat_render: viewport wider or taller than 65536 pixels");
-    // Digit passes of the 32-bit (tile << 16 | half-depth) keys: 15 significant depth bits (the sign bit is 0)
-    // then the tile bits. TILE sorts its pairs with all of them. LAYER50 sorts the depth-ordered copy the same way and
-    // the arrival-ordered list by the tile digits only (pairs are emitted in instance order and the sort is
-    // stable); see layer_plan().
-    // MLAB walks its pairs in instance order only: tile-digit passes alone (as layer_plan()).
-    plan = SortPlan{};
-    int p = 0;
-    if (d.mode != SPLAT_MODE_MLAB) {
-        plan.shift[p] = 0; plan.mask[p++] = 0xFF;
-        plan.shift[p] = 8; plan.mask[p++] = 0xFF;
-    }
-    if (tb > 0) { plan.shift[p] = 16; plan.mask[p++] = tb >= 8 ? 0xFFu : ((1u << tb) - 1u); }
-    if (tb > 8) { plan.shift[p] = 24; plan.mask[p++] = (1u << (tb - 8)) - 1u; }
-    for (int k = 0; k < SPLAT_MAX_SORT_PASSES; ++k) { plan.slot[k] = k; plan.ticket[k] = k; }
-    plan.n_pass = p;
     return SPLAT_OK;
 }
 
-// LAYER50's arrival-ordered list: only the tile-digit passes of `full`, reading their histograms (same
-// digits, same counts) and drawing tickets from the upper half of the ticket array.
-static SortPlan layer_plan(const SortPlan& full) {
-    SortPlan a{};
-    for (int p = 0; p < full.n_pass; ++p)
-        if (full.shift[p] >= 16) {
-            a.shift[a.n_pass] = full.shift[p]; a.mask[a.n_pass] = full.mask[p];
-            a.slot[a.n_pass] = full.slot[p]; a.ticket[a.n_pass] = 4 + a.n_pass;
-            ++a.n_pass;
-        }
-    return a;
+// Looks at the status slots of the frames enqueued since the last look (their tile_offsets_kernel writes them into
+// page-locked memory): an overflowed frame has built no lists (its framebuffer is empty), so the buffers are grown now
+// and the caller is told once, SPLAT_ERR_OVERFLOW, to render again. Frames still in flight are looked at next time.
+// wait = true: the device has been synchronised, every enqueued frame has landed.
+static int check_overflow(splat_ctx* c, bool wait, unsigned long long* worst_out = nullptr) {
+    unsigned long long worst = 0;
+    if (c->frame_no - c->checked_frame > STATUS_RING) c->checked_frame = c->frame_no - STATUS_RING;     // older slots are overwritten
+    while (c->checked_frame != c->frame_no) {
+        const uint32_t f = c->checked_frame + 1;
+        const volatile FrameStatusSlot* sl = c->status_ring + (f % STATUS_RING);
+        if (sl->frame_no != f) { if (!wait) break; c->checked_frame = f; continue; }    // not landed (or a frame without kernels)
+        if (sl->overflow && sl->total_cand > worst) worst = sl->total_cand;
+        c->checked_frame = f;
+    }
+    if (worst_out) *worst_out = worst;
+    if (!worst) return SPLAT_OK;
+    const int set = c->cur_set;
+    use_set(c, 0);
+    int rc = ensure_pairs(c, worst + worst / 4 + 4096);
+    if (rc == SPLAT_OK && c->alt_ready) { swap_sets(c); rc = ensure_pairs(c, worst + worst / 4 + 4096); swap_sets(c); }
+    use_set(c, set);
+    if (rc) return rc;
+    g_err = "an earlier frame overflowed the pair buffers and was rendered empty; the buffers have been grown: render it again";
+    return SPLAT_ERR_OVERFLOW;
 }
 
 thread_local bool g_pdl_frame = true;
 // Internal flag (not a splat_opts flag): launch this frame's kernels without programmatic dependent launch.
 #define FRAME_NO_PDL (1 << 30)
-static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUniforms& U, const SortPlan& plan, int flags) {
+static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUniforms& U, int flags) {
     g_pdl_frame = (flags & FRAME_NO_PDL) == 0;
     const unsigned int T = (unsigned int)(U.tiles_x * U.tiles_y);
     if (T > c->ranges_cap) {
@@ -446,61 +437,34 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
         c->ranges_cap = T;
     }
     const bool timed = (flags & SPLAT_FLAG_TIMING) != 0;
-    const bool keep = (flags & SPLAT_FLAG_KEEP_UNSORTED) != 0;
-    if (keep && c->dbg_cap < c->capacity) {
-        CK(cudaDeviceSynchronize());
-        cudaFree(c->dbg_keys); cudaFree(c->dbg_vals); c->dbg_keys = nullptr; c->dbg_vals = nullptr;
-        CK(cudaMalloc(&c->dbg_keys, c->capacity * 4)); CK(cudaMalloc(&c->dbg_vals, c->capacity * 4));
-        c->dbg_cap = c->capacity;
-    }
     const bool layer = U.mode == SPLAT_MODE_LAYER50;
-    const unsigned long long pairs_hint = c->ctl_host->total_pairs;     // of the last frame whose status was read back; shapes the sort
-    if (layer && c->capacity_d < c->capacity) {
+    if (layer && c->capacity_arr < c->capacity) {
         CK(cudaDeviceSynchronize());
-        for (int k = 0; k < 2; ++k) {
-            cudaFree(c->keys_d[k]); cudaFree(c->vals_d[k]); c->keys_d[k] = nullptr; c->vals_d[k] = nullptr;
-            CK(cudaMalloc(&c->keys_d[k], c->capacity * 4)); CK(cudaMalloc(&c->vals_d[k], c->capacity * 4));
-            CK(cudaMemset(c->vals_d[k], 0, c->capacity * 4)); CK(cudaMemset(c->keys_d[k], 0, c->capacity * 4));
-        }
-        c->capacity_d = c->capacity;
+        cudaFree(c->arrival); c->arrival = nullptr;
+        CK(cudaMalloc(&c->arrival, c->capacity * 4));
+        c->capacity_arr = c->capacity;
     }
     c->frame_no = c->frame_no + 1;
-    if (c->frame_no >= (1u << 25)) c->frame_no = 1;
-    const unsigned int epoch = c->frame_no * 16u;       // < 2^30; +0 scan, +1.. sort passes
+    if (c->frame_no == 0) { c->frame_no = 1; c->checked_frame = 0; }
+    FrameStatusSlot* slot = c->status_ring + (c->frame_no % STATUS_RING);
     if (timed) CK(cudaEventRecord(c->ev[0], s));
-    CK(cudaMemsetAsync(c->ctl, 0, sizeof(FrameCtl), s));
+    CK(cudaMemsetAsync(c->ctl, 0, sizeof(FrameCtl) + ((size_t)T + 1) * 4, s));       // control block + tile counters
     if (c->n) {
-        ScenePlanes sp{c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->scr, c->row, c->sh, c->n_pad};
+        ScenePlanes sp{c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->sh, c->n_pad};
         unsigned int* scan_prefix = c->tile_sums + c->n_pad / (SCAN_TILE_ITEMS / 2);
-        launch_preprocess(sp, U, c->rec, c->binw, c->tile_sums, scan_prefix, c->visbits, c->capacity, c->ctl, s);
+        launch_preprocess(sp, U, c->rec, c->binw, c->tile_sums, scan_prefix, c->capacity, c->ctl, s);
         if (timed) CK(cudaEventRecord(c->ev[1], s));
-        launch_scan_duplicate(U, c->binw, c->offsets, c->keys[0], c->vals[0], layer ? c->keys_d[0] : nullptr,
-                              layer ? c->vals_d[0] : nullptr, c->capacity, c->ctl, c->tile_sums, scan_prefix, c->visbits, plan, c->sm_count, s);
-        if (keep) {
-            CK(cudaMemcpyAsync(c->dbg_keys, c->keys[0], c->capacity * 4, cudaMemcpyDeviceToDevice, s));
-            CK(cudaMemcpyAsync(c->dbg_vals, c->vals[0], c->capacity * 4, cudaMemcpyDeviceToDevice, s));
-        }
-        if (timed) CK(cudaEventRecord(c->ev[2], s));
-        if (layer) {
-            launch_radix_sort(c->keys_d[0], c->vals_d[0], c->keys_d[1], c->vals_d[1], 4, pairs_hint, c->ctl, c->sort_status, epoch + 1, plan,
-                              c->sm_count, false, s);
-            launch_radix_sort(c->keys[0], c->vals[0], c->keys[1], c->vals[1], 4, pairs_hint, c->ctl, c->sort_status, epoch + 1 + plan.n_pass,
-                              layer_plan(plan), c->sm_count, false, s);
-        } else {
-            launch_radix_sort(c->keys[0], c->vals[0], c->keys[1], c->vals[1], 4, pairs_hint, c->ctl, c->sort_status, epoch + 1, plan,
-                              c->sm_count, false, s);
-        }
-    } else if (timed) { CK(cudaEventRecord(c->ev[1], s)); CK(cudaEventRecord(c->ev[2], s)); }
-    if (timed) CK(cudaEventRecord(c->ev[3], s));
-    const int sb = (layer ? layer_plan(plan).n_pass : plan.n_pass) & 1;    // arrival-ordered (LAYER50) or the only (TILE) list
-    const int sd = plan.n_pass & 1;
-    launch_tile_bounds(c->keys[sb], c->ctl, (unsigned int)(U.row_begin * U.tiles_x),
-                       (unsigned int)((U.row_end - U.row_begin) * U.tiles_x), c->bounds, s);
-    if (timed) CK(cudaEventRecord(c->ev[4], s));
-    launch_blend(U, c->rec, c->vals[sb], layer ? c->vals_d[sd] : nullptr, c->bounds, fb, s);
+        launch_bin_pairs(U, c->binw, c->rec, c->tmp_key, c->tmp_ts, c->capacity, c->ctl, c->tile_sums, scan_prefix, c->sm_count, s);
+    } else if (timed) CK(cudaEventRecord(c->ev[1], s));
+    launch_tile_offsets(U, c->ctl, c->bounds, slot, c->frame_no, s);
+    if (c->n) launch_scatter_pairs(c->ctl, c->tmp_key, c->tmp_ts, c->bounds, c->pairs, c->sm_count, s);
+    if (timed) CK(cudaEventRecord(c->ev[2], s));
+    if (c->n) launch_tile_sort(U, c->ctl, c->bounds, c->pairs, c->arrival, s);
+    if (timed) { CK(cudaEventRecord(c->ev[3], s)); CK(cudaEventRecord(c->ev[4], s)); }
+    launch_blend(U, c->rec, c->pairs, c->arrival, c->bounds, fb, s);
     if (timed) CK(cudaEventRecord(c->ev[5], s));
     CK(cudaGetLastError());
-    c->lastU = U; c->lastPlan = plan; if (layer) c->lastPlan.n_pass = plan.n_pass + layer_plan(plan).n_pass; c->sorted_buf = sb; c->have_frame = true; c->timed = timed; c->kept_unsorted = keep;
+    c->lastU = U; c->have_frame = true; c->timed = timed;
     return SPLAT_OK;
 }
 
@@ -512,11 +476,13 @@ int splat_render(splat_ctx* c, void* stream, void* fb, const float* view, const 
     if (!fb) ARG_FAIL("splat_render: framebuffer is NULL");
     CK(cudaSetDevice(c->device));
     use_set(c, 0);
-    FrameUniforms U; SortPlan plan;
-    int rc = build_frame(c, view, proj, w, h, o, U, plan);
+    FrameUniforms U;
+    int rc = build_frame(c, view, proj, w, h, o, U);
     if (rc) return rc;
     if (c->capacity == 0) { rc = ensure_pairs(c, 1ull << 20); if (rc) return rc; }
-    return enqueue_frame(c, (cudaStream_t)stream, fb, U, plan, o ? o->flags : 0);
+    rc = check_overflow(c, false);          // an earlier frame that overflowed: buffers grown, reported once
+    if (rc) return rc;
+    return enqueue_frame(c, (cudaStream_t)stream, fb, U, o ? o->flags : 0);
 }
 
 // Two frames in flight only pay while one frame leaves SMs idle in its latency-bound stages. Measured on B200:
@@ -545,6 +511,7 @@ int splat_render_batch(splat_ctx* c, void* stream, void* const* fbs, const float
     use_set(c, 0);
     if (c->capacity == 0) { const int rc = ensure_pairs(c, 1ull << 20); if (rc) return rc; }
     { const int rc = ensure_alt(c); if (rc) return rc; }
+    { const int rc = check_overflow(c, false); if (rc) return rc; }
     const int flags = o ? (o->flags & ~(SPLAT_FLAG_TIMING | SPLAT_FLAG_KEEP_UNSORTED)) : 0;
     cudaStream_t user = (cudaStream_t)stream;
     CK(cudaEventRecord(c->ev_fork, user));
@@ -552,10 +519,10 @@ int splat_render_batch(splat_ctx* c, void* stream, void* const* fbs, const float
         if (!fbs[v]) ARG_FAIL("splat_render_batch: NULL framebuffer");
         use_set(c, v & 1);
         if (v < 2) CK(cudaStreamWaitEvent(c->own_stream, c->ev_fork, 0));
-        FrameUniforms U; SortPlan plan;
-        int rc = build_frame(c, views + 16 * v, projs + 16 * v, w, h, o, U, plan);
+        FrameUniforms U;
+        int rc = build_frame(c, views + 16 * v, projs + 16 * v, w, h, o, U);
         if (rc) return rc;
-        rc = enqueue_frame(c, c->own_stream, fbs[v], U, plan, flags | FRAME_NO_PDL);
+        rc = enqueue_frame(c, c->own_stream, fbs[v], U, flags | FRAME_NO_PDL);
         if (rc) return rc;
         if (v >= n_views - 2) {                      // join: the caller's stream continues after both sets drain
             CK(cudaEventRecord(c->ev_rendered[v & 1], c->own_stream));
@@ -569,19 +536,19 @@ int splat_frame_status(splat_ctx* c, splat_status* out) {
     if (!c || !out) ARG_FAIL("splat_frame_status: NULL argument");
     CK(cudaSetDevice(c->device));
     CK(cudaDeviceSynchronize());
-    CK(cudaMemcpy(c->ctl_host, c->ctl, 64, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(c->ctl_host, c->ctl, sizeof(FrameCtl), cudaMemcpyDeviceToHost));
     std::memset(out, 0, sizeof(*out));
     out->n_splats = c->n;
     out->n_pairs = c->ctl_host->total_pairs;
     out->pair_capacity = c->capacity;
     out->overflow = c->ctl_host->overflow;
-    out->sort_passes = (uint32_t)c->lastPlan.n_pass;
-    if (out->overflow) {
-        unsigned long long want = out->n_pairs + out->n_pairs / 4 + SORT_TILE_KEYS;
-        const int rc = ensure_pairs_all(c, want);
-        if (rc) return rc;
-    }
-    return SPLAT_OK;
+    out->sort_passes = 1;            // one shared-memory sort per tile list
+    // every frame since the last look (a camera batch: all its views), not only the last one
+    unsigned long long worst = 0;
+    const int rc = check_overflow(c, true, &worst);
+    if (worst) { out->overflow = 1; if (worst > out->n_pairs) out->n_pairs = worst; }
+    out->pair_capacity = c->capacity;
+    return rc == SPLAT_ERR_OVERFLOW ? SPLAT_OK : rc;      // the overflow is reported in *out; the buffers are grown
 }
 
 int splat_render_host(splat_ctx* c, void* fb_host, const float* view, const float* proj, int w, int h,
@@ -590,8 +557,8 @@ int splat_render_host(splat_ctx* c, void* fb_host, const float* view, const floa
     if (!fb_host) ARG_FAIL("splat_render_host: framebuffer is NULL");
     CK(cudaSetDevice(c->device));
     use_set(c, 0);
-    FrameUniforms U; SortPlan plan;
-    int rc = build_frame(c, view, proj, w, h, o, U, plan);
+    FrameUniforms U;
+    int rc = build_frame(c, view, proj, w, h, o, U);
     if (rc) return rc;
     const size_t bytes = (size_t)w * h * 8;
     if (bytes > c->fb_scratch_bytes) {
@@ -610,7 +577,7 @@ int splat_render_host(splat_ctx* c, void* fb_host, const float* view, const floa
     // rows outside the band are not rendered: only the band is copied back
     const size_t row0 = (size_t)U.row_begin * SPLAT_TILE, row1 = (size_t)U.row_end * SPLAT_TILE < (size_t)h ? (size_t)U.row_end * SPLAT_TILE : (size_t)h;
     for (int attempt = 0; attempt < 4; ++attempt) {
-        rc = enqueue_frame(c, c->own_stream, c->fb_scratch, U, plan, o ? o->flags : 0);
+        rc = enqueue_frame(c, c->own_stream, c->fb_scratch, U, o ? o->flags : 0);
         if (rc) return rc;
         CK(cudaMemcpyAsync(c->ctl_host, c->ctl, 64, cudaMemcpyDeviceToHost, c->own_stream));
         if (row1 > row0 && bgra) {
@@ -621,9 +588,10 @@ int splat_render_host(splat_ctx* c, void* fb_host, const float* view, const floa
             CK(cudaMemcpyAsync((char*)fb_host + row0 * w * 8, (char*)c->fb_scratch + row0 * w * 8, (row1 - row0) * w * 8,
                                cudaMemcpyDeviceToHost, c->own_stream));
         CK(cudaStreamSynchronize(c->own_stream));
+        c->checked_frame = c->frame_no;          // this frame's status is handled right here
         if (!c->ctl_host->overflow) return SPLAT_OK;
-        const unsigned long long D = c->ctl_host->total_pairs;
-        rc = ensure_pairs_all(c, D + D / 4 + SORT_TILE_KEYS);
+        const unsigned long long D = c->ctl_host->total_cand;
+        rc = ensure_pairs_all(c, D + D / 4 + 4096);
         if (rc) return rc;
     }
     g_err = "splat_render_host: pair buffers still overflow after regrowth";
@@ -645,7 +613,7 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
     }
     if (n_views > c->batch_flags_cap) {
         cudaFreeHost(c->batch_flags); c->batch_flags = nullptr;
-        CK(cudaMallocHost(&c->batch_flags, (size_t)n_views * 16));
+        CK(cudaMallocHost(&c->batch_flags, (size_t)n_views * 24));
         c->batch_flags_cap = n_views;
     }
     use_set(c, 0);
@@ -666,13 +634,13 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
             if (!fb_host[v]) ARG_FAIL("splat_render_batch_host: NULL framebuffer");
             const int b = v % FB_RING;
             use_set(c, two ? (v & 1) : 0);                  // frame set and stream (two in flight); framebuffer ring slot b
-            FrameUniforms U; SortPlan plan;
-            int rc = build_frame(c, views + 16 * v, projs + 16 * v, w, h, o, U, plan);
+            FrameUniforms U;
+            int rc = build_frame(c, views + 16 * v, projs + 16 * v, w, h, o, U);
             if (rc) return rc;
             if (v >= FB_RING) CK(cudaStreamWaitEvent(c->own_stream, c->ev_copied[b], 0));     // slot b is free again
-            rc = enqueue_frame(c, c->own_stream, buf[b], U, plan, flags);
+            rc = enqueue_frame(c, c->own_stream, buf[b], U, flags);
             if (rc) return rc;
-            CK(cudaMemcpyAsync(c->batch_flags + 4 * v, c->ctl, 16, cudaMemcpyDeviceToHost, c->own_stream));   // D, overflow
+            CK(cudaMemcpyAsync(c->batch_flags + 6 * v, c->ctl, 24, cudaMemcpyDeviceToHost, c->own_stream));   // D, overflow, candidates
             const size_t row0 = (size_t)U.row_begin * SPLAT_TILE;
             const size_t row1 = (size_t)U.row_end * SPLAT_TILE < (size_t)h ? (size_t)U.row_end * SPLAT_TILE : (size_t)h;
             if (bgra && row1 > row0)
@@ -688,13 +656,14 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
         CK(cudaStreamSynchronize(c->own_stream));
         if (c->alt_ready) CK(cudaStreamSynchronize(c->alt.own_stream));
         CK(cudaStreamSynchronize(c->copy_stream));
+        c->checked_frame = c->frame_no;          // the views' status is handled right here
         unsigned long long worst = 0; bool over = false;
         for (int v = 0; v < n_views; ++v) {
-            unsigned long long D; std::memcpy(&D, c->batch_flags + 4 * v, 8);
-            if (c->batch_flags[4 * v + 2]) { over = true; if (D > worst) worst = D; }
+            unsigned long long D; std::memcpy(&D, c->batch_flags + 6 * v + 4, 8);      // FrameCtl::total_cand
+            if (c->batch_flags[6 * v + 2]) { over = true; if (D > worst) worst = D; }
         }
         if (!over) return SPLAT_OK;
-        const int rc = ensure_pairs_all(c, worst + worst / 4 + SORT_TILE_KEYS);
+        const int rc = ensure_pairs_all(c, worst + worst / 4 + 4096);
         if (rc) return rc;
     }
     g_err = "splat_render_batch_host: pair buffers still overflow after regrowth";
@@ -706,17 +675,19 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
 // ------------------------------------------------------ debug / timing / sort
 extern "C" {
 
-// Bin words of the last frame with the culled splats' entries zeroed. A band frame leaves stale words where its
-// visibility bitmap has no bit (K1 only writes the live ones).
-static cudaError_t fetch_binw(splat_ctx* c, std::vector<unsigned long long>& w) {
-    w.resize(c->n);
-    if (!c->n) return cudaSuccess;
-    cudaError_t e = cudaMemcpy(w.data(), c->binw, (size_t)c->n * 8, cudaMemcpyDeviceToHost);
-    if (e != cudaSuccess || !frame_is_band(c->lastU)) return e;
-    std::vector<uint32_t> bits(((size_t)c->n + 31) / 32);
-    e = cudaMemcpy(bits.data(), c->visbits, bits.size() * 4, cudaMemcpyDeviceToHost);
+// The pairs of the last frame as K2 parked them (candidate order; holes removed), in the order the CPU restatement
+// emits them: instance order, a splat's tiles row-major. Candidate order is exactly that (tile prefixes come from an
+// ordered scan), so no sorting is needed here. tile[k], key[k] = depth field << 32 | instance index.
+static cudaError_t fetch_parked(splat_ctx* c, std::vector<uint32_t>& tile, std::vector<unsigned long long>& key) {
+    const size_t nc = c->ctl_host->n_cand;
+    std::vector<unsigned long long> ts(nc), k(nc);
+    tile.clear(); key.clear();
+    if (!nc) return cudaSuccess;
+    cudaError_t e = cudaMemcpy(ts.data(), c->tmp_ts, nc * 8, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(k.data(), c->tmp_key, nc * 8, cudaMemcpyDeviceToHost);
     if (e != cudaSuccess) return e;
-    for (uint32_t i = 0; i < c->n; ++i) if (!((bits[i >> 5] >> (i & 31)) & 1u)) w[i] = 0;
+    for (size_t g = 0; g < nc; ++g)
+        if (ts[g] != 0xFFFFFFFFFFFFFFFFull) { tile.push_back((uint32_t)(ts[g] >> 32)); key.push_back(k[g]); }
     return cudaSuccess;
 }
 
@@ -725,10 +696,11 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
     CK(cudaSetDevice(c->device));
     CK(cudaDeviceSynchronize());
     if (what == SPLAT_FETCH_DIGIT_HISTOGRAMS) {
-        const size_t need = sizeof(c->ctl->hist);
+        const size_t need = sizeof(c->sort_ctl->hist);
+        if (!c->sort_ctl) { g_err = "splat_debug_fetch: no stand-alone sort has run"; return SPLAT_ERR_STATE; }
         if (!dst) { *bytes = need; return SPLAT_OK; }
         if (*bytes < need) { *bytes = need; ARG_FAIL("splat_debug_fetch: destination too small"); }
-        CK(cudaMemcpy(dst, c->ctl->hist, need, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(dst, c->sort_ctl->hist, need, cudaMemcpyDeviceToHost));
         *bytes = need;
         return SPLAT_OK;
     }
@@ -766,74 +738,71 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
         return SPLAT_OK;
     }
     if (!c->have_frame) { g_err = "splat_debug_fetch: no frame rendered"; return SPLAT_ERR_STATE; }
-    CK(cudaMemcpy(c->ctl_host, c->ctl, 64, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(c->ctl_host, c->ctl, sizeof(FrameCtl), cudaMemcpyDeviceToHost));
     if (c->ctl_host->overflow) { g_err = "splat_debug_fetch: last frame overflowed the pair buffers"; return SPLAT_ERR_OVERFLOW; }
-    const size_t D = (size_t)c->ctl_host->n_sort;
+    const size_t D = (size_t)c->ctl_host->total_pairs;
     const size_t T = (size_t)c->lastU.tiles_x * c->lastU.tiles_y;
-    const void* src = nullptr; size_t need = 0;
+    const bool by_instance = c->lastU.mode != SPLAT_MODE_TILE;     // documented key = tile << 32 | instance index (D3)
+    size_t need = 0;
     switch (what) {
-        case SPLAT_FETCH_RECORDS:       src = nullptr;     need = (size_t)c->n * sizeof(splat_record); break;
-        case SPLAT_FETCH_TILES_TOUCHED: src = nullptr;     need = (size_t)c->n * 4; break;   // derived from the bin words below
-        case SPLAT_FETCH_OFFSETS:       src = c->offsets;  need = (size_t)c->n * 4; break;
-        case SPLAT_FETCH_KEYS_UNSORTED: src = c->dbg_keys; need = D * 8; break;
-        case SPLAT_FETCH_VALS_UNSORTED: src = c->dbg_vals; need = D * 4; break;
-        case SPLAT_FETCH_KEYS_SORTED:   src = c->keys[c->sorted_buf]; need = D * 8; break;
-        case SPLAT_FETCH_VALS_SORTED:   src = c->vals[c->sorted_buf]; need = D * 4; break;
-        case SPLAT_FETCH_TILE_RANGES:   src = nullptr;     need = T * 8; break;   // built from bounds below
+        case SPLAT_FETCH_RECORDS:       need = (size_t)c->n * sizeof(splat_record); break;
+        case SPLAT_FETCH_TILES_TOUCHED: need = (size_t)c->n * 4; break;
+        case SPLAT_FETCH_OFFSETS:       need = (size_t)c->n * 4; break;
+        case SPLAT_FETCH_KEYS_UNSORTED: need = D * 8; break;
+        case SPLAT_FETCH_VALS_UNSORTED: need = D * 4; break;
+        case SPLAT_FETCH_KEYS_SORTED:   need = D * 8; break;
+        case SPLAT_FETCH_VALS_SORTED:   need = D * 4; break;
+        case SPLAT_FETCH_TILE_RANGES:   need = T * 8; break;
         default: ARG_FAIL("splat_debug_fetch: unknown item");
-    }
-    if ((what == SPLAT_FETCH_KEYS_UNSORTED || what == SPLAT_FETCH_VALS_UNSORTED) && !c->kept_unsorted) {
-        g_err = "splat_debug_fetch: frame was not rendered with SPLAT_FLAG_KEEP_UNSORTED"; return SPLAT_ERR_STATE;
     }
     if (!dst) { *bytes = need; return SPLAT_OK; }
     if (*bytes < need) { *bytes = need; ARG_FAIL("splat_debug_fetch: destination too small"); }
+    std::vector<uint32_t> b(T + 1);
+    CK(cudaMemcpy(b.data(), c->bounds, (T + 1) * 4, cudaMemcpyDeviceToHost));
     if (what == SPLAT_FETCH_TILE_RANGES) {
-        uint32_t* b = new uint32_t[T + 1];
-        cudaError_t e = cudaMemcpy(b, c->bounds, (T + 1) * 4, cudaMemcpyDeviceToHost);
         uint32_t* r = (uint32_t*)dst;
-        const size_t t_lo = (size_t)c->lastU.row_begin * c->lastU.tiles_x, t_hi = (size_t)c->lastU.row_end * c->lastU.tiles_x;
-        for (size_t t = 0; t < T && e == cudaSuccess; ++t) {
-            const bool any = t >= t_lo && t < t_hi && b[t] < b[t + 1];      // only the band's boundaries were computed
+        for (size_t t = 0; t < T; ++t) {
+            const bool any = b[t] < b[t + 1];
             r[2 * t] = any ? b[t] : 0u; r[2 * t + 1] = any ? b[t + 1] : 0u;
         }
-        delete[] b;
-        CK(e);
-    } else if (what == SPLAT_FETCH_TILES_TOUCHED) {
-        std::vector<unsigned long long> w;
-        CK(fetch_binw(c, w));
-        for (uint32_t i = 0; i < c->n; ++i) ((uint32_t*)dst)[i] = binw_count(w[i]);
-    } else if (what == SPLAT_FETCH_OFFSETS && frame_is_band(c->lastU)) {
-        // a band frame's K2 walks only the visible splats and writes no per-splat offsets: the exclusive,
-        // saturating scan of the pair counts is rebuilt here from the bin words
-        std::vector<unsigned long long> w;
-        CK(fetch_binw(c, w));
-        unsigned long long run = 0;
-        for (uint32_t i = 0; i < c->n; ++i) {
-            ((uint32_t*)dst)[i] = run > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)run;
-            run += binw_count(w[i]);
+    } else if (what == SPLAT_FETCH_KEYS_SORTED || what == SPLAT_FETCH_VALS_SORTED) {
+        // the list the pixels walk first: depth order (TILE), instance order (MLAB: the pairs carry no depth; LAYER50: the
+        // arrival list), presented as tile << 32 | half-depth field, or | instance index for lists kept in instance order
+        std::vector<unsigned long long> pr(D);
+        std::vector<uint32_t> arr;
+        if (D) CK(cudaMemcpy(pr.data(), c->pairs, D * 8, cudaMemcpyDeviceToHost));
+        if (D && c->lastU.mode == SPLAT_MODE_LAYER50) { arr.resize(D); CK(cudaMemcpy(arr.data(), c->arrival, D * 4, cudaMemcpyDeviceToHost)); }
+        size_t t = 0;
+        for (size_t i = 0; i < D; ++i) {
+            while (t < T && b[t + 1] <= i) ++t;
+            const uint32_t idx = arr.empty() ? (uint32_t)pr[i] : arr[i];
+            if (what == SPLAT_FETCH_VALS_SORTED) ((uint32_t*)dst)[i] = idx;
+            else ((uint64_t*)dst)[i] = ((uint64_t)t << 32) | (by_instance ? idx : (uint32_t)(pr[i] >> 32));
         }
-    } else if (what == SPLAT_FETCH_KEYS_UNSORTED || what == SPLAT_FETCH_KEYS_SORTED) {
-        // presented in the documented 64-bit form, tile << 32 | half-depth field (TILE) or | instance index (lists kept
-        // in instance order); the device holds tile << 16 | depth, and the instance index is the pair's value
-        const bool sorted = what == SPLAT_FETCH_KEYS_SORTED;
-        const bool by_instance = c->lastU.mode != SPLAT_MODE_TILE;
-        std::vector<uint32_t> k32(D), v32(by_instance ? D : 0);
-        if (D) CK(cudaMemcpy(k32.data(), src, D * 4, cudaMemcpyDeviceToHost));
-        if (D && by_instance) CK(cudaMemcpy(v32.data(), sorted ? c->vals[c->sorted_buf] : c->dbg_vals, D * 4, cudaMemcpyDeviceToHost));
-        for (size_t i = 0; i < D; ++i)
-            ((uint64_t*)dst)[i] = ((uint64_t)(k32[i] >> 16) << 32) | (by_instance ? v32[i] : (k32[i] & 0xFFFFu));
-    } else if (need && src) CK(cudaMemcpy(dst, src, need, cudaMemcpyDeviceToHost));
-    if (what == SPLAT_FETCH_RECORDS && c->n) {
-        {   // device rows are 64 bytes (splat_record_row): present the 48-byte records
-            std::vector<splat_record_row> rows(c->n);
-            CK(cudaMemcpy(rows.data(), c->rec, (size_t)c->n * sizeof(splat_record_row), cudaMemcpyDeviceToHost));
-            for (uint32_t i = 0; i < c->n; ++i) ((splat_record*)dst)[i] = rows[i].r;
+    } else {
+        std::vector<uint32_t> tile; std::vector<unsigned long long> key;
+        CK(fetch_parked(c, tile, key));
+        if (key.size() != D) { g_err = "splat_debug_fetch: parked pairs disagree with the tile counters"; return SPLAT_ERR_STATE; }
+        if (what == SPLAT_FETCH_KEYS_UNSORTED)
+            for (size_t i = 0; i < D; ++i) ((uint64_t*)dst)[i] = ((uint64_t)tile[i] << 32) | (by_instance ? (uint32_t)key[i] : (uint32_t)(key[i] >> 32));
+        else if (what == SPLAT_FETCH_VALS_UNSORTED)
+            for (size_t i = 0; i < D; ++i) ((uint32_t*)dst)[i] = (uint32_t)key[i];
+        else {
+            // pairs per splat (a splat whose tiles all failed the tile test counts as culled)
+            std::vector<uint32_t> touched(c->n, 0u);
+            for (size_t i = 0; i < D; ++i) touched[(uint32_t)key[i]]++;
+            if (what == SPLAT_FETCH_TILES_TOUCHED) std::memcpy(dst, touched.data(), (size_t)c->n * 4);
+            else if (what == SPLAT_FETCH_OFFSETS) {
+                unsigned long long run = 0;
+                for (uint32_t i = 0; i < c->n; ++i) { ((uint32_t*)dst)[i] = run > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)run; run += touched[i]; }
+            } else if (c->n) {
+                // device rows are 64 bytes (splat_record_row): present the 48-byte records, culled ones zeroed
+                std::vector<splat_record_row> rows(c->n);
+                CK(cudaMemcpy(rows.data(), c->rec, (size_t)c->n * sizeof(splat_record_row), cudaMemcpyDeviceToHost));
+                splat_record* r = (splat_record*)dst;
+                for (uint32_t i = 0; i < c->n; ++i) { if (touched[i]) r[i] = rows[i].r; else std::memset(r + i, 0, sizeof(splat_record)); }
+            }
         }
-        // culled splats have no record written: present them zeroed
-        std::vector<unsigned long long> t;
-        CK(fetch_binw(c, t));
-        splat_record* r = (splat_record*)dst;
-        for (uint32_t i = 0; i < c->n; ++i) if (!t[i]) std::memset(r + i, 0, sizeof(splat_record));
     }
     *bytes = need;
     return SPLAT_OK;
@@ -878,16 +847,18 @@ static int sort_pairs_impl(splat_ctx* c, void* stream, void* keys, uint32_t* val
     int rc = ensure_sort_status(c, n);
     if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
-    c->frame_no = c->frame_no + 1;
-    if (c->frame_no >= (1u << 25)) c->frame_no = 1;
-    CK(cudaMemsetAsync(c->ctl, 0, sizeof(FrameCtl), s));
-    set_n_sort_kernel<<<1, 1, 0, s>>>(c->ctl, (unsigned int)n);
-    launch_sort_histogram(keys, key_bytes, n, c->ctl, plan, c->sm_count, s);
+    c->sort_epoch = c->sort_epoch + 1;
+    if (c->sort_epoch >= (1u << 25)) {      // epoch tags wrap: forget every lookback word of the previous cycle
+        c->sort_epoch = 1;
+        CK(cudaMemsetAsync(c->sort_status, 0, c->sort_status_tiles * 256 * 8, s));
+    }
+    CK(cudaMemsetAsync(c->sort_ctl, 0, sizeof(SortCtl), s));
+    set_n_sort_kernel<<<1, 1, 0, s>>>(c->sort_ctl, (unsigned int)n);
+    launch_sort_histogram(keys, key_bytes, n, c->sort_ctl, plan, c->sm_count, s);
     g_pdl_frame = true;
-    launch_radix_sort(keys, vals, keys_alt, vals_alt, key_bytes, n, c->ctl, c->sort_status,
-                      c->frame_no * 16u + 1, plan, c->sm_count, false, s);
+    launch_radix_sort(keys, vals, keys_alt, vals_alt, key_bytes, n, c->sort_ctl, c->sort_status,
+                      c->sort_epoch * 16u + 1, plan, c->sm_count, false, s);
     CK(cudaGetLastError());
-    c->have_frame = false;
     return SPLAT_OK;
 }
 

@@ -15,7 +15,6 @@
 #define SCAN_THREADS 256
 #define SCAN_ITEMS 4
 #define SCAN_TILE_ITEMS (SCAN_THREADS * SCAN_ITEMS)  // splats per scan/duplicate tile
-#define FRAME_MAX_PASSES 4                           // frame keys: <= 2 depth + <= 2 tile digits
 
 // Per-frame uniforms: role of the reference's Uniforms buffer
 // (shaders/gaussian_splat_tile.metal:16-21, src/instanced_splat_renderer.mm:456-469),
@@ -36,16 +35,30 @@ struct FrameUniforms {
 // Device layout of the records: the 48-byte splat_record padded to one aligned 64-byte row, so K1's scattered record
 // writes fill whole 32-byte sectors (a 48-byte stride left partial sectors: read-modify-write in L2 / DRAM, ncu had
 // 182 MB of DRAM reads on a band frame whose inputs are 125 MB) and the blend's gathers touch exactly two sectors.
-struct alignas(64) splat_record_row { splat_record r; unsigned int pad[4]; };
+// pad: kx, ky of the D9' tile test (splat_math.cuh: tile_ratios), then two unused words
+struct alignas(64) splat_record_row { splat_record r; float kx, ky; unsigned int pad[2]; };
 
-// Device control block, zeroed by one memsetAsync at the start of every frame.
+// Device control block of a frame, followed in the same allocation by the per-tile pair counters
+// (tile_count[T + 1], then rounded up): one memsetAsync zeroes both at the start of every frame.
 struct FrameCtl {
-    unsigned long long total_pairs;   // D (exact even when it exceeds capacity)
-    unsigned int overflow;
-    unsigned int reserved0;
+    unsigned long long total_pairs;   // D: pairs that passed the tile test (tile_offsets_kernel); on overflow the candidate total
+    unsigned int overflow;            // candidate slots exceed the pair capacity: the frame's lists are not built
+    unsigned int n_cand;              // candidate (splat, tile-of-rectangle) slots = min(total_cand, capacity) (tile_scan_kernel)
+    unsigned long long total_cand;    // exact even when it exceeds the capacity
+    unsigned int n_live_blocks;       // 256-splat blocks that survived block culling (block_cull_kernel)
+    unsigned int max_tile_pairs;      // longest tile list (tile_offsets_kernel)
+    unsigned int pad[8];
+};
+static_assert(sizeof(FrameCtl) == 64, "FrameCtl is 64 bytes");
+#define FRAME_CTL_WORDS (sizeof(FrameCtl) / 4)
+__host__ __device__ __forceinline__ unsigned int* ctl_tile_count(FrameCtl* c) { return reinterpret_cast<unsigned int*>(c + 1); }
+
+// Control block of the stand-alone radix sort (splat_sort_pairs_*; also sorts the scene's Morton codes at upload).
+struct SortCtl {
+    unsigned int n_sort;
+    unsigned int overflow;            // always 0 (kept so the kernels read one flag)
     unsigned int sort_ticket[SPLAT_MAX_SORT_PASSES];
-    unsigned int n_sort;              // min(D, capacity), written by the tile-sum scan
-    unsigned int pad[5];
+    unsigned int pad[6];
     unsigned int hist[SPLAT_MAX_SORT_PASSES][256];
 };
 
@@ -56,8 +69,6 @@ struct ScenePlanes {
     const float4* syz_op_rg;  // scale.y, scale.z, opacity, bits(half r | half g << 16)
     const uint16_t* b;        // half(b)
     const float4* base_rgb;   // fp32 r g b (loader colour) for the SH extension; .w unused
-    const float4* scr;        // position.xyz, max(scale): the 16 bytes the screening kernel reads
-    const float4* row;        // [n][4]: rot, pos_sx, syz_op_rg, (half b bits, -, -, -): one 64-byte row per splat for gathers
     const float4* sh;         // SH planes [12][n_pad]: float4 j of splat i holds coefficients f' = 4j..4j+3,
                               // f' = 3*k + channel (coefficient-major, so degree L reads planes 0 .. 3*((L+1)^2-1)/4)
     size_t n_pad;
@@ -122,7 +133,7 @@ static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 b
 
 // Launchers (each enqueues on `s` and returns).
 void launch_upload_soa(const float* aos_dev, unsigned int n, float4* rot, float4* pos_sx, float4* syz_op_rg,
-                       uint16_t* b, float4* base_rgb, float4* scr, float4* row, cudaStream_t s);
+                       uint16_t* b, float4* base_rgb, cudaStream_t s);
 // sh_rest45_dev: [n][45] as the loader stores it (channel-major: f = channel*15 + k) -> coefficient-major planes
 void launch_upload_sh(const float* sh_rest45_dev, unsigned int n, size_t n_pad, float4* planes, cudaStream_t s);
 // Per-splat "bin word" written by K1 and read by K2 (8 bytes, 0 = culled): the tile rectangle and the half depth,
@@ -140,40 +151,37 @@ __host__ __device__ __forceinline__ unsigned int binw_count(unsigned long long w
     return (tx1 - tx0 + 1u) * (ty1 - ty0 + 1u);
 }
 
-// Band shape (a tile-row band of at most half the frame: most splats are culled): K1 owns BAND_TILE splats per CTA,
-// writes bin words only for the splats that produced pairs and says which in a bitmap (BAND_TILE / 32 words per
-// CTA); K2 walks those bitmaps instead of every bin word.
-#define BAND_TILE 2048u
-static inline bool frame_is_band(const FrameUniforms& U) { return (U.row_end - U.row_begin) * 2 <= U.tiles_y; }
 void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record_row* rec, unsigned long long* binw,
-                       unsigned int* tile_sums, unsigned int* scan_prefix, unsigned int* visbits, unsigned long long capacity, FrameCtl* ctl,
+                       unsigned int* tile_sums, unsigned int* scan_prefix, unsigned long long capacity, FrameCtl* ctl,
                        cudaStream_t s);
-void launch_scan_duplicate(const FrameUniforms& U, const unsigned long long* binw,
-                           unsigned int* offsets, unsigned int* keys, unsigned int* vals,
-                           unsigned int* keys_depth, unsigned int* vals_depth,
-                           unsigned long long capacity, FrameCtl* ctl, const unsigned int* tile_sums,
-                           const unsigned int* scan_prefix, const unsigned int* visbits, SortPlan plan, int sm_count, cudaStream_t s);
-// Frame keys are 32 bits: tile << 16 | half-depth field (TILE), or tile << 16 alone for a list kept in instance
-// order (pairs are emitted in instance order and the sort is stable, so only the tile digits are sorted).
-// LAYER50 keeps two orders of the same pairs: (keys, vals) in arrival order (D3) and (keys_depth, vals_depth) in
-// tile | depth order for the composite. keys_depth may be NULL (TILE, MLAB).
-// Per-pass digit histograms of keys[0..n) into ctl->hist (stand-alone sort only; frames get
-// them from the duplication kernel).
-void launch_sort_histogram(const void* keys, int key_bytes, unsigned long long n, FrameCtl* ctl, SortPlan plan,
+// K2 binning (k_bin.cu). Every (splat, tile of its rectangle) candidate is tested (D9' tile_touch); a passing pair draws
+// its slot in the tile's list from the tile's counter and is parked in (tmp_key, tmp_ts) at its candidate position; the
+// tile counters are scanned into bounds[T + 1]; the pairs are scattered to pairs[bounds[tile] + slot]; every tile's list
+// is sorted in shared memory on the whole 64-bit pair (depth field << 32 | instance index: a total order, so the result
+// equals a stable sort of instance-ordered pairs on tile | depth). LAYER50 also gets the list in instance order (arrival).
+void launch_bin_pairs(const FrameUniforms& U, const unsigned long long* binw, const splat_record_row* rec,
+                      unsigned long long* tmp_key, unsigned long long* tmp_ts, unsigned long long capacity, FrameCtl* ctl,
+                      const unsigned int* tile_sums, const unsigned int* scan_prefix, int sm_count, cudaStream_t s);
+// status_slot: 32 bytes of mapped page-locked memory that receive D / candidates / overflow / longest list and, last, frame_no
+void launch_tile_offsets(const FrameUniforms& U, FrameCtl* ctl, unsigned int* bounds, void* status_slot, unsigned int frame_no, cudaStream_t s);
+void launch_scatter_pairs(const FrameCtl* ctl, const unsigned long long* tmp_key, const unsigned long long* tmp_ts,
+                          const unsigned int* bounds, unsigned long long* pairs, int sm_count, cudaStream_t s);
+void launch_tile_sort(const FrameUniforms& U, const FrameCtl* ctl, const unsigned int* bounds, unsigned long long* pairs,
+                      unsigned int* arrival, cudaStream_t s);
+// Stand-alone sort (k_sort.cu). Per-pass digit histograms of keys[0..n) into ctl->hist.
+void launch_sort_histogram(const void* keys, int key_bytes, unsigned long long n, SortCtl* ctl, SortPlan plan,
                            int sm_count, cudaStream_t s);
 // Sorts n pairs, n read from ctl->n_sort on the device. Result lands in (keys, vals) when
 // plan.n_pass is even, in (keys_alt, vals_alt) when odd. Uses epochs epoch_base .. +n_pass-1.
-// key_bytes: 4 (frame keys, tile << 16 | half depth) or 8 (stand-alone entry point). n_hint: the host's estimate of n
-// (the pair count it last read back; 0 = unknown), used only to pick a kernel shape.
+// key_bytes: 4 or 8. n_hint: the host's estimate of n, used only to pick a kernel shape.
 void launch_radix_sort(void* keys, unsigned int* vals, void* keys_alt, unsigned int* vals_alt, int key_bytes,
-                       unsigned long long n_hint, FrameCtl* ctl, unsigned long long* sort_status,
+                       unsigned long long n_hint, SortCtl* ctl, unsigned long long* sort_status,
                        unsigned int epoch_base, SortPlan plan, int sm_count, bool small_tiles, cudaStream_t s);
-// bounds[t] = first sorted pair of tile t (t = 0..n_tiles); tile t owns [bounds[t], bounds[t+1]).
-void launch_tile_bounds(const unsigned int* keys_sorted, const FrameCtl* ctl, unsigned int first_tile,
-                        unsigned int n_tiles, unsigned int* bounds, cudaStream_t s);
 void launch_pack_bgra8(const void* fb_half4, void* bgra8, size_t n_pixels, cudaStream_t s);
 cudaError_t launch_ply_decode_chunk(const float* rows_dev, unsigned int n_rows, unsigned int stride, const int* slot_dst_dev,
                                     int jx, int jy, int jz, float crop, unsigned int* block_counts, unsigned int* running,
                                     float* aos_out, float* sh_out, cudaStream_t s);
-void launch_blend(const FrameUniforms& U, const splat_record_row* rec, const unsigned int* vals_sorted,
-                  const unsigned int* vals_depth_sorted, const unsigned int* bounds, void* fb_half4, cudaStream_t s);
+// pairs: the tile lists (u64 per pair, instance index in the low word), depth-ordered (TILE, LAYER50) or instance-ordered
+// (MLAB); arrival: LAYER50's instance-ordered list (u32 per pair). bounds[t] .. bounds[t + 1] = tile t's list.
+void launch_blend(const FrameUniforms& U, const splat_record_row* rec, const unsigned long long* pairs,
+                  const unsigned int* arrival, const unsigned int* bounds, void* fb_half4, cudaStream_t s);

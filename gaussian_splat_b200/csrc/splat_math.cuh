@@ -155,8 +155,11 @@ __device__ __forceinline__ unsigned int preprocess_one(
     // viewport transform (y down) and tile rectangle (D9)
     const float cx = (ndcx * 0.5f + 0.5f) * U.W;
     const float cy = (0.5f - 0.5f * ndcy) * U.H;
-    const float hx = fabsf(r1 * e1x) + fabsf(r2 * e1y);
-    const float hy = fabsf(r1 * e1y) + fabsf(r2 * e1x);
+    // D9': the quad's AABB (:142-143) intersected with the AABB of the ellipse u*u + v*v <= 2 ln 100 (:191), whose half
+    // extents are (rho / 3) sqrt((r1 e1x)^2 + (r2 e2x)^2), rho / 3 = 1.011618 rounded UP to 1.0117
+    const float ax1 = r1 * e1x, ax2 = r2 * e1y, ay1 = r1 * e1y, ay2 = r2 * e1x;
+    const float hx = fminf(fabsf(ax1) + fabsf(ax2), 1.0117f * sqrtf(ax1 * ax1 + ax2 * ax2));
+    const float hy = fminf(fabsf(ay1) + fabsf(ay2), 1.0117f * sqrtf(ay1 * ay1 + ay2 * ay2));
     float fi0 = ceilf((cx - hx) - 0.5f), fi1 = floorf((cx + hx) - 0.5f);
     float fj0 = ceilf((cy - hy) - 0.5f), fj1 = floorf((cy + hy) - 0.5f);
     const float Wm1 = U.W - 1.0f, Hm1 = U.H - 1.0f;
@@ -178,4 +181,34 @@ __device__ __forceinline__ unsigned int preprocess_one(
     rec.rect_lo = (unsigned int)tx0 | ((unsigned int)ty0 << 16);
     rec.rect_hi = (unsigned int)tx1 | ((unsigned int)ty1 << 16);
     return (unsigned int)((tx1 - tx0 + 1) * (ty1 - ty0 + 1));
+}
+
+// D9' per-tile test: can the splat cover a pixel centre of tile (tx, ty)? The minimum of q = u*u + v*v over the tile's
+// pixel-centre box lies on a box edge facing the splat centre (q grows along every ray from the centre), i.e. on the
+// vertical line x = clamp(cx) or the horizontal line y = clamp(cy); on each line the minimiser is the clamped root of
+// dq/dt = 0 (kx = B / C, ky = B / A of the quadratic form, computed once per splat by tile_ratios) and q is evaluated
+// there with the fragment's own formula. The threshold carries a slack proportional to that formula's rounding error at
+// this distance, so a tile holding a covered pixel is never dropped: images do not change, S2 stays exact per pixel.
+// The CPU restatement carries the same text (tile_touch there too); the set of pairs is bit-identical.
+__device__ __forceinline__ void tile_ratios(float ux, float uy, float vx, float vy, float& kx, float& ky) {
+    const float A = ux * ux + vx * vx, B = ux * uy + vx * vy, C = uy * uy + vy * vy;
+    kx = B / C; ky = B / A;
+}
+__device__ __forceinline__ bool tile_touch(float cx, float cy, float ux, float uy, float vx, float vy, float kx, float ky,
+                                           int tx, int ty, int w, int h) {
+    const float X0 = (float)(tx * 16) + 0.5f, X1 = (float)min(tx * 16 + 15, w - 1) + 0.5f;
+    const float Y0 = (float)(ty * 16) + 0.5f, Y1 = (float)min(ty * 16 + 15, h - 1) + 0.5f;
+    const float xc = fminf(fmaxf(cx, X0), X1), yc = fminf(fmaxf(cy, Y0), Y1);
+    const float dxa = xc - cx;
+    const float dya = fminf(fmaxf(-(dxa * kx), Y0 - cy), Y1 - cy);
+    const float ua = fmaf(dxa, ux, dya * uy), va = fmaf(dxa, vx, dya * vy);
+    const float qa = fmaf(ua, ua, va * va);
+    const float dyb = yc - cy;
+    const float dxb = fminf(fmaxf(-(dyb * ky), X0 - cx), X1 - cx);
+    const float ub = fmaf(dxb, ux, dyb * uy), vb = fmaf(dxb, vx, dyb * vy);
+    const float qb = fmaf(ub, ub, vb * vb);
+    const float m = fmaxf(fabsf(cx - X0), fabsf(cx - X1)) + fmaxf(fabsf(cy - Y0), fabsf(cy - Y1));
+    const float e = (m * (((fabsf(ux) + fabsf(uy)) + fabsf(vx)) + fabsf(vy))) * 9.5367431640625e-07f;   // 2^-20
+    const float thr = (9.25f + 8.0f * e) + e * e;
+    return !(fminf(qa, qb) > thr);
 }

@@ -27,7 +27,7 @@ assert RECORD_DTYPE.itemsize == 48
 class Opts(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "mode", "max_fragments", "order", "sh_degree", "tile_row_begin", "tile_row_end",
-        "cap_policy", "reserved")]
+        "cap_policy", "tile_test")]
 
 
 def build(force: bool = False) -> str:
@@ -103,12 +103,12 @@ class Frame:
     """All stages up to tile ranges for one (scene, camera, options)."""
 
     def __init__(self, instances, view, proj, w, h, mode=MODE_TILE, max_fragments=None,
-                 order=ORDER_NEAR_FIRST, tile_row_begin=0, tile_row_end=0, sh_rest=None, sh_degree=0):
+                 order=ORDER_NEAR_FIRST, tile_row_begin=0, tile_row_end=0, sh_rest=None, sh_degree=0, tile_test=1):
         L = lib()
         inst = np.ascontiguousarray(instances, np.float32).reshape(-1, 14)
         if max_fragments is None:
             max_fragments = 50 if mode == MODE_LAYER50 else 32
-        self.opts = Opts(mode, max_fragments, order, sh_degree, tile_row_begin, tile_row_end, 0, 0)
+        self.opts = Opts(mode, max_fragments, order, sh_degree, tile_row_begin, tile_row_end, 0, tile_test)
         self.w, self.h = w, h
         v = np.ascontiguousarray(view, np.float32); p = np.ascontiguousarray(proj, np.float32)
         shp = None

@@ -57,6 +57,7 @@ struct Uni {
     float W, H;
     int w, h, tiles_x, tiles_y, row_begin, row_end;
     float cam[3];
+    int tight;   /* 1 = D9' (ellipse-clipped rectangle + per-tile test), 0 = the plain quad AABB of D9 */
 };
 
 /* M * (x,y,z,1), column-major, k = 0,1,2,3 left to right (D5). */
@@ -191,8 +192,14 @@ uint32_t preprocess_one(const float* inst, const Uni& U, orb_record& rec) {
     /* viewport transform, y down (D9) */
     const float cx = (ndcx * 0.5f + 0.5f) * U.W;
     const float cy = (0.5f - 0.5f * ndcy) * U.H;
-    const float hx = std::fabs(r1 * e1x) + std::fabs(r2 * e1y);
-    const float hy = std::fabs(r1 * e1y) + std::fabs(r2 * e1x);
+    /* D9': AABB of the quad (:142-143) intersected with the AABB of the ellipse u*u + v*v <= 2 ln 100 (:191):
+     * half extents (rho/3) sqrt((r1 e1x)^2 + (r2 e2x)^2), rho/3 = 1.011618 rounded UP to 1.0117 */
+    const float ax1 = r1 * e1x, ax2 = r2 * e1y, ay1 = r1 * e1y, ay2 = r2 * e1x;
+    float hx = std::fabs(ax1) + std::fabs(ax2), hy = std::fabs(ay1) + std::fabs(ay2);
+    if (U.tight) {
+        hx = std::fmin(hx, 1.0117f * std::sqrt(ax1 * ax1 + ax2 * ax2));
+        hy = std::fmin(hy, 1.0117f * std::sqrt(ay1 * ay1 + ay2 * ay2));
+    }
     float fi0 = std::ceil((cx - hx) - 0.5f), fi1 = std::floor((cx + hx) - 0.5f);
     float fj0 = std::ceil((cy - hy) - 0.5f), fj1 = std::floor((cy + hy) - 0.5f);
     const float Wm1 = U.W - 1.0f, Hm1 = U.H - 1.0f;
@@ -215,6 +222,35 @@ uint32_t preprocess_one(const float* inst, const Uni& U, orb_record& rec) {
     rec.rect_lo = (uint32_t)tx0 | ((uint32_t)ty0 << 16);
     rec.rect_hi = (uint32_t)tx1 | ((uint32_t)ty1 << 16);
     return (uint32_t)((tx1 - tx0 + 1) * (ty1 - ty0 + 1));
+}
+
+/* D9' per-tile test: can the splat cover a pixel centre of tile (tx, ty)? Conservative: the minimum of
+ * q = u*u + v*v over the tile's pixel-centre box is attained on a box edge facing the splat centre (q grows
+ * along every ray from the centre), i.e. on the vertical line x = clamp(cx) or the horizontal line
+ * y = clamp(cy); on each line the minimiser is the clamped root of dq/dt = 0, and q is evaluated there with the
+ * fragment's own formula (:178-191). The threshold carries a slack proportional to the rounding error of that
+ * formula at this distance, so a tile holding a covered pixel is never dropped (images do not change: S2 stays
+ * exact per pixel). Same text as gaussian_splat_b200/csrc/splat_math.cuh: tile_touch. */
+inline void tile_ratios(const orb_record& r, float& kx, float& ky) {
+    const float A = r.ux * r.ux + r.vx * r.vx, B = r.ux * r.uy + r.vx * r.vy, C = r.uy * r.uy + r.vy * r.vy;
+    kx = B / C; ky = B / A;
+}
+inline bool tile_touch(const orb_record& r, float kx, float ky, int tx, int ty, int w, int h) {
+    const float X0 = (float)(tx * 16) + 0.5f, X1 = (float)std::min(tx * 16 + 15, w - 1) + 0.5f;
+    const float Y0 = (float)(ty * 16) + 0.5f, Y1 = (float)std::min(ty * 16 + 15, h - 1) + 0.5f;
+    const float xc = std::fmin(std::fmax(r.cx, X0), X1), yc = std::fmin(std::fmax(r.cy, Y0), Y1);
+    const float dxa = xc - r.cx;
+    const float dya = std::fmin(std::fmax(-(dxa * kx), Y0 - r.cy), Y1 - r.cy);
+    const float ua = std::fmaf(dxa, r.ux, dya * r.uy), va = std::fmaf(dxa, r.vx, dya * r.vy);
+    const float qa = std::fmaf(ua, ua, va * va);
+    const float dyb = yc - r.cy;
+    const float dxb = std::fmin(std::fmax(-(dyb * ky), X0 - r.cx), X1 - r.cx);
+    const float ub = std::fmaf(dxb, r.ux, dyb * r.uy), vb = std::fmaf(dxb, r.vx, dyb * r.vy);
+    const float qb = std::fmaf(ub, ub, vb * vb);
+    const float m = std::fmax(std::fabs(r.cx - X0), std::fabs(r.cx - X1)) + std::fmax(std::fabs(r.cy - Y0), std::fabs(r.cy - Y1));
+    const float e = (m * (((std::fabs(r.ux) + std::fabs(r.uy)) + std::fabs(r.vx)) + std::fabs(r.vy))) * 9.5367431640625e-07f;   /* 2^-20 */
+    const float thr = (9.25f + 8.0f * e) + e * e;
+    return !(std::fmin(qa, qb) > thr);
 }
 
 } // namespace
@@ -398,6 +434,7 @@ orb_frame* orb_frame_create(const float* inst, uint32_t n, const float* sh_rest,
     U.tiles_x = (w + 15) / 16; U.tiles_y = (h + 15) / 16;
     U.row_begin = 0; U.row_end = U.tiles_y;
     if (opts->tile_row_end > 0) { U.row_begin = opts->tile_row_begin; U.row_end = std::min(opts->tile_row_end, U.tiles_y); }
+    U.tight = opts->tile_test;
     F->n = n; F->T = (uint32_t)(U.tiles_x * U.tiles_y);
     for (int j = 0; j < 3; ++j) {                   /* camera position = -R^T t */
         const float m0 = view[j * 4 + 0] * view[12], m1 = view[j * 4 + 1] * view[13], m2 = view[j * 4 + 2] * view[14];
@@ -427,7 +464,31 @@ orb_frame* orb_frame_create(const float* inst, uint32_t n, const float* sh_rest,
             for (auto& x : th) x.join();
         }
     }
-    /* K2: exclusive scan + duplication, row-major (ty outer, tx inner) */
+    /* K2: duplication, row-major (ty outer, tx inner), of the tiles that pass the D9' test; touched[] becomes the
+     * number of pairs emitted (a splat whose tiles all fail is culled: record zeroed), offsets[] their exclusive scan */
+    {
+        auto count = [&](uint32_t b, uint32_t e) {
+            for (uint32_t i = b; i < e; ++i) {
+                if (!F->touched[i] || !F->opts.tile_test) continue;     /* D9' off: every tile of the rectangle */
+                const orb_record& r = F->rec[i];
+                const uint32_t tx0 = r.rect_lo & 0xFFFF, ty0 = r.rect_lo >> 16, tx1 = r.rect_hi & 0xFFFF, ty1 = r.rect_hi >> 16;
+                float kx, ky; tile_ratios(r, kx, ky);
+                uint32_t c = 0;
+                for (uint32_t ty = ty0; ty <= ty1; ++ty) for (uint32_t tx = tx0; tx <= tx1; ++tx)
+                    c += tile_touch(r, kx, ky, (int)tx, (int)ty, U.w, U.h) ? 1u : 0u;
+                F->touched[i] = c;
+                if (!c) F->rec[i] = orb_record{};
+            }
+        };
+        const int nt = g_threads;
+        if (nt <= 1 || n < 4096) count(0, n);
+        else {
+            std::vector<std::thread> th;
+            for (int t = 0; t < nt; ++t)
+                th.emplace_back(count, (uint32_t)((uint64_t)n * t / nt), (uint32_t)((uint64_t)n * (t + 1) / nt));
+            for (auto& x : th) x.join();
+        }
+    }
     uint64_t D = 0;
     for (uint32_t i = 0; i < n; ++i) { F->offsets[i] = (uint32_t)D; D += F->touched[i]; }
     F->keys_u.resize(D); F->vals_u.resize(D);
@@ -436,8 +497,10 @@ orb_frame* orb_frame_create(const float* inst, uint32_t n, const float* sh_rest,
         const orb_record& r = F->rec[i];
         const uint32_t tx0 = r.rect_lo & 0xFFFF, ty0 = r.rect_lo >> 16, tx1 = r.rect_hi & 0xFFFF, ty1 = r.rect_hi >> 16;
         const uint32_t df = depth_field(F->opts, r, i);
+        float kx, ky; tile_ratios(r, kx, ky);
         uint64_t o = F->offsets[i];
         for (uint32_t ty = ty0; ty <= ty1; ++ty) for (uint32_t tx = tx0; tx <= tx1; ++tx) {
+            if (F->opts.tile_test && !tile_touch(r, kx, ky, (int)tx, (int)ty, U.w, U.h)) continue;
             F->keys_u[o] = ((uint64_t)(ty * (uint32_t)U.tiles_x + tx) << 32) | df;
             F->vals_u[o] = i; ++o;
         }

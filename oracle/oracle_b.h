@@ -45,7 +45,7 @@ typedef struct {
     int32_t tile_row_begin; /* band of tile rows rendered: [begin, end)     */
     int32_t tile_row_end;   /* <= 0 means "all rows"                        */
     int32_t cap_policy;     /* 0 = mode default (D4); 1 = arrival; 2 = sorted */
-    int32_t reserved;
+    int32_t tile_test;      /* 1 = D9' (ellipse-clipped tile rectangle + per-tile test; what the CUDA path does), 0 = plain quad AABB (D9) */
 } orb_opts;
 
 /* 48-byte per-splat record, identical to the CUDA path's layout. */
