@@ -103,18 +103,18 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(self.sm)}
 
 
-def algorithmic_bytes(n, visible, D, n_pass, P, sh_degree=0, layer=False):
-    """SURVEY 8(d) per-stage algorithmic bytes of one frame. LAYER50 keeps the pairs in two orders
-    (arrival and depth): the duplication writes both, the sort passes are counted over both lists, the
-    blend walks both."""
+def algorithmic_bytes(n, visible, D, C, P, sh_degree=0, layer=False):
+    """Per-stage algorithmic bytes of one frame (SURVEY 8(d) adapted to the per-tile binning).
+    n splats, V visible, C candidate (splat, tile-of-rectangle) slots, D pairs that pass the tile test, P pixels."""
     sh = {0: 0, 1: 36, 2: 96, 3: 180}[sh_degree]
-    lists = 2 if layer else 1
     return {
         "preprocess": n * (56 + 4) + visible * (48 + sh),
-        "scan_duplicate": n * 8 + n * 4 + D * 8 * lists,            # bin words in, offsets out, (u32 key, u32 value) pairs out
-        "sort": D * n_pass * 16,                                    # every pass reads and writes 4 + 4 B per pair
-        "ranges": D * 4,
-        "blend": D * (4 + 48) * lists + P * 8,
+        # bin words in, the visible splats' record rows for the tile test, candidates parked (key + tile|slot),
+        # parked pairs read back, pairs scattered
+        "scan_duplicate": n * 8 + visible * 64 + C * 16 + C * 16 + D * 8,
+        "sort": D * 16 + (D * 4 if layer else 0),                   # every tile list read and written once (+ LAYER50's arrival list)
+        "ranges": 0,
+        "blend": D * (8 + 48) + (D * (4 + 48) if layer else 0) + P * 8,
     }
 
 
@@ -429,7 +429,7 @@ def main():
     frames_per_step = 1 if bands else world
     fps = frames_per_step * 1e3 / ms_per_step
     st = ctx.status()
-    D = int(st.n_pairs); n_pass = int(st.sort_passes)
+    D = int(st.n_pairs); n_pass = int(st.sort_passes); C = int(getattr(st, 'n_candidates', 0)) or D
 
     # ---- e2e: through the public host-buffer API. Scene resident (uploaded once, as the reference's
     # initialize() does, src/instanced_splat_renderer.mm:399-422); every step copies that step's
@@ -540,7 +540,7 @@ def main():
         hbm_peak, peak_kind, sm_max = peaks()
         visible = int((ctx.fetch(capi.FETCH_TILES_TOUCHED) > 0).sum())
         P = band_px if bands else w * h
-        ab = algorithmic_bytes(n, visible, D, n_pass, P, args.sh_degree, layer=bool(mode))
+        ab = algorithmic_bytes(n, visible, D, C, P, args.sh_degree, layer=bool(mode))
         stage_ms = {k: v / args.steps for k, v in stage_acc.items()}
         stages = {}
         for k in STAGES:
@@ -549,8 +549,8 @@ def main():
             stages[k] = {"ms": ms, "alg_bytes": ab[k], "gb_per_s": gbs, "frac_of_hbm_peak": gbs / hbm_peak}
         dom = max(STAGES, key=lambda k: stage_ms.get(k, 0.0))
         clocks = sampler.result()
-        roof = {"kernel": {"blend": "blend_kernel", "sort": "onesweep_pass_kernel", "preprocess": "preprocess_kernel",
-                           "scan_duplicate": "scan_duplicate_kernel", "ranges": "tile_bounds_kernel"}[dom],
+        roof = {"kernel": {"blend": "blend_kernel", "sort": "tile_sort_kernel", "preprocess": "preprocess_kernel",
+                           "scan_duplicate": "bin_pairs_kernel", "ranges": "-"}[dom],
                 "bound": "hbm", "achieved": stages[dom]["gb_per_s"], "peak": hbm_peak, "unit": "GB/s",
                 "frac": stages[dom]["frac_of_hbm_peak"], "frac_of_8TBs_nominal": stages[dom]["gb_per_s"] / 8000.0,
                 "traffic": measured_traffic(wl, dom), "peak_kind": peak_kind,
@@ -586,7 +586,7 @@ def main():
                         "value": e2e_bgra_fps, "d2h_bytes_per_step": w * h * 4 + 16,
                         "note": "same call with SPLAT_FLAG_HOST_BGRA8: frames delivered as the reference drawable's BGRA8Unorm"}},
             "camera_batch_device": inflight,
-            "gpu_launches": args.steps * (5 + n_pass),      # K1 (preprocess + tile scan), K2, K3 x n_pass, K4, K5 (+1 memset node, not counted)
+            "gpu_launches": args.steps * 7,      # preprocess, tile scan, bin pairs, tile offsets, scatter, tile sort, blend (+1 memset node, not counted)
             "clocks": clocks, "wall_s": t_wall, "numa": numa,
         }
         if world == 1 and not args.no_sort_bench:

@@ -40,7 +40,8 @@ class SplatOpts(C.Structure):
 
 class SplatStatus(C.Structure):
     _fields_ = [("n_splats", C.c_uint32), ("n_visible_unused", C.c_uint32), ("n_pairs", C.c_uint64),
-                ("pair_capacity", C.c_uint64), ("overflow", C.c_uint32), ("sort_passes", C.c_uint32)]
+                ("pair_capacity", C.c_uint64), ("overflow", C.c_uint32), ("sort_passes", C.c_uint32),
+                ("n_candidates", C.c_uint64), ("max_tile_pairs", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 class SplatError(RuntimeError):

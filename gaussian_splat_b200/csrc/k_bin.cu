@@ -1,12 +1,12 @@
-// K2: binning of the visible splats into per-tile lists. Replaces the hardware tiler's binning of the instanced
-// quads (src/instanced_splat_renderer.mm:496-499 draw call) and the per-pixel insertion sorts of
+// K2: from K1's parked (splat, tile) pairs to sorted per-tile lists. Replaces the hardware tiler's binning of the
+// instanced quads (src/instanced_splat_renderer.mm:496-499 draw call) and the per-pixel insertion sorts of
 // shaders/gaussian_splat_tile.metal:240-249 / gaussian_splat_50layer.metal:198-206.
 //
-//   bin_pairs_kernel     every (splat, tile of its rectangle) candidate is tested (D9' tile_touch); a passing pair draws
-//                        its slot in the tile's list from the tile's counter (one L2 atomic) and is parked at its
-//                        candidate position in (tmp_key, tmp_ts)
-//   tile_offsets_kernel  exclusive scan of the T tile counters -> bounds[T + 1], D, the longest list
-//   scatter_pairs_kernel pairs[bounds[tile] + slot] = depth field << 32 | instance index
+//   (K1)                 every (splat, tile of its rectangle) candidate that passes the D9' tile test bumps its tile's
+//                        counter and is parked (key = depth field << 32 | instance index, tile) - k_preprocess.cu
+//   tile_offsets_kernel  exclusive scan of the T tile counters -> bounds[T + 1] (+ the copy the scatter advances), D,
+//                        the longest list
+//   scatter_pairs_kernel pairs[cursor[tile]++] = key
 //   tile_sort_kernel     one CTA per tile sorts its list on the whole 64-bit pair. Instance indices are unique within a
 //                        list, so the key is total and the result is what a stable sort of instance-ordered pairs on
 //                        tile | depth gives, whatever order the atomics handed the slots out in.
@@ -16,146 +16,35 @@
 // twice and read twice, and the sort runs on T independent lists of a few hundred pairs.
 #include "splat_math.cuh"
 
-#define HOLE 0xFFFFFFFFFFFFFFFFull
-
-// Persistent grid: a CTA walks tiles of 1024 splats with a fixed stride. Per tile: one block scan gives every splat its
-// first candidate slot AND the visible splats their rank, so the visible ones are compacted into shared memory (first
-// slot, rectangle, depth field, index) straight from K1's 8-byte bin words. The expansion then works warp by warp on 32
-// consecutive candidate slots: one binary search for the owner of the first slot, and because every visible splat owns
-// at least one slot the other 31 owners lie within the next 32 compact entries - each lane finds its own with five
-// shuffles. The lanes of one splat read the same record row (one L2 request), run the tile test and draw a slot.
-__global__ void __launch_bounds__(SCAN_THREADS, 8) bin_pairs_kernel(
-    const __grid_constant__ FrameUniforms U, const unsigned long long* binw, const splat_record_row* rec,
-    unsigned long long* __restrict__ tmp_key, unsigned long long* __restrict__ tmp_ts,
-    unsigned long long capacity, FrameCtl* ctl, const unsigned int* tile_sums, const unsigned int* scan_prefix,
-    unsigned int n_tiles, unsigned int n_cells)
-{
-    __shared__ unsigned int s_start[SCAN_TILE_ITEMS + 1];      // first candidate slot of the v-th visible splat (+ sentinel)
-    __shared__ unsigned int s_rect[SCAN_TILE_ITEMS], s_wdt[SCAN_TILE_ITEMS];   // tx0 | ty0 << 12, rectangle width in tiles
-    __shared__ unsigned int s_dfi[SCAN_TILE_ITEMS];            // depth field << 16 | splat index within the tile
-    __shared__ unsigned int s_warp[SCAN_THREADS / 32], s_wvis[SCAN_THREADS / 32];
-
-    const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    pdl_prologue();
-    if (__ldcg(&ctl->overflow)) return;
-    unsigned int* const tile_count = ctl_tile_count(ctl);
-    const bool by_instance = U.mode == SPLAT_MODE_MLAB;       // the only list MLAB walks is in instance order: no depth in the key
-
-    for (unsigned int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const unsigned int base = tile * SCAN_TILE_ITEMS;
-        unsigned int btotal = __ldcg(tile_sums + 2 * tile);
-        if (2 * tile + 1 < n_cells) btotal += __ldcg(tile_sums + 2 * tile + 1);
-        if (btotal == 0) continue;      // nothing visible in this tile of splats
-        const unsigned int prefix = __ldcg(scan_prefix + tile);
-        // ---- 4 consecutive splats per thread (buffers are padded to the tile size); scan of candidates and of visible splats
-        unsigned long long bw[SCAN_ITEMS];
-        {
-            const ulonglong2 w01 = __ldcg(reinterpret_cast<const ulonglong2*>(binw + base + tid * SCAN_ITEMS));
-            const ulonglong2 w23 = __ldcg(reinterpret_cast<const ulonglong2*>(binw + base + tid * SCAN_ITEMS + 2));
-            bw[0] = w01.x; bw[1] = w01.y; bw[2] = w23.x; bw[3] = w23.y;
-        }
-        unsigned int cnt[SCAN_ITEMS];
-#pragma unroll
-        for (int k = 0; k < SCAN_ITEMS; ++k) cnt[k] = base + tid * SCAN_ITEMS + k < U.n ? binw_count(bw[k]) : 0u;
-        unsigned int tsum = 0, tvis = 0;
-#pragma unroll
-        for (int k = 0; k < SCAN_ITEMS; ++k) { tsum += cnt[k]; tvis += cnt[k] ? 1u : 0u; }
-        unsigned int incl = tsum, ivis = tvis;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const unsigned int a = __shfl_up_sync(0xFFFFFFFFu, incl, d), b = __shfl_up_sync(0xFFFFFFFFu, ivis, d);
-            if (lane >= d) { incl += a; ivis += b; }
-        }
-        if (lane == 31) { s_warp[warp] = incl; s_wvis[warp] = ivis; }
-        __syncthreads();
-        unsigned int wbase = 0, vbase = 0, n_vis = 0, ctotal = 0;
-#pragma unroll
-        for (int k = 0; k < SCAN_THREADS / 32; ++k) {
-            const unsigned int a = s_warp[k], b = s_wvis[k];
-            if (k < (int)warp) { wbase += a; vbase += b; }
-            n_vis += b; ctotal += a;
-        }
-        unsigned int excl = wbase + incl - tsum;   // first candidate slot of this thread's first splat, tile-local
-        unsigned int v = vbase + ivis - tvis;      // rank of this thread's first visible splat
-#pragma unroll
-        for (int k = 0; k < SCAN_ITEMS; ++k) {
-            if (cnt[k]) {
-                const unsigned int h = (unsigned int)(bw[k] >> 48);
-                const unsigned int df = by_instance ? 0u : (U.order == SPLAT_ORDER_REFERENCE ? (0xFFFFu - h) : h);   // half-depth field (D3)
-                s_start[v] = excl;
-                s_dfi[v] = (df << 16) | (tid * SCAN_ITEMS + k);
-                s_rect[v] = (unsigned int)bw[k] & 0xFFFFFFu;              // tx0 | ty0 << 12
-                s_wdt[v] = ((unsigned int)(bw[k] >> 24) & 0xFFFu) - ((unsigned int)bw[k] & 0xFFFu) + 1u;
-                ++v;
-            }
-            excl += cnt[k];
-        }
-        if (tid == 0) s_start[n_vis] = ctotal;              // sentinel: end of the last owner
-        __syncthreads();
-
-        // ---- expansion: a warp takes 32 consecutive candidate slots at a time
-        for (unsigned int j0 = warp * 32u; j0 < ctotal; j0 += SCAN_THREADS) {
-            const unsigned int j = j0 + lane;
-            // owner of slot j0: last compact entry whose first slot is <= j0 (uniform across the warp)
-            unsigned int lo = 0, hi = n_vis;
-            while (hi - lo > 1) { const unsigned int mid = (lo + hi) >> 1; if (s_start[mid] <= j0) lo = mid; else hi = mid; }
-            // ends of the 32 owners from there on; lane's owner = lo + #{ends <= j}
-            const unsigned int end_l = s_start[min(lo + lane + 1u, n_vis)];
-            unsigned int c = 0;
-#pragma unroll
-            for (int st = 16; st > 0; st >>= 1) {
-                const unsigned int e = __shfl_sync(0xFFFFFFFFu, end_l, c + st - 1);
-                if (e <= j) c += st;
-            }
-            const unsigned long long g = (unsigned long long)prefix + j;
-            if (j < ctotal && g < capacity) {
-                const unsigned int vi = lo + c;
-                const unsigned int k = j - s_start[vi];
-                const unsigned int rect = s_rect[vi], wdt = s_wdt[vi], dfi = s_dfi[vi];
-                const unsigned int tx0 = rect & 0xFFFu, ty0 = rect >> 12;
-                const unsigned int ry = k / wdt, rx = k - ry * wdt;
-                const unsigned int tx = tx0 + rx, ty = ty0 + ry;
-                const unsigned int splat = base + (dfi & 0xFFFFu), df = dfi >> 16;
-                const float4* r = reinterpret_cast<const float4*>(rec + splat);
-                const float4 A = __ldcg(r), B = __ldcg(r + 1), R = __ldcg(r + 3);
-                if (tile_touch(A.x, A.y, A.z, A.w, B.x, B.y, R.x, R.y, (int)tx, (int)ty, U.w, U.h)) {
-                    const unsigned int t = ty * (unsigned int)U.tiles_x + tx;
-                    const unsigned int slot = atomicAdd(tile_count + t, 1u);
-                    tmp_key[g] = ((unsigned long long)df << 32) | splat;
-                    tmp_ts[g] = ((unsigned long long)t << 32) | slot;
-                } else tmp_ts[g] = HOLE;
-            }
-        }
-        __syncthreads();            // the compact arrays are reused by the next tile
-    }
-}
-
-void launch_bin_pairs(const FrameUniforms& U, const unsigned long long* binw, const splat_record_row* rec,
-                      unsigned long long* tmp_key, unsigned long long* tmp_ts, unsigned long long capacity, FrameCtl* ctl,
-                      const unsigned int* tile_sums, const unsigned int* scan_prefix, int sm_count, cudaStream_t s)
-{
-    if (U.n == 0) return;
-    const unsigned int n_cells = (U.n + SCAN_TILE_ITEMS / 2 - 1) / (SCAN_TILE_ITEMS / 2);
-    const unsigned int n_tiles = (U.n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS;
-    const unsigned int grid = n_tiles < (unsigned int)sm_count * 8u ? n_tiles : (unsigned int)sm_count * 8u;
-    launch_pdl(bin_pairs_kernel, dim3(grid), dim3(SCAN_THREADS), 0, s, U, binw, rec, tmp_key, tmp_ts, capacity, ctl,
-               tile_sums, scan_prefix, n_tiles, n_cells);
-}
-
-// bounds[t] = pairs of tiles 0 .. t-1 (t = 0 .. T); one CTA, a contiguous chunk of counters per thread.
-struct FrameStatusSlotDev { unsigned long long total_pairs, total_cand; unsigned int overflow, max_tile_pairs, frame_no, pad; };
+// bounds[t] = pairs of tiles 0 .. t-1 (t = 0 .. T). One CTA: a thread owns a contiguous run of counters, read with up to
+// sixteen independent 16-byte loads (one L2 round trip), scanned in registers, written back as vectors. The counter and
+// bounds arrays are padded to 65536 + 8 words; counters beyond T are ignored.
+template <int V>      // 16-byte vectors per thread: frames of up to 4096 V tiles
 __global__ void __launch_bounds__(1024) tile_offsets_kernel(FrameCtl* ctl, unsigned int n_tiles, unsigned int* __restrict__ bounds,
-                                                            volatile FrameStatusSlotDev* slot, unsigned int frame_no)
+                                                            unsigned int* __restrict__ cursor)
 {
     __shared__ unsigned int s_wsum[32], s_wmax[32];
     pdl_prologue();
     const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned int* tile_count = ctl_tile_count(ctl);
     const bool over = __ldcg(&ctl->overflow) != 0;
-    const unsigned int per = (n_tiles + 1023u) / 1024u;
-    const unsigned int j0 = min(tid * per, n_tiles), j1 = min(j0 + per, n_tiles);
+    const unsigned int per4 = (n_tiles + 4095u) / 4096u;          // 16-byte vectors per thread (<= 16)
+    const unsigned int first = tid * per4 * 4u;
+    uint4 v[V];
+#pragma unroll
+    for (int q = 0; q < V; ++q)
+        if ((unsigned)q < per4) v[q] = __ldcg(reinterpret_cast<const uint4*>(tile_count + first) + q);
     unsigned int part = 0, big = 0;
-    for (unsigned int j = j0; j < j1; ++j) { const unsigned int c = over ? 0u : __ldcg(tile_count + j); part += c; big = max(big, c); }
+#pragma unroll
+    for (int q = 0; q < V; ++q)
+        if ((unsigned)q < per4) {
+            unsigned int* e = &v[q].x;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (over || first + 4u * q + k >= n_tiles) e[k] = 0u;
+                part += e[k]; big = max(big, e[k]);
+            }
+        }
     unsigned int incl = part;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -167,45 +56,87 @@ __global__ void __launch_bounds__(1024) tile_offsets_kernel(FrameCtl* ctl, unsig
     if (lane == 0) s_wmax[warp] = big;
     __syncthreads();
     unsigned int run = incl - part, total = 0, mx = 0;
+#pragma unroll
     for (int k = 0; k < 32; ++k) { const unsigned int x = s_wsum[k]; if (k < (int)warp) run += x; total += x; mx = max(mx, s_wmax[k]); }
-    for (unsigned int j = j0; j < j1; ++j) { bounds[j] = run; run += over ? 0u : __ldcg(tile_count + j); }
+#pragma unroll
+    for (int q = 0; q < V; ++q)
+        if ((unsigned)q < per4) {
+            uint4 o;
+            o.x = run; run += v[q].x; o.y = run; run += v[q].y; o.z = run; run += v[q].z; o.w = run; run += v[q].w;
+            reinterpret_cast<uint4*>(bounds + first)[q] = o;
+#ifdef CURSOR_STRIDE
+            cursor[(size_t)(first + 4 * q) * CURSOR_STRIDE] = o.x; cursor[(size_t)(first + 4 * q + 1) * CURSOR_STRIDE] = o.y;
+            cursor[(size_t)(first + 4 * q + 2) * CURSOR_STRIDE] = o.z; cursor[(size_t)(first + 4 * q + 3) * CURSOR_STRIDE] = o.w;
+#else
+            reinterpret_cast<uint4*>(cursor + first)[q] = o;
+#endif
+        }
     if (tid == 0) {
         bounds[n_tiles] = total;
-        const unsigned long long cand = __ldcg(&ctl->total_cand);
-        ctl->total_pairs = over ? cand : (unsigned long long)total;
+        ctl->total_pairs = total;
         ctl->max_tile_pairs = mx;
-        // the frame's status, straight into page-locked host memory; the frame number is written last
-        slot->total_pairs = over ? cand : (unsigned long long)total; slot->total_cand = cand;
-        slot->overflow = over ? 1u : 0u; slot->max_tile_pairs = mx;
+    }
+}
+
+void launch_tile_offsets(const FrameUniforms& U, FrameCtl* ctl, unsigned int* bounds, unsigned int* cursor, cudaStream_t s)
+{
+    const unsigned int T = (unsigned int)(U.tiles_x * U.tiles_y);
+    if (T <= 16384u) launch_pdl(tile_offsets_kernel<4>, dim3(1), dim3(1024), 0, s, ctl, T, bounds, cursor);
+    else if (T <= 32768u) launch_pdl(tile_offsets_kernel<8>, dim3(1), dim3(1024), 0, s, ctl, T, bounds, cursor);
+    else launch_pdl(tile_offsets_kernel<16>, dim3(1), dim3(1024), 0, s, ctl, T, bounds, cursor);
+}
+
+// A CTA takes four parking chunks at a time, one slot per thread and chunk: the four (tile, key) loads, the four returning
+// atomics on the tiles' cursors and the four stores are independent chains. Thread 0 of CTA 0 also leaves the frame's
+// status in page-locked host memory (the frame number last), where the next entry-point call finds it without a copy.
+struct FrameStatusSlotDev { unsigned long long total_pairs, total_slots; unsigned int overflow, max_tile_pairs, frame_no, pad; };
+__global__ void __launch_bounds__(PARK_CHUNK) scatter_pairs_kernel(const FrameCtl* ctl, const unsigned long long* park_key,
+                                                                   const unsigned int* park_tile, const unsigned int* chunk_fill,
+                                                                   unsigned int* cursor, unsigned long long* __restrict__ pairs,
+                                                                   unsigned long long capacity, volatile FrameStatusSlotDev* slot,
+                                                                   unsigned int frame_no)
+{
+    pdl_prologue();
+    const unsigned int over = __ldcg(&ctl->overflow), n_chunks = __ldcg(&ctl->n_chunks);
+#ifndef SCATTER_NO_STATUS
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        slot->total_pairs = __ldcg(&ctl->total_pairs); slot->total_slots = (unsigned long long)n_chunks * PARK_CHUNK;
+        slot->overflow = over; slot->max_tile_pairs = __ldcg(&ctl->max_tile_pairs);
         __threadfence_system();
         slot->frame_no = frame_no;
     }
-}
-
-void launch_tile_offsets(const FrameUniforms& U, FrameCtl* ctl, unsigned int* bounds, void* status_slot, unsigned int frame_no, cudaStream_t s)
-{
-    launch_pdl(tile_offsets_kernel, dim3(1), dim3(1024), 0, s, ctl, (unsigned int)(U.tiles_x * U.tiles_y), bounds,
-               (volatile FrameStatusSlotDev*)status_slot, frame_no);
-}
-
-__global__ void __launch_bounds__(256) scatter_pairs_kernel(const FrameCtl* ctl, const unsigned long long* tmp_key,
-                                                            const unsigned long long* tmp_ts, const unsigned int* bounds,
-                                                            unsigned long long* __restrict__ pairs)
-{
-    pdl_prologue();
-    if (__ldcg(&ctl->overflow)) return;
-    const unsigned int n = __ldcg(&ctl->n_cand);
-    for (unsigned int g = blockIdx.x * 256u + threadIdx.x; g < n; g += gridDim.x * 256u) {
-        const unsigned long long ts = __ldcg(tmp_ts + g);
-        if (ts == HOLE) continue;
-        pairs[__ldcg(bounds + (unsigned int)(ts >> 32)) + (unsigned int)ts] = __ldcg(tmp_key + g);
+#endif
+    if (over) return;
+    const unsigned int tid = threadIdx.x;
+    for (unsigned int c0 = blockIdx.x * 4u; c0 < n_chunks; c0 += gridDim.x * 4u) {
+        unsigned int t[4]; unsigned long long k[4]; bool on[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) on[q] = c0 + q < n_chunks && tid < __ldcg(chunk_fill + c0 + q);
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            if (on[q]) { const size_t g = (size_t)(c0 + q) * PARK_CHUNK + tid; t[q] = __ldcg(park_tile + g); k[q] = __ldcg(park_key + g); }
+        unsigned int pos[4];
+#pragma unroll
+#ifdef SCATTER_NO_ATOMIC
+        for (int q = 0; q < 4; ++q) if (on[q]) pos[q] = (c0 + q) * PARK_CHUNK + tid + (t[q] & 0u);
+#else
+#ifdef CURSOR_STRIDE
+        for (int q = 0; q < 4; ++q) if (on[q]) pos[q] = atomicAdd(cursor + (size_t)t[q] * CURSOR_STRIDE, 1u);
+#else
+        for (int q = 0; q < 4; ++q) if (on[q]) pos[q] = atomicAdd(cursor + t[q], 1u);
+#endif
+#endif
+#pragma unroll
+        for (int q = 0; q < 4; ++q) if (on[q]) pairs[pos[q]] = k[q];
     }
 }
 
-void launch_scatter_pairs(const FrameCtl* ctl, const unsigned long long* tmp_key, const unsigned long long* tmp_ts,
-                          const unsigned int* bounds, unsigned long long* pairs, int sm_count, cudaStream_t s)
+void launch_scatter_pairs(const FrameCtl* ctl, const unsigned long long* park_key, const unsigned int* park_tile,
+                          const unsigned int* chunk_fill, unsigned int* cursor, unsigned long long* pairs, unsigned long long capacity,
+                          void* status_slot, unsigned int frame_no, int sm_count, cudaStream_t s)
 {
-    launch_pdl(scatter_pairs_kernel, dim3(sm_count * 8), dim3(256), 0, s, ctl, tmp_key, tmp_ts, bounds, pairs);
+    launch_pdl(scatter_pairs_kernel, dim3(sm_count * 8), dim3(PARK_CHUNK), 0, s, ctl, park_key, park_tile, chunk_fill, cursor, pairs,
+               capacity, (volatile FrameStatusSlotDev*)status_slot, frame_no);
 }
 
 // ------------------------------------------------------------------ per-tile sort
@@ -278,6 +209,7 @@ struct UpperLevels {
             RegisterStages<E, (k / 2) / TS_THREADS>::run(x, k);
             exchange_stage<E>(x, s_x, tid, 64, k);
             exchange_stage<E>(x, s_x, tid, 32, k);
+#pragma unroll
             for (int j = 16; j >= 1; j >>= 1) shuffle_stage<E>(x, tid, j, k);
         }
     }
@@ -287,12 +219,16 @@ struct UpperLevels<E, 0> { static __device__ __forceinline__ void run(unsigned l
 
 template <int E>
 __device__ __forceinline__ void bitonic_sort_regs(unsigned long long (&x)[E], unsigned long long* s_x, unsigned int tid) {
+#pragma unroll
     for (int k = 2; k <= 32; k <<= 1)
+#pragma unroll
         for (int j = k >> 1; j >= 1; j >>= 1) shuffle_stage<E>(x, tid, j, k);
     exchange_stage<E>(x, s_x, tid, 32, 64);
+#pragma unroll
     for (int j = 16; j >= 1; j >>= 1) shuffle_stage<E>(x, tid, j, 64);
     exchange_stage<E>(x, s_x, tid, 64, 128);
     exchange_stage<E>(x, s_x, tid, 32, 128);
+#pragma unroll
     for (int j = 16; j >= 1; j >>= 1) shuffle_stage<E>(x, tid, j, 128);
     UpperLevels<E, 4>::run(x, s_x, tid);        // levels 256 .. 2048, those beyond 128 E compiled out
 }
@@ -384,7 +320,9 @@ __global__ void __launch_bounds__(TS_THREADS) tile_sort_kernel(const __grid_cons
         if (tid >= 32) return;
         unsigned long long x = tid < len ? __ldcg(seg + tid) : SENTINEL;
         for (int pass = 0; pass < (layer ? 2 : 1); ++pass) {
+#pragma unroll
             for (int k = 2; k <= 32; k <<= 1)
+#pragma unroll
                 for (int j = k >> 1; j >= 1; j >>= 1) {
                     const unsigned long long p = shfl_xor64(x, j);
                     const bool keep_min = ((tid & j) == 0) == ((tid & k) == 0);

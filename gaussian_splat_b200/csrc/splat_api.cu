@@ -4,6 +4,7 @@
 // render() only encodes (src/instanced_splat_renderer.mm:424-528).
 #include "splat_internal.cuh"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -28,20 +29,22 @@ __global__ void set_n_sort_kernel(SortCtl* ctl, unsigned int n) { ctl->n_sort = 
 // frame entry points use set 0 only; the second set is allocated on the first batch call.
 #define CTL_BYTES (sizeof(FrameCtl) + (65536 + 8) * 4)      // control block + tile counters of the largest frame (65536 tiles)
 struct FrameSet {
-    splat_record_row* rec = nullptr; unsigned long long* binw = nullptr;
-    // tile lists: pairs[cap] (depth field << 32 | instance index, sorted per tile), the candidates' parking arrays
-    // tmp_key / tmp_ts[cap], and LAYER50's instance-ordered copy arrival[cap_arr] (allocated on the first LAYER50 frame)
-    unsigned long long *pairs = nullptr, *tmp_key = nullptr, *tmp_ts = nullptr; unsigned long long capacity = 0;
+    splat_record_row* rec = nullptr;        // [n_pad] records, indexed by ORIGINAL instance index
+    unsigned int* live = nullptr;           // [n_blocks] blocks that survived block culling
+    // parked pairs (K1): park_key / park_tile[cap] in chunks of PARK_CHUNK slots, chunk_fill[cap / PARK_CHUNK];
+    // tile lists: pairs[cap] (depth field << 32 | instance index, sorted per tile) and LAYER50's instance-ordered copy
+    // arrival[cap_arr] (allocated on the first LAYER50 frame)
+    unsigned long long *pairs = nullptr, *park_key = nullptr; unsigned int *park_tile = nullptr, *chunk_fill = nullptr;
+    unsigned long long capacity = 0;
     uint32_t* arrival = nullptr; unsigned long long capacity_arr = 0;
     FrameCtl* ctl = nullptr;                // + tile counters (CTL_BYTES)
-    unsigned int* tile_sums = nullptr;      // K1 candidate counts per 512 splats, then tile_scan's prefixes per 1024
-    uint32_t* bounds = nullptr; uint32_t ranges_cap = 0;   // [T+1] first pair of every tile's list
+    uint32_t *bounds = nullptr, *cursor = nullptr;      // [65536 + 8]: first pair of every tile's list; the scatter's running copy
     cudaStream_t own_stream = nullptr;
 };
 
 // Status of frame `frame_no`, written by its tile_offsets_kernel straight into page-locked host memory (no copy is
 // enqueued): the next entry-point call sees an overflow without synchronising.
-struct FrameStatusSlot { unsigned long long total_pairs, total_cand; unsigned int overflow, max_tile_pairs, frame_no, pad; };
+struct FrameStatusSlot { unsigned long long total_pairs, total_slots; unsigned int overflow, max_tile_pairs, frame_no, pad; };
 #define STATUS_RING 64
 
 #define FB_RING 4
@@ -50,6 +53,7 @@ struct splat_ctx : FrameSet {
     int device = 0, sm_count = 148;
     uint32_t n = 0; size_t n_pad = 0;
     float4 *rot = nullptr, *pos_sx = nullptr, *syz = nullptr, *base_rgb = nullptr, *sh = nullptr; uint16_t* bq = nullptr;
+    unsigned int* orig = nullptr; float4 *blk_lo = nullptr, *blk_hi = nullptr; uint32_t n_blocks = 0;     // Morton order + block bounds
     int sh_degree = 0;
     FrameCtl* ctl_host = nullptr;
     FrameStatusSlot* status_ring = nullptr;      // page-locked, mapped
@@ -90,8 +94,8 @@ static void mat4_mul_host(const float* a, const float* b, float* o) {
 }
 
 static int free_pairs(splat_ctx* c) {
-    cudaFree(c->pairs); cudaFree(c->tmp_key); cudaFree(c->tmp_ts); cudaFree(c->arrival);
-    c->pairs = c->tmp_key = c->tmp_ts = nullptr; c->arrival = nullptr;
+    cudaFree(c->pairs); cudaFree(c->park_key); cudaFree(c->park_tile); cudaFree(c->chunk_fill); cudaFree(c->arrival);
+    c->pairs = c->park_key = nullptr; c->park_tile = c->chunk_fill = nullptr; c->arrival = nullptr;
     c->capacity = 0; c->capacity_arr = 0;
     return 0;
 }
@@ -108,16 +112,23 @@ static int ensure_sort_status(splat_ctx* c, unsigned long long n_keys) {
     return 0;
 }
 
-// Pair capacity = candidate slots (tile-rectangle areas; the pairs that pass the tile test are fewer). Nothing needs
-// clearing: every slot a kernel reads was written earlier in the same frame.
+// Pair capacity = parking slots (whole chunks of PARK_CHUNK; a warp's last chunk is partly used, so the pairs are fewer).
+// Nothing needs clearing: every slot a kernel reads was written earlier in the same frame.
 static int ensure_pairs(splat_ctx* c, unsigned long long cap) {
     if (cap <= c->capacity) return 0;
     if (cap >= 0xFFFF0000ull) ARG_FAIL("pair capacity would exceed 2^32");
     CK(cudaDeviceSynchronize());
     free_pairs(c);
     cap = (cap + 4095) / 4096 * 4096;
-    CK(cudaMalloc(&c->pairs, cap * 8)); CK(cudaMalloc(&c->tmp_key, cap * 8)); CK(cudaMalloc(&c->tmp_ts, cap * 8));
+    CK(cudaMalloc(&c->pairs, cap * 8)); CK(cudaMalloc(&c->park_key, cap * 8)); CK(cudaMalloc(&c->park_tile, cap * 4));
+    CK(cudaMalloc(&c->chunk_fill, cap / PARK_CHUNK * 4));
     c->capacity = cap;
+    return 0;
+}
+static int alloc_frame_fixed(splat_ctx* c) {        // control block + tile counters, bounds, cursor of the CURRENT set
+    CK(cudaMalloc(&c->ctl, CTL_BYTES)); CK(cudaMemset(c->ctl, 0, CTL_BYTES));
+    CK(cudaMalloc(&c->bounds, (65536 + 8) * 4)); CK(cudaMemset(c->bounds, 0, (65536 + 8) * 4));
+    CK(cudaMalloc(&c->cursor, (size_t)(65536 + 8) * 4 * 32));      // room for padded cursors (tuning variants)
     return 0;
 }
 
@@ -136,8 +147,7 @@ int splat_create(int device, splat_ctx** out) {
     splat_ctx* c = new splat_ctx();
     c->device = device;
     CK(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
-    CK(cudaMalloc(&c->ctl, CTL_BYTES));
-    CK(cudaMemset(c->ctl, 0, CTL_BYTES));
+    { const int rc = alloc_frame_fixed(c); if (rc) return rc; }
     CK(cudaMallocHost(&c->ctl_host, sizeof(FrameCtl)));
     std::memset(c->ctl_host, 0, sizeof(FrameCtl));
     CK(cudaHostAlloc(&c->status_ring, STATUS_RING * sizeof(FrameStatusSlot), cudaHostAllocMapped | cudaHostAllocPortable));
@@ -154,19 +164,15 @@ int splat_create(int device, splat_ctx** out) {
     return SPLAT_OK;
 }
 
-// Per-splat scratch of the CURRENT frame set (records, bin words, candidate counts).
+// Per-splat scratch of the CURRENT frame set (records, live-block list).
 static void free_scene_scratch(splat_ctx* c) {
-    cudaFree(c->rec); cudaFree(c->binw); cudaFree(c->tile_sums);
-    c->rec = nullptr; c->binw = nullptr; c->tile_sums = nullptr;
+    cudaFree(c->rec); cudaFree(c->live);
+    c->rec = nullptr; c->live = nullptr;
 }
 static int alloc_scene_scratch(splat_ctx* c, size_t n_pad) {
     CK(cudaMalloc(&c->rec, n_pad * sizeof(splat_record_row)));
-    CK(cudaMalloc(&c->binw, n_pad * 8));
-    CK(cudaMemset(c->binw, 0, n_pad * 8));
     CK(cudaMemset(c->rec, 0, n_pad * sizeof(splat_record_row)));
-    const size_t sums = n_pad / (SCAN_TILE_ITEMS / 2) + n_pad / SCAN_TILE_ITEMS + 2;   // [n/512] sums, then [n/1024] prefixes
-    CK(cudaMalloc(&c->tile_sums, sums * 4));
-    CK(cudaMemset(c->tile_sums, 0, sums * 4));
+    CK(cudaMalloc(&c->live, (n_pad / 256 + 4) * 4));
     return SPLAT_OK;
 }
 // Releases the second frame set completely (it is rebuilt by the next camera-batch call).
@@ -175,7 +181,7 @@ static void drop_alt(splat_ctx* c) {
     if (!c->alt_ready) return;
     swap_sets(c);
     free_scene_scratch(c); free_pairs(c);
-    cudaFree(c->bounds); cudaFree(c->ctl);
+    cudaFree(c->bounds); cudaFree(c->cursor); cudaFree(c->ctl);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     *static_cast<FrameSet*>(c) = FrameSet{};
     swap_sets(c);
@@ -188,7 +194,7 @@ static int ensure_alt(splat_ctx* c) {
     swap_sets(c);
     int rc = SPLAT_OK;
     do {
-        if (cudaMalloc(&c->ctl, CTL_BYTES) != cudaSuccess || cudaMemset(c->ctl, 0, CTL_BYTES) != cudaSuccess ||
+        if (alloc_frame_fixed(c) != 0 ||
             cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) { g_err = "second frame set: allocation failed"; rc = SPLAT_ERR_CUDA; break; }
         if (c->n_pad) { rc = alloc_scene_scratch(c, c->n_pad); if (rc) break; }
         rc = ensure_pairs(c, cap ? cap : (1ull << 20));
@@ -208,8 +214,9 @@ static int ensure_pairs_all(splat_ctx* c, unsigned long long cap) {
 static void free_scene(splat_ctx* c) {
     drop_alt(c);
     cudaFree(c->rot); cudaFree(c->pos_sx); cudaFree(c->syz); cudaFree(c->bq); cudaFree(c->sh); cudaFree(c->base_rgb);
+    cudaFree(c->orig); cudaFree(c->blk_lo); cudaFree(c->blk_hi);
     free_scene_scratch(c);
-    c->rot = c->pos_sx = c->syz = c->base_rgb = c->sh = nullptr; c->bq = nullptr;
+    c->rot = c->pos_sx = c->syz = c->base_rgb = c->sh = c->blk_lo = c->blk_hi = nullptr; c->bq = nullptr; c->orig = nullptr; c->n_blocks = 0;
     c->n = 0; c->n_pad = 0; c->sh_degree = 0;
 }
 
@@ -218,7 +225,7 @@ int splat_destroy(splat_ctx* c) {
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     free_scene(c); free_pairs(c);
-    cudaFree(c->bounds); cudaFree(c->ctl); cudaFree(c->fb_scratch); cudaFree(c->sort_ctl); cudaFree(c->sort_status);
+    cudaFree(c->bounds); cudaFree(c->cursor); cudaFree(c->ctl); cudaFree(c->fb_scratch); cudaFree(c->sort_ctl); cudaFree(c->sort_status);
     cudaFreeHost(c->ctl_host); cudaFreeHost(c->status_ring);
     for (int k = 0; k < 6; ++k) if (c->ev[k]) cudaEventDestroy(c->ev[k]);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -232,14 +239,47 @@ int splat_destroy(splat_ctx* c) {
 }
 
 // Installs n SplatInstance rows that already sit in device memory as the scene (planes + per-frame scratch).
+static int sort_pairs_impl(splat_ctx* c, void* stream, void* keys, uint32_t* vals, void* keys_alt, uint32_t* vals_alt,
+                           uint64_t n, int begin_bit, int end_bit, int key_bytes, int* result_in_alt);
+static float ordered_to_float(unsigned int k) { k ^= (k >> 31) ? 0x80000000u : 0xFFFFFFFFu; float f; std::memcpy(&f, &k, 4); return f; }
+
+// Installs n SplatInstance rows that already sit in device memory as the scene: Morton order of the positions (our own
+// radix sort on 63-bit codes), planes written in that order with the original index beside them, block bounds,
+// per-frame scratch. SPLAT_SCENE_ORDER=0 keeps instance order (tuning / debugging aid; results are the same).
 static int install_scene(splat_ctx* c, const float* aos_dev, uint32_t n) {
-    const size_t n_pad = ((size_t)n + SCAN_TILE_ITEMS - 1) / SCAN_TILE_ITEMS * SCAN_TILE_ITEMS;
+    const size_t n_pad = ((size_t)n + 1023) / 1024 * 1024;
     CK(cudaMalloc(&c->rot, n_pad * 16)); CK(cudaMalloc(&c->pos_sx, n_pad * 16)); CK(cudaMalloc(&c->syz, n_pad * 16));
-    CK(cudaMalloc(&c->bq, n_pad * 2)); CK(cudaMalloc(&c->base_rgb, n_pad * 16));
+    CK(cudaMalloc(&c->bq, n_pad * 2)); CK(cudaMalloc(&c->base_rgb, n_pad * 16)); CK(cudaMalloc(&c->orig, n_pad * 4));
+    c->n_blocks = (uint32_t)((n + 255u) / 256u);
+    CK(cudaMalloc(&c->blk_lo, ((size_t)c->n_blocks + 1) * 16)); CK(cudaMalloc(&c->blk_hi, ((size_t)c->n_blocks + 1) * 16));
     { const int rc = alloc_scene_scratch(c, n_pad); if (rc) return rc; }
-    launch_upload_soa(aos_dev, n, c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, 0);
-    CK(cudaGetLastError());
-    CK(cudaDeviceSynchronize());
+    static const bool ordered = [] { const char* e = getenv("SPLAT_SCENE_ORDER"); return !(e && e[0] == '0'); }();
+    unsigned long long *keys = nullptr, *keys_alt = nullptr; unsigned int *vals = nullptr, *vals_alt = nullptr, *mm = nullptr;
+    const unsigned int* perm = nullptr;
+    int rc = SPLAT_OK;
+    if (ordered && n > 256) {
+        do {
+            if (cudaMalloc(&keys, (size_t)n * 8) != cudaSuccess || cudaMalloc(&keys_alt, (size_t)n * 8) != cudaSuccess ||
+                cudaMalloc(&vals, (size_t)n * 4) != cudaSuccess || cudaMalloc(&vals_alt, (size_t)n * 4) != cudaSuccess ||
+                cudaMalloc(&mm, 32) != cudaSuccess) { g_err = "scene order: allocation failed"; rc = SPLAT_ERR_CUDA; break; }
+            launch_scene_aabb(aos_dev, n, mm, 0);
+            unsigned int h[6];
+            if (cudaMemcpy(h, mm, 24, cudaMemcpyDeviceToHost) != cudaSuccess) { g_err = "scene order: bounding box failed"; rc = SPLAT_ERR_CUDA; break; }
+            float lo[3], hi[3];
+            for (int a = 0; a < 3; ++a) { lo[a] = ordered_to_float(h[a]); hi[a] = ordered_to_float(h[3 + a]); if (!(lo[a] <= hi[a])) { lo[a] = 0.0f; hi[a] = 0.0f; } }
+            launch_morton(aos_dev, n, lo, hi, keys, vals, 0);
+            int alt = 0;
+            rc = sort_pairs_impl(c, nullptr, keys, vals, keys_alt, vals_alt, n, 0, 64, 8, &alt);
+            if (rc) break;
+            perm = alt ? vals_alt : vals;
+        } while (0);
+    }
+    if (rc == SPLAT_OK) {
+        launch_upload_soa(aos_dev, perm, n, c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->orig, c->blk_lo, c->blk_hi, 0);
+        if (cudaGetLastError() != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) { g_err = "scene upload kernels failed"; rc = SPLAT_ERR_CUDA; }
+    }
+    cudaFree(keys); cudaFree(keys_alt); cudaFree(vals); cudaFree(vals_alt); cudaFree(mm);
+    if (rc) return rc;
     c->n = n; c->n_pad = n_pad;
     unsigned long long want = (unsigned long long)n * 12ull;
     if (want < (1ull << 20)) want = 1ull << 20;
@@ -249,7 +289,7 @@ static int install_scene(splat_ctx* c, const float* aos_dev, uint32_t n) {
 
 static int install_sh(splat_ctx* c, const float* sh_dev, uint32_t n, int degree) {
     CK(cudaMalloc(&c->sh, c->n_pad * 12 * 16));
-    launch_upload_sh(sh_dev, n, c->n_pad, c->sh, 0);
+    launch_upload_sh(sh_dev, c->orig, n, c->n_pad, c->sh, 0);
     CK(cudaGetLastError());
     CK(cudaDeviceSynchronize());
     c->sh_degree = degree;
@@ -409,7 +449,7 @@ static int check_overflow(splat_ctx* c, bool wait, unsigned long long* worst_out
         const uint32_t f = c->checked_frame + 1;
         const volatile FrameStatusSlot* sl = c->status_ring + (f % STATUS_RING);
         if (sl->frame_no != f) { if (!wait) break; c->checked_frame = f; continue; }    // not landed (or a frame without kernels)
-        if (sl->overflow && sl->total_cand > worst) worst = sl->total_cand;
+        if (sl->overflow && sl->total_slots > worst) worst = sl->total_slots;
         c->checked_frame = f;
     }
     if (worst_out) *worst_out = worst;
@@ -430,12 +470,6 @@ thread_local bool g_pdl_frame = true;
 static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUniforms& U, int flags) {
     g_pdl_frame = (flags & FRAME_NO_PDL) == 0;
     const unsigned int T = (unsigned int)(U.tiles_x * U.tiles_y);
-    if (T > c->ranges_cap) {
-        CK(cudaDeviceSynchronize());
-        cudaFree(c->bounds); c->bounds = nullptr;
-        CK(cudaMalloc(&c->bounds, ((size_t)T + 1) * 4));
-        c->ranges_cap = T;
-    }
     const bool timed = (flags & SPLAT_FLAG_TIMING) != 0;
     const bool layer = U.mode == SPLAT_MODE_LAYER50;
     if (layer && c->capacity_arr < c->capacity) {
@@ -450,14 +484,13 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
     if (timed) CK(cudaEventRecord(c->ev[0], s));
     CK(cudaMemsetAsync(c->ctl, 0, sizeof(FrameCtl) + ((size_t)T + 1) * 4, s));       // control block + tile counters
     if (c->n) {
-        ScenePlanes sp{c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->sh, c->n_pad};
-        unsigned int* scan_prefix = c->tile_sums + c->n_pad / (SCAN_TILE_ITEMS / 2);
-        launch_preprocess(sp, U, c->rec, c->binw, c->tile_sums, scan_prefix, c->capacity, c->ctl, s);
-        if (timed) CK(cudaEventRecord(c->ev[1], s));
-        launch_bin_pairs(U, c->binw, c->rec, c->tmp_key, c->tmp_ts, c->capacity, c->ctl, c->tile_sums, scan_prefix, c->sm_count, s);
-    } else if (timed) CK(cudaEventRecord(c->ev[1], s));
-    launch_tile_offsets(U, c->ctl, c->bounds, slot, c->frame_no, s);
-    if (c->n) launch_scatter_pairs(c->ctl, c->tmp_key, c->tmp_ts, c->bounds, c->pairs, c->sm_count, s);
+        ScenePlanes sp{c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->orig, c->blk_lo, c->blk_hi, c->n_blocks, c->sh, c->n_pad};
+        launch_preprocess(sp, U, c->rec, c->ctl, c->live, c->park_key, c->park_tile, c->chunk_fill, c->capacity, s);
+    }
+    if (timed) CK(cudaEventRecord(c->ev[1], s));
+    launch_tile_offsets(U, c->ctl, c->bounds, c->cursor, s);
+    if (c->n) launch_scatter_pairs(c->ctl, c->park_key, c->park_tile, c->chunk_fill, c->cursor, c->pairs, c->capacity, slot, c->frame_no, c->sm_count, s);
+    else { slot->total_pairs = 0; slot->total_slots = 0; slot->overflow = 0; slot->max_tile_pairs = 0; slot->frame_no = c->frame_no; }
     if (timed) CK(cudaEventRecord(c->ev[2], s));
     if (c->n) launch_tile_sort(U, c->ctl, c->bounds, c->pairs, c->arrival, s);
     if (timed) { CK(cudaEventRecord(c->ev[3], s)); CK(cudaEventRecord(c->ev[4], s)); }
@@ -543,6 +576,7 @@ int splat_frame_status(splat_ctx* c, splat_status* out) {
     out->pair_capacity = c->capacity;
     out->overflow = c->ctl_host->overflow;
     out->sort_passes = 1;            // one shared-memory sort per tile list
+    out->n_candidates = (unsigned long long)c->ctl_host->n_chunks * PARK_CHUNK; out->max_tile_pairs = c->ctl_host->max_tile_pairs;
     // every frame since the last look (a camera batch: all its views), not only the last one
     unsigned long long worst = 0;
     const int rc = check_overflow(c, true, &worst);
@@ -590,7 +624,7 @@ int splat_render_host(splat_ctx* c, void* fb_host, const float* view, const floa
         CK(cudaStreamSynchronize(c->own_stream));
         c->checked_frame = c->frame_no;          // this frame's status is handled right here
         if (!c->ctl_host->overflow) return SPLAT_OK;
-        const unsigned long long D = c->ctl_host->total_cand;
+        const unsigned long long D = (unsigned long long)c->ctl_host->n_chunks * PARK_CHUNK;
         rc = ensure_pairs_all(c, D + D / 4 + 4096);
         if (rc) return rc;
     }
@@ -640,7 +674,7 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
             if (v >= FB_RING) CK(cudaStreamWaitEvent(c->own_stream, c->ev_copied[b], 0));     // slot b is free again
             rc = enqueue_frame(c, c->own_stream, buf[b], U, flags);
             if (rc) return rc;
-            CK(cudaMemcpyAsync(c->batch_flags + 6 * v, c->ctl, 24, cudaMemcpyDeviceToHost, c->own_stream));   // D, overflow, candidates
+            CK(cudaMemcpyAsync(c->batch_flags + 6 * v, c->ctl, 24, cudaMemcpyDeviceToHost, c->own_stream));   // D, overflow, chunks
             const size_t row0 = (size_t)U.row_begin * SPLAT_TILE;
             const size_t row1 = (size_t)U.row_end * SPLAT_TILE < (size_t)h ? (size_t)U.row_end * SPLAT_TILE : (size_t)h;
             if (bgra && row1 > row0)
@@ -659,7 +693,7 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
         c->checked_frame = c->frame_no;          // the views' status is handled right here
         unsigned long long worst = 0; bool over = false;
         for (int v = 0; v < n_views; ++v) {
-            unsigned long long D; std::memcpy(&D, c->batch_flags + 6 * v + 4, 8);      // FrameCtl::total_cand
+            const unsigned long long D = (unsigned long long)c->batch_flags[6 * v + 3] * PARK_CHUNK;      // FrameCtl::n_chunks
             if (c->batch_flags[6 * v + 2]) { over = true; if (D > worst) worst = D; }
         }
         if (!over) return SPLAT_OK;
@@ -675,19 +709,28 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
 // ------------------------------------------------------ debug / timing / sort
 extern "C" {
 
-// The pairs of the last frame as K2 parked them (candidate order; holes removed), in the order the CPU restatement
-// emits them: instance order, a splat's tiles row-major. Candidate order is exactly that (tile prefixes come from an
-// ordered scan), so no sorting is needed here. tile[k], key[k] = depth field << 32 | instance index.
+// The pairs of the last frame as K1 parked them, put in the order the CPU restatement emits them: instance order, a
+// splat's tiles row-major (= ascending tile id). The parking order itself depends on which warp got which chunk.
+// tile[k], key[k] = depth field << 32 | instance index.
 static cudaError_t fetch_parked(splat_ctx* c, std::vector<uint32_t>& tile, std::vector<unsigned long long>& key) {
-    const size_t nc = c->ctl_host->n_cand;
-    std::vector<unsigned long long> ts(nc), k(nc);
+    const size_t nch = c->ctl_host->n_chunks;
     tile.clear(); key.clear();
-    if (!nc) return cudaSuccess;
-    cudaError_t e = cudaMemcpy(ts.data(), c->tmp_ts, nc * 8, cudaMemcpyDeviceToHost);
-    if (e == cudaSuccess) e = cudaMemcpy(k.data(), c->tmp_key, nc * 8, cudaMemcpyDeviceToHost);
+    if (!nch) return cudaSuccess;
+    std::vector<unsigned long long> k(nch * PARK_CHUNK);
+    std::vector<uint32_t> t(nch * PARK_CHUNK), fill(nch);
+    cudaError_t e = cudaMemcpy(k.data(), c->park_key, k.size() * 8, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(t.data(), c->park_tile, t.size() * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(fill.data(), c->chunk_fill, nch * 4, cudaMemcpyDeviceToHost);
     if (e != cudaSuccess) return e;
-    for (size_t g = 0; g < nc; ++g)
-        if (ts[g] != 0xFFFFFFFFFFFFFFFFull) { tile.push_back((uint32_t)(ts[g] >> 32)); key.push_back(k[g]); }
+    std::vector<std::pair<unsigned long long, unsigned long long>> all;      // (instance << 32 | tile, key)
+    for (size_t ch = 0; ch < nch; ++ch)
+        for (uint32_t q = 0; q < fill[ch] && q < PARK_CHUNK; ++q) {
+            const size_t g = ch * PARK_CHUNK + q;
+            all.emplace_back(((k[g] & 0xFFFFFFFFull) << 32) | t[g], k[g]);
+        }
+    std::sort(all.begin(), all.end());
+    tile.reserve(all.size()); key.reserve(all.size());
+    for (const auto& a : all) { tile.push_back((uint32_t)a.first); key.push_back(a.second); }
     return cudaSuccess;
 }
 
@@ -711,6 +754,8 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
         if (!dst) { *bytes = need; return SPLAT_OK; }
         if (*bytes < need) { *bytes = need; ARG_FAIL("splat_debug_fetch: destination too small"); }
         float* o = (float*)dst;
+        std::vector<uint32_t> orig(c->n);            // plane entry i holds instance orig[i]
+        if (c->n) CK(cudaMemcpy(orig.data(), c->orig, (size_t)c->n * 4, cudaMemcpyDeviceToHost));
         if (!sh && c->n) {
             std::vector<float> rot((size_t)c->n * 4), pos((size_t)c->n * 4), syz((size_t)c->n * 4), rgb((size_t)c->n * 4);
             CK(cudaMemcpy(rot.data(), c->rot, rot.size() * 4, cudaMemcpyDeviceToHost));
@@ -718,7 +763,7 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
             CK(cudaMemcpy(syz.data(), c->syz, syz.size() * 4, cudaMemcpyDeviceToHost));
             CK(cudaMemcpy(rgb.data(), c->base_rgb, rgb.size() * 4, cudaMemcpyDeviceToHost));
             for (size_t i = 0; i < c->n; ++i) {
-                float* a = o + i * 14;
+                float* a = o + (size_t)orig[i] * 14;
                 for (int k = 0; k < 4; ++k) a[k] = rot[i * 4 + k];
                 a[4] = pos[i * 4 + 3]; a[5] = syz[i * 4 + 0]; a[6] = syz[i * 4 + 1];
                 a[7] = pos[i * 4 + 0]; a[8] = pos[i * 4 + 1]; a[9] = pos[i * 4 + 2];
@@ -731,7 +776,7 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
             for (size_t i = 0; i < c->n; ++i)
                 for (int q = 0; q < 45; ++q) {
                     const int coef = q / 3, ch = q % 3;                   // plane order: coefficient-major, rgb interleaved
-                    o[i * 45 + ch * 15 + coef] = pl[((size_t)(q / 4) * c->n_pad + i) * 4 + (q % 4)];
+                    o[(size_t)orig[i] * 45 + ch * 15 + coef] = pl[((size_t)(q / 4) * c->n_pad + i) * 4 + (q % 4)];
                 }
         }
         *bytes = need;

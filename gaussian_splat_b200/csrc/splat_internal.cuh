@@ -12,9 +12,6 @@
 #define SORT_ITEMS_NARROW 24                         // 32-bit keys: 6144 pairs per tile
 #define SORT_TILE_KEYS (SORT_THREADS * SORT_ITEMS)   // keys per onesweep tile (large sorts)
 #define SORT_TILE_KEYS_SMALL (SORT_THREADS * SORT_ITEMS_SMALL)  // frame-sized sorts
-#define SCAN_THREADS 256
-#define SCAN_ITEMS 4
-#define SCAN_TILE_ITEMS (SCAN_THREADS * SCAN_ITEMS)  // splats per scan/duplicate tile
 
 // Per-frame uniforms: role of the reference's Uniforms buffer
 // (shaders/gaussian_splat_tile.metal:16-21, src/instanced_splat_renderer.mm:456-469),
@@ -41,17 +38,16 @@ struct alignas(64) splat_record_row { splat_record r; float kx, ky; unsigned int
 // Device control block of a frame, followed in the same allocation by the per-tile pair counters
 // (tile_count[T + 1], then rounded up): one memsetAsync zeroes both at the start of every frame.
 struct FrameCtl {
-    unsigned long long total_pairs;   // D: pairs that passed the tile test (tile_offsets_kernel); on overflow the candidate total
-    unsigned int overflow;            // candidate slots exceed the pair capacity: the frame's lists are not built
-    unsigned int n_cand;              // candidate (splat, tile-of-rectangle) slots = min(total_cand, capacity) (tile_scan_kernel)
-    unsigned long long total_cand;    // exact even when it exceeds the capacity
+    unsigned long long total_pairs;   // D: pairs that passed the tile test (tile_offsets_kernel)
+    unsigned int overflow;            // the parking chunks exceed the pair capacity: the frame's lists are not built
+    unsigned int n_chunks;            // parking chunks handed out by K1 (PARK_CHUNK slots each; counted even beyond the capacity)
     unsigned int n_live_blocks;       // 256-splat blocks that survived block culling (block_cull_kernel)
     unsigned int max_tile_pairs;      // longest tile list (tile_offsets_kernel)
-    unsigned int pad[8];
+    unsigned int pad[10];
 };
 static_assert(sizeof(FrameCtl) == 64, "FrameCtl is 64 bytes");
-#define FRAME_CTL_WORDS (sizeof(FrameCtl) / 4)
 __host__ __device__ __forceinline__ unsigned int* ctl_tile_count(FrameCtl* c) { return reinterpret_cast<unsigned int*>(c + 1); }
+#define PARK_CHUNK 256u               // slots per parking chunk (one warp owns a chunk at a time)
 
 // Control block of the stand-alone radix sort (splat_sort_pairs_*; also sorts the scene's Morton codes at upload).
 struct SortCtl {
@@ -69,6 +65,10 @@ struct ScenePlanes {
     const float4* syz_op_rg;  // scale.y, scale.z, opacity, bits(half r | half g << 16)
     const uint16_t* b;        // half(b)
     const float4* base_rgb;   // fp32 r g b (loader colour) for the SH extension; .w unused
+    const unsigned int* orig; // original instance index of plane entry i (the planes are in Morton order of the positions)
+    const float4* blk_lo;     // per block of 256 entries: min xyz of the finite positions, largest scale
+    const float4* blk_hi;     // max xyz
+    unsigned int n_blocks;
     const float4* sh;         // SH planes [12][n_pad]: float4 j of splat i holds coefficients f' = 4j..4j+3,
                               // f' = 3*k + channel (coefficient-major, so degree L reads planes 0 .. 3*((L+1)^2-1)/4)
     size_t n_pad;
@@ -132,40 +132,28 @@ static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 b
 #endif
 
 // Launchers (each enqueues on `s` and returns).
-void launch_upload_soa(const float* aos_dev, unsigned int n, float4* rot, float4* pos_sx, float4* syz_op_rg,
-                       uint16_t* b, float4* base_rgb, cudaStream_t s);
+// Scene order at upload: bounding box of the finite positions (as order-preserving unsigned keys: min xyz, max xyz),
+// 63-bit Morton codes + identity values for the sort, then the permuted planes + block bounds.
+void launch_scene_aabb(const float* aos_dev, unsigned int n, unsigned int* mm6_dev, cudaStream_t s);
+void launch_morton(const float* aos_dev, unsigned int n, const float lo[3], const float hi[3], unsigned long long* keys, unsigned int* vals, cudaStream_t s);
+void launch_upload_soa(const float* aos_dev, const unsigned int* perm, unsigned int n, float4* rot, float4* pos_sx, float4* syz_op_rg,
+                       uint16_t* b, float4* base_rgb, unsigned int* orig, float4* blk_lo, float4* blk_hi, cudaStream_t s);
 // sh_rest45_dev: [n][45] as the loader stores it (channel-major: f = channel*15 + k) -> coefficient-major planes
-void launch_upload_sh(const float* sh_rest45_dev, unsigned int n, size_t n_pad, float4* planes, cudaStream_t s);
-// Per-splat "bin word" written by K1 and read by K2 (8 bytes, 0 = culled): the tile rectangle and the half depth,
-// everything K2 needs, so it never gathers from the 48-byte records.
-//   bits  0-11 tx0 | 12-23 ty0 | 24-35 tx1 | 36-47 ty1 (inclusive, < 4096 each) | 48-63 bits of half(zFront)
-__host__ __device__ __forceinline__ unsigned long long binw_pack(unsigned int rect_lo, unsigned int rect_hi, unsigned int half_depth) {
-    return (unsigned long long)(rect_lo & 0xFFFu) | ((unsigned long long)(rect_lo >> 16) << 12) |
-           ((unsigned long long)(rect_hi & 0xFFFu) << 24) | ((unsigned long long)(rect_hi >> 16) << 36) |
-           ((unsigned long long)half_depth << 48);
-}
-__host__ __device__ __forceinline__ unsigned int binw_count(unsigned long long w) {
-    if (w == 0) return 0u;
-    const unsigned int tx0 = (unsigned int)w & 0xFFFu, ty0 = (unsigned int)(w >> 12) & 0xFFFu;
-    const unsigned int tx1 = (unsigned int)(w >> 24) & 0xFFFu, ty1 = (unsigned int)(w >> 36) & 0xFFFu;
-    return (tx1 - tx0 + 1u) * (ty1 - ty0 + 1u);
-}
-
-void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record_row* rec, unsigned long long* binw,
-                       unsigned int* tile_sums, unsigned int* scan_prefix, unsigned long long capacity, FrameCtl* ctl,
+void launch_upload_sh(const float* sh_rest45_dev, const unsigned int* perm, unsigned int n, size_t n_pad, float4* planes, cudaStream_t s);
+// K1 (k_preprocess.cu): block culling, then per live block the records (rec[original index]) and the parked candidates.
+void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record_row* rec, FrameCtl* ctl, unsigned int* live,
+                       unsigned long long* park_key, unsigned int* park_tile, unsigned int* chunk_fill, unsigned long long capacity,
                        cudaStream_t s);
-// K2 binning (k_bin.cu). Every (splat, tile of its rectangle) candidate is tested (D9' tile_touch); a passing pair draws
-// its slot in the tile's list from the tile's counter and is parked in (tmp_key, tmp_ts) at its candidate position; the
-// tile counters are scanned into bounds[T + 1]; the pairs are scattered to pairs[bounds[tile] + slot]; every tile's list
-// is sorted in shared memory on the whole 64-bit pair (depth field << 32 | instance index: a total order, so the result
-// equals a stable sort of instance-ordered pairs on tile | depth). LAYER50 also gets the list in instance order (arrival).
-void launch_bin_pairs(const FrameUniforms& U, const unsigned long long* binw, const splat_record_row* rec,
-                      unsigned long long* tmp_key, unsigned long long* tmp_ts, unsigned long long capacity, FrameCtl* ctl,
-                      const unsigned int* tile_sums, const unsigned int* scan_prefix, int sm_count, cudaStream_t s);
-// status_slot: 32 bytes of mapped page-locked memory that receive D / candidates / overflow / longest list and, last, frame_no
-void launch_tile_offsets(const FrameUniforms& U, FrameCtl* ctl, unsigned int* bounds, void* status_slot, unsigned int frame_no, cudaStream_t s);
-void launch_scatter_pairs(const FrameCtl* ctl, const unsigned long long* tmp_key, const unsigned long long* tmp_ts,
-                          const unsigned int* bounds, unsigned long long* pairs, int sm_count, cudaStream_t s);
+// K2 binning (k_bin.cu). K1 parked every (splat, tile) pair that passed the D9' tile test as (key = depth field << 32 |
+// instance index, tile) and counted the pairs per tile. tile_offsets scans the counters into bounds[T + 1] (and a copy,
+// cursor[], that the scatter advances); scatter_pairs moves every parked pair to pairs[cursor[tile]++]; tile_sort sorts
+// every tile's list in shared memory on the whole 64-bit pair: a total order, so the result equals a stable sort of
+// instance-ordered pairs on tile | depth. LAYER50 also gets the list in instance order (arrival).
+void launch_tile_offsets(const FrameUniforms& U, FrameCtl* ctl, unsigned int* bounds, unsigned int* cursor, cudaStream_t s);
+// status_slot: 32 bytes of mapped page-locked memory that receive D / slots used / overflow / longest list and, last, frame_no
+void launch_scatter_pairs(const FrameCtl* ctl, const unsigned long long* park_key, const unsigned int* park_tile,
+                          const unsigned int* chunk_fill, unsigned int* cursor, unsigned long long* pairs, unsigned long long capacity,
+                          void* status_slot, unsigned int frame_no, int sm_count, cudaStream_t s);
 void launch_tile_sort(const FrameUniforms& U, const FrameCtl* ctl, const unsigned int* bounds, unsigned long long* pairs,
                       unsigned int* arrival, cudaStream_t s);
 // Stand-alone sort (k_sort.cu). Per-pass digit histograms of keys[0..n) into ctl->hist.

@@ -79,8 +79,12 @@ typedef struct {
     uint32_t n_splats, n_visible_unused;
     uint64_t n_pairs;       /* D of the last completed frame                            */
     uint64_t pair_capacity;
-    uint32_t overflow;      /* 1 if D exceeded capacity (frame truncated; see splat_frame_status) */
-    uint32_t sort_passes;
+    uint32_t overflow;      /* 1 if the candidate slots exceeded the capacity: the frame was rendered EMPTY, the buffers
+                               have been grown; render it again (n_pairs then holds the candidate count)        */
+    uint32_t sort_passes;   /* 1: every tile list is sorted once in shared memory                                */
+    uint64_t n_candidates;  /* (splat, tile of its rectangle) slots examined; the pairs are those that pass the tile test */
+    uint32_t max_tile_pairs;/* longest tile list of the last frame                                              */
+    uint32_t reserved;
 } splat_status;
 
 typedef struct splat_ctx splat_ctx;
