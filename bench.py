@@ -6,9 +6,10 @@
 A step = one frame of the hot path (K1 preprocess .. K5 blend) over one synthetic scene.
 N=1 default workload = BASELINE.json configs[1]: 1M gaussians, 1920x1080, TILE mode, single frame.
 N>1 default: every rank renders the same scene from its own orbit cameras (views sharded, no
-data-path collective, weak scaling: value = frames of all ranks / max-over-ranks time);
-`--workload c3` is the 4K/6M single frame split into tile-row bands with an NCCL gather of the
-framebuffer (strong scaling). Prints ONE JSON line on rank 0.
+data-path collective, weak scaling: value = frames of all ranks / max-over-ranks time), and in the
+same invocation the config-3 leg - the 4K/6M single frame split into tile-row bands with an NCCL
+gather of the framebuffer (strong scaling), its one-GPU rate measured by rank 0 in the same run -
+reported under config.c3; `--workload c3` makes that leg the headline. Prints ONE JSON line on rank 0.
 """
 from __future__ import annotations
 
@@ -179,7 +180,8 @@ def run_reference(args):
         "config": {"workload": name, "n_gaussians": n, "width": w, "height": h, "mode": "LAYER50" if mode else "TILE",
                    "order": "near_first",
                    "reference_kind": "CPU restatement of the reference shaders (oracle/oracle_b.cpp); the Metal path is unavailable on this box"},
-        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample, "cpu_model": cpu_model(),
+                         "note": "K1 and the blend use every core; the restatement's scan / duplication / sort / tile ranges are single-threaded"},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -234,6 +236,211 @@ def sort_bench(ctx, torch, n=1 << 26, reps=5):
             "bytes": by, "note": "8 onesweep passes + the histogram pass (the +8 B/pair); inputs larger than L2"}
 
 
+def cpu_model():
+    try:
+        with open("/proc/cpuinfo") as f:
+            for ln in f:
+                if ln.lower().startswith("model name"):
+                    return ln.split(":", 1)[1].strip()
+    except Exception:
+        pass
+    return "unknown"
+
+
+def c3_bands_leg(ctx, torch, dist, args, dev, rank, world, steps, sh_degree=0, even_bands=False):
+    """Config 3: the 6M-gaussian / 3840x2160 single frame split into tile-row bands over the ranks with the NCCL gather of
+    the framebuffer (the one multi-GPU path north_star defines; strong scaling). In the same run: the one-GPU frame rate
+    (rank 0 alone, the others idle at a barrier) and a check that the gathered frame equals the one-GPU frame bit for bit.
+    Returns the result dict (meaningful on rank 0)."""
+    from gaussian_splat_b200 import camera, capi, multigpu, scene
+    n, w, h, mode, cfg, name = WORKLOADS["c3"]
+    inst, sh = scene.make_instances(n, scene.CONFIG_SEEDS[cfg], sh_rest=sh_degree > 0)
+    n = inst.shape[0]
+    ctx.upload(inst)
+    if sh_degree:
+        ctx.upload_sh(sh, 3)
+    del inst
+    stream = torch.cuda.current_stream().cuda_stream
+    tiles_x, tiles_y = (w + 15) // 16, (h + 15) // 16
+    V, P = camera.app_camera(w, h)
+    fb = torch.zeros((h, w, 4), dtype=torch.float16, device=dev)
+    full = capi.make_opts(mode=mode, sh_degree=sh_degree)
+
+    # ---- the whole frame on one GPU (every rank renders it once: warm-up, buffer growth, pairs per tile row)
+    for _ in range(3):
+        ctx.render(stream, fb.data_ptr(), V, P, w, h, full); torch.cuda.synchronize()
+        st_full = ctx.status()
+        if not st_full.overflow:
+            break
+    assert not st_full.overflow
+    r = ctx.fetch(capi.FETCH_TILE_RANGES).astype(np.int64)
+    row_pairs = (r[:, 1] - r[:, 0]).reshape(tiles_y, tiles_x).sum(axis=1)
+    fb_single = fb.clone() if rank == 0 else None
+    one_gpu = None
+    dist.barrier()
+    if rank == 0:       # same run, same box: rank 0 alone, frames back to back like the banded loop below
+        tim = capi.make_opts(mode=mode, sh_degree=sh_degree, flags=capi.FLAG_TIMING)
+        acc = {}
+        for it in range(8):
+            ctx.render(stream, fb.data_ptr(), V, P, w, h, tim); torch.cuda.synchronize()
+            if it >= 3:
+                for k, v in ctx.stage_times().items():
+                    acc[k] = acc.get(k, 0.0) + v / 5
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            ctx.render(stream, fb.data_ptr(), V, P, w, h, full)
+        e1.record(); torch.cuda.synchronize()
+        one_gpu = {"frames_per_s": steps * 1e3 / e0.elapsed_time(e1), "ms_per_frame": e0.elapsed_time(e1) / steps,
+                   "stage_us": {k: round(v * 1e3, 1) for k, v in acc.items()}, "pairs_D": int(st_full.n_pairs)}
+    dist.barrier()
+
+    # ---- bands: boundaries balanced on the pairs per tile row, then three rounds of measured-time balancing (untimed
+    # set-up: pairs are not the cost, rows of large near splats blend slower per pair)
+    band_list = multigpu.band_rows(tiles_y, world, None if even_bands else row_pairs)
+    if not even_bands:
+        wts = row_pairs.astype(np.float64)
+        for _ in range(3):
+            a, b = band_list[rank]
+            o = capi.make_opts(mode=mode, sh_degree=sh_degree, tile_row_begin=a, tile_row_end=b, flags=capi.FLAG_TIMING)
+            acc = []
+            for it in range(6):
+                var = 0.0
+                if b > a:
+                    ctx.render(stream, fb.data_ptr(), V, P, w, h, o); torch.cuda.synchronize()
+                    st_ = ctx.stage_times()
+                    var = st_["total"] - 0.6 * st_["preprocess"]      # the part of the band's time that moves with its rows
+                if it >= 2:
+                    acc.append(var)
+            tt = torch.tensor([float(np.median(acc))], dtype=torch.float64, device=dev)
+            allt = [torch.zeros_like(tt) for _ in range(world)]
+            dist.all_gather(allt, tt)
+            wts = multigpu.reweight_rows(wts, band_list, [float(x.item()) for x in allt])
+            band_list = multigpu.band_rows(tiles_y, world, wts)
+    row0, row1 = band_list[rank]
+    rows_px = multigpu.bands_to_pixel_rows(band_list, h)
+    have_rows = row1 > row0
+    plain = capi.make_opts(mode=mode, sh_degree=sh_degree, tile_row_begin=row0, tile_row_end=row1)
+    timed = capi.make_opts(mode=mode, sh_degree=sh_degree, tile_row_begin=row0, tile_row_end=row1, flags=capi.FLAG_TIMING)
+
+    # ---- parity of the real NCCL path: bands rendered by the ranks, gathered on rank 0, against rank 0's own whole frame
+    fb.zero_()
+    if have_rows:
+        ctx.render(stream, fb.data_ptr(), V, P, w, h, plain)
+    multigpu.gather_bands(fb, rows_px, rank, world, dst=0)
+    torch.cuda.synchronize(); dist.barrier()
+    equal = bool(torch.equal(fb, fb_single)) if rank == 0 else True
+    assert equal, "the NCCL-gathered band frame differs from the single-GPU frame"
+
+    # ---- timed: frame i's gather (side stream, framebuffer i & 1) overlaps frame i+1's kernels; one region of K frames,
+    # device-timed, the render stream finally waits for the last gather. No L2 flush: scene planes + records are several
+    # times the 126 MB L2.
+    fbs = [fb, torch.zeros_like(fb)]
+    comm = torch.cuda.Stream(device=dev)
+    ev_r = [torch.cuda.Event() for _ in range(2)]; ev_g = [torch.cuda.Event() for _ in range(2)]
+    main_s = torch.cuda.current_stream()
+
+    def frame(i):
+        b = i & 1
+        if i >= 2:
+            main_s.wait_event(ev_g[b])
+        if have_rows:
+            ctx.render(stream, fbs[b].data_ptr(), V, P, w, h, plain)
+        ev_r[b].record(main_s)
+        with torch.cuda.stream(comm):
+            comm.wait_event(ev_r[b])
+            multigpu.gather_bands(fbs[b], rows_px, rank, world, dst=0)
+            ev_g[b].record(comm)
+    for i in range(6):
+        frame(i)
+    torch.cuda.synchronize(); dist.barrier()
+    sampler = ClockSampler(dev.index)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.start()
+    e0.record(main_s)
+    for i in range(steps):
+        frame(i)
+    main_s.wait_stream(comm)
+    e1.record(main_s)
+    torch.cuda.synchronize()
+    dist.barrier()
+    sampler.stop_flag = True; sampler.join()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_per_frame = float(t.item()) / steps
+
+    # ---- per-stage times of every rank's band (a short separate, synchronising loop) and the gather on its own
+    acc = {}
+    for it in range(10):
+        if have_rows:
+            ctx.render(stream, fb.data_ptr(), V, P, w, h, timed)
+        torch.cuda.synchronize()
+        if have_rows and it >= 3:
+            for k, v in ctx.stage_times().items():
+                acc[k] = acc.get(k, 0.0) + v / 7
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    gts = []
+    for it in range(6):
+        dist.barrier(); torch.cuda.synchronize()
+        g0.record(); multigpu.gather_bands(fb, rows_px, rank, world, dst=0); g1.record(); torch.cuda.synchronize()
+        gts.append(g0.elapsed_time(g1))
+    st_band = ctx.status()
+    mine = {"rank": rank, "rows": [row0, row1], "pairs": int(st_band.n_pairs), "live_blocks": int(st_band.n_live_blocks),
+            "stage_us": {k: round(v * 1e3, 1) for k, v in acc.items()}, "gather_us": round(float(np.median(gts[1:])) * 1e3, 1)}
+    everyone = [None] * world
+    dist.all_gather_object(everyone, mine)
+
+    # ---- end to end: host delivery needs no collective. Every rank copies its own band over its own PCIe link into ONE
+    # page-locked host frame shared by the ranks; frame i's copy (side stream) overlaps frame i+1's kernels.
+    e2e_steps = max(8, min(steps, 64))
+    frames = [multigpu.SharedHostFrame("splat_bench_%d_%d" % (os.getppid(), k), h, w, rank, world) for k in range(2)]
+    copy_s = torch.cuda.Stream(device=dev)
+    ev_r2 = [torch.cuda.Event() for _ in range(2)]; ev_c2 = [torch.cuda.Event() for _ in range(2)]
+
+    def e2e_run(k):
+        for i in range(k):
+            b = i & 1
+            if i >= 2:
+                main_s.wait_event(ev_c2[b])
+            if have_rows:
+                ctx.render(stream, fbs[b].data_ptr(), V, P, w, h, plain)      # matrices come from host memory
+            ev_r2[b].record(main_s)
+            with torch.cuda.stream(copy_s):
+                copy_s.wait_event(ev_r2[b])
+                frames[b].deliver(fbs[b], rows_px[rank])
+                ev_c2[b].record(copy_s)
+        torch.cuda.synchronize()
+    e2e_run(4)
+    dist.barrier()
+    t0 = time.perf_counter(); e2e_run(e2e_steps); dist.barrier(); e2e_s = time.perf_counter() - t0
+    host_equal = True
+    if rank == 0:
+        host_equal = bool(torch.equal(frames[(e2e_steps - 1) & 1].tensor, fb_single.cpu()))
+        assert host_equal, "the shared host frame differs from the single-GPU frame"
+    for fr in frames:
+        fr.close()
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_fps = e2e_steps / float(t.item())
+    fps = 1e3 / ms_per_frame
+    slow = max(everyone, key=lambda d: d["stage_us"].get("total", 0.0))
+    out = {
+        "workload": name, "n_gaussians": n, "width": w, "height": h, "mode": "TILE", "parallelism": "bands%d+nccl_gather" % world,
+        "frames_per_s": fps, "ms_per_frame": ms_per_frame, "steps": steps,
+        "frames_per_s_1gpu": None, "speedup": None, "one_gpu": None,
+        "bands": band_list, "band_balance": "even" if even_bands else "pairs per tile row, then 3 rounds of measured-time balancing",
+        "per_rank": everyone, "slowest_rank_stage_us": slow["stage_us"], "gather_us": max(d["gather_us"] for d in everyone),
+        "gather_bytes_per_frame": w * h * 8,
+        "e2e_frames_per_s": e2e_fps, "e2e_steps": e2e_steps, "e2e_d2h_bytes_per_step_per_rank": (rows_px[rank][1] - rows_px[rank][0]) * w * 8,
+        "band_frame_equals_single_gpu": equal, "shared_host_frame_equals_single_gpu": host_equal,
+        "clocks": sampler.result(),
+        "l2": "inputs larger than L2 (scene planes + records ~700 MB); frames back to back, the gather of frame i overlapped with frame i+1",
+    }
+    if rank == 0:
+        out["frames_per_s_1gpu"] = one_gpu["frames_per_s"]; out["speedup"] = fps / one_gpu["frames_per_s"]; out["one_gpu"] = one_gpu
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -244,7 +451,8 @@ def main():
     ap.add_argument("--sh-degree", type=int, default=0, choices=[0, 1, 2, 3])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sort-bench", action="store_true")
-    ap.add_argument("--even-bands", action="store_true", help="c3: equal tile-row bands instead of pair-balanced ones")
+    ap.add_argument("--no-c3-leg", action="store_true", help="N > 1: skip the config-3 band + gather leg reported in config.c3")
+    ap.add_argument("--even-bands", action="store_true", help="c3: equal tile-row bands instead of balanced ones")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
@@ -274,78 +482,60 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     wl = args.workload or "c2"
+    ctx = capi.Context(local)
+    hbm_peak, peak_kind, sm_max = peaks()
+
+    if wl == "c3" and world > 1:
+        # --workload c3 at N > 1: the band + gather leg IS the headline (strong scaling)
+        leg = c3_bands_leg(ctx, torch, dist, args, dev, rank, world, args.steps, args.sh_degree, args.even_bands)
+        if rank == 0:
+            n, w, h = leg["n_gaussians"], leg["width"], leg["height"]
+            line = {
+                "metric": "frames_per_s", "value": leg["frames_per_s"], "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": leg["ms_per_frame"], "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "f32+f16", "data": "synthetic", "mgaussians_per_s": n * leg["frames_per_s"] / 1e6,
+                "config": {"workload": leg["workload"], "n_gaussians": n, "width": w, "height": h, "mode": "TILE", "order": "near_first",
+                           "parallelism": leg["parallelism"], "c3": leg, "l2": leg["l2"]},
+                "e2e": {"value": leg["e2e_frames_per_s"], "unit": "frames/s", "h2d_bytes_per_step": 128,
+                        "d2h_bytes_per_step": leg["e2e_d2h_bytes_per_step_per_rank"], "steps": leg["e2e_steps"],
+                        "note": "per frame: matrices from host, band rendered, band copied device -> shared page-locked host frame by "
+                                "every rank in parallel (no collective; copies overlap the next frame); d2h bytes are rank 0's band"},
+                "gpu_launches": args.steps * 6, "clocks": leg["clocks"], "numa": numa,
+            }
+            emit(line)
+        ctx.close()
+        dist.barrier(); dist.destroy_process_group()
+        return
+
     n, w, h, mode, cfg, name = WORKLOADS[wl]
-    bands = wl == "c3" and world > 1
     inst, sh = scene.make_instances(n, scene.CONFIG_SEEDS[cfg], sh_rest=args.sh_degree > 0)
     n = inst.shape[0]
-    ctx = capi.Context(local)
     ctx.upload(inst)
     if args.sh_degree:
         ctx.upload_sh(sh, 3)
     stream = torch.cuda.current_stream().cuda_stream
-    tiles_x, tiles_y = (w + 15) // 16, (h + 15) // 16
     fb = torch.zeros((h, w, 4), dtype=torch.float16, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     n_views = 64
-    view_sharded = (world > 1 and not bands) or wl == "c4"
+    view_sharded = world > 1 or wl == "c4"
 
-    def cam(step):      # N=1 uses the app camera (configs 2/3/5); view-sharded runs walk the orbit
+    def cam(step):      # N=1 uses the app camera (configs 2/3/5); view-sharded runs walk the 64-view orbit
         if view_sharded:
             return orbit_camera((step * world + rank) % n_views, n_views, w, h)
         return camera.app_camera(w, h)
 
-    # ---- tile-row bands (c3, N>1): boundaries balanced on the pairs per tile row of a first full frame
-    row0, row1, band_list = 0, tiles_y, [(0, tiles_y)]
-    if bands:
-        ctx.render(stream, fb.data_ptr(), *cam(0), w, h, capi.make_opts(mode=mode))
-        torch.cuda.synchronize()
-        if ctx.status().overflow:
-            ctx.render(stream, fb.data_ptr(), *cam(0), w, h, capi.make_opts(mode=mode)); torch.cuda.synchronize(); ctx.status()
-        r = ctx.fetch(capi.FETCH_TILE_RANGES).astype(np.int64)
-        row_pairs = (r[:, 1] - r[:, 0]).reshape(tiles_y, tiles_x).sum(axis=1)
-        band_list = multigpu.band_rows(tiles_y, world, None if args.even_bands else row_pairs)
-        if not args.even_bands:
-            # Measured-time balancing (untimed set-up, like the pair count above): pairs per row are not the cost
-            # (rows of large near splats blend slower per pair), so three rounds of "render the band, exchange
-            # the band-proportional stage times, move the boundaries" follow.
-            wts = row_pairs.astype(np.float64)
-            for _ in range(3):
-                a, b = band_list[rank]
-                o = capi.make_opts(mode=mode, sh_degree=args.sh_degree, tile_row_begin=a, tile_row_end=b, flags=capi.FLAG_TIMING)
-                acc = []
-                for it in range(6):
-                    var = 0.0
-                    if b > a:
-                        ctx.render(stream, fb.data_ptr(), *cam(0), w, h, o); torch.cuda.synchronize()
-                        st_ = ctx.stage_times()
-                        var = st_["sort"] + st_["ranges"] + st_["blend"] + 0.5 * st_["scan_duplicate"]
-                    if it >= 2:
-                        acc.append(var)
-                tt = torch.tensor([float(np.median(acc))], dtype=torch.float64, device=dev)
-                allt = [torch.zeros_like(tt) for _ in range(world)]
-                dist.all_gather(allt, tt)
-                wts = multigpu.reweight_rows(wts, band_list, [float(x.item()) for x in allt])
-                band_list = multigpu.band_rows(tiles_y, world, wts)
-        row0, row1 = band_list[rank]
-    rows_px = multigpu.bands_to_pixel_rows(band_list, h) if bands else [(0, h)]
-    have_rows = row1 > row0
-
-    def opts_for(flags):
-        return capi.make_opts(mode=mode, sh_degree=args.sh_degree, tile_row_begin=row0 if bands else 0,
-                              tile_row_end=row1 if bands else 0, flags=flags)
-    opts = opts_for(capi.FLAG_TIMING)
+    opts = capi.make_opts(mode=mode, sh_degree=args.sh_degree, flags=capi.FLAG_TIMING)
 
     def step(i):
-        if have_rows:
-            ctx.render(stream, fb.data_ptr(), *cam(i), w, h, opts)
-        if bands:      # NCCL gather of the framebuffer bands to rank 0 (the path's one exchange step)
-            multigpu.gather_bands(fb, rows_px, rank, world, dst=0)
+        ctx.render(stream, fb.data_ptr(), *cam(i), w, h, opts)
 
-    # warm-up (also grows the pair buffers if the first frame overflowed)
-    for i in range(args.warmup):
+    # warm-up (also grows the pair buffers if a frame overflowed: status() reports it and the frame is rendered again)
+    for i in range(max(args.warmup, n_views // world if view_sharded else 0)):
         step(i)
         torch.cuda.synchronize()
-        st = ctx.status()
+        if ctx.status().overflow:
+            step(i); torch.cuda.synchronize(); ctx.status()
+    st = ctx.status()
     assert not st.overflow, "pair buffers still overflow after warm-up"
 
     sampler = ClockSampler(local)
@@ -353,175 +543,94 @@ def main():
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
-    if bands:
-        # Single frame over tile-row bands: frame i's NCCL gather (side stream, framebuffer i&1) overlaps
-        # frame i+1's kernels. Timed as one region of K frames on the device (events on the render
-        # stream, which finally waits for the last gather). No L2 flush: scene planes + records
-        # (6M x 98 B) are several times the 126 MB L2.
-        fbs = [fb, torch.zeros_like(fb)]
-        comm = torch.cuda.Stream(device=dev)
-        ev_r = [torch.cuda.Event() for _ in range(2)]; ev_g = [torch.cuda.Event() for _ in range(2)]
-        main = torch.cuda.current_stream()
-        plain = capi.make_opts(mode=mode, sh_degree=args.sh_degree, tile_row_begin=row0, tile_row_end=row1)
-
-        def frame(i):
-            b = i & 1
-            if i >= 2:
-                main.wait_event(ev_g[b])
-            if have_rows:
-                ctx.render(stream, fbs[b].data_ptr(), *cam(i), w, h, plain)
-            ev_r[b].record(main)
-            with torch.cuda.stream(comm):
-                comm.wait_event(ev_r[b])
-                multigpu.gather_bands(fbs[b], rows_px, rank, world, dst=0)
-                ev_g[b].record(comm)
-        for i in range(4):
-            frame(i)
-        torch.cuda.synchronize(); dist.barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        sampler.start()
-        t_wall0 = time.perf_counter()
-        e0.record(main)
-        for i in range(args.steps):
-            frame(i)
-        main.wait_stream(comm)
-        e1.record(main)
-        torch.cuda.synchronize()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    sampler.start()
+    t_wall0 = time.perf_counter()
+    for i in range(args.steps):
+        flush.fill_(i & 0xFF)                    # L2 flush between timed iterations (not timed)
+        ev[i][0].record()
+        step(args.warmup + i)
+        ev[i][1].record()
+        ev[i][1].synchronize()
+        for k, v in ctx.stage_times().items():
+            stage_acc[k] = stage_acc.get(k, 0.0) + v
+    torch.cuda.synchronize()
+    if world > 1:
         dist.barrier()
-        t_wall = time.perf_counter() - t_wall0
-        sampler.stop_flag = True; sampler.join()
-        total_ms = e0.elapsed_time(e1)
-        for i in range(10):                        # per-stage times from a short separate, synchronising loop
-            step(i)
-            torch.cuda.synchronize()
-            if have_rows:
-                for k, v in ctx.stage_times().items():
-                    stage_acc[k] = stage_acc.get(k, 0.0) + v * args.steps / 10.0
-    else:
-        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-        sampler.start()
-        t_wall0 = time.perf_counter()
-        for i in range(args.steps):
-            flush.fill_(i & 0xFF)                    # L2 flush between timed iterations (not timed)
-            ev[i][0].record()
-            step(args.warmup + i)
-            ev[i][1].record()
-            ev[i][1].synchronize()
-            for k, v in ctx.stage_times().items():
-                stage_acc[k] = stage_acc.get(k, 0.0) + v
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        t_wall = time.perf_counter() - t_wall0
-        sampler.stop_flag = True
-        sampler.join()
-        per_step = [a.elapsed_time(b) for a, b in ev]
-        total_ms = sum(per_step)
+    t_wall = time.perf_counter() - t_wall0
+    sampler.stop_flag = True
+    sampler.join()
+    per_step = [a.elapsed_time(b) for a, b in ev]
+    total_ms = sum(per_step)
     if world > 1:
         t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         total_ms = float(t.item())
     ms_per_step = total_ms / args.steps
-    step_pct = None
-    if not bands:      # this rank's per-step distribution (median and p10 / p90)
-        q = np.percentile(np.asarray(per_step), [10, 50, 90])
-        step_pct = {"p10": float(q[0]), "p50": float(q[1]), "p90": float(q[2])}
-    frames_per_step = 1 if bands else world
-    fps = frames_per_step * 1e3 / ms_per_step
+    q = np.percentile(np.asarray(per_step), [10, 50, 90])      # this rank's per-step distribution
+    step_pct = {"p10": float(q[0]), "p50": float(q[1]), "p90": float(q[2])}
+    fps = world * 1e3 / ms_per_step
+    # the app-camera frame's counts (view-sharded runs end on some orbit view: render the app camera once more for them)
+    ctx.render(stream, fb.data_ptr(), *camera.app_camera(w, h), w, h, capi.make_opts(mode=mode, sh_degree=args.sh_degree,
+                                                                                       flags=capi.FLAG_COUNT_WORK))
+    torch.cuda.synchronize()
     st = ctx.status()
-    D = int(st.n_pairs); n_pass = int(st.sort_passes); C = int(getattr(st, 'n_candidates', 0)) or D
+    D = int(st.n_pairs); slots = int(st.n_candidates); warp_cand = int(st.blend_warp_candidates)
+    visible = int((ctx.fetch(capi.FETCH_TILES_TOUCHED) > 0).sum()) if rank == 0 else 0
 
     # ---- e2e: through the public host-buffer API. Scene resident (uploaded once, as the reference's
     # initialize() does, src/instanced_splat_renderer.mm:399-422); every step copies that step's
     # matrices from host memory and brings the finished framebuffer back to pinned host memory.
     e2e_steps = max(8, min(args.steps, 64))
-    eopts = opts_for(0)
-    band_px = (rows_px[rank][1] - rows_px[rank][0]) * w if bands else w * h
-    if bands:
-        # Host delivery needs no collective: every rank copies its own band over its own PCIe link into ONE
-        # page-locked host frame shared by the ranks (multigpu.SharedHostFrame); frame i's copy (side stream,
-        # device framebuffer i & 1) overlaps frame i+1's kernels. Two shared frames alternate so a consumer
-        # could read frame i while i+1 lands.
-        frames = [multigpu.SharedHostFrame("splat_bench_%d_%d" % (os.getppid(), k), h, w, rank, world) for k in range(2)]
-        efbs = [fb, torch.zeros_like(fb)]
-        copy_s = torch.cuda.Stream(device=dev)
-        ev_r2 = [torch.cuda.Event() for _ in range(2)]; ev_c2 = [torch.cuda.Event() for _ in range(2)]
-        main2 = torch.cuda.current_stream()
-        eplain = capi.make_opts(mode=mode, sh_degree=args.sh_degree, tile_row_begin=row0, tile_row_end=row1)
-
-        def e2e_run(k):
-            for i in range(k):
-                b = i & 1
-                if i >= 2:
-                    main2.wait_event(ev_c2[b])
-                if have_rows:
-                    ctx.render(stream, efbs[b].data_ptr(), *cam(i), w, h, eplain)      # matrices come from host memory
-                ev_r2[b].record(main2)
-                with torch.cuda.stream(copy_s):
-                    copy_s.wait_event(ev_r2[b])
-                    frames[b].deliver(efbs[b], rows_px[rank])
-                    ev_c2[b].record(copy_s)
-            torch.cuda.synchronize()
-        e2e_run(4)
-        dist.barrier()
-        t0 = time.perf_counter(); e2e_run(e2e_steps); dist.barrier(); e2e_s = time.perf_counter() - t0
-        if rank == 0:       # the delivered frame is the whole frame: compare its last copy with a gathered one
-            multigpu_check = frames[(e2e_steps - 1) & 1].tensor.clone()
-        step(e2e_steps - 1)
-        torch.cuda.synchronize(); dist.barrier()
-        if rank == 0:
-            assert torch.equal(multigpu_check, fb.cpu()), "shared host frame differs from the gathered frame"
-        for fr in frames:
-            fr.close()
-        d2h = band_px * 8
-        e2e_note = ("per frame: matrices from host, band rendered, band copied device -> shared page-locked host frame by every "
-                    "rank in parallel (no collective; copies overlap the next frame); d2h bytes are this rank's band")
-        lat_ms = None
-    else:
-        host_fbs = torch.empty((e2e_steps, h, w, 4), dtype=torch.float16).pin_memory()
-        ptrs = [host_fbs[k].data_ptr() for k in range(e2e_steps)]
-        cams = [cam(i) for i in range(e2e_steps)]
-        views = np.stack([c[0] for c in cams]); projs = np.stack([c[1] for c in cams])
-        ctx.render_batch_host(ptrs[:4], views[:4], projs[:4], w, h, eopts)
-        t0 = time.perf_counter()
-        for i in range(8):
-            ctx.render_host(ptrs[i], views[i], projs[i], w, h, eopts)
-        lat_ms = 1e3 * (time.perf_counter() - t0) / 8
-        if world > 1:
-            dist.barrier()
-        t0 = time.perf_counter()
-        ctx.render_batch_host(ptrs, views, projs, w, h, eopts)
-        e2e_s = time.perf_counter() - t0
-        # the same, delivered in the reference drawable's format (BGRA8Unorm, 4 B / pixel, packed on the device)
-        bgra_fbs = torch.empty((e2e_steps, h, w, 4), dtype=torch.uint8).pin_memory()
-        bptrs = [bgra_fbs[k].data_ptr() for k in range(e2e_steps)]
-        bopts = opts_for(capi.FLAG_HOST_BGRA8)
-        ctx.render_batch_host(bptrs[:4], views[:4], projs[:4], w, h, bopts)
-        if world > 1:
-            dist.barrier()
-        t0 = time.perf_counter()
-        ctx.render_batch_host(bptrs, views, projs, w, h, bopts)
-        e2e_bgra_s = time.perf_counter() - t0
-        del bgra_fbs
-        d2h = w * h * 8 + 16
-        e2e_note = ("splat_render_batch_host: %d frames, each frame's matrices from host and its framebuffer to pinned "
-                    "host memory, copies pipelined behind the next frame's kernels" % e2e_steps)
+    eopts = capi.make_opts(mode=mode, sh_degree=args.sh_degree)
+    host_fbs = torch.empty((e2e_steps, h, w, 4), dtype=torch.float16).pin_memory()
+    ptrs = [host_fbs[k].data_ptr() for k in range(e2e_steps)]
+    cams = [cam(i) for i in range(e2e_steps)]
+    views = np.stack([c[0] for c in cams]); projs = np.stack([c[1] for c in cams])
+    ctx.render_batch_host(ptrs[:4], views[:4], projs[:4], w, h, eopts)
+    t0 = time.perf_counter()
+    for i in range(8):
+        ctx.render_host(ptrs[i], views[i], projs[i], w, h, eopts)
+    lat_ms = 1e3 * (time.perf_counter() - t0) / 8
     if world > 1:
-        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+        dist.barrier()
+    t0 = time.perf_counter()
+    ctx.render_batch_host(ptrs, views, projs, w, h, eopts)
+    e2e_s = time.perf_counter() - t0
+    del host_fbs
+    # the same, delivered in the reference drawable's format (BGRA8Unorm, 4 B / pixel, packed on the device)
+    bgra_fbs = torch.empty((e2e_steps, h, w, 4), dtype=torch.uint8).pin_memory()
+    bptrs = [bgra_fbs[k].data_ptr() for k in range(e2e_steps)]
+    bopts = capi.make_opts(mode=mode, sh_degree=args.sh_degree, flags=capi.FLAG_HOST_BGRA8)
+    ctx.render_batch_host(bptrs[:4], views[:4], projs[:4], w, h, bopts)
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    ctx.render_batch_host(bptrs, views, projs, w, h, bopts)
+    e2e_bgra_s = time.perf_counter() - t0
+    # the box's host-write ceiling: the same number of plain device-to-pinned-host copies of one half4 frame, all ranks at once
+    if world > 1:
+        dist.barrier()
+    hb = torch.empty((4, h, w, 4), dtype=torch.uint8).pin_memory()
+    src = torch.zeros((h, w, 4), dtype=torch.uint8, device=dev)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for i in range(e2e_steps):
+        hb[i & 3].copy_(src, non_blocking=True)
+    torch.cuda.synchronize()
+    d2h_s = time.perf_counter() - t0
+    del bgra_fbs, hb, src
+    if world > 1:
+        t = torch.tensor([e2e_s, e2e_bgra_s, d2h_s], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    e2e_fps = frames_per_step * e2e_steps / e2e_s
-    e2e_bgra_fps = None
-    if not bands:
-        if world > 1:
-            t = torch.tensor([e2e_bgra_s], dtype=torch.float64, device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            e2e_bgra_s = float(t.item())
-        e2e_bgra_fps = frames_per_step * e2e_steps / e2e_bgra_s
+        e2e_s, e2e_bgra_s, d2h_s = (float(x) for x in t.tolist())
+    e2e_fps = world * e2e_steps / e2e_s
+    e2e_bgra_fps = world * e2e_steps / e2e_bgra_s
+    bgra_ceiling_fps = world * e2e_steps / d2h_s
 
     # ---- device-resident camera batch (splat_render_batch: two frames in flight on two internal streams)
     inflight = None
-    if not bands and world == 1:
+    if world == 1:
         nb = 8
         dfb = torch.zeros((nb, h, w, 4), dtype=torch.float16, device=dev)
         dptrs = [dfb[k % nb].data_ptr() for k in range(e2e_steps)]
@@ -536,11 +645,26 @@ def main():
                     "note": "splat_render_batch, framebuffers stay on the device; no L2 flush (a frame touches ~2x the L2)"}
         del dfb
 
+    sb = None
+    if world == 1 and not args.no_sort_bench:
+        sb = sort_bench(ctx, torch)
+        sb["frac_of_hbm_peak"] = sb["gb_per_s"] / hbm_peak
+        sb["frac_of_8TBs_nominal"] = sb["gb_per_s"] / 8000.0
+    cpu_leg = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu_leg = cpu_baseline_leg(inst, *camera.app_camera(w, h), w, h, mode, name)
+        cpu_leg["cpu_model"] = cpu_model()
+        cpu_leg["note"] = "single thread = the named baseline; the --impl reference arm uses all cores (its binning stages stay single-threaded)"
+    del inst
+    c3 = None
+    if world > 1 and wl == "c2" and not args.no_c3_leg:
+        del fb, flush
+        torch.cuda.empty_cache()
+        c3 = c3_bands_leg(ctx, torch, dist, args, dev, rank, world, min(args.steps, 100), 0, args.even_bands)
+
     if rank == 0:
-        hbm_peak, peak_kind, sm_max = peaks()
-        visible = int((ctx.fetch(capi.FETCH_TILES_TOUCHED) > 0).sum())
-        P = band_px if bands else w * h
-        ab = algorithmic_bytes(n, visible, D, C, P, args.sh_degree, layer=bool(mode))
+        P = w * h
+        ab = algorithmic_bytes(n, visible, D, slots, P, args.sh_degree, layer=bool(mode))
         stage_ms = {k: v / args.steps for k, v in stage_acc.items()}
         stages = {}
         for k in STAGES:
@@ -549,53 +673,61 @@ def main():
             stages[k] = {"ms": ms, "alg_bytes": ab[k], "gb_per_s": gbs, "frac_of_hbm_peak": gbs / hbm_peak}
         dom = max(STAGES, key=lambda k: stage_ms.get(k, 0.0))
         clocks = sampler.result()
-        roof = {"kernel": {"blend": "blend_kernel", "sort": "tile_sort_kernel", "preprocess": "preprocess_kernel",
-                           "scan_duplicate": "bin_pairs_kernel", "ranges": "-"}[dom],
-                "bound": "hbm", "achieved": stages[dom]["gb_per_s"], "peak": hbm_peak, "unit": "GB/s",
-                "frac": stages[dom]["frac_of_hbm_peak"], "frac_of_8TBs_nominal": stages[dom]["gb_per_s"] / 8000.0,
-                "traffic": measured_traffic(wl, dom), "peak_kind": peak_kind,
-                "alg_bytes_per_launch": ab[dom], "ms_per_launch": stage_ms.get(dom),
-                "share_of_step": stage_ms.get(dom, 0.0) / max(1e-9, stage_ms.get("total", 0.0)),
-                "note": ("the blend is bound by SM instruction issue, not HBM (ncu: issue slots ~89% busy, DRAM ~2%); "
-                         "its HBM fraction is reported as the contract asks, sm_issue below is the number that bounds it")
-                if dom == "blend" else ""}
+        kernel_of = {"blend": "blend_kernel", "sort": "tile_sort_kernel", "preprocess": "preprocess_kernel",
+                     "scan_duplicate": "scatter_pairs_kernel", "ranges": "-"}
+        hbm = {"achieved": stages[dom]["gb_per_s"], "peak": hbm_peak, "unit": "GB/s", "frac": stages[dom]["frac_of_hbm_peak"],
+               "frac_of_8TBs_nominal": stages[dom]["gb_per_s"] / 8000.0, "peak_kind": peak_kind, "alg_bytes_per_launch": ab[dom]}
+        roof = {"kernel": kernel_of[dom], "traffic": measured_traffic(wl, dom), "ms_per_launch": stage_ms.get(dom),
+                "share_of_step": stage_ms.get(dom, 0.0) / max(1e-9, stage_ms.get("total", 0.0))}
         if dom == "blend":
-            # unit = one (pixel, splat) test at ~16 fp32 ops; lane peak = SMs * 128 lanes * clock / 16
+            # The blend is bound by SM instruction issue, not HBM (ncu: issue slots ~86% busy, DRAM ~4%). Its work unit
+            #  is one (pixel, splat) test at ~16 fp32 ops; EXECUTED tests = the (8x4-pixel warp, splat)
+            # candidates the kernel actually ran (counted by the kernel itself in an untimed frame) x 32 lanes.
+            # Peak = SMs x 128 lanes x clock / 16 ops.
             sm_mhz = clocks["sm_mhz"] or sm_max
             lane_peak = 148 * 128 * sm_mhz * 1e6 / 16.0
-            tests = float(D) * 256.0                                  # upper bound: every pair against the whole tile
-            roof["sm_issue"] = {"pair_tile_tests_per_s": tests / (stage_ms["blend"] * 1e-3), "lane_peak_tests_per_s": lane_peak,
-                                "frac": tests / (stage_ms["blend"] * 1e-3) / lane_peak,
-                                "note": "D*256 tests counted although 8x4-block culling skips most of them"}
+            tests_per_s = warp_cand * 32.0 / (stage_ms["blend"] * 1e-3)
+            roof.update({"bound": "sm_issue", "achieved": tests_per_s, "peak": lane_peak, "unit": "lane-tests/s", "frac": tests_per_s / lane_peak,
+                         "warp_candidates_per_frame": warp_cand, "hbm": hbm,
+                         "note": "bound = SM instruction issue; achieved counts executed lane-tests only (warp candidates x 32), not D x 256; "
+                                 "the HBM view of the same kernel is under 'hbm' (small by construction: records are shared through L2)"})
+        else:
+            roof.update({"bound": "hbm", **hbm})
+        config = {"workload": name, "n_gaussians": n, "width": w, "height": h,
+                  "mode": "LAYER50" if mode else "TILE", "order": "near_first", "sh_degree": args.sh_degree,
+                  "pairs_D": D, "parking_slots": slots, "visible": visible, "sort_passes": 1,
+                  "live_blocks": int(st.n_live_blocks), "blocks": (n + 255) // 256, "longest_tile_list": int(st.max_tile_pairs),
+                  "parallelism": "views%d" % world,
+                  "l2": "flushed between timed steps (256 MiB write, untimed)",
+                  "e2e_bgra8_frames_per_s": e2e_bgra_fps, "e2e_half4_frames_per_s": e2e_fps,
+                  "host_write_ceiling_frames_per_s": bgra_ceiling_fps,
+                  "host_write_ceiling_note": "plain cudaMemcpyAsync of one BGRA8-sized frame (w*h*4 B) per step to pinned host memory on every rank at once: what the box's host memory takes"}
+        if sb is not None:
+            config.update({"sort_bench_gb_per_s": sb["gb_per_s"], "sort_bench_frac_measured": sb["frac_of_hbm_peak"],
+                           "sort_bench_frac_8TBs": sb["frac_of_8TBs_nominal"], "sort_bench_n_pairs": sb["n_pairs"], "sort_bench_ms": sb["ms"]})
+        if c3 is not None:
+            config["c3"] = c3
+            config["band_frame_equals_single_gpu"] = c3["band_frame_equals_single_gpu"]
         line = {
             "metric": "frames_per_s", "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-            "scaling": "strong" if bands else "weak", "vs_baseline": None, "dtype": "f32+f16", "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32+f16", "data": "synthetic",
             "mgaussians_per_s": n * fps / 1e6, "ms_per_step_percentiles": step_pct,
-            "config": {"workload": name, "n_gaussians": n, "width": w, "height": h,
-                       "mode": "LAYER50" if mode else "TILE", "order": "near_first", "sh_degree": args.sh_degree,
-                       "pairs_D": D, "visible": visible, "sort_passes": n_pass,
-                       "parallelism": ("bands%d+nccl_gather" % world) if bands else ("views%d" % world),
-                       "bands": band_list if bands else None,
-                       "l2": ("inputs larger than L2 (scene planes + records ~590 MB); frames back to back, gather of frame i "
-                              "overlapped with frame i+1") if bands else "flushed between timed steps (256 MiB write, untimed)"},
-            "roofline": roof, "stages": stages,
-            "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": 128, "d2h_bytes_per_step": d2h,
-                    "steps": e2e_steps, "single_frame_ms": lat_ms, "note": e2e_note,
-                    "bgra8": None if bands else {
-                        "value": e2e_bgra_fps, "d2h_bytes_per_step": w * h * 4 + 16,
-                        "note": "same call with SPLAT_FLAG_HOST_BGRA8: frames delivered as the reference drawable's BGRA8Unorm"}},
+            "config": config, "roofline": roof, "stages": stages,
+            "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": 128, "d2h_bytes_per_step": w * h * 8 + 24,
+                    "steps": e2e_steps, "single_frame_ms": lat_ms,
+                    "note": "splat_render_batch_host: %d frames, each frame's matrices from host and its framebuffer to pinned "
+                            "host memory, copies pipelined behind the next frame's kernels" % e2e_steps,
+                    "bgra8": {"value": e2e_bgra_fps, "d2h_bytes_per_step": w * h * 4 + 24,
+                              "note": "same call with SPLAT_FLAG_HOST_BGRA8: frames delivered as the reference drawable's BGRA8Unorm"}},
             "camera_batch_device": inflight,
-            "gpu_launches": args.steps * 7,      # preprocess, tile scan, bin pairs, tile offsets, scatter, tile sort, blend (+1 memset node, not counted)
+            "gpu_launches": args.steps * 6,      # block cull, preprocess, tile offsets, scatter, tile sort, blend (+1 memset node, not counted)
             "clocks": clocks, "wall_s": t_wall, "numa": numa,
         }
-        if world == 1 and not args.no_sort_bench:
-            sb = sort_bench(ctx, torch)
-            sb["frac_of_hbm_peak"] = sb["gb_per_s"] / hbm_peak
-            sb["frac_of_8TBs_nominal"] = sb["gb_per_s"] / 8000.0
+        if sb is not None:
             line["sort_bench"] = sb
-        if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline_leg(inst, *camera.app_camera(w, h), w, h, mode, name)
+        if cpu_leg is not None:
+            line["cpu_baseline"] = cpu_leg
         emit(line)
     ctx.close()
     if world > 1:

@@ -16,7 +16,7 @@ LIB_PATH = os.environ.get("SPLAT_CUDA_LIB") or os.path.join(_HERE, "libsplat_cud
 
 MODE_TILE, MODE_LAYER50, MODE_MLAB = 0, 1, 2
 ORDER_NEAR_FIRST, ORDER_REFERENCE = 0, 1
-FLAG_TIMING, FLAG_KEEP_UNSORTED, FLAG_HOST_BGRA8 = 1, 2, 4
+FLAG_TIMING, FLAG_KEEP_UNSORTED, FLAG_HOST_BGRA8, FLAG_COUNT_WORK = 1, 2, 4, 8
 (FETCH_RECORDS, FETCH_TILES_TOUCHED, FETCH_OFFSETS, FETCH_KEYS_UNSORTED, FETCH_VALS_UNSORTED,
  FETCH_KEYS_SORTED, FETCH_VALS_SORTED, FETCH_TILE_RANGES, FETCH_DIGIT_HISTOGRAMS, FETCH_INSTANCES,
  FETCH_SH_REST) = range(11)
@@ -30,6 +30,7 @@ EXPORTS = [
     "splat_create", "splat_destroy", "splat_upload", "splat_upload_sh", "splat_render",
     "splat_render_host", "splat_render_batch", "splat_render_batch_host", "splat_pack_bgra8", "splat_upload_ply_rows", "splat_frame_status", "splat_debug_fetch",
     "splat_stage_times", "splat_sort_pairs_u64_u32", "splat_sort_pairs_u32_u32", "splat_last_error_string", "splat_version",
+    "splat_band_rows", "splat_gather_bands",
 ]
 
 
@@ -41,7 +42,7 @@ class SplatOpts(C.Structure):
 class SplatStatus(C.Structure):
     _fields_ = [("n_splats", C.c_uint32), ("n_visible_unused", C.c_uint32), ("n_pairs", C.c_uint64),
                 ("pair_capacity", C.c_uint64), ("overflow", C.c_uint32), ("sort_passes", C.c_uint32),
-                ("n_candidates", C.c_uint64), ("max_tile_pairs", C.c_uint32), ("reserved", C.c_uint32)]
+                ("n_candidates", C.c_uint64), ("max_tile_pairs", C.c_uint32), ("n_live_blocks", C.c_uint32), ("blend_warp_candidates", C.c_uint64)]
 
 
 class SplatError(RuntimeError):
@@ -76,6 +77,8 @@ def lib():
         L.splat_sort_pairs_u64_u32.argtypes = [vp, vp, vp, vp, vp, vp, C.c_uint64, C.c_int, C.c_int,
                                                C.POINTER(C.c_int)]
         L.splat_sort_pairs_u32_u32.argtypes = L.splat_sort_pairs_u64_u32.argtypes
+        L.splat_band_rows.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int32)]
+        L.splat_gather_bands.argtypes = [vp, vp, vp, C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
         L.splat_last_error_string.restype = C.c_char_p
         L.splat_version.restype = C.c_int
         _LIB = L
@@ -201,3 +204,25 @@ class Context:
         _check(fn(self._h, stream_ptr, keys_ptr, vals_ptr, keys_alt_ptr, vals_alt_ptr,
                   n, begin_bit, min(end_bit, key_bits), C.byref(res)), "splat_sort_pairs")
         return res.value
+
+
+def band_rows(tiles_y: int, world: int, weights=None):
+    """splat_band_rows: contiguous bands of tile rows for `world` ranks (even split, or minimising the heaviest band)."""
+    out = np.zeros(2 * world, np.int32)
+    wp = None
+    if weights is not None:
+        wt = np.ascontiguousarray(weights, np.float64)
+        if wt.shape != (tiles_y,):
+            raise ValueError("weights must be one non-negative number per tile row")
+        wp = wt.ctypes.data_as(C.POINTER(C.c_double))
+    _check(lib().splat_band_rows(tiles_y, world, wp, out.ctypes.data_as(C.POINTER(C.c_int32))), "splat_band_rows")
+    return [(int(out[2 * r]), int(out[2 * r + 1])) for r in range(world)]
+
+
+def gather_bands(nccl_comm_ptr: int, stream_ptr: int, fb_dev_ptr: int, pixel_rows, w: int, bytes_per_pixel: int, rank: int,
+                 world: int, dst: int = 0):
+    """splat_gather_bands: grouped ncclSend / ncclRecv of the framebuffer bands to rank dst, on the given stream."""
+    rows = np.ascontiguousarray(np.asarray(pixel_rows, np.int32).reshape(-1))
+    _check(lib().splat_gather_bands(C.c_void_p(nccl_comm_ptr), C.c_void_p(stream_ptr), C.c_void_p(fb_dev_ptr),
+                                    rows.ctypes.data_as(C.POINTER(C.c_int32)), w, bytes_per_pixel, rank, world, dst),
+           "splat_gather_bands")

@@ -16,24 +16,26 @@
 // twice and read twice, and the sort runs on T independent lists of a few hundred pairs.
 #include "splat_math.cuh"
 
-// bounds[t] = pairs of tiles 0 .. t-1 (t = 0 .. T). One CTA: a thread owns a contiguous run of counters, read with up to
-// sixteen independent 16-byte loads (one L2 round trip), scanned in registers, written back as vectors. The counter and
-// bounds arrays are padded to 65536 + 8 words; counters beyond T are ignored.
-template <int V>      // 16-byte vectors per thread: frames of up to 4096 V tiles
-__global__ void __launch_bounds__(1024) tile_offsets_kernel(FrameCtl* ctl, unsigned int n_tiles, unsigned int* __restrict__ bounds,
-                                                            unsigned int* __restrict__ cursor)
+// bounds[t] = first pair of tile t's list, for the tiles [first, first + count] of the frame's band (the blend and the sort
+// read nothing else). One CTA: a thread owns a contiguous run of counters, read with up to V independent 16-byte loads (one
+// L2 round trip), scanned in registers, written back as vectors. The counter, bounds and cursor arrays are padded to
+// 65536 + 8 words; the run starts at `first` rounded down to a vector boundary, counters outside the band count as 0.
+template <int V>      // 16-byte vectors per thread: bands of up to 4096 V - 4 tiles
+__global__ void __launch_bounds__(1024) tile_offsets_kernel(FrameCtl* ctl, unsigned int first, unsigned int count,
+                                                            unsigned int* __restrict__ bounds, unsigned int* __restrict__ cursor)
 {
     __shared__ unsigned int s_wsum[32], s_wmax[32];
     pdl_prologue();
     const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned int* tile_count = ctl_tile_count(ctl);
     const bool over = __ldcg(&ctl->overflow) != 0;
-    const unsigned int per4 = (n_tiles + 4095u) / 4096u;          // 16-byte vectors per thread (<= 16)
-    const unsigned int first = tid * per4 * 4u;
+    const unsigned int lo = first & ~3u, end = first + count;                // counters [lo, lo + 4096 V) are looked at
+    const unsigned int per4 = (end - lo + 4095u) / 4096u;                    // 16-byte vectors per thread (<= V)
+    const unsigned int mine = lo + tid * per4 * 4u;
     uint4 v[V];
 #pragma unroll
     for (int q = 0; q < V; ++q)
-        if ((unsigned)q < per4) v[q] = __ldcg(reinterpret_cast<const uint4*>(tile_count + first) + q);
+        if ((unsigned)q < per4 && mine + 4u * q < end) v[q] = __ldcg(reinterpret_cast<const uint4*>(tile_count + mine) + q);
     unsigned int part = 0, big = 0;
 #pragma unroll
     for (int q = 0; q < V; ++q)
@@ -41,7 +43,8 @@ __global__ void __launch_bounds__(1024) tile_offsets_kernel(FrameCtl* ctl, unsig
             unsigned int* e = &v[q].x;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                if (over || first + 4u * q + k >= n_tiles) e[k] = 0u;
+                const unsigned int t = mine + 4u * q + k;
+                if (over || t < first || t >= end) e[k] = 0u;
                 part += e[k]; big = max(big, e[k]);
             }
         }
@@ -60,19 +63,14 @@ __global__ void __launch_bounds__(1024) tile_offsets_kernel(FrameCtl* ctl, unsig
     for (int k = 0; k < 32; ++k) { const unsigned int x = s_wsum[k]; if (k < (int)warp) run += x; total += x; mx = max(mx, s_wmax[k]); }
 #pragma unroll
     for (int q = 0; q < V; ++q)
-        if ((unsigned)q < per4) {
+        if ((unsigned)q < per4 && mine + 4u * q <= end) {        // <= : the vector holding bounds[end] = total is written too
             uint4 o;
             o.x = run; run += v[q].x; o.y = run; run += v[q].y; o.z = run; run += v[q].z; o.w = run; run += v[q].w;
-            reinterpret_cast<uint4*>(bounds + first)[q] = o;
-#ifdef CURSOR_STRIDE
-            cursor[(size_t)(first + 4 * q) * CURSOR_STRIDE] = o.x; cursor[(size_t)(first + 4 * q + 1) * CURSOR_STRIDE] = o.y;
-            cursor[(size_t)(first + 4 * q + 2) * CURSOR_STRIDE] = o.z; cursor[(size_t)(first + 4 * q + 3) * CURSOR_STRIDE] = o.w;
-#else
-            reinterpret_cast<uint4*>(cursor + first)[q] = o;
-#endif
+            reinterpret_cast<uint4*>(bounds + mine)[q] = o;
+            reinterpret_cast<uint4*>(cursor + mine)[q] = o;
         }
     if (tid == 0) {
-        bounds[n_tiles] = total;
+        bounds[end] = total;
         ctl->total_pairs = total;
         ctl->max_tile_pairs = mx;
     }
@@ -80,10 +78,11 @@ __global__ void __launch_bounds__(1024) tile_offsets_kernel(FrameCtl* ctl, unsig
 
 void launch_tile_offsets(const FrameUniforms& U, FrameCtl* ctl, unsigned int* bounds, unsigned int* cursor, cudaStream_t s)
 {
-    const unsigned int T = (unsigned int)(U.tiles_x * U.tiles_y);
-    if (T <= 16384u) launch_pdl(tile_offsets_kernel<4>, dim3(1), dim3(1024), 0, s, ctl, T, bounds, cursor);
-    else if (T <= 32768u) launch_pdl(tile_offsets_kernel<8>, dim3(1), dim3(1024), 0, s, ctl, T, bounds, cursor);
-    else launch_pdl(tile_offsets_kernel<16>, dim3(1), dim3(1024), 0, s, ctl, T, bounds, cursor);
+    const unsigned int first = (unsigned int)(U.row_begin * U.tiles_x), count = (unsigned int)(max(U.row_end - U.row_begin, 0) * U.tiles_x);
+    const unsigned int span = first + count - (first & ~3u) + 4u;
+    if (span <= 16384u) launch_pdl(tile_offsets_kernel<4>, dim3(1), dim3(1024), 0, s, ctl, first, count, bounds, cursor);
+    else if (span <= 32768u) launch_pdl(tile_offsets_kernel<8>, dim3(1), dim3(1024), 0, s, ctl, first, count, bounds, cursor);
+    else launch_pdl(tile_offsets_kernel<16>, dim3(1), dim3(1024), 0, s, ctl, first, count, bounds, cursor);
 }
 
 // A CTA takes four parking chunks at a time, one slot per thread and chunk: the four (tile, key) loads, the four returning

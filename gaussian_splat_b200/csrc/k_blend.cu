@@ -73,10 +73,10 @@ struct PixelState {
 // vals[VSTRIDE * e] = instance index of list entry e (VSTRIDE 2: the low words of the 64-bit pairs, 1: LAYER50's arrival list).
 // rec / vals are written earlier in the same frame by kernels this one is linked to by programmatic dependent launch:
 // they are read through L2 (ld.global.cg), not through the non-coherent path.
-template <int WALK, int VSTRIDE>
+template <int WALK, int VSTRIDE, bool COUNT>
 __device__ __forceinline__ void walk_list(const splat_record_row* rec, const unsigned int* vals,
                                           uint2 range, int K, float pxc, float pyc, float tox, float toy,
-                                          float4* s_ab, unsigned int* s_cm, PixelState& px, KBuffer& kb)
+                                          float4* s_ab, unsigned int* s_cm, PixelState& px, KBuffer& kb, unsigned int& n_cand)
 {
     float4* const s_a = s_ab; float4* const s_b = s_ab + BLEND_BATCH;
     unsigned int* const s_c = s_cm; unsigned int* const s_m = s_cm + BLEND_BATCH; unsigned int* const s_i = s_cm + 2 * BLEND_BATCH;
@@ -133,6 +133,7 @@ __device__ __forceinline__ void walk_list(const splat_record_row* rec, const uns
                 const unsigned int a_top = a_ab + (c0 + 31u) * 16u, c_top = a_cm + (c0 + 31u) * 4u;
                 while (bits) {
                     unsigned int j;
+                    if (COUNT) ++n_cand;            // warp-candidates executed (SPLAT_FLAG_COUNT_WORK: the roofline's work count)
                     asm("bfind.u32 %0, %1;" : "=r"(j) : "r"(bits));
                     {   // clear the top bit: keep bits [0, j)
                         unsigned int below;
@@ -208,11 +209,11 @@ __device__ __forceinline__ void walk_list(const splat_record_row* rec, const uns
 #undef done
 }
 
-template <int MODE>
+template <int MODE, bool COUNT>
 __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
     const __grid_constant__ FrameUniforms U, const splat_record_row* rec,
     const unsigned int* pairs_lo, const unsigned int* arrival,
-    const unsigned int* bounds, uint2* __restrict__ fb)
+    const unsigned int* bounds, uint2* __restrict__ fb, FrameCtl* ctl)
 {
     __shared__ float4 s_ab[2 * BLEND_BATCH];        // [0..B): cx cy ux uy   [B..2B): vx vy opacity rg
     __shared__ unsigned int s_cm[3 * BLEND_BATCH];  // [0..B): bd   [B..2B): 8x4-block mask   [2B..3B): instance index
@@ -230,19 +231,20 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
 
     PixelState px;
     KBuffer kb;
+    unsigned int n_cand = 0;
     px.accRG = __halves2half2(__ushort_as_half(0), __ushort_as_half(0));
     px.cutoff = 0xFFFFFFFFu;
     if (MODE == SPLAT_MODE_TILE) {
         px.accBA = px.accRG;
         px.rem = inside ? K : 0;
-        walk_list<WALK_TILE, 2>(rec, pairs_lo, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
+        walk_list<WALK_TILE, 2, COUNT>(rec, pairs_lo, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb, n_cand);
     } else if (MODE == SPLAT_MODE_MLAB) {
         const __half h0 = __ushort_as_half(0), h1 = __ushort_as_half(0x3C00);
 #pragma unroll
         for (int k = 0; k < 6; ++k) { kb.rg[k] = __halves2half2(h0, h0); kb.ba[k] = __halves2half2(h0, h1); kb.d[k] = k == 3 ? h1 : h0; }
         px.accBA = px.accRG;
         px.rem = inside ? K : 0;                       // K = INT_MAX: a pixel never closes
-        walk_list<WALK_MLAB, 2>(rec, pairs_lo, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
+        walk_list<WALK_MLAB, 2, COUNT>(rec, pairs_lo, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb, n_cand);
         // resolve_main: composite the six layers front to back
         __half2 crg = __halves2half2(h0, h0); __half cb = h0, at = h1;
 #pragma unroll
@@ -260,13 +262,14 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
         // the reference (504 B/pixel in device memory) are never materialised.
         if (range.y - range.x > (unsigned int)K) {
             px.rem = inside ? K : 0;
-            walk_list<WALK_COUNT, 1>(rec, arrival, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
+            walk_list<WALK_COUNT, 1, COUNT>(rec, arrival, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb, n_cand);
             __syncthreads();
         }
         px.accBA = __halves2half2(__ushort_as_half(0), __ushort_as_half(0x3C00));   // accumVis = 1
         px.rem = inside ? K : 0;
-        walk_list<WALK_UNDER, 2>(rec, pairs_lo, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb);
+        walk_list<WALK_UNDER, 2, COUNT>(rec, pairs_lo, range, K, pxc, pyc, tox, toy, s_ab, s_cm, px, kb, n_cand);
     }
+    if (COUNT && (threadIdx.x & 31) == 0 && n_cand) atomicAdd(&ctl->blend_warp_candidates, (unsigned long long)n_cand);
     if (!inside) return;
     uint2 out;
     out.x = *reinterpret_cast<const unsigned int*>(&px.accRG);
@@ -280,17 +283,25 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
     fb[(size_t)pj * U.w + pi] = out;
 }
 
+template <bool COUNT>
+static void launch_blend_t(const FrameUniforms& U, const splat_record_row* rec, const unsigned int* lo, const unsigned int* arrival,
+                           const unsigned int* bounds, void* fb_half4, FrameCtl* ctl, cudaStream_t s)
+{
+    const dim3 grid(U.tiles_x, U.row_end - U.row_begin);
+    if (U.mode == SPLAT_MODE_MLAB)
+        launch_pdl(blend_kernel<SPLAT_MODE_MLAB, COUNT>, grid, dim3(BLEND_THREADS), 0, s, U, rec, lo, arrival, bounds, reinterpret_cast<uint2*>(fb_half4), ctl);
+    else if (U.mode == SPLAT_MODE_LAYER50)
+        launch_pdl(blend_kernel<SPLAT_MODE_LAYER50, COUNT>, grid, dim3(BLEND_THREADS), 0, s, U, rec, lo, arrival, bounds, reinterpret_cast<uint2*>(fb_half4), ctl);
+    else
+        launch_pdl(blend_kernel<SPLAT_MODE_TILE, COUNT>, grid, dim3(BLEND_THREADS), 0, s, U, rec, lo, arrival, bounds, reinterpret_cast<uint2*>(fb_half4), ctl);
+}
+
 void launch_blend(const FrameUniforms& U, const splat_record_row* rec, const unsigned long long* pairs,
-                  const unsigned int* arrival, const unsigned int* bounds, void* fb_half4, cudaStream_t s)
+                  const unsigned int* arrival, const unsigned int* bounds, void* fb_half4, FrameCtl* ctl, bool count_work, cudaStream_t s)
 {
     const int rows = U.row_end - U.row_begin;
     if (rows <= 0 || U.tiles_x <= 0) return;
-    const dim3 grid(U.tiles_x, rows);
     const unsigned int* lo = reinterpret_cast<const unsigned int*>(pairs);      // little endian: the instance index is word 0 of a pair
-    if (U.mode == SPLAT_MODE_MLAB)
-        launch_pdl(blend_kernel<SPLAT_MODE_MLAB>, grid, dim3(BLEND_THREADS), 0, s, U, rec, lo, arrival, bounds, reinterpret_cast<uint2*>(fb_half4));
-    else if (U.mode == SPLAT_MODE_LAYER50)
-        launch_pdl(blend_kernel<SPLAT_MODE_LAYER50>, grid, dim3(BLEND_THREADS), 0, s, U, rec, lo, arrival, bounds, reinterpret_cast<uint2*>(fb_half4));
-    else
-        launch_pdl(blend_kernel<SPLAT_MODE_TILE>, grid, dim3(BLEND_THREADS), 0, s, U, rec, lo, arrival, bounds, reinterpret_cast<uint2*>(fb_half4));
+    if (count_work) launch_blend_t<true>(U, rec, lo, arrival, bounds, fb_half4, ctl, s);
+    else launch_blend_t<false>(U, rec, lo, arrival, bounds, fb_half4, ctl, s);
 }

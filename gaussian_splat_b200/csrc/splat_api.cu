@@ -494,7 +494,7 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
     if (timed) CK(cudaEventRecord(c->ev[2], s));
     if (c->n) launch_tile_sort(U, c->ctl, c->bounds, c->pairs, c->arrival, s);
     if (timed) { CK(cudaEventRecord(c->ev[3], s)); CK(cudaEventRecord(c->ev[4], s)); }
-    launch_blend(U, c->rec, c->pairs, c->arrival, c->bounds, fb, s);
+    launch_blend(U, c->rec, c->pairs, c->arrival, c->bounds, fb, c->ctl, (flags & SPLAT_FLAG_COUNT_WORK) != 0, s);
     if (timed) CK(cudaEventRecord(c->ev[5], s));
     CK(cudaGetLastError());
     c->lastU = U; c->have_frame = true; c->timed = timed;
@@ -576,7 +576,8 @@ int splat_frame_status(splat_ctx* c, splat_status* out) {
     out->pair_capacity = c->capacity;
     out->overflow = c->ctl_host->overflow;
     out->sort_passes = 1;            // one shared-memory sort per tile list
-    out->n_candidates = (unsigned long long)c->ctl_host->n_chunks * PARK_CHUNK; out->max_tile_pairs = c->ctl_host->max_tile_pairs;
+    out->n_candidates = (unsigned long long)c->ctl_host->n_chunks * PARK_CHUNK; out->max_tile_pairs = c->ctl_host->max_tile_pairs; out->n_live_blocks = c->ctl_host->n_live_blocks;
+    out->blend_warp_candidates = c->ctl_host->blend_warp_candidates;
     // every frame since the last look (a camera batch: all its views), not only the last one
     unsigned long long worst = 0;
     const int rc = check_overflow(c, true, &worst);
@@ -806,8 +807,9 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
     CK(cudaMemcpy(b.data(), c->bounds, (T + 1) * 4, cudaMemcpyDeviceToHost));
     if (what == SPLAT_FETCH_TILE_RANGES) {
         uint32_t* r = (uint32_t*)dst;
+        const size_t t_lo = (size_t)c->lastU.row_begin * c->lastU.tiles_x, t_hi = (size_t)c->lastU.row_end * c->lastU.tiles_x;
         for (size_t t = 0; t < T; ++t) {
-            const bool any = b[t] < b[t + 1];
+            const bool any = t >= t_lo && t < t_hi && b[t] < b[t + 1];      // only the band's bounds were computed
             r[2 * t] = any ? b[t] : 0u; r[2 * t + 1] = any ? b[t + 1] : 0u;
         }
     } else if (what == SPLAT_FETCH_KEYS_SORTED || what == SPLAT_FETCH_VALS_SORTED) {
@@ -817,7 +819,7 @@ int splat_debug_fetch(splat_ctx* c, int what, void* dst, size_t* bytes) {
         std::vector<uint32_t> arr;
         if (D) CK(cudaMemcpy(pr.data(), c->pairs, D * 8, cudaMemcpyDeviceToHost));
         if (D && c->lastU.mode == SPLAT_MODE_LAYER50) { arr.resize(D); CK(cudaMemcpy(arr.data(), c->arrival, D * 4, cudaMemcpyDeviceToHost)); }
-        size_t t = 0;
+        size_t t = (size_t)c->lastU.row_begin * c->lastU.tiles_x;      // the band's first tile: its list starts at pair 0
         for (size_t i = 0; i < D; ++i) {
             while (t < T && b[t + 1] <= i) ++t;
             const uint32_t idx = arr.empty() ? (uint32_t)pr[i] : arr[i];
@@ -915,6 +917,98 @@ int splat_sort_pairs_u64_u32(splat_ctx* c, void* stream, uint64_t* keys, uint32_
 int splat_sort_pairs_u32_u32(splat_ctx* c, void* stream, uint32_t* keys, uint32_t* vals, uint32_t* keys_alt,
                              uint32_t* vals_alt, uint64_t n, int begin_bit, int end_bit, int* result_in_alt) {
     return sort_pairs_impl(c, stream, keys, vals, keys_alt, vals_alt, n, begin_bit, end_bit, 4, result_in_alt);
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------ multi-GPU single frame: tile-row bands + NCCL gather
+// one context per device, each renders a band of tile rows (splat_opts.tile_row_begin / end) into a
+// framebuffer of the full size; the path's one exchange step brings the bands together on rank `dst`. NCCL is taken from
+// the calling process (the symbols are looked up at run time: a host that links NCCL, or PyTorch's bundled copy), so this
+// library has no link-time dependency on it.
+#include <dlfcn.h>
+#include <nccl.h>
+
+extern "C" {
+
+int splat_band_rows(int tiles_y, int world, const double* row_weights, int32_t* bands) {
+    if (tiles_y < 0 || world <= 0 || !bands) ARG_FAIL("splat_band_rows: bad arguments");
+    if (!row_weights) {
+        for (int r = 0; r < world; ++r) { bands[2 * r] = (int32_t)((long long)tiles_y * r / world); bands[2 * r + 1] = (int32_t)((long long)tiles_y * (r + 1) / world); }
+        return SPLAT_OK;
+    }
+    // boundaries that minimise the heaviest band (binary search on the bottleneck), no rank left without a row while rows remain
+    std::vector<double> wt(row_weights, row_weights + tiles_y);
+    double sum = 0.0, mx = 0.0;
+    for (double v : wt) { if (!(v >= 0.0)) ARG_FAIL("splat_band_rows: weights must be non-negative"); sum += v; }
+    const double eps = 1e-9 * (sum > 1.0 ? sum : 1.0) / (tiles_y > 1 ? tiles_y : 1);
+    sum = 0.0;
+    for (double& v : wt) { v += eps; sum += v; if (v > mx) mx = v; }
+    auto cuts = [&](double limit, std::vector<int32_t>& out) {
+        out.clear();
+        int start = 0; double acc = 0.0;
+        for (int i = 0; i < tiles_y; ++i) {
+            if (acc + wt[i] > limit && i > start) { out.push_back(start); out.push_back(i); start = i; acc = 0.0; }
+            acc += wt[i];
+        }
+        out.push_back(start); out.push_back(tiles_y);
+    };
+    double lo = tiles_y ? mx : 0.0, hi = sum;
+    std::vector<int32_t> b;
+    for (int it = 0; it < 60; ++it) {
+        const double mid = 0.5 * (lo + hi);
+        cuts(mid, b);
+        if ((int)b.size() / 2 <= world) hi = mid; else lo = mid;
+    }
+    cuts(hi, b);
+    while ((int)b.size() / 2 < world) {          // more ranks than needed: split the widest band
+        int k = 0;
+        for (int j = 0; j < (int)b.size() / 2; ++j) if (b[2 * j + 1] - b[2 * j] > b[2 * k + 1] - b[2 * k]) k = j;
+        const int32_t s0 = b[2 * k], e0 = b[2 * k + 1];
+        if (e0 - s0 < 2) { b.push_back(tiles_y); b.push_back(tiles_y); continue; }
+        const int32_t m = (s0 + e0) / 2;
+        b[2 * k + 1] = m;
+        b.insert(b.begin() + 2 * k + 2, {m, e0});
+    }
+    std::vector<std::pair<int32_t, int32_t>> srt;
+    for (int j = 0; j < world; ++j) srt.emplace_back(b[2 * j], b[2 * j + 1]);
+    std::sort(srt.begin(), srt.end());
+    for (int j = 0; j < world; ++j) { bands[2 * j] = srt[j].first; bands[2 * j + 1] = srt[j].second; }
+    return SPLAT_OK;
+}
+
+int splat_gather_bands(void* nccl_comm, void* stream, void* fb_dev, const int32_t* pixel_rows, int w, int bytes_per_pixel,
+                       int rank, int world, int dst) {
+    if (!nccl_comm || !fb_dev || !pixel_rows || w <= 0 || bytes_per_pixel <= 0 || world <= 0 || rank < 0 || rank >= world || dst < 0 || dst >= world)
+        ARG_FAIL("splat_gather_bands: bad arguments");
+    if (world == 1) return SPLAT_OK;
+    typedef ncclResult_t (*group_fn)(void);
+    typedef ncclResult_t (*p2p_send_fn)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+    typedef ncclResult_t (*p2p_recv_fn)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+    static group_fn g_start = nullptr, g_end = nullptr; static p2p_send_fn g_send = nullptr; static p2p_recv_fn g_recv = nullptr;
+    if (!g_start) {
+        void* h = RTLD_DEFAULT;
+        if (!dlsym(h, "ncclGroupStart")) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) { g_err = "splat_gather_bands: NCCL is not loaded in this process and libnccl.so.2 was not found"; return SPLAT_ERR_STATE; }
+        g_end = (group_fn)dlsym(h, "ncclGroupEnd"); g_send = (p2p_send_fn)dlsym(h, "ncclSend"); g_recv = (p2p_recv_fn)dlsym(h, "ncclRecv");
+        g_start = (group_fn)dlsym(h, "ncclGroupStart");
+        if (!g_start || !g_end || !g_send || !g_recv) { g_start = nullptr; g_err = "splat_gather_bands: NCCL symbols not found"; return SPLAT_ERR_STATE; }
+    }
+    ncclComm_t comm = (ncclComm_t)nccl_comm; cudaStream_t s = (cudaStream_t)stream;
+    const size_t row_bytes = (size_t)w * bytes_per_pixel;
+    ncclResult_t rc = g_start();
+    if (rank == dst) {
+        for (int r = 0; r < world && rc == ncclSuccess; ++r) {
+            const int32_t a = pixel_rows[2 * r], b = pixel_rows[2 * r + 1];
+            if (r != dst && b > a) rc = g_recv((char*)fb_dev + (size_t)a * row_bytes, (size_t)(b - a) * row_bytes, ncclUint8, r, comm, s);
+        }
+    } else {
+        const int32_t a = pixel_rows[2 * rank], b = pixel_rows[2 * rank + 1];
+        if (b > a && rc == ncclSuccess) rc = g_send((const char*)fb_dev + (size_t)a * row_bytes, (size_t)(b - a) * row_bytes, ncclUint8, dst, comm, s);
+    }
+    const ncclResult_t rc2 = g_end();
+    if (rc != ncclSuccess || rc2 != ncclSuccess) { g_err = "splat_gather_bands: NCCL send / recv failed"; return SPLAT_ERR_CUDA; }
+    return SPLAT_OK;
 }
 
 }  // extern "C"

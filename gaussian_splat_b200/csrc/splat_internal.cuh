@@ -43,7 +43,8 @@ struct FrameCtl {
     unsigned int n_chunks;            // parking chunks handed out by K1 (PARK_CHUNK slots each; counted even beyond the capacity)
     unsigned int n_live_blocks;       // 256-splat blocks that survived block culling (block_cull_kernel)
     unsigned int max_tile_pairs;      // longest tile list (tile_offsets_kernel)
-    unsigned int pad[10];
+    unsigned long long blend_warp_candidates;     // SPLAT_FLAG_COUNT_WORK: (warp, splat) candidates the blend executed
+    unsigned int pad[8];
 };
 static_assert(sizeof(FrameCtl) == 64, "FrameCtl is 64 bytes");
 __host__ __device__ __forceinline__ unsigned int* ctl_tile_count(FrameCtl* c) { return reinterpret_cast<unsigned int*>(c + 1); }
@@ -172,4 +173,4 @@ cudaError_t launch_ply_decode_chunk(const float* rows_dev, unsigned int n_rows, 
 // pairs: the tile lists (u64 per pair, instance index in the low word), depth-ordered (TILE, LAYER50) or instance-ordered
 // (MLAB); arrival: LAYER50's instance-ordered list (u32 per pair). bounds[t] .. bounds[t + 1] = tile t's list.
 void launch_blend(const FrameUniforms& U, const splat_record_row* rec, const unsigned long long* pairs,
-                  const unsigned int* arrival, const unsigned int* bounds, void* fb_half4, cudaStream_t s);
+                  const unsigned int* arrival, const unsigned int* bounds, void* fb_half4, FrameCtl* ctl, bool count_work, cudaStream_t s);

@@ -12,7 +12,10 @@
 class InstancedSplatRenderer::Impl {
 public:
     splat_ctx* ctx = nullptr;
-    splat_opts opts{};
+    // What an unmodified caller gets is what the reference app runs: the 50-layer mode (use50LayerMode = true,
+    // src/instanced_splat_renderer.mm:38) with the shader's literal, descending depth order
+    // (shaders/gaussian_splat_50layer.metal:201).
+    splat_opts opts{SPLAT_MODE_LAYER50, 0, SPLAT_ORDER_REFERENCE, 0, 0, 0, 0, 0};
     std::vector<float> sh_rest;   // [n][45], kept only so a later setOptions(sh_degree > 0) can upload it
     bool sh_uploaded = false;
     bool device_decode = false;
@@ -107,7 +110,12 @@ void InstancedSplatRenderer::render(void* commandBuffer, void* drawableTexture, 
         }
         impl->sh_uploaded = true;
     }
-    const int rc = splat_render(impl->ctx, commandBuffer, drawableTexture, &view.columns[0].x, &proj.columns[0].x,
-                                (int)viewportWidth, (int)viewportHeight, &impl->opts);
+    int rc = splat_render(impl->ctx, commandBuffer, drawableTexture, &view.columns[0].x, &proj.columns[0].x,
+                          (int)viewportWidth, (int)viewportHeight, &impl->opts);
+    // An EARLIER frame overflowed the pair buffers (it was rendered empty): the library has grown them and says so once.
+    // The reference never drops splats (src/instanced_splat_renderer.mm:496-499), so this frame is simply enqueued again.
+    if (rc == SPLAT_ERR_OVERFLOW)
+        rc = splat_render(impl->ctx, commandBuffer, drawableTexture, &view.columns[0].x, &proj.columns[0].x,
+                          (int)viewportWidth, (int)viewportHeight, &impl->opts);
     if (rc != SPLAT_OK) std::cerr << "InstancedSplatRenderer::render: " << splat_last_error_string() << std::endl;
 }

@@ -41,7 +41,8 @@ public:
     int getPointCount() const { return (int)_count; }
 
     // --- additions (no counterpart in the reference) ---
-    // mode / K / depth order / SH degree / tile-row band; defaults = TILE, K 32, near-first, degree 0.
+    // mode / K / depth order / SH degree / tile-row band. Defaults = what the reference app runs: LAYER50, K 50, the
+    // shader's literal (descending) depth order (src/instanced_splat_renderer.mm:38; gaussian_splat_50layer.metal:201).
     void setOptions(const splat_opts& opts);
     // Per-stage ms of the last frame rendered with SPLAT_FLAG_TIMING (synchronises).
     bool stageTimes(float ms[8]);

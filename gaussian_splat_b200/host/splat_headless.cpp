@@ -44,7 +44,7 @@ int main(int argc, char** argv) {
     const char* out = nullptr;
     const char* trace = nullptr;
     SplatDecode decode = SplatDecode::Host;
-    splat_opts opts{};
+    splat_opts opts{};                     // the driver's own default stays TILE / near-first (BASELINE config 2); --mode / --order choose
     opts.flags = SPLAT_FLAG_TIMING;
     for (int a = 2; a + 1 < argc; a += 2) {
         const std::string k = argv[a]; const char* v = argv[a + 1];

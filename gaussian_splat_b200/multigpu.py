@@ -15,47 +15,21 @@ import numpy as np
 
 
 def band_rows(tiles_y: int, world: int, weights: Sequence[float] | None = None) -> List[Tuple[int, int]]:
-    """Split tile rows [0, tiles_y) into `world` contiguous bands [begin, end).
+    """Split tile rows [0, tiles_y) into `world` contiguous bands [begin, end) (the C ABI's splat_band_rows).
 
     weights: per-row cost (e.g. pairs per tile row of a previous frame). Without weights rows are
     split evenly (4K: 135 rows -> 17/17/.../16 at 8 ranks). With weights the boundaries minimise the
     heaviest band (exact, by binary search on the bottleneck), never leaving a rank without a row while
     rows remain."""
+    from . import capi
     if world <= 0 or tiles_y < 0:
         raise ValueError("bad arguments")
-    if weights is None:
-        return [(tiles_y * r // world, tiles_y * (r + 1) // world) for r in range(world)]
-    wt = np.asarray(weights, np.float64)
-    if wt.shape != (tiles_y,) or np.any(wt < 0):
-        raise ValueError("weights must be one non-negative number per tile row")
-    wt = wt + 1e-9 * max(1.0, wt.sum()) / max(1, tiles_y)        # every row costs something: keeps bands non-empty
-
-    def cuts(limit):
-        out, start, acc = [], 0, 0.0
-        for i in range(tiles_y):
-            if acc + wt[i] > limit and i > start:
-                out.append((start, i)); start, acc = i, 0.0
-            acc += wt[i]
-        out.append((start, tiles_y))
-        return out
-
-    lo, hi = float(wt.max()) if tiles_y else 0.0, float(wt.sum())
-    for _ in range(60):
-        mid = 0.5 * (lo + hi)
-        if len(cuts(mid)) <= world:
-            hi = mid
-        else:
-            lo = mid
-    bands = cuts(hi)
-    while len(bands) < world:                                    # more ranks than needed: split the widest band
-        k = max(range(len(bands)), key=lambda j: bands[j][1] - bands[j][0])
-        b, e = bands[k]
-        if e - b < 2:
-            bands.append((tiles_y, tiles_y))
-            continue
-        m = (b + e) // 2
-        bands[k:k + 1] = [(b, m), (m, e)]
-    return sorted(bands)
+    if weights is not None:
+        wt = np.asarray(weights, np.float64)
+        if wt.shape != (tiles_y,) or np.any(wt < 0):
+            raise ValueError("weights must be one non-negative number per tile row")
+        weights = wt
+    return capi.band_rows(tiles_y, world, weights)
 
 
 def reweight_rows(weights: Sequence[float], bands: Sequence[Tuple[int, int]], band_times: Sequence[float],
@@ -88,12 +62,33 @@ def shard_views(n_views: int, rank: int, world: int) -> List[int]:
     return list(range(n_views * rank // world, n_views * (rank + 1) // world))
 
 
+def _nccl_comm_ptr(device):
+    """ncclComm_t of the default process group (PyTorch's ProcessGroupNCCL), or None when the backend is not NCCL."""
+    import torch.distributed as dist
+    try:
+        pg = dist.distributed_c10d._get_default_group()
+        be = pg._get_backend(device)
+        return int(be._comm_ptr())
+    except Exception:      # noqa: BLE001 - gloo (CPU tests) or a PyTorch without the accessor
+        return None
+
+
 def gather_bands(fb, pixel_rows: Sequence[Tuple[int, int]], rank: int, world: int, dst: int = 0):
     """The path's one exchange step: every rank sends its band fb[a:b] to `dst`, which receives each
-    band in place. fb: [H, W, 4] tensor on every rank (same shape). Grouped send/recv (uneven bands)."""
+    band in place. fb: [H, W, C] tensor on every rank (same shape). On CUDA tensors under the nccl backend this is the
+    C ABI's splat_gather_bands (grouped ncclSend / ncclRecv on the current stream, PyTorch's communicator); otherwise
+    (gloo, the CPU tests) torch.distributed's grouped isend / irecv."""
+    import torch
     import torch.distributed as dist
     if world == 1:
         return
+    if fb.is_cuda and dist.get_backend() == "nccl":
+        comm = _nccl_comm_ptr(fb.device)
+        if comm:
+            from . import capi
+            capi.gather_bands(comm, torch.cuda.current_stream(fb.device).cuda_stream, fb.data_ptr(), list(pixel_rows),
+                              fb.shape[1], fb.shape[2] * fb.element_size(), rank, world, dst)
+            return
     ops = []
     if rank == dst:
         for r in range(world):

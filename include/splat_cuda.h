@@ -38,6 +38,8 @@ enum {
 enum {
     SPLAT_FLAG_TIMING = 1,        /* record per-stage CUDA events (adds event overhead)          */
     SPLAT_FLAG_KEEP_UNSORTED = 2, /* keep a copy of the unsorted pairs for splat_debug_fetch      */
+    SPLAT_FLAG_COUNT_WORK = 8,    /* the blend counts the (warp, splat) candidates it executes (splat_status.blend_warp_candidates):
+                                     the work count of the blend's roofline; a slower instantiation, not for timed frames */
     SPLAT_FLAG_HOST_BGRA8 = 4     /* splat_render_host / splat_render_batch_host deliver the frame as the
                                      reference's drawable format, BGRA8Unorm (4 B / pixel, packed on the
                                      device by the splat_pack_bgra8 kernel) instead of half4 (8 B / pixel) */
@@ -82,9 +84,10 @@ typedef struct {
     uint32_t overflow;      /* 1 if the candidate slots exceeded the capacity: the frame was rendered EMPTY, the buffers
                                have been grown; render it again (n_pairs then holds the candidate count)        */
     uint32_t sort_passes;   /* 1: every tile list is sorted once in shared memory                                */
-    uint64_t n_candidates;  /* (splat, tile of its rectangle) slots examined; the pairs are those that pass the tile test */
+    uint64_t n_candidates;  /* parking slots handed out for the pairs (whole chunks of 256: >= n_pairs); what the capacity must hold */
     uint32_t max_tile_pairs;/* longest tile list of the last frame                                              */
-    uint32_t reserved;
+    uint32_t n_live_blocks; /* 256-splat blocks of the scene that survived block culling (of ceil(n_splats / 256)) */
+    uint64_t blend_warp_candidates; /* frames rendered with SPLAT_FLAG_COUNT_WORK: (8x4-pixel warp, splat) tests the blend executed */
 } splat_status;
 
 typedef struct splat_ctx splat_ctx;
@@ -179,6 +182,19 @@ int splat_upload_ply_rows(splat_ctx* ctx, const void* rows_host, uint64_t n_rows
  * byte = rint(clamp(x, 0, 1) * 255), NaN -> 0; bytes in memory B G R A. Device pointers (16- and 8-byte
  * aligned); enqueues on stream. */
 int splat_pack_bgra8(splat_ctx* ctx, void* stream, const void* fb_half4, void* bgra8, int w, int h);
+
+/* Multi-GPU single frame: one context per device, each renders a band of tile rows (splat_opts.tile_row_begin /
+ * tile_row_end) into a framebuffer of the full size; the reference has a single Metal device and no counterpart
+ * (src/instanced_splat_renderer.mm:424-528).
+ * splat_band_rows: contiguous bands [begin, end) of tile rows for `world` ranks into bands[2 * world]; row_weights (one
+ * non-negative cost per tile row, e.g. the pairs per row of a previous frame) or NULL for an even split. The boundaries
+ * minimise the heaviest band.
+ * splat_gather_bands: the path's one exchange step, grouped ncclSend / ncclRecv of the bands' pixel rows
+ * (pixel_rows[2 * world] = [begin, end) per rank, w pixels of bytes_per_pixel each) to rank dst's copy of the framebuffer, on
+ * `stream`. nccl_comm is the caller's ncclComm_t; NCCL itself is looked up in the calling process at run time. */
+int splat_band_rows(int tiles_y, int world, const double* row_weights, int32_t* bands);
+int splat_gather_bands(void* nccl_comm, void* stream, void* fb_dev, const int32_t* pixel_rows, int w, int bytes_per_pixel,
+                       int rank, int world, int dst);
 
 const char* splat_last_error_string(void);
 int splat_version(void);

@@ -54,6 +54,7 @@ def lib():
                      "keys_sorted", "vals_sorted", "tile_ranges"):
             f = getattr(L, "orb_" + name); f.restype = vp; f.argtypes = [vp]
         L.orb_blend.restype = C.c_uint64; L.orb_blend.argtypes = [vp, vp, C.c_int]
+        L.orb_blend_rows.restype = C.c_uint64; L.orb_blend_rows.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int]
         L.orb_look_at.argtypes = [fp, fp, fp, fp]
         L.orb_perspective.argtypes = [C.c_float, C.c_int, C.c_int, C.c_float, C.c_float, fp]
         L.orb_mat4_mul.argtypes = [fp, fp, fp]
@@ -144,11 +145,15 @@ class Frame:
     @property
     def tile_ranges(self): return self._get("tile_ranges", np.uint32, self.T * 2).reshape(-1, 2)
 
-    def blend(self, n_threads=1, fb=None):
-        """Returns (image uint16 [h,w,4] of half bits, number of (pixel,splat) tests)."""
+    def blend(self, n_threads=1, fb=None, rows=None):
+        """Returns (image uint16 [h,w,4] of half bits, number of (pixel,splat) tests). rows = (begin, end): only those
+        tile rows (of the frame's band) are blended, the rest of fb is left as it is."""
         if fb is None:
             fb = np.zeros((self.h, self.w, 4), np.uint16)
-        tests = lib().orb_blend(self._h, fb.ctypes.data, n_threads)
+        if rows is None:
+            tests = lib().orb_blend(self._h, fb.ctypes.data, n_threads)
+        else:
+            tests = lib().orb_blend_rows(self._h, fb.ctypes.data, int(rows[0]), int(rows[1]), n_threads)
         return fb, int(tests)
 
 

@@ -531,11 +531,12 @@ const uint64_t* orb_keys_sorted(const orb_frame* F) { return F->keys_s.data(); }
 const uint32_t* orb_vals_sorted(const orb_frame* F) { return F->vals_s.data(); }
 const uint32_t* orb_tile_ranges(const orb_frame* F) { return F->ranges.data(); }
 
-uint64_t orb_blend(const orb_frame* F, uint16_t* fb, int n_threads) {
-    const int rb = F->U.row_begin, re = F->U.row_end;
+uint64_t orb_blend_rows(const orb_frame* F, uint16_t* fb, int row_begin, int row_end, int n_threads) {
+    const int rb = std::max(row_begin, F->U.row_begin), re = std::min(row_end, F->U.row_end);
     auto blend_rows = [](const orb_frame& f, uint16_t* o, int a, int b) {
         return f.opts.mode == ORB_MODE_MLAB ? blend_rows_mlab(f, o, a, b) : ::blend_rows(f, o, a, b);
     };
+    if (re <= rb) return 0;
     if (n_threads <= 1) return blend_rows(*F, fb, rb, re);
     std::vector<std::thread> th; std::vector<uint64_t> cnt((size_t)n_threads, 0);
     /* interleave rows for balance */
@@ -544,6 +545,10 @@ uint64_t orb_blend(const orb_frame* F, uint16_t* fb, int n_threads) {
     uint64_t tot = 0;
     for (int t = 0; t < n_threads; ++t) { th[t].join(); tot += cnt[t]; }
     return tot;
+}
+
+uint64_t orb_blend(const orb_frame* F, uint16_t* fb, int n_threads) {
+    return orb_blend_rows(F, fb, F->U.row_begin, F->U.row_end, n_threads);
 }
 
 /* src/trackball_camera.mm:136-148 */

@@ -89,6 +89,8 @@ const uint32_t* orb_tile_ranges(const orb_frame*);      /* [T][2] = begin,end   
  * left untouched. n_threads <= 1: the named single-thread baseline; > 1 splits
  * tile rows over std::thread (informational). Returns (pixel,splat) tests done. */
 uint64_t orb_blend(const orb_frame*, uint16_t* fb_half4, int n_threads);
+/* The same for the tile rows [row_begin, row_end) of the frame's band only (full-size spot checks). */
+uint64_t orb_blend_rows(const orb_frame*, uint16_t* fb_half4, int row_begin, int row_end, int n_threads);
 
 /* Host helpers restating the camera and the uniform set-up. */
 void orb_look_at(const float eye[3], const float center[3], const float up[3], float out16[16]);

@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_struct_layouts_match_header():
     assert C.sizeof(capi.SplatOpts) == 32
-    assert C.sizeof(capi.SplatStatus) == 48
+    assert C.sizeof(capi.SplatStatus) == 56
     assert capi.RECORD_DTYPE.itemsize == 48
     # SplatInstance: src/instanced_splat_renderer.h:6-11 = 14 floats, 56 bytes, no padding
     from gaussian_splat_b200 import scene

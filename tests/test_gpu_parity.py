@@ -348,3 +348,55 @@ def test_host_delivery_as_bgra8(gpu_ctx, small_scene):
     one = np.zeros((h, w, 4), np.uint8)
     gpu_ctx.render_host(one.ctypes.data, views[1], projs[1], w, h, capi.make_opts(flags=capi.FLAG_HOST_BGRA8))
     assert np.array_equal(one, want[1])
+
+
+def test_two_contexts_in_one_process(gpu_ctx, small_scene):
+    """SURVEY 8(b) threading row: one context per device, several contexts per process. A second context (on the second
+    device when there is one, else on device 0 again) renders and sorts while the first stays usable; kernels that need
+    more dynamic shared memory than the default set the attribute per device, not once per process."""
+    import torch
+    from gaussian_splat_b200 import capi
+    from oracle import oracle as O
+    dev = 1 if torch.cuda.device_count() > 1 else 0
+    w, h = 320, 200
+    V, P = O.app_camera(w, h)
+    F = O.Frame(small_scene, V, P, w, h)
+    ref, _ = F.blend()
+    other = capi.Context(dev)
+    try:
+        other.upload(small_scene)
+        with torch.cuda.device(dev):
+            fb = torch.zeros((h, w, 4), dtype=torch.float16, device="cuda:%d" % dev)
+            other.render(torch.cuda.current_stream().cuda_stream, fb.data_ptr(), V, P, w, h, capi.make_opts())
+            torch.cuda.synchronize()
+            assert np.array_equal(fb.cpu().numpy().view(np.uint16), ref)
+            n = 100_000
+            k = torch.randint(0, 2 ** 62, (n,), dtype=torch.int64, device="cuda:%d" % dev)
+            v = torch.arange(n, dtype=torch.int32, device="cuda:%d" % dev)
+            ka, va = torch.empty_like(k), torch.empty_like(v)
+            alt = other.sort_pairs(torch.cuda.current_stream().cuda_stream, k.data_ptr(), v.data_ptr(), ka.data_ptr(), va.data_ptr(), n, 0, 64)
+            torch.cuda.synchronize()
+            rk = (ka if alt else k).cpu().numpy()
+            assert np.all(np.diff(rk) >= 0)
+        gpu_ctx.upload(small_scene)
+        got, _ = _render(gpu_ctx, small_scene, V, P, w, h, mode=0)
+        assert np.array_equal(got, ref)
+    finally:
+        other.close()
+
+
+def test_status_reports_block_culling_and_chunks(gpu_ctx, small_scene):
+    """splat_status: live blocks of the Morton-ordered scene (a tile-row band keeps fewer than the whole frame), parking
+    slots >= pairs, the longest tile list."""
+    from gaussian_splat_b200 import capi
+    from oracle import oracle as O
+    w, h = 640, 360
+    V, P = O.app_camera(w, h)
+    gpu_ctx.upload(small_scene)
+    _, full = _render(gpu_ctx, small_scene, V, P, w, h, mode=0)
+    _, band = _render(gpu_ctx, small_scene, V, P, w, h, mode=0, tile_row_begin=2, tile_row_end=5)
+    n_blocks = (len(small_scene) + 255) // 256
+    assert 0 < band.n_live_blocks < full.n_live_blocks <= n_blocks
+    assert full.n_candidates >= full.n_pairs and full.n_candidates % 256 == 0
+    r = gpu_ctx.fetch(capi.FETCH_TILE_RANGES).astype(np.int64)
+    assert band.max_tile_pairs == int((r[:, 1] - r[:, 0]).max())

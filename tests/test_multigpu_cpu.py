@@ -131,3 +131,23 @@ def test_shared_host_frame_composes_bands_without_a_collective(tmp_path):
     for r, (a, b) in enumerate(M.bands_to_pixel_rows(bands, h)):
         assert np.all(fr[a:b] == r + 1)
     assert not os.path.exists(os.path.join("/dev/shm", name))
+
+
+def test_band_rows_c_entry_matches_properties():
+    """splat_band_rows (C ABI): contiguous, covering, heaviest band minimal against brute force on small cases."""
+    import itertools
+    import numpy as np
+    from gaussian_splat_b200 import capi
+    rng = np.random.default_rng(3)
+    for tiles_y, world in ((7, 3), (9, 4), (12, 2), (5, 5), (3, 5)):
+        wt = rng.integers(0, 50, tiles_y).astype(np.float64)
+        bands = capi.band_rows(tiles_y, world, wt)
+        assert len(bands) == world and bands[0][0] == 0 and max(b[1] for b in bands) == tiles_y
+        flat = [x for b in bands if b[1] > b[0] for x in b]
+        assert all(flat[i] <= flat[i + 1] for i in range(len(flat) - 1))
+        assert sum(b[1] - b[0] for b in bands) == tiles_y
+        heaviest = max(wt[a:b].sum() for a, b in bands)
+        best = min(max(wt[a:b].sum() for a, b in zip((0,) + c, c + (tiles_y,)))
+                   for k in range(0, min(world, tiles_y)) for c in itertools.combinations(range(1, tiles_y), k))
+        assert heaviest <= best + 1e-6
+    assert capi.band_rows(135, 8) == [(135 * r // 8, 135 * (r + 1) // 8) for r in range(8)]

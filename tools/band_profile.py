@@ -30,5 +30,5 @@ for (a, b) in [(0, tiles_y)] + list(bands):
             for k, v in ctx.stage_times().items():
                 acc[k] = acc.get(k, 0.0) + v / 20
     st = ctx.status()
-    row = {"rows": [a, b], "pairs": int(st.n_pairs), **{k: round(v * 1e3, 1) for k, v in acc.items()}}
+    row = {"rows": [a, b], "pairs": int(st.n_pairs), "live_blocks": int(st.n_live_blocks), "slots": int(st.n_candidates), "max_list": int(st.max_tile_pairs), **{k: round(v * 1e3, 1) for k, v in acc.items()}}
     out.append(row); print(json.dumps(row))
