@@ -2,11 +2,11 @@
 // instanced quads (src/instanced_splat_renderer.mm:496-499 draw call) and the per-pixel insertion sorts of
 // shaders/gaussian_splat_tile.metal:240-249 / gaussian_splat_50layer.metal:198-206.
 //
-//   (K1)                 every (splat, tile of its rectangle) candidate that passes the D9' tile test bumps its tile's
-//                        counter and is parked (key = depth field << 32 | instance index, tile) - k_preprocess.cu
-//   tile_offsets_kernel  exclusive scan of the T tile counters -> bounds[T + 1] (+ the copy the scatter advances), D,
+//   (K1)                 every (splat, tile of its rectangle) candidate that passes the D9' tile test draws its slot from its
+//                        tile's counter and is parked (key = depth field << 32 | instance index; tile, slot) - k_preprocess.cu
+//   tile_offsets_kernel  exclusive scan of the T tile counters -> bounds[T + 1], D,
 //                        the longest list
-//   scatter_pairs_kernel pairs[cursor[tile]++] = key
+//   scatter_pairs_kernel pairs[bounds[tile] + slot] = key
 //   tile_sort_kernel     one CTA per tile sorts its list on the whole 64-bit pair. Instance indices are unique within a
 //                        list, so the key is total and the result is what a stable sort of instance-ordered pairs on
 //                        tile | depth gives, whatever order the atomics handed the slots out in.
@@ -18,11 +18,11 @@
 
 // bounds[t] = first pair of tile t's list, for the tiles [first, first + count] of the frame's band (the blend and the sort
 // read nothing else). One CTA: a thread owns a contiguous run of counters, read with up to V independent 16-byte loads (one
-// L2 round trip), scanned in registers, written back as vectors. The counter, bounds and cursor arrays are padded to
+// L2 round trip), scanned in registers, written back as vectors. The counter and bounds arrays are padded to
 // 65536 + 8 words; the run starts at `first` rounded down to a vector boundary, counters outside the band count as 0.
 template <int V>      // 16-byte vectors per thread: bands of up to 4096 V - 4 tiles
 __global__ void __launch_bounds__(1024) tile_offsets_kernel(FrameCtl* ctl, unsigned int first, unsigned int count,
-                                                            unsigned int* __restrict__ bounds, unsigned int* __restrict__ cursor)
+                                                            unsigned int* __restrict__ bounds)
 {
     __shared__ unsigned int s_wsum[32], s_wmax[32];
     pdl_prologue();
@@ -67,7 +67,6 @@ __global__ void __launch_bounds__(1024) tile_offsets_kernel(FrameCtl* ctl, unsig
             uint4 o;
             o.x = run; run += v[q].x; o.y = run; run += v[q].y; o.z = run; run += v[q].z; o.w = run; run += v[q].w;
             reinterpret_cast<uint4*>(bounds + mine)[q] = o;
-            reinterpret_cast<uint4*>(cursor + mine)[q] = o;
         }
     if (tid == 0) {
         bounds[end] = total;
@@ -76,66 +75,55 @@ __global__ void __launch_bounds__(1024) tile_offsets_kernel(FrameCtl* ctl, unsig
     }
 }
 
-void launch_tile_offsets(const FrameUniforms& U, FrameCtl* ctl, unsigned int* bounds, unsigned int* cursor, cudaStream_t s)
+void launch_tile_offsets(const FrameUniforms& U, FrameCtl* ctl, unsigned int* bounds, cudaStream_t s)
 {
     const unsigned int first = (unsigned int)(U.row_begin * U.tiles_x), count = (unsigned int)(max(U.row_end - U.row_begin, 0) * U.tiles_x);
     const unsigned int span = first + count - (first & ~3u) + 4u;
-    if (span <= 16384u) launch_pdl(tile_offsets_kernel<4>, dim3(1), dim3(1024), 0, s, ctl, first, count, bounds, cursor);
-    else if (span <= 32768u) launch_pdl(tile_offsets_kernel<8>, dim3(1), dim3(1024), 0, s, ctl, first, count, bounds, cursor);
-    else launch_pdl(tile_offsets_kernel<16>, dim3(1), dim3(1024), 0, s, ctl, first, count, bounds, cursor);
+    if (span <= 16384u) launch_pdl(tile_offsets_kernel<4>, dim3(1), dim3(1024), 0, s, ctl, first, count, bounds);
+    else if (span <= 32768u) launch_pdl(tile_offsets_kernel<8>, dim3(1), dim3(1024), 0, s, ctl, first, count, bounds);
+    else launch_pdl(tile_offsets_kernel<16>, dim3(1), dim3(1024), 0, s, ctl, first, count, bounds);
 }
 
-// A CTA takes four parking chunks at a time, one slot per thread and chunk: the four (tile, key) loads, the four returning
-// atomics on the tiles' cursors and the four stores are independent chains. Thread 0 of CTA 0 also leaves the frame's
+// A CTA takes four parking chunks at a time, one slot per thread and chunk: the (key; tile, slot) loads, the bounds lookups
+// and the stores are four independent chains, no atomics (K1 drew the slots). Thread 0 of CTA 0 also leaves the frame's
 // status in page-locked host memory (the frame number last), where the next entry-point call finds it without a copy.
 struct FrameStatusSlotDev { unsigned long long total_pairs, total_slots; unsigned int overflow, max_tile_pairs, frame_no, pad; };
 __global__ void __launch_bounds__(PARK_CHUNK) scatter_pairs_kernel(const FrameCtl* ctl, const unsigned long long* park_key,
-                                                                   const unsigned int* park_tile, const unsigned int* chunk_fill,
-                                                                   unsigned int* cursor, unsigned long long* __restrict__ pairs,
-                                                                   unsigned long long capacity, volatile FrameStatusSlotDev* slot,
-                                                                   unsigned int frame_no)
+                                                                   const unsigned long long* park_ts, const unsigned int* chunk_fill,
+                                                                   const unsigned int* bounds, unsigned long long* __restrict__ pairs,
+                                                                   volatile FrameStatusSlotDev* slot, unsigned int frame_no)
 {
     pdl_prologue();
     const unsigned int over = __ldcg(&ctl->overflow), n_chunks = __ldcg(&ctl->n_chunks);
-#ifndef SCATTER_NO_STATUS
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         slot->total_pairs = __ldcg(&ctl->total_pairs); slot->total_slots = (unsigned long long)n_chunks * PARK_CHUNK;
         slot->overflow = over; slot->max_tile_pairs = __ldcg(&ctl->max_tile_pairs);
         __threadfence_system();
         slot->frame_no = frame_no;
     }
-#endif
     if (over) return;
     const unsigned int tid = threadIdx.x;
     for (unsigned int c0 = blockIdx.x * 4u; c0 < n_chunks; c0 += gridDim.x * 4u) {
-        unsigned int t[4]; unsigned long long k[4]; bool on[4];
+        unsigned long long ts[4], k[4]; bool on[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) on[q] = c0 + q < n_chunks && tid < __ldcg(chunk_fill + c0 + q);
 #pragma unroll
         for (int q = 0; q < 4; ++q)
-            if (on[q]) { const size_t g = (size_t)(c0 + q) * PARK_CHUNK + tid; t[q] = __ldcg(park_tile + g); k[q] = __ldcg(park_key + g); }
+            if (on[q]) { const size_t g = (size_t)(c0 + q) * PARK_CHUNK + tid; ts[q] = __ldcg(park_ts + g); k[q] = __ldcg(park_key + g); }
         unsigned int pos[4];
 #pragma unroll
-#ifdef SCATTER_NO_ATOMIC
-        for (int q = 0; q < 4; ++q) if (on[q]) pos[q] = (c0 + q) * PARK_CHUNK + tid + (t[q] & 0u);
-#else
-#ifdef CURSOR_STRIDE
-        for (int q = 0; q < 4; ++q) if (on[q]) pos[q] = atomicAdd(cursor + (size_t)t[q] * CURSOR_STRIDE, 1u);
-#else
-        for (int q = 0; q < 4; ++q) if (on[q]) pos[q] = atomicAdd(cursor + t[q], 1u);
-#endif
-#endif
+        for (int q = 0; q < 4; ++q) if (on[q]) pos[q] = __ldcg(bounds + (unsigned int)(ts[q] >> 32)) + (unsigned int)ts[q];
 #pragma unroll
         for (int q = 0; q < 4; ++q) if (on[q]) pairs[pos[q]] = k[q];
     }
 }
 
-void launch_scatter_pairs(const FrameCtl* ctl, const unsigned long long* park_key, const unsigned int* park_tile,
-                          const unsigned int* chunk_fill, unsigned int* cursor, unsigned long long* pairs, unsigned long long capacity,
+void launch_scatter_pairs(const FrameCtl* ctl, const unsigned long long* park_key, const unsigned long long* park_ts,
+                          const unsigned int* chunk_fill, const unsigned int* bounds, unsigned long long* pairs,
                           void* status_slot, unsigned int frame_no, int sm_count, cudaStream_t s)
 {
-    launch_pdl(scatter_pairs_kernel, dim3(sm_count * 8), dim3(PARK_CHUNK), 0, s, ctl, park_key, park_tile, chunk_fill, cursor, pairs,
-               capacity, (volatile FrameStatusSlotDev*)status_slot, frame_no);
+    launch_pdl(scatter_pairs_kernel, dim3(sm_count * 8), dim3(PARK_CHUNK), 0, s, ctl, park_key, park_ts, chunk_fill, bounds, pairs,
+               (volatile FrameStatusSlotDev*)status_slot, frame_no);
 }
 
 // ------------------------------------------------------------------ per-tile sort

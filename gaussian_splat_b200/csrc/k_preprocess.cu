@@ -5,7 +5,7 @@
 
 // ------------------------------------------------------------------ K0: scene order
 // The scene is stored in Morton order of the splat positions (63-bit codes, 21 bits per axis over the bounding box of
-// the finite positions), 256 consecutive splats = one block with an axis-aligned bounding box and its largest scale.
+// the finite positions), SCENE_BLOCK (64) consecutive splats = one block with an axis-aligned bounding box and its largest scale.
 // A frame first culls whole blocks against the view frustum / tile-row band (block_cull_kernel), so K1 touches only
 // the splats of live blocks: a band of eight of the 6M / 4K frame keeps about a fifth of them instead of screening all
 // 6M on every rank. Results do not depend on the order: every pair carries the ORIGINAL instance index (orig[]) and
@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(256) upload_soa_kernel(const float* __restrict
     orig[i] = src;
 }
 
-// Bounds of every block of 256 consecutive (Morton-ordered) splats: lo = (min xyz of the finite positions, largest
+// Bounds of every block of SCENE_BLOCK consecutive (Morton-ordered) splats: lo = (min xyz of the finite positions, largest
 // scale), hi = (max xyz, -). One warp per block. A block without a finite position keeps lo > hi (never visible).
 __global__ void __launch_bounds__(256) block_bounds_kernel(const float4* __restrict__ pos_sx, const float4* __restrict__ syz_op_rg,
                                                            unsigned int n, unsigned int n_blocks, float4* __restrict__ blk_lo, float4* __restrict__ blk_hi)
@@ -101,8 +101,8 @@ __global__ void __launch_bounds__(256) block_bounds_kernel(const float4* __restr
     if (blk >= n_blocks) return;
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY}, sm = 0.0f;
     bool wild = false;          // a non-finite or negative scale: the screening bound cannot be trusted, keep the block
-    for (unsigned int k = lane; k < 256u; k += 32u) {
-        const unsigned int i = blk * 256u + k;
+    for (unsigned int k = lane; k < SCENE_BLOCK; k += 32u) {
+        const unsigned int i = blk * SCENE_BLOCK + k;
         if (i >= n) break;
         const float4 p = pos_sx[i], t = syz_op_rg[i];
         if (isfinite(p.x) && isfinite(p.y) && isfinite(p.z)) {
@@ -153,7 +153,7 @@ void launch_upload_soa(const float* aos_dev, const unsigned int* perm, unsigned 
 {
     if (n == 0) return;
     upload_soa_kernel<<<(n + 255) / 256, 256, 0, s>>>(aos_dev, perm, n, rot, pos_sx, syz_op_rg, b, base_rgb, orig);
-    const unsigned int nb = (n + 255u) / 256u;
+    const unsigned int nb = (n + SCENE_BLOCK - 1u) / SCENE_BLOCK;
     block_bounds_kernel<<<(nb + 7) / 8, 256, 0, s>>>(pos_sx, syz_op_rg, n, nb, blk_lo, blk_hi);
 }
 
@@ -241,44 +241,50 @@ __global__ void __launch_bounds__(256) block_cull_kernel(ScenePlanes sp, const _
     if (keep) live[base + __popc(m & ((1u << lane) - 1u))] = blk;
 }
 
-// K1: a CTA owns four live blocks (1024 splats). (1) Screening, 4 splats per thread with all loads issued first (position
+// K1: a CTA owns 1024 splats = 1024 / SCENE_BLOCK live blocks. (1) Screening, 4 splats per thread with all loads issued first (position
 // / scale planes read coalesced and kept in shared memory for phase 2). (2) The survivors' local indices are compacted in
 // shared memory, so the exactly rounded ~600-instruction pipeline runs on dense warps of survivors (splat order is
 // unrelated to screen position inside a block; without this every warp holding one survivor pays the exact path).
 // (3) A warp takes 32 survivors at a time: record rows are written, then the warp expands its splats' tile rectangles
 // cooperatively - 32 consecutive candidate (splat, tile) slots per step, each lane finding its owner among the warp's
 // 32 rectangles with five shuffles on the running sums and fetching the owner's test parameters with twelve more, all
-// from registers. A candidate that passes the D9' tile test bumps its tile's counter (a fire-and-forget RED) and is
-// parked (key, tile) in the warp's current 256-slot chunk of the parking arrays; chunks are handed out by one global
+// from registers. A candidate that passes the D9' tile test draws its slot in its tile's list from the tile's counter and is
+// parked (key; tile, slot) in the warp's current 256-slot chunk of the parking arrays; chunks are handed out by one global
 // atomic each and their fill is recorded, so the scatter kernel reads only what was written.
 // History: 512-splat CTAs left two warps working while six waited at the barrier; separate screening / exact kernels
 // lost more to the extra launch and the list round trip than they won; round 1's bin words + one-CTA prefix scan +
 // separate duplication kernel (binary search per 32 slots, record gathers, returning atomics) took 40 + 6.5 + 41 us at
 // 1M / 1080p where this kernel takes the 40 us of the first alone.
+#ifndef K1_ITEMS
 #define K1_ITEMS 4
-__global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const __grid_constant__ FrameUniforms U,
+#endif
+#ifndef K1_MIN_CTAS
+#define K1_MIN_CTAS 1
+#endif
+__global__ void __launch_bounds__(256, K1_MIN_CTAS) preprocess_kernel(ScenePlanes sp, const __grid_constant__ FrameUniforms U,
                                                          splat_record_row* __restrict__ rec, FrameCtl* ctl,
                                                          const unsigned int* live, unsigned long long* __restrict__ park_key,
-                                                         unsigned int* __restrict__ park_tile, unsigned int* __restrict__ chunk_fill,
+                                                         unsigned long long* __restrict__ park_ts, unsigned int* __restrict__ chunk_fill,
                                                          unsigned long long capacity)
 {
     constexpr int K1_CTA_SPLATS = 256 * K1_ITEMS;
     __shared__ unsigned short s_list[K1_CTA_SPLATS];
-    __shared__ unsigned int s_count, s_blk[K1_ITEMS];
+    constexpr int K1_BLOCKS = K1_CTA_SPLATS / (int)SCENE_BLOCK;      // live blocks a CTA takes
+    __shared__ unsigned int s_count, s_blk[K1_BLOCKS];
     __shared__ float4 s_p[K1_CTA_SPLATS], s_t[K1_CTA_SPLATS];
     const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     pdl_prologue();
     const unsigned int n_live = __ldcg(&ctl->n_live_blocks);
-    if (blockIdx.x * K1_ITEMS >= n_live) return;
+    if (blockIdx.x * K1_BLOCKS >= n_live) return;
     if (tid == 0) s_count = 0;
-    if (tid < K1_ITEMS) s_blk[tid] = blockIdx.x * K1_ITEMS + tid < n_live ? __ldcg(live + blockIdx.x * K1_ITEMS + tid) : 0xFFFFFFFFu;
+    if (tid < K1_BLOCKS) s_blk[tid] = blockIdx.x * K1_BLOCKS + tid < n_live ? __ldcg(live + blockIdx.x * K1_BLOCKS + tid) : 0xFFFFFFFFu;
     __syncthreads();
     float4 p[K1_ITEMS], t[K1_ITEMS];
     unsigned int idx[K1_ITEMS];
 #pragma unroll
     for (int k = 0; k < K1_ITEMS; ++k) {
-        const unsigned int b = s_blk[k];
-        idx[k] = b == 0xFFFFFFFFu ? 0xFFFFFFFFu : b * 256u + tid;
+        const unsigned int li = k * 256u + tid, b = s_blk[li / SCENE_BLOCK];
+        idx[k] = b == 0xFFFFFFFFu ? 0xFFFFFFFFu : b * SCENE_BLOCK + (li % SCENE_BLOCK);
         if (idx[k] < U.n) { p[k] = __ldg(sp.pos_sx + idx[k]); t[k] = __ldg(sp.syz_op_rg + idx[k]); }
     }
     // ---- phase 1: screen, compact the survivors' local indices (one shared atomic per warp for all its items)
@@ -309,13 +315,14 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
     unsigned int* const tile_count = ctl_tile_count(ctl);
     const bool by_instance = U.mode == SPLAT_MODE_MLAB;       // the only list MLAB walks is in instance order: no depth in the key
     unsigned int chunk = 0xFFFFFFFFu, used = PARK_CHUNK;      // the warp's current parking chunk (none yet) and its fill
+    unsigned int pend_g = 0xFFFFFFFFu, pend_tile = 0, pend_slot = 0;      // (tile, slot) of the previous step, stored one step late
     for (unsigned int j0 = warp * 32u; j0 < n_keep; j0 += 256u) {
         const unsigned int j = j0 + lane;
         unsigned int cnt = 0, o = 0;
         splat_record r;
         float kx = 0.0f, ky = 0.0f;
         if (j < n_keep) {
-            const unsigned int li = s_list[j], i = s_blk[li >> 8] * 256u + (li & 255u);
+            const unsigned int li = s_list[j], i = s_blk[li / SCENE_BLOCK] * SCENE_BLOCK + (li % SCENE_BLOCK);
             const float4 pp = s_p[li], tt = s_t[li];
             const float4 q = __ldg(sp.rot + i);
             const unsigned int bh = (unsigned int)__ldg(sp.b + i);
@@ -392,7 +399,11 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
                 pass = tile_touch(o_cx, o_cy, o_ux, o_uy, o_vx, o_vy, o_kx, o_ky, tx, ty, U.w, U.h);
                 tile = (unsigned int)(ty * U.tiles_x + tx);
             }
+            // the pair's slot in its tile's list: a returning atomic whose result is only stored - one step later, so its
+            // round trip to L2 hides behind the next step's shuffles and tile test
+            const unsigned int slot = pass ? atomicAdd(tile_count + tile, 1u) : 0u;
             const unsigned int m = __ballot_sync(0xFFFFFFFFu, pass);
+            if (pend_g != 0xFFFFFFFFu) { park_ts[pend_g] = ((unsigned long long)pend_tile << 32) | pend_slot; pend_g = 0xFFFFFFFFu; }
             if (!m) continue;
             const unsigned int np = __popc(m);
             if (used + np > PARK_CHUNK) {           // next chunk: the fill of the old one is final
@@ -405,22 +416,23 @@ __global__ void __launch_bounds__(256) preprocess_kernel(ScenePlanes sp, const _
                 if (pass) {
                     const unsigned int g = chunk * PARK_CHUNK + used + __popc(m & ((1u << lane) - 1u));
                     park_key[g] = ((unsigned long long)(o_pk >> 16) << 32) | o_id;
-                    park_tile[g] = tile;
-                    atomicAdd(tile_count + tile, 1u);
+                    pend_g = g; pend_tile = tile; pend_slot = slot;
                 }
             } else if (lane == 0) ctl->overflow = 1u;       // the parking arrays are full: the frame builds no lists
             used += np;
         }
     }
+    if (pend_g != 0xFFFFFFFFu) park_ts[pend_g] = ((unsigned long long)pend_tile << 32) | pend_slot;
     if (chunk != 0xFFFFFFFFu && (unsigned long long)(chunk + 1u) * PARK_CHUNK <= capacity && lane == 0) chunk_fill[chunk] = used;
 }
 
 void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record_row* rec, FrameCtl* ctl, unsigned int* live,
-                       unsigned long long* park_key, unsigned int* park_tile, unsigned int* chunk_fill, unsigned long long capacity,
+                       unsigned long long* park_key, unsigned long long* park_ts, unsigned int* chunk_fill, unsigned long long capacity,
                        cudaStream_t s)
 {
     if (U.n == 0) return;
     launch_pdl(block_cull_kernel, dim3((sp.n_blocks + 255u) / 256u), dim3(256), 0, s, sp, U, ctl, live);
-    launch_pdl(preprocess_kernel, dim3((sp.n_blocks + K1_ITEMS - 1) / K1_ITEMS), dim3(256), 0, s, sp, U, rec, ctl,
-               (const unsigned int*)live, park_key, park_tile, chunk_fill, capacity);
+    const unsigned int per_cta = 256u * K1_ITEMS / SCENE_BLOCK;
+    launch_pdl(preprocess_kernel, dim3((sp.n_blocks + per_cta - 1) / per_cta), dim3(256), 0, s, sp, U, rec, ctl,
+               (const unsigned int*)live, park_key, park_ts, chunk_fill, capacity);
 }

@@ -3,6 +3,7 @@
 // enqueues K1..K5 on the caller's stream without synchronising, as the reference's
 // render() only encodes (src/instanced_splat_renderer.mm:424-528).
 #include "splat_internal.cuh"
+#include <nvtx3/nvToolsExt.h>      // header-only NVTX 3: ranges cost nothing unless a tool is attached
 
 #include <algorithm>
 #include <cstdio>
@@ -31,14 +32,14 @@ __global__ void set_n_sort_kernel(SortCtl* ctl, unsigned int n) { ctl->n_sort = 
 struct FrameSet {
     splat_record_row* rec = nullptr;        // [n_pad] records, indexed by ORIGINAL instance index
     unsigned int* live = nullptr;           // [n_blocks] blocks that survived block culling
-    // parked pairs (K1): park_key / park_tile[cap] in chunks of PARK_CHUNK slots, chunk_fill[cap / PARK_CHUNK];
+    // parked pairs (K1): park_key / park_ts[cap] in chunks of PARK_CHUNK slots, chunk_fill[cap / PARK_CHUNK];
     // tile lists: pairs[cap] (depth field << 32 | instance index, sorted per tile) and LAYER50's instance-ordered copy
     // arrival[cap_arr] (allocated on the first LAYER50 frame)
-    unsigned long long *pairs = nullptr, *park_key = nullptr; unsigned int *park_tile = nullptr, *chunk_fill = nullptr;
+    unsigned long long *pairs = nullptr, *park_key = nullptr, *park_ts = nullptr; unsigned int* chunk_fill = nullptr;
     unsigned long long capacity = 0;
     uint32_t* arrival = nullptr; unsigned long long capacity_arr = 0;
     FrameCtl* ctl = nullptr;                // + tile counters (CTL_BYTES)
-    uint32_t *bounds = nullptr, *cursor = nullptr;      // [65536 + 8]: first pair of every tile's list; the scatter's running copy
+    uint32_t* bounds = nullptr;             // [65536 + 8]: first pair of every tile's list
     cudaStream_t own_stream = nullptr;
 };
 
@@ -94,8 +95,8 @@ static void mat4_mul_host(const float* a, const float* b, float* o) {
 }
 
 static int free_pairs(splat_ctx* c) {
-    cudaFree(c->pairs); cudaFree(c->park_key); cudaFree(c->park_tile); cudaFree(c->chunk_fill); cudaFree(c->arrival);
-    c->pairs = c->park_key = nullptr; c->park_tile = c->chunk_fill = nullptr; c->arrival = nullptr;
+    cudaFree(c->pairs); cudaFree(c->park_key); cudaFree(c->park_ts); cudaFree(c->chunk_fill); cudaFree(c->arrival);
+    c->pairs = c->park_key = c->park_ts = nullptr; c->chunk_fill = nullptr; c->arrival = nullptr;
     c->capacity = 0; c->capacity_arr = 0;
     return 0;
 }
@@ -120,15 +121,14 @@ static int ensure_pairs(splat_ctx* c, unsigned long long cap) {
     CK(cudaDeviceSynchronize());
     free_pairs(c);
     cap = (cap + 4095) / 4096 * 4096;
-    CK(cudaMalloc(&c->pairs, cap * 8)); CK(cudaMalloc(&c->park_key, cap * 8)); CK(cudaMalloc(&c->park_tile, cap * 4));
+    CK(cudaMalloc(&c->pairs, cap * 8)); CK(cudaMalloc(&c->park_key, cap * 8)); CK(cudaMalloc(&c->park_ts, cap * 8));
     CK(cudaMalloc(&c->chunk_fill, cap / PARK_CHUNK * 4));
     c->capacity = cap;
     return 0;
 }
-static int alloc_frame_fixed(splat_ctx* c) {        // control block + tile counters, bounds, cursor of the CURRENT set
+static int alloc_frame_fixed(splat_ctx* c) {        // control block + tile counters and bounds of the CURRENT set
     CK(cudaMalloc(&c->ctl, CTL_BYTES)); CK(cudaMemset(c->ctl, 0, CTL_BYTES));
     CK(cudaMalloc(&c->bounds, (65536 + 8) * 4)); CK(cudaMemset(c->bounds, 0, (65536 + 8) * 4));
-    CK(cudaMalloc(&c->cursor, (size_t)(65536 + 8) * 4 * 32));      // room for padded cursors (tuning variants)
     return 0;
 }
 
@@ -172,7 +172,7 @@ static void free_scene_scratch(splat_ctx* c) {
 static int alloc_scene_scratch(splat_ctx* c, size_t n_pad) {
     CK(cudaMalloc(&c->rec, n_pad * sizeof(splat_record_row)));
     CK(cudaMemset(c->rec, 0, n_pad * sizeof(splat_record_row)));
-    CK(cudaMalloc(&c->live, (n_pad / 256 + 4) * 4));
+    CK(cudaMalloc(&c->live, (n_pad / SCENE_BLOCK + 4) * 4));
     return SPLAT_OK;
 }
 // Releases the second frame set completely (it is rebuilt by the next camera-batch call).
@@ -181,7 +181,7 @@ static void drop_alt(splat_ctx* c) {
     if (!c->alt_ready) return;
     swap_sets(c);
     free_scene_scratch(c); free_pairs(c);
-    cudaFree(c->bounds); cudaFree(c->cursor); cudaFree(c->ctl);
+    cudaFree(c->bounds); cudaFree(c->ctl);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     *static_cast<FrameSet*>(c) = FrameSet{};
     swap_sets(c);
@@ -225,7 +225,7 @@ int splat_destroy(splat_ctx* c) {
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     free_scene(c); free_pairs(c);
-    cudaFree(c->bounds); cudaFree(c->cursor); cudaFree(c->ctl); cudaFree(c->fb_scratch); cudaFree(c->sort_ctl); cudaFree(c->sort_status);
+    cudaFree(c->bounds); cudaFree(c->ctl); cudaFree(c->fb_scratch); cudaFree(c->sort_ctl); cudaFree(c->sort_status);
     cudaFreeHost(c->ctl_host); cudaFreeHost(c->status_ring);
     for (int k = 0; k < 6; ++k) if (c->ev[k]) cudaEventDestroy(c->ev[k]);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -250,7 +250,7 @@ static int install_scene(splat_ctx* c, const float* aos_dev, uint32_t n) {
     const size_t n_pad = ((size_t)n + 1023) / 1024 * 1024;
     CK(cudaMalloc(&c->rot, n_pad * 16)); CK(cudaMalloc(&c->pos_sx, n_pad * 16)); CK(cudaMalloc(&c->syz, n_pad * 16));
     CK(cudaMalloc(&c->bq, n_pad * 2)); CK(cudaMalloc(&c->base_rgb, n_pad * 16)); CK(cudaMalloc(&c->orig, n_pad * 4));
-    c->n_blocks = (uint32_t)((n + 255u) / 256u);
+    c->n_blocks = (uint32_t)((n + SCENE_BLOCK - 1u) / SCENE_BLOCK);
     CK(cudaMalloc(&c->blk_lo, ((size_t)c->n_blocks + 1) * 16)); CK(cudaMalloc(&c->blk_hi, ((size_t)c->n_blocks + 1) * 16));
     { const int rc = alloc_scene_scratch(c, n_pad); if (rc) return rc; }
     static const bool ordered = [] { const char* e = getenv("SPLAT_SCENE_ORDER"); return !(e && e[0] == '0'); }();
@@ -483,18 +483,27 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
     FrameStatusSlot* slot = c->status_ring + (c->frame_no % STATUS_RING);
     if (timed) CK(cudaEventRecord(c->ev[0], s));
     CK(cudaMemsetAsync(c->ctl, 0, sizeof(FrameCtl) + ((size_t)T + 1) * 4, s));       // control block + tile counters
+    // stage labels for Nsight (the reference labels its encoders: src/instanced_splat_renderer.mm:487,504)
+    nvtxRangePushA("splat: K1 block cull + preprocess + candidates");
     if (c->n) {
         ScenePlanes sp{c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->orig, c->blk_lo, c->blk_hi, c->n_blocks, c->sh, c->n_pad};
-        launch_preprocess(sp, U, c->rec, c->ctl, c->live, c->park_key, c->park_tile, c->chunk_fill, c->capacity, s);
+        launch_preprocess(sp, U, c->rec, c->ctl, c->live, c->park_key, c->park_ts, c->chunk_fill, c->capacity, s);
     }
+    nvtxRangePop();
     if (timed) CK(cudaEventRecord(c->ev[1], s));
-    launch_tile_offsets(U, c->ctl, c->bounds, c->cursor, s);
-    if (c->n) launch_scatter_pairs(c->ctl, c->park_key, c->park_tile, c->chunk_fill, c->cursor, c->pairs, c->capacity, slot, c->frame_no, c->sm_count, s);
+    nvtxRangePushA("splat: K2 tile offsets + scatter");
+    launch_tile_offsets(U, c->ctl, c->bounds, s);
+    if (c->n) launch_scatter_pairs(c->ctl, c->park_key, c->park_ts, c->chunk_fill, c->bounds, c->pairs, slot, c->frame_no, c->sm_count, s);
     else { slot->total_pairs = 0; slot->total_slots = 0; slot->overflow = 0; slot->max_tile_pairs = 0; slot->frame_no = c->frame_no; }
+    nvtxRangePop();
     if (timed) CK(cudaEventRecord(c->ev[2], s));
+    nvtxRangePushA("splat: K3 per-tile sort");
     if (c->n) launch_tile_sort(U, c->ctl, c->bounds, c->pairs, c->arrival, s);
+    nvtxRangePop();
     if (timed) { CK(cudaEventRecord(c->ev[3], s)); CK(cudaEventRecord(c->ev[4], s)); }
+    nvtxRangePushA("splat: K5 blend");
     launch_blend(U, c->rec, c->pairs, c->arrival, c->bounds, fb, c->ctl, (flags & SPLAT_FLAG_COUNT_WORK) != 0, s);
+    nvtxRangePop();
     if (timed) CK(cudaEventRecord(c->ev[5], s));
     CK(cudaGetLastError());
     c->lastU = U; c->have_frame = true; c->timed = timed;
@@ -718,16 +727,16 @@ static cudaError_t fetch_parked(splat_ctx* c, std::vector<uint32_t>& tile, std::
     tile.clear(); key.clear();
     if (!nch) return cudaSuccess;
     std::vector<unsigned long long> k(nch * PARK_CHUNK);
-    std::vector<uint32_t> t(nch * PARK_CHUNK), fill(nch);
+    std::vector<unsigned long long> t(nch * PARK_CHUNK); std::vector<uint32_t> fill(nch);
     cudaError_t e = cudaMemcpy(k.data(), c->park_key, k.size() * 8, cudaMemcpyDeviceToHost);
-    if (e == cudaSuccess) e = cudaMemcpy(t.data(), c->park_tile, t.size() * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(t.data(), c->park_ts, t.size() * 8, cudaMemcpyDeviceToHost);
     if (e == cudaSuccess) e = cudaMemcpy(fill.data(), c->chunk_fill, nch * 4, cudaMemcpyDeviceToHost);
     if (e != cudaSuccess) return e;
     std::vector<std::pair<unsigned long long, unsigned long long>> all;      // (instance << 32 | tile, key)
     for (size_t ch = 0; ch < nch; ++ch)
         for (uint32_t q = 0; q < fill[ch] && q < PARK_CHUNK; ++q) {
             const size_t g = ch * PARK_CHUNK + q;
-            all.emplace_back(((k[g] & 0xFFFFFFFFull) << 32) | t[g], k[g]);
+            all.emplace_back(((k[g] & 0xFFFFFFFFull) << 32) | (t[g] >> 32), k[g]);
         }
     std::sort(all.begin(), all.end());
     tile.reserve(all.size()); key.reserve(all.size());

@@ -48,6 +48,9 @@ struct FrameCtl {
 };
 static_assert(sizeof(FrameCtl) == 64, "FrameCtl is 64 bytes");
 __host__ __device__ __forceinline__ unsigned int* ctl_tile_count(FrameCtl* c) { return reinterpret_cast<unsigned int*>(c + 1); }
+#ifndef SCENE_BLOCK
+#define SCENE_BLOCK 64u                 // splats per culling block of the Morton-ordered scene (a power of two, 32 .. 256)
+#endif
 #define PARK_CHUNK 256u               // slots per parking chunk (one warp owns a chunk at a time)
 
 // Control block of the stand-alone radix sort (splat_sort_pairs_*; also sorts the scene's Morton codes at upload).
@@ -143,17 +146,17 @@ void launch_upload_soa(const float* aos_dev, const unsigned int* perm, unsigned 
 void launch_upload_sh(const float* sh_rest45_dev, const unsigned int* perm, unsigned int n, size_t n_pad, float4* planes, cudaStream_t s);
 // K1 (k_preprocess.cu): block culling, then per live block the records (rec[original index]) and the parked candidates.
 void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record_row* rec, FrameCtl* ctl, unsigned int* live,
-                       unsigned long long* park_key, unsigned int* park_tile, unsigned int* chunk_fill, unsigned long long capacity,
+                       unsigned long long* park_key, unsigned long long* park_ts, unsigned int* chunk_fill, unsigned long long capacity,
                        cudaStream_t s);
 // K2 binning (k_bin.cu). K1 parked every (splat, tile) pair that passed the D9' tile test as (key = depth field << 32 |
-// instance index, tile) and counted the pairs per tile. tile_offsets scans the counters into bounds[T + 1] (and a copy,
-// cursor[], that the scatter advances); scatter_pairs moves every parked pair to pairs[cursor[tile]++]; tile_sort sorts
-// every tile's list in shared memory on the whole 64-bit pair: a total order, so the result equals a stable sort of
-// instance-ordered pairs on tile | depth. LAYER50 also gets the list in instance order (arrival).
-void launch_tile_offsets(const FrameUniforms& U, FrameCtl* ctl, unsigned int* bounds, unsigned int* cursor, cudaStream_t s);
+// instance index; tile << 32 | slot in the tile's list) and counted the pairs per tile. tile_offsets scans the counters
+// into bounds[T + 1]; scatter_pairs moves every parked pair to pairs[bounds[tile] + slot]; tile_sort sorts every tile's
+// list in shared memory on the whole 64-bit pair: a total order, so the result equals a stable sort of instance-ordered
+// pairs on tile | depth. LAYER50 also gets the list in instance order (arrival).
+void launch_tile_offsets(const FrameUniforms& U, FrameCtl* ctl, unsigned int* bounds, cudaStream_t s);
 // status_slot: 32 bytes of mapped page-locked memory that receive D / slots used / overflow / longest list and, last, frame_no
-void launch_scatter_pairs(const FrameCtl* ctl, const unsigned long long* park_key, const unsigned int* park_tile,
-                          const unsigned int* chunk_fill, unsigned int* cursor, unsigned long long* pairs, unsigned long long capacity,
+void launch_scatter_pairs(const FrameCtl* ctl, const unsigned long long* park_key, const unsigned long long* park_ts,
+                          const unsigned int* chunk_fill, const unsigned int* bounds, unsigned long long* pairs,
                           void* status_slot, unsigned int frame_no, int sm_count, cudaStream_t s);
 void launch_tile_sort(const FrameUniforms& U, const FrameCtl* ctl, const unsigned int* bounds, unsigned long long* pairs,
                       unsigned int* arrival, cudaStream_t s);

@@ -41,6 +41,25 @@ if A.available("metal"):
         out["ora_" + name + "_image"] = img
         out["ora_" + name + "_arrivals"] = arrivals
         print("oracle-A", name, "arrivals max", arrivals.max())
+    # more of the same for the cases that stress the vertex stage (tests/test_oracle_a_cpu.py has the generators):
+    # an orbit view on a ragged viewport, 20:1 needles seen along an axis, a camera inside the cloud (near-face clipping)
+    import math
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import test_oracle_a_cpu as T
+    small, _ = scene.make_instances(8000, 0x5EED0001)
+    cases = {
+        "orbit": (small, O.app_camera(333, 217, eye=(5.0 * math.sin(2.0 * math.pi * 3 / 8), 2.0, 5.0 * math.cos(2.0 * math.pi * 3 / 8))), 333, 217),
+        "needles": (T.anisotropic_scene(), O.app_camera(480, 270, eye=(0.0, 0.0, 6.0)), 480, 270),
+        "near": (T.near_plane_scene(), O.app_camera(400, 300, eye=(0.05, 0.02, 0.3), target=(0.0, 0.0, -1.0)), 400, 300),
+    }
+    for cname, (ci, (cv, cp), cw, ch) in cases.items():
+        out[f"ora2_{cname}_instances"] = ci; out[f"ora2_{cname}_view"] = cv; out[f"ora2_{cname}_proj"] = cp
+        out[f"ora2_{cname}_wh"] = np.array([cw, ch])
+        for name, mode in (("tile", 0), ("layer50", 1)):
+            img, arrivals = A.render(ci, cv, cp, cw, ch, mode)
+            out[f"ora2_{cname}_{name}_image"] = img
+            out[f"ora2_{cname}_{name}_arrivals"] = arrivals.astype(np.uint8 if arrivals.max() < 256 else np.uint16)
+            print("oracle-A", cname, name, "arrivals max", arrivals.max())
 else:
     raise SystemExit("oracle/_ref/libref_metal.so missing: run `make -C oracle` where /root/reference exists")
 np.savez_compressed(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden_small.npz"), **out)

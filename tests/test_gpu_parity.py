@@ -395,8 +395,32 @@ def test_status_reports_block_culling_and_chunks(gpu_ctx, small_scene):
     gpu_ctx.upload(small_scene)
     _, full = _render(gpu_ctx, small_scene, V, P, w, h, mode=0)
     _, band = _render(gpu_ctx, small_scene, V, P, w, h, mode=0, tile_row_begin=2, tile_row_end=5)
-    n_blocks = (len(small_scene) + 255) // 256
+    n_blocks = (len(small_scene) + 63) // 64               # SCENE_BLOCK = 64 splats per culling block
     assert 0 < band.n_live_blocks < full.n_live_blocks <= n_blocks
     assert full.n_candidates >= full.n_pairs and full.n_candidates % 256 == 0
     r = gpu_ctx.fetch(capi.FETCH_TILE_RANGES).astype(np.int64)
     assert band.max_tile_pairs == int((r[:, 1] - r[:, 0]).max())
+
+
+@pytest.mark.parametrize("case", ["orbit", "needles", "near"])
+@pytest.mark.parametrize("name,mode,K", [("tile", 0, 32), ("layer50", 1, 50)])
+def test_reference_shader_golden_images_vertex_stage_cases(gpu_ctx, case, name, mode, K):
+    """More committed Oracle-A images (tests/golden/make_golden.py): an orbit view on a ragged viewport, 20:1 needles seen
+    along an axis (the |b| <= 1e-8 eigenvector branch, gaussian_splat_tile.metal:76-80), a camera inside the cloud (the
+    clip volume's near face). The CUDA path agrees with the reference's shader statements wherever the list stayed under
+    the cap, and is bit-identical to Oracle-B on the whole frame."""
+    import os
+    from oracle import oracle as O
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "golden_small.npz"))
+    inst, V, P = g[f"ora2_{case}_instances"], g[f"ora2_{case}_view"], g[f"ora2_{case}_proj"]
+    w, h = (int(x) for x in g[f"ora2_{case}_wh"])
+    gpu_ctx.upload(inst)
+    got, _ = _render(gpu_ctx, inst, V, P, w, h, mode=mode, order=1)
+    ref = g[f"ora2_{case}_{name}_image"]; under = g[f"ora2_{case}_{name}_arrivals"] <= K
+    a, b = O.half_bits_to_float(got), O.half_bits_to_float(ref)
+    tol = np.maximum(1.0 / 255.0, 8.0 * np.exp2(np.floor(np.log2(np.maximum(np.maximum(np.abs(a), np.abs(b)), 2.0 ** -14)))) * 2.0 ** -10)
+    bad = (np.abs(a - b) > tol).any(axis=2) & under
+    assert bad.sum() <= max(6, 5e-4 * w * h)                 # coverage ties only (enumerated on the CPU side of the test suite)
+    assert (got == ref).all(axis=2)[under].mean() > 0.9
+    F = O.Frame(inst, V, P, w, h, mode=mode, order=1)
+    assert np.array_equal(got, F.blend()[0])

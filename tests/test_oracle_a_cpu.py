@@ -40,30 +40,97 @@ def _tie_margin(F, px, py):
     return float(m.min()) if m.size else 1e9
 
 
-@pytest.mark.parametrize("mode", [O.MODE_TILE, O.MODE_LAYER50, O.MODE_MLAB])
-def test_oracle_b_matches_reference_shader_text(small_scene, mode):
-    """Same scene, same camera, the shaders' literal descending-depth order. Wherever the per-pixel cap
-    is not hit (D4 differs beyond it by design), images agree to 1/255 or a few half ulps (Oracle-A uses
-    libm expf and barycentric uv, Oracle-B the pinned exp and the closed-form uv), except pixels that sit
+def _compare_a_b(inst, V, P, w, h, mode, min_under_cap=0.99, min_covered=0.5, min_exact=0.97, max_bad=1e-4, tie_tol=1e-4, ulps=4.0):
+    """Oracle-B against the reference's shader statements (Oracle-A), the shaders' literal descending-depth order.
+    Wherever the per-pixel cap is not hit (D4 differs beyond it by design), images agree to 1/255 or a few half ulps
+    (Oracle-A uses libm expf and barycentric uv, Oracle-B the pinned exp and the closed-form uv), except pixels that sit
     on a coverage boundary, which are enumerated and must be demonstrable ties."""
-    w, h = 640, 360
-    V, P = O.app_camera(w, h)
-    img_a, arrivals = A.render(small_scene, V, P, w, h, mode)
-    F = O.Frame(small_scene, V, P, w, h, mode=mode, order=O.ORDER_REFERENCE)
+    img_a, arrivals = A.render(inst, V, P, w, h, mode)
+    F = O.Frame(inst, V, P, w, h, mode=mode, order=O.ORDER_REFERENCE)
     img_b, _ = F.blend()
     a, b = O.half_bits_to_float(img_a), O.half_bits_to_float(img_b)
     K = (1 << 30) if mode == O.MODE_MLAB else A.max_fragments(mode)      # the K-buffer has no cap
     assert mode == O.MODE_MLAB or K == (50 if mode else 32)
     under_cap = arrivals <= K
-    assert under_cap.mean() > 0.99 and (arrivals > 0).mean() > 0.5
-    tol = np.maximum(1.0 / 255.0, 4.0 * _half_ulp(np.maximum(np.abs(a), np.abs(b))))
+    assert under_cap.mean() > min_under_cap and (arrivals > 0).mean() > min_covered
+    tol = np.maximum(1.0 / 255.0, ulps * _half_ulp(np.maximum(np.abs(a), np.abs(b))))
     bad = (np.abs(a - b) > tol).any(axis=2) & under_cap
     ys, xs = np.nonzero(bad)
-    assert len(xs) <= 1e-4 * w * h, f"{len(xs)} pixels differ"
+    assert len(xs) <= max(3, max_bad * w * h), f"{len(xs)} pixels differ"
     for x, y in zip(xs, ys):
-        assert _tie_margin(F, int(x), int(y)) < 1e-4, (x, y)
+        assert _tie_margin(F, int(x), int(y)) < tie_tol, (x, y, _tie_margin(F, int(x), int(y)))
     exact = (img_a == img_b).all(axis=2)[under_cap].mean()
-    assert exact > 0.97, exact            # most pixels are bit-identical
+    assert exact > min_exact, exact            # most pixels are bit-identical
+    return F, arrivals
+
+
+@pytest.mark.parametrize("mode", [O.MODE_TILE, O.MODE_LAYER50, O.MODE_MLAB])
+def test_oracle_b_matches_reference_shader_text(small_scene, mode):
+    _compare_a_b(small_scene, *O.app_camera(640, 360), 640, 360, mode)
+
+
+@pytest.mark.parametrize("k", range(8))
+def test_oracle_b_matches_reference_shader_text_on_orbit_views(small_scene, k):
+    """Eight orbit cameras (config 4's path) on a ragged viewport: the off-axis Jacobian terms with the shader's literal
+    sign (gaussian_splat_tile.metal:122-123) change with the view direction."""
+    w, h = 333, 217
+    t = 2.0 * math.pi * k / 8
+    V, P = O.app_camera(w, h, eye=(5.0 * math.sin(t), 2.0, 5.0 * math.cos(t)))
+    _compare_a_b(small_scene[:8000], V, P, w, h, O.MODE_TILE if k % 2 == 0 else O.MODE_LAYER50)
+
+
+def anisotropic_scene(n=3000, seed=11):
+    """Needles and discs: one scale axis 20x the others, half the splats with an exactly axis-aligned covariance (the
+    |b| <= 1e-8 branch of eigenSym2x2, gaussian_splat_tile.metal:76-80, fires for view-aligned ones)."""
+    from gaussian_splat_b200 import scene
+    inst, _ = scene.make_instances(n, 0x5EED0A15 + seed)
+    rng = np.random.default_rng(seed)
+    inst[:, 4:7] = 0.01
+    axis = rng.integers(0, 3, n)
+    inst[np.arange(n), 4 + axis] = 0.2                       # 20 : 1
+    half = n // 2
+    inst[:half, 0:4] = (1.0, 0.0, 0.0, 0.0)                 # identity rotation
+    inst[:, 7:10] *= 0.5
+    return inst
+
+
+@pytest.mark.parametrize("mode", [O.MODE_TILE, O.MODE_LAYER50])
+def test_oracle_b_matches_reference_shader_text_anisotropic(mode):
+    w, h = 480, 270
+    inst = anisotropic_scene()
+    # a camera looking straight down an axis: axis-aligned splats hit the b == 0 eigenvector branch
+    for eye in ((0.0, 0.0, 6.0), (3.0, 2.0, 4.0)):
+        V, P = O.app_camera(w, h, eye=eye)
+        # a 20 : 1 needle's quad is hundreds of pixels long: Oracle-A's barycentric interpolation of uv across it carries
+        # about 1e-3 in u, so a coverage tie is a pixel within 2e-2 of a boundary here (a handful of pixels at most)
+        _compare_a_b(inst, V, P, w, h, mode, min_covered=0.02, min_exact=0.95, tie_tol=2e-2)
+
+
+def near_plane_scene(n=4000, seed=5):
+    """Splats on both sides of the clip volume's near face (zNDC = 0 at zFront = 2 f n / (f + n) = 0.19998 for the app's
+    projection, src/trackball_camera.mm:150-163) and of zFront = 1e-4 (gaussian_splat_tile.metal:104), seen from a camera
+    placed inside the cloud."""
+    from gaussian_splat_b200 import scene
+    inst, _ = scene.make_instances(n, 0x5EED0BEE + seed)
+    rng = np.random.default_rng(seed)
+    inst[:, 7:10] = rng.uniform(-0.6, 0.6, (n, 3)).astype(np.float32)
+    inst[:, 4:7] = rng.uniform(0.004, 0.03, (n, 3)).astype(np.float32)
+    return inst
+
+
+@pytest.mark.parametrize("mode", [O.MODE_TILE, O.MODE_LAYER50])
+def test_oracle_b_matches_reference_shader_text_across_the_near_plane(mode):
+    w, h = 400, 300
+    inst = near_plane_scene()
+    V, P = O.app_camera(w, h, eye=(0.05, 0.02, 0.3), target=(0.0, 0.0, -1.0))
+    # every pixel sums 10-30 fragments here and LAYER50's un-premultiplied colour sums reach 3-5: libm expf against the
+    # pinned exp moves single half roundings, which add up to a few ulps of the sum (8 allowed instead of 4)
+    F, _ = _compare_a_b(inst, V, P, w, h, mode, min_under_cap=0.9, min_covered=0.3, min_exact=0.9, max_bad=5e-4, ulps=8.0)
+    z = F.records["z_front"][F.tiles_touched > 0]
+    assert z.min() < 0.25 and (z > 0.19).all()                # kept splats hug the near face; nothing in front of it survives
+    # and the cull really bites: many splats have 1e-4 <= zFront < 0.19998 (dropped by the clip volume, not by zFront)
+    vz = -(inst[:, 7:10] @ V.reshape(4, 4).T[:3, 2] + V[14])
+    assert ((vz > 1e-4) & (vz < 0.19)).sum() > 100 and (vz < 1e-4).sum() > 100
 
 
 def test_reference_camera_matches_restatements_bitwise():
