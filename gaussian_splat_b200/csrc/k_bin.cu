@@ -84,8 +84,9 @@ void launch_tile_offsets(const FrameUniforms& U, FrameCtl* ctl, unsigned int* bo
     else launch_pdl(tile_offsets_kernel<16>, dim3(1), dim3(1024), 0, s, ctl, first, count, bounds);
 }
 
-// A CTA takes four parking chunks at a time, one slot per thread and chunk: the (key; tile, slot) loads, the bounds lookups
-// and the stores are four independent chains, no atomics (K1 drew the slots). Thread 0 of CTA 0 also leaves the frame's
+#define SCATTER_WAYS 8
+// A CTA takes eight parking chunks at a time, one slot per thread and chunk: the (key; tile, slot) loads, the bounds lookups
+// and the stores are eight independent chains, no atomics (K1 drew the slots). Thread 0 of CTA 0 also leaves the frame's
 // status in page-locked host memory (the frame number last), where the next entry-point call finds it without a copy.
 struct FrameStatusSlotDev { unsigned long long total_pairs, total_slots; unsigned int overflow, max_tile_pairs, frame_no, pad; };
 __global__ void __launch_bounds__(PARK_CHUNK) scatter_pairs_kernel(const FrameCtl* ctl, const unsigned long long* park_key,
@@ -103,18 +104,18 @@ __global__ void __launch_bounds__(PARK_CHUNK) scatter_pairs_kernel(const FrameCt
     }
     if (over) return;
     const unsigned int tid = threadIdx.x;
-    for (unsigned int c0 = blockIdx.x * 4u; c0 < n_chunks; c0 += gridDim.x * 4u) {
-        unsigned long long ts[4], k[4]; bool on[4];
+    for (unsigned int c0 = blockIdx.x * SCATTER_WAYS; c0 < n_chunks; c0 += gridDim.x * SCATTER_WAYS) {
+        unsigned long long ts[SCATTER_WAYS], k[SCATTER_WAYS]; bool on[SCATTER_WAYS];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) on[q] = c0 + q < n_chunks && tid < __ldcg(chunk_fill + c0 + q);
+        for (int q = 0; q < SCATTER_WAYS; ++q) on[q] = c0 + q < n_chunks && tid < __ldcg(chunk_fill + c0 + q);
 #pragma unroll
-        for (int q = 0; q < 4; ++q)
+        for (int q = 0; q < SCATTER_WAYS; ++q)
             if (on[q]) { const size_t g = (size_t)(c0 + q) * PARK_CHUNK + tid; ts[q] = __ldcg(park_ts + g); k[q] = __ldcg(park_key + g); }
-        unsigned int pos[4];
+        unsigned int pos[SCATTER_WAYS];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) if (on[q]) pos[q] = __ldcg(bounds + (unsigned int)(ts[q] >> 32)) + (unsigned int)ts[q];
+        for (int q = 0; q < SCATTER_WAYS; ++q) if (on[q]) pos[q] = __ldcg(bounds + (unsigned int)(ts[q] >> 32)) + (unsigned int)ts[q];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) if (on[q]) pairs[pos[q]] = k[q];
+        for (int q = 0; q < SCATTER_WAYS; ++q) if (on[q]) pairs[pos[q]] = k[q];
     }
 }
 
