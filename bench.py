@@ -295,12 +295,12 @@ def c3_bands_leg(ctx, torch, dist, args, dev, rank, world, steps, sh_degree=0, e
                    "stage_us": {k: round(v * 1e3, 1) for k, v in acc.items()}, "pairs_D": int(st_full.n_pairs)}
     dist.barrier()
 
-    # ---- bands: boundaries balanced on the pairs per tile row, then three rounds of measured-time balancing (untimed
+    # ---- bands: boundaries balanced on the pairs per tile row, then six rounds of measured-time balancing (untimed
     # set-up: pairs are not the cost, rows of large near splats blend slower per pair)
     band_list = multigpu.band_rows(tiles_y, world, None if even_bands else row_pairs)
     if not even_bands:
         wts = row_pairs.astype(np.float64)
-        for _ in range(3):
+        for _ in range(6):
             a, b = band_list[rank]
             o = capi.make_opts(mode=mode, sh_degree=sh_degree, tile_row_begin=a, tile_row_end=b, flags=capi.FLAG_TIMING)
             acc = []
@@ -428,7 +428,7 @@ def c3_bands_leg(ctx, torch, dist, args, dev, rank, world, steps, sh_degree=0, e
         "workload": name, "n_gaussians": n, "width": w, "height": h, "mode": "TILE", "parallelism": "bands%d+nccl_gather" % world,
         "frames_per_s": fps, "ms_per_frame": ms_per_frame, "steps": steps,
         "frames_per_s_1gpu": None, "speedup": None, "one_gpu": None,
-        "bands": band_list, "band_balance": "even" if even_bands else "pairs per tile row, then 3 rounds of measured-time balancing",
+        "bands": band_list, "band_balance": "even" if even_bands else "pairs per tile row, then 6 rounds of measured-time balancing",
         "per_rank": everyone, "slowest_rank_stage_us": slow["stage_us"], "gather_us": max(d["gather_us"] for d in everyone),
         "gather_bytes_per_frame": w * h * 8,
         "e2e_frames_per_s": e2e_fps, "e2e_steps": e2e_steps, "e2e_d2h_bytes_per_step_per_rank": (rows_px[rank][1] - rows_px[rank][0]) * w * 8,
