@@ -17,6 +17,7 @@ LIB_PATH = os.environ.get("SPLAT_CUDA_LIB") or os.path.join(_HERE, "libsplat_cud
 MODE_TILE, MODE_LAYER50, MODE_MLAB = 0, 1, 2
 ORDER_NEAR_FIRST, ORDER_REFERENCE = 0, 1
 FLAG_TIMING, FLAG_KEEP_UNSORTED, FLAG_HOST_BGRA8, FLAG_COUNT_WORK = 1, 2, 4, 8
+STATIC_SORT_MAX_PAIRS = 2097152      # splat_cuda.h: SPLAT_STATIC_SORT_MAX_PAIRS
 (FETCH_RECORDS, FETCH_TILES_TOUCHED, FETCH_OFFSETS, FETCH_KEYS_UNSORTED, FETCH_VALS_UNSORTED,
  FETCH_KEYS_SORTED, FETCH_VALS_SORTED, FETCH_TILE_RANGES, FETCH_DIGIT_HISTOGRAMS, FETCH_INSTANCES,
  FETCH_SH_REST) = range(11)
@@ -30,7 +31,7 @@ EXPORTS = [
     "splat_create", "splat_destroy", "splat_upload", "splat_upload_sh", "splat_render",
     "splat_render_host", "splat_render_batch", "splat_render_batch_host", "splat_pack_bgra8", "splat_upload_ply_rows", "splat_frame_status", "splat_debug_fetch",
     "splat_stage_times", "splat_sort_pairs_u64_u32", "splat_sort_pairs_u32_u32", "splat_last_error_string", "splat_version",
-    "splat_band_rows", "splat_gather_bands",
+    "splat_band_rows", "splat_gather_bands", "splat_sort_pairs_u64_u32_static",
 ]
 
 
@@ -77,6 +78,7 @@ def lib():
         L.splat_sort_pairs_u64_u32.argtypes = [vp, vp, vp, vp, vp, vp, C.c_uint64, C.c_int, C.c_int,
                                                C.POINTER(C.c_int)]
         L.splat_sort_pairs_u32_u32.argtypes = L.splat_sort_pairs_u64_u32.argtypes
+        L.splat_sort_pairs_u64_u32_static.argtypes = [vp, vp, vp, vp, vp, C.c_uint64, C.c_int, C.c_int, C.POINTER(C.c_int)]
         L.splat_band_rows.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int32)]
         L.splat_gather_bands.argtypes = [vp, vp, vp, C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
         L.splat_last_error_string.restype = C.c_char_p

@@ -12,6 +12,8 @@
 #include <vector>
 
 static thread_local std::string g_err;
+// for entry points that live in other files (sort_static.cu): sets this thread's splat_last_error_string()
+void splat_set_last_error(const char* msg) { g_err = msg ? msg : ""; }
 
 #define CK(call)                                                                          \
     do {                                                                                  \

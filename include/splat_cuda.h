@@ -164,6 +164,18 @@ int splat_sort_pairs_u32_u32(splat_ctx* ctx, void* stream, uint32_t* keys, uint3
                              uint32_t* keys_alt, uint32_t* vals_alt, uint64_t n,
                              int begin_bit, int end_bit, int* result_in_alt);
 
+/* The (uint64 key, uint32 value) sort for callers that cannot allocate: code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc. NO COUNTERPART IN THE REFERENCE.
+ * Same kernels and same result as splat_sort_pairs_u64_u32, but it takes no context and calls no cudaMalloc / cudaFree /
+ * allocating routine: its scratch (digit histograms, tickets, lookback words) is one fixed array in device memory, about
+ * 1 MiB, that every GPU loading this library holds until the process exits. It runs on the CURRENT device (the one `stream`
+ * belongs to). n above SPLAT_STATIC_SORT_MAX_PAIRS is refused with SPLAT_ERR_ARG (splat_last_error_string() says why). Every
+ * call on a device shares that array (it is cleared on `stream` at the start of each call): calls whose work overlaps on
+ * the same GPU - two streams, two threads - race; calls on one stream are safe back to back. */
+#define SPLAT_STATIC_SORT_MAX_PAIRS 2097152
+int splat_sort_pairs_u64_u32_static(void* stream, uint64_t* keys, uint32_t* vals, uint64_t* keys_alt, uint32_t* vals_alt,
+                                    uint64_t n, int begin_bit, int end_bit, int* result_in_alt);
+
 /* GPU-side PLY vertex decode (the step before the path): `rows_host` is the binary body of a PLY vertex
  * element, n_rows rows of stride_floats 4-byte little-endian floats (the reference reads every property as
  * a float, src/ply_loader.cpp:104-110). slot_dst[j] says where the j-th property goes in the reference's
