@@ -16,15 +16,17 @@
 // twice and read twice, and the sort runs on T independent lists of a few hundred pairs.
 #include "splat_math.cuh"
 
+#define TILE_CLASSES 24u        // list-length classes of the tile order: 0 = empty, c = lists of 2^(c-1) .. 2^c - 1 pairs
+
 // bounds[t] = first pair of tile t's list, for the tiles [first, first + count] of the frame's band (the blend and the sort
 // read nothing else). One CTA: a thread owns a contiguous run of counters, read with up to V independent 16-byte loads (one
 // L2 round trip), scanned in registers, written back as vectors. The counter and bounds arrays are padded to
 // 65536 + 8 words; the run starts at `first` rounded down to a vector boundary, counters outside the band count as 0.
 template <int V>      // 16-byte vectors per thread: bands of up to 4096 V - 4 tiles
 __global__ void __launch_bounds__(1024) tile_offsets_kernel(FrameCtl* ctl, unsigned int first, unsigned int count,
-                                                            unsigned int* __restrict__ bounds)
+                                                            unsigned int* __restrict__ bounds, unsigned int* __restrict__ order)
 {
-    __shared__ unsigned int s_wsum[32], s_wmax[32];
+    __shared__ unsigned int s_wsum[32], s_wmax[32], s_cls[TILE_CLASSES];
     pdl_prologue();
     const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned int* tile_count = ctl_tile_count(ctl);
@@ -73,15 +75,47 @@ __global__ void __launch_bounds__(1024) tile_offsets_kernel(FrameCtl* ctl, unsig
         ctl->total_pairs = total;
         ctl->max_tile_pairs = mx;
     }
+    // order[0 .. count): the band's tiles, longest lists first (classes of list length, one per power of two; the order inside
+    // a class is whatever the shared-memory atomics give - nothing depends on it). The sort and the blend take their tiles in
+    // this order: in row-major order the long lists of a dense screen region started late and were each kernel's tail
+    // (a band of eight of the 6M / 4K frame: sort 34 .. 79 us for the same number of pairs).
+    if (tid < TILE_CLASSES) s_cls[tid] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < V; ++q)
+        if ((unsigned)q < per4) {
+            const unsigned int* e = &v[q].x;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const unsigned int t = mine + 4u * q + k;
+                if (t >= first && t < end) atomicAdd(&s_cls[min(32u - (unsigned int)__clz(e[k]), TILE_CLASSES - 1u)], 1u);
+            }
+        }
+    __syncthreads();
+    if (tid == 0) {           // class c starts after every longer class
+        unsigned int run2 = 0;
+        for (int c = TILE_CLASSES - 1; c >= 0; --c) { const unsigned int x = s_cls[c]; s_cls[c] = run2; run2 += x; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < V; ++q)
+        if ((unsigned)q < per4) {
+            const unsigned int* e = &v[q].x;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const unsigned int t = mine + 4u * q + k;
+                if (t >= first && t < end) order[atomicAdd(&s_cls[min(32u - (unsigned int)__clz(e[k]), TILE_CLASSES - 1u)], 1u)] = t;
+            }
+        }
 }
 
-void launch_tile_offsets(const FrameUniforms& U, FrameCtl* ctl, unsigned int* bounds, cudaStream_t s)
+void launch_tile_offsets(const FrameUniforms& U, FrameCtl* ctl, unsigned int* bounds, unsigned int* order, cudaStream_t s)
 {
     const unsigned int first = (unsigned int)(U.row_begin * U.tiles_x), count = (unsigned int)(max(U.row_end - U.row_begin, 0) * U.tiles_x);
     const unsigned int span = first + count - (first & ~3u) + 4u;
-    if (span <= 16384u) launch_pdl(tile_offsets_kernel<4>, dim3(1), dim3(1024), 0, s, ctl, first, count, bounds);
-    else if (span <= 32768u) launch_pdl(tile_offsets_kernel<8>, dim3(1), dim3(1024), 0, s, ctl, first, count, bounds);
-    else launch_pdl(tile_offsets_kernel<16>, dim3(1), dim3(1024), 0, s, ctl, first, count, bounds);
+    if (span <= 16384u) launch_pdl(tile_offsets_kernel<4>, dim3(1), dim3(1024), 0, s, ctl, first, count, bounds, order);
+    else if (span <= 32768u) launch_pdl(tile_offsets_kernel<8>, dim3(1), dim3(1024), 0, s, ctl, first, count, bounds, order);
+    else launch_pdl(tile_offsets_kernel<16>, dim3(1), dim3(1024), 0, s, ctl, first, count, bounds, order);
 }
 
 #define SCATTER_WAYS 8
@@ -129,114 +163,151 @@ void launch_scatter_pairs(const FrameCtl* ctl, const unsigned long long* park_ke
 
 // ------------------------------------------------------------------ per-tile sort
 #define TS_THREADS 128
-#define TS_MAX_E 16                                   // pairs per thread: lists of up to 2048 pairs are sorted in registers
-#define TS_CHUNK (TS_THREADS * TS_MAX_E)              // pairs the shared buffer holds
+#define TS_MAX_E 16                                   // keys per thread: lists of up to 2048 pairs are sorted in registers
+#define TS_CHUNK (TS_THREADS * TS_MAX_E)              // pairs the shared buffers hold
+#define TS_MAX_RUN 48u                                // longest run of equal half depths the tie fix-up walks (else: 64-bit network)
 #define SENTINEL 0xFFFFFFFFFFFFFFFFull
 
-// Bitonic network over P = 128 E keys, key i = e * 128 + tid held by thread tid in x[e]: partners at distance >= 128 sit
-// in the same thread (registers), at distance 32 and 64 in another warp (exchanged through shared memory), below that in
-// the same warp (shuffles). Position i keeps the smaller key when bit j of i is clear in an ascending block.
+// Bitonic network over P = 128 E keys of type T, key i = e * 128 + tid held by thread tid in x[e]: partners at distance >= 128
+// sit in the same thread (registers), at distance 32 and 64 in another warp (exchanged through shared memory), below that in
+// the same warp (shuffles). Position i keeps the smaller key when bit j of i is clear in an ascending block (bit k of i
+// clear). Every loop unrolls: register indices, strides and direction bits are compile-time constants.
 __device__ __forceinline__ unsigned long long shfl_xor64(unsigned long long v, int m) {
     const unsigned int lo = __shfl_xor_sync(0xFFFFFFFFu, (unsigned int)v, m), hi = __shfl_xor_sync(0xFFFFFFFFu, (unsigned int)(v >> 32), m);
     return ((unsigned long long)hi << 32) | lo;
 }
-template <int E>
-__device__ __forceinline__ void exchange_stage(unsigned long long (&x)[E], unsigned long long* s_x, unsigned int tid, int j, int k) {
-    // partner in another warp: through shared memory
+__device__ __forceinline__ unsigned long long shfl_xor_key(unsigned long long v, int m) { return shfl_xor64(v, m); }
+__device__ __forceinline__ unsigned int shfl_xor_key(unsigned int v, int m) { return __shfl_xor_sync(0xFFFFFFFFu, v, m); }
+
+// One level (block size K) of the network: its stages j = K/2 .. 1. A template parameter per level keeps every unrolled loop
+// small (at most 11 stages x 16 keys); one nested loop over all 66 stages of a 2048-key network was not unrolled and left
+// the keys in local memory.
+template <typename T, int E, int K>
+__device__ __forceinline__ void bitonic_level(T (&x)[E], T* s_x, unsigned int tid) {
+    constexpr int W = TS_THREADS;
 #pragma unroll
-    for (int e = 0; e < E; ++e) s_x[e * TS_THREADS + tid] = x[e];
-    __syncthreads();
+    for (int j = K >> 1; j >= 1; j >>= 1) {
+        if (j >= W) {
+            // partner e ^ (j / W) in the same thread; bits of i at and above W come from e alone
 #pragma unroll
-    for (int e = 0; e < E; ++e) {
-        const unsigned int i = e * TS_THREADS + tid;
-        const unsigned long long p = s_x[i ^ j];
-        const bool keep_min = ((i & j) == 0) == ((i & k) == 0);
-        x[e] = (keep_min == (x[e] < p)) ? x[e] : p;
-    }
-    __syncthreads();
-}
-template <int E>
-__device__ __forceinline__ void shuffle_stage(unsigned long long (&x)[E], unsigned int tid, int j, int k) {
+            for (int e = 0; e < E; ++e)
+                if ((e & (j / W)) == 0) {
+                    const bool asc = ((e * W) & K) == 0;
+                    const T a = x[e], b = x[e | (j / W)];
+                    const bool sw = (a > b) == asc;
+                    x[e] = sw ? b : a; x[e | (j / W)] = sw ? a : b;
+                }
+        } else if (j >= 32) {
 #pragma unroll
-    for (int e = 0; e < E; ++e) {
-        const unsigned int i = e * TS_THREADS + tid;
-        const unsigned long long p = shfl_xor64(x[e], j);
-        const bool keep_min = ((i & j) == 0) == ((i & k) == 0);
-        x[e] = (keep_min == (x[e] < p)) ? x[e] : p;
-    }
-}
-template <int E, int JE>
-__device__ __forceinline__ void register_stage(unsigned long long (&x)[E], int k) {
-    // partner e ^ JE in the same thread; bits of i at and above 128 come from e alone
+            for (int e = 0; e < E; ++e) s_x[e * W + tid] = x[e];
+            __syncthreads();
 #pragma unroll
-    for (int e = 0; e < E; ++e) {
-        if ((e & JE) == 0) {
-            const bool asc = ((e * TS_THREADS) & k) == 0;
-            const unsigned long long a = x[e], b = x[e | JE];
-            const bool sw = (a > b) == asc;
-            x[e] = sw ? b : a; x[e | JE] = sw ? a : b;
+            for (int e = 0; e < E; ++e) {
+                const unsigned int i = e * W + tid;
+                const T p = s_x[i ^ j];
+                const bool keep_min = ((i & j) == 0) == ((i & K) == 0);
+                x[e] = (keep_min == (x[e] < p)) ? x[e] : p;
+            }
+            __syncthreads();
+        } else {
+#pragma unroll
+            for (int e = 0; e < E; ++e) {
+                const unsigned int i = e * W + tid;
+                const T p = shfl_xor_key(x[e], j);
+                const bool keep_min = ((i & j) == 0) == ((i & K) == 0);
+                x[e] = (keep_min == (x[e] < p)) ? x[e] : p;
+            }
         }
     }
 }
-template <int E, int JE>
-struct RegisterStages {
-    static __device__ __forceinline__ void run(unsigned long long (&x)[E], int k) {
-        register_stage<E, JE>(x, k);
-        RegisterStages<E, JE / 2>::run(x, k);
+template <typename T, int E, int K>
+struct BitonicLevels {
+    static __device__ __forceinline__ void run(T (&x)[E], T* s_x, unsigned int tid) {
+        BitonicLevels<T, E, K / 2>::run(x, s_x, tid);
+        bitonic_level<T, E, K>(x, s_x, tid);
     }
 };
-template <int E>
-struct RegisterStages<E, 0> { static __device__ __forceinline__ void run(unsigned long long (&)[E], int) {} };
+template <typename T, int E>
+struct BitonicLevels<T, E, 1> { static __device__ __forceinline__ void run(T (&)[E], T*, unsigned int) {} };
 
-template <int E, int M>     // level k = 128 << M (M = 1 .. log2 E): register stages 64 << M .. 128, then the tail
-struct UpperLevels {
-    static __device__ __forceinline__ void run(unsigned long long (&x)[E], unsigned long long* s_x, unsigned int tid) {
-        UpperLevels<E, M - 1>::run(x, s_x, tid);
-        constexpr int k = TS_THREADS << M;
-        if constexpr (k <= E * TS_THREADS) {
-            RegisterStages<E, (k / 2) / TS_THREADS>::run(x, k);
-            exchange_stage<E>(x, s_x, tid, 64, k);
-            exchange_stage<E>(x, s_x, tid, 32, k);
-#pragma unroll
-            for (int j = 16; j >= 1; j >>= 1) shuffle_stage<E>(x, tid, j, k);
-        }
-    }
-};
-template <int E>
-struct UpperLevels<E, 0> { static __device__ __forceinline__ void run(unsigned long long (&)[E], unsigned long long*, unsigned int) {} };
-
-template <int E>
-__device__ __forceinline__ void bitonic_sort_regs(unsigned long long (&x)[E], unsigned long long* s_x, unsigned int tid) {
-#pragma unroll
-    for (int k = 2; k <= 32; k <<= 1)
-#pragma unroll
-        for (int j = k >> 1; j >= 1; j >>= 1) shuffle_stage<E>(x, tid, j, k);
-    exchange_stage<E>(x, s_x, tid, 32, 64);
-#pragma unroll
-    for (int j = 16; j >= 1; j >>= 1) shuffle_stage<E>(x, tid, j, 64);
-    exchange_stage<E>(x, s_x, tid, 64, 128);
-    exchange_stage<E>(x, s_x, tid, 32, 128);
-#pragma unroll
-    for (int j = 16; j >= 1; j >>= 1) shuffle_stage<E>(x, tid, j, 128);
-    UpperLevels<E, 4>::run(x, s_x, tid);        // levels 256 .. 2048, those beyond 128 E compiled out
+template <typename T, int E>
+__device__ __forceinline__ void bitonic_sort_regs(T (&x)[E], T* s_x, unsigned int tid) {
+    BitonicLevels<T, E, E * TS_THREADS>::run(x, s_x, tid);
 }
 
+// One tile list of 33 .. 128 E pairs. The network runs on 32-bit keys, half the instructions of the 64-bit pairs:
+//   depth order   key = half-depth field << 16 | position in the unsorted list. Equal half depths (a few per list: a half has
+//                 ~3000 distinct values over a scene's depth range) then sit together in arbitrary order; every element walks
+//                 its run of equal depths, counts the members with a smaller instance index and takes that place in the run:
+//                 exactly the order of the 64-bit key depth << 32 | instance index. A list with a run longer than
+//                 TS_MAX_RUN (a wall of splats at one depth) is sorted once more by the 64-bit network instead.
+//   MLAB          pairs carry no depth: the key is the instance index itself.
+//   LAYER50       also wants the list in instance (= arrival) order: a second run on the instance indices.
 template <int E>
-__device__ __forceinline__ void sort_list_regs(unsigned long long* seg, unsigned int* arrival, unsigned int len, bool layer,
-                                               unsigned long long* s_x, unsigned int tid) {
-    unsigned long long x[E];
+__device__ __forceinline__ void sort_list_fast(unsigned long long* seg, unsigned int* arrival, unsigned int len, bool by_instance,
+                                               bool layer, unsigned long long* s_pairs, unsigned int* s_k, unsigned int* s_flag,
+                                               unsigned int tid) {
+    unsigned int x[E];
+    if (tid == 0) *s_flag = 0u;
 #pragma unroll
-    for (int e = 0; e < E; ++e) { const unsigned int i = e * TS_THREADS + tid; x[e] = i < len ? __ldcg(seg + i) : SENTINEL; }
-    bitonic_sort_regs<E>(x, s_x, tid);
+    for (int e = 0; e < E; ++e) {
+        const unsigned int i = e * TS_THREADS + tid;
+        x[e] = 0xFFFFFFFFu;
+        if (i < len) {
+            const unsigned long long pr = __ldcg(seg + i);
+            s_pairs[i] = pr;
+            x[e] = by_instance ? (unsigned int)pr : (((unsigned int)(pr >> 32) << 16) | i);
+        }
+    }
+    __syncthreads();
+    bitonic_sort_regs<unsigned int, E>(x, s_k, tid);
+    if (by_instance) {
 #pragma unroll
-    for (int e = 0; e < E; ++e) { const unsigned int i = e * TS_THREADS + tid; if (i < len) seg[i] = x[e]; }
-    if (!layer) return;
-    // LAYER50: the same pairs once more in instance (= arrival) order
+        for (int e = 0; e < E; ++e) { const unsigned int i = e * TS_THREADS + tid; if (i < len) seg[i] = (unsigned long long)x[e]; }
+        return;
+    }
 #pragma unroll
-    for (int e = 0; e < E; ++e) if (x[e] != SENTINEL) x[e] &= 0xFFFFFFFFull;
-    bitonic_sort_regs<E>(x, s_x, tid);
+    for (int e = 0; e < E; ++e) s_k[e * TS_THREADS + tid] = x[e];
+    __syncthreads();
+    bool too_long = false;
+    for (unsigned int i = tid; i < len; i += TS_THREADS) {          // the thread's own sorted keys, read back from shared memory
+        const unsigned int key = s_k[i], d = key >> 16;
+        const unsigned long long pr = s_pairs[key & 0xFFFFu];
+        const unsigned int idx = (unsigned int)pr;
+        unsigned int left = 0, right = 0, rank = 0;
+        for (unsigned int j = i; j > 0u && left <= TS_MAX_RUN; --j) {
+            const unsigned int kj = s_k[j - 1u];
+            if ((kj >> 16) != d) break;
+            ++left; rank += (unsigned int)s_pairs[kj & 0xFFFFu] < idx ? 1u : 0u;
+        }
+        for (unsigned int j = i + 1u; j < len && right <= TS_MAX_RUN; ++j) {
+            const unsigned int kj = s_k[j];
+            if ((kj >> 16) != d) break;
+            ++right; rank += (unsigned int)s_pairs[kj & 0xFFFFu] < idx ? 1u : 0u;
+        }
+        if (left > TS_MAX_RUN || right > TS_MAX_RUN) too_long = true;
+        else seg[i - left + rank] = pr;
+    }
+    if (too_long) *s_flag = 1u;
+    __syncthreads();
+    const bool fallback = *s_flag != 0u;
+    if (layer) {
 #pragma unroll
-    for (int e = 0; e < E; ++e) { const unsigned int i = e * TS_THREADS + tid; if (i < len) arrival[i] = (unsigned int)x[e]; }
+        for (int e = 0; e < E; ++e) { const unsigned int i = e * TS_THREADS + tid; x[e] = i < len ? (unsigned int)s_pairs[i] : 0xFFFFFFFFu; }
+        bitonic_sort_regs<unsigned int, E>(x, s_k, tid);
+#pragma unroll
+        for (int e = 0; e < E; ++e) { const unsigned int i = e * TS_THREADS + tid; if (i < len) arrival[i] = x[e]; }
+    }
+    if (fallback) {
+        // a long run of equal half depths: the whole pairs through the 64-bit network (s_pairs doubles as its exchange buffer)
+        unsigned long long y[E];
+#pragma unroll
+        for (int e = 0; e < E; ++e) { const unsigned int i = e * TS_THREADS + tid; y[e] = i < len ? s_pairs[i] : SENTINEL; }
+        __syncthreads();
+        bitonic_sort_regs<unsigned long long, E>(y, s_pairs, tid);
+#pragma unroll
+        for (int e = 0; e < E; ++e) { const unsigned int i = e * TS_THREADS + tid; if (i < len) seg[i] = y[e]; }
+    }
 }
 
 // Lists longer than TS_CHUNK: the same network run by the one CTA on the list in global memory, every comparator
@@ -291,20 +362,22 @@ __device__ void sort_list_global(unsigned long long* seg, unsigned int len, unsi
 }
 
 __global__ void __launch_bounds__(TS_THREADS) tile_sort_kernel(const __grid_constant__ FrameUniforms U, const FrameCtl* ctl,
-                                                               const unsigned int* bounds, unsigned long long* pairs,
-                                                               unsigned int* arrival)
+                                                               const unsigned int* bounds, const unsigned int* order,
+                                                               unsigned long long* pairs, unsigned int* arrival)
 {
-    __shared__ unsigned long long s_x[TS_CHUNK];
+    __shared__ unsigned long long s_x[TS_CHUNK];           // the list's pairs (and the exchange buffer of the 64-bit network)
+    __shared__ unsigned int s_k[TS_CHUNK];                 // exchange buffer of the 32-bit network, then the sorted keys
+    __shared__ unsigned int s_flag;
     pdl_prologue();
-    const unsigned int tile = (unsigned int)((U.row_begin + blockIdx.y) * U.tiles_x) + blockIdx.x;
+    const unsigned int tile = __ldcg(order + blockIdx.x);          // longest lists first
     const unsigned int b0 = __ldcg(bounds + tile), len = __ldcg(bounds + tile + 1) - b0;
     const unsigned int tid = threadIdx.x;
     if (len <= 1 && U.mode != SPLAT_MODE_LAYER50) return;
     if (len == 0) return;
     unsigned long long* seg = pairs + b0;
-    const bool layer = U.mode == SPLAT_MODE_LAYER50;
+    const bool layer = U.mode == SPLAT_MODE_LAYER50, by_instance = U.mode == SPLAT_MODE_MLAB;
     if (len <= 32) {
-        // one warp, shuffles only
+        // one warp, shuffles only, on the whole 64-bit pairs
         if (tid >= 32) return;
         unsigned long long x = tid < len ? __ldcg(seg + tid) : SENTINEL;
         for (int pass = 0; pass < (layer ? 2 : 1); ++pass) {
@@ -321,11 +394,11 @@ __global__ void __launch_bounds__(TS_THREADS) tile_sort_kernel(const __grid_cons
         }
         return;
     }
-    if (len <= 1 * TS_THREADS) sort_list_regs<1>(seg, arrival + b0, len, layer, s_x, tid);
-    else if (len <= 2 * TS_THREADS) sort_list_regs<2>(seg, arrival + b0, len, layer, s_x, tid);
-    else if (len <= 4 * TS_THREADS) sort_list_regs<4>(seg, arrival + b0, len, layer, s_x, tid);
-    else if (len <= 8 * TS_THREADS) sort_list_regs<8>(seg, arrival + b0, len, layer, s_x, tid);
-    else if (len <= 16 * TS_THREADS) sort_list_regs<16>(seg, arrival + b0, len, layer, s_x, tid);
+    if (len <= 1 * TS_THREADS) sort_list_fast<1>(seg, arrival + b0, len, by_instance, layer, s_x, s_k, &s_flag, tid);
+    else if (len <= 2 * TS_THREADS) sort_list_fast<2>(seg, arrival + b0, len, by_instance, layer, s_x, s_k, &s_flag, tid);
+    else if (len <= 4 * TS_THREADS) sort_list_fast<4>(seg, arrival + b0, len, by_instance, layer, s_x, s_k, &s_flag, tid);
+    else if (len <= 8 * TS_THREADS) sort_list_fast<8>(seg, arrival + b0, len, by_instance, layer, s_x, s_k, &s_flag, tid);
+    else if (len <= 16 * TS_THREADS) sort_list_fast<16>(seg, arrival + b0, len, by_instance, layer, s_x, s_k, &s_flag, tid);
     else {
         if (layer) {
             // instance order first (on the low words), copied out, then the depth order in place
@@ -337,10 +410,10 @@ __global__ void __launch_bounds__(TS_THREADS) tile_sort_kernel(const __grid_cons
     }
 }
 
-void launch_tile_sort(const FrameUniforms& U, const FrameCtl* ctl, const unsigned int* bounds, unsigned long long* pairs,
-                      unsigned int* arrival, cudaStream_t s)
+void launch_tile_sort(const FrameUniforms& U, const FrameCtl* ctl, const unsigned int* bounds, const unsigned int* order,
+                      unsigned long long* pairs, unsigned int* arrival, cudaStream_t s)
 {
     const int rows = U.row_end - U.row_begin;
     if (rows <= 0 || U.tiles_x <= 0) return;
-    launch_pdl(tile_sort_kernel, dim3(U.tiles_x, rows), dim3(TS_THREADS), 0, s, U, ctl, bounds, pairs, arrival);
+    launch_pdl(tile_sort_kernel, dim3((unsigned int)(U.tiles_x * rows)), dim3(TS_THREADS), 0, s, U, ctl, bounds, order, pairs, arrival);
 }

@@ -213,14 +213,14 @@ template <int MODE, bool COUNT>
 __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
     const __grid_constant__ FrameUniforms U, const splat_record_row* rec,
     const unsigned int* pairs_lo, const unsigned int* arrival,
-    const unsigned int* bounds, uint2* __restrict__ fb, FrameCtl* ctl)
+    const unsigned int* bounds, const unsigned int* order, uint2* __restrict__ fb, FrameCtl* ctl)
 {
     __shared__ float4 s_ab[2 * BLEND_BATCH];        // [0..B): cx cy ux uy   [B..2B): vx vy opacity rg
     __shared__ unsigned int s_cm[3 * BLEND_BATCH];  // [0..B): bd   [B..2B): 8x4-block mask   [2B..3B): instance index
     pdl_prologue();
 
-    const int tx = blockIdx.x, ty = U.row_begin + blockIdx.y;
-    const unsigned int tile = (unsigned int)(ty * U.tiles_x + tx);
+    const unsigned int tile = __ldcg(order + blockIdx.x);          // the band's tiles, longest lists first (tile_offsets_kernel)
+    const int ty = (int)(tile / (unsigned int)U.tiles_x), tx = (int)(tile - (unsigned int)ty * (unsigned int)U.tiles_x);
     int lx, ly; pixel_of_thread(lx, ly);
     const int pi = tx * 16 + lx, pj = ty * 16 + ly;
     const bool inside = pi < U.w && pj < U.h;
@@ -285,23 +285,24 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(
 
 template <bool COUNT>
 static void launch_blend_t(const FrameUniforms& U, const splat_record_row* rec, const unsigned int* lo, const unsigned int* arrival,
-                           const unsigned int* bounds, void* fb_half4, FrameCtl* ctl, cudaStream_t s)
+                           const unsigned int* bounds, const unsigned int* order, void* fb_half4, FrameCtl* ctl, cudaStream_t s)
 {
-    const dim3 grid(U.tiles_x, U.row_end - U.row_begin);
+    const dim3 grid((unsigned int)(U.tiles_x * (U.row_end - U.row_begin)));
     if (U.mode == SPLAT_MODE_MLAB)
-        launch_pdl(blend_kernel<SPLAT_MODE_MLAB, COUNT>, grid, dim3(BLEND_THREADS), 0, s, U, rec, lo, arrival, bounds, reinterpret_cast<uint2*>(fb_half4), ctl);
+        launch_pdl(blend_kernel<SPLAT_MODE_MLAB, COUNT>, grid, dim3(BLEND_THREADS), 0, s, U, rec, lo, arrival, bounds, order, reinterpret_cast<uint2*>(fb_half4), ctl);
     else if (U.mode == SPLAT_MODE_LAYER50)
-        launch_pdl(blend_kernel<SPLAT_MODE_LAYER50, COUNT>, grid, dim3(BLEND_THREADS), 0, s, U, rec, lo, arrival, bounds, reinterpret_cast<uint2*>(fb_half4), ctl);
+        launch_pdl(blend_kernel<SPLAT_MODE_LAYER50, COUNT>, grid, dim3(BLEND_THREADS), 0, s, U, rec, lo, arrival, bounds, order, reinterpret_cast<uint2*>(fb_half4), ctl);
     else
-        launch_pdl(blend_kernel<SPLAT_MODE_TILE, COUNT>, grid, dim3(BLEND_THREADS), 0, s, U, rec, lo, arrival, bounds, reinterpret_cast<uint2*>(fb_half4), ctl);
+        launch_pdl(blend_kernel<SPLAT_MODE_TILE, COUNT>, grid, dim3(BLEND_THREADS), 0, s, U, rec, lo, arrival, bounds, order, reinterpret_cast<uint2*>(fb_half4), ctl);
 }
 
 void launch_blend(const FrameUniforms& U, const splat_record_row* rec, const unsigned long long* pairs,
-                  const unsigned int* arrival, const unsigned int* bounds, void* fb_half4, FrameCtl* ctl, bool count_work, cudaStream_t s)
+                  const unsigned int* arrival, const unsigned int* bounds, const unsigned int* order, void* fb_half4, FrameCtl* ctl,
+                  bool count_work, cudaStream_t s)
 {
     const int rows = U.row_end - U.row_begin;
     if (rows <= 0 || U.tiles_x <= 0) return;
     const unsigned int* lo = reinterpret_cast<const unsigned int*>(pairs);      // little endian: the instance index is word 0 of a pair
-    if (count_work) launch_blend_t<true>(U, rec, lo, arrival, bounds, fb_half4, ctl, s);
-    else launch_blend_t<false>(U, rec, lo, arrival, bounds, fb_half4, ctl, s);
+    if (count_work) launch_blend_t<true>(U, rec, lo, arrival, bounds, order, fb_half4, ctl, s);
+    else launch_blend_t<false>(U, rec, lo, arrival, bounds, order, fb_half4, ctl, s);
 }

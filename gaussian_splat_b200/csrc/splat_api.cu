@@ -42,6 +42,7 @@ struct FrameSet {
     uint32_t* arrival = nullptr; unsigned long long capacity_arr = 0;
     FrameCtl* ctl = nullptr;                // + tile counters (CTL_BYTES)
     uint32_t* bounds = nullptr;             // [65536 + 8]: first pair of every tile's list
+    uint32_t* order = nullptr;              // [65536 + 8]: the band's tiles, longest lists first
     cudaStream_t own_stream = nullptr;
 };
 
@@ -131,6 +132,7 @@ static int ensure_pairs(splat_ctx* c, unsigned long long cap) {
 static int alloc_frame_fixed(splat_ctx* c) {        // control block + tile counters and bounds of the CURRENT set
     CK(cudaMalloc(&c->ctl, CTL_BYTES)); CK(cudaMemset(c->ctl, 0, CTL_BYTES));
     CK(cudaMalloc(&c->bounds, (65536 + 8) * 4)); CK(cudaMemset(c->bounds, 0, (65536 + 8) * 4));
+    CK(cudaMalloc(&c->order, (65536 + 8) * 4)); CK(cudaMemset(c->order, 0, (65536 + 8) * 4));
     return 0;
 }
 
@@ -183,7 +185,7 @@ static void drop_alt(splat_ctx* c) {
     if (!c->alt_ready) return;
     swap_sets(c);
     free_scene_scratch(c); free_pairs(c);
-    cudaFree(c->bounds); cudaFree(c->ctl);
+    cudaFree(c->bounds); cudaFree(c->order); cudaFree(c->ctl);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     *static_cast<FrameSet*>(c) = FrameSet{};
     swap_sets(c);
@@ -227,7 +229,7 @@ int splat_destroy(splat_ctx* c) {
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     free_scene(c); free_pairs(c);
-    cudaFree(c->bounds); cudaFree(c->ctl); cudaFree(c->fb_scratch); cudaFree(c->sort_ctl); cudaFree(c->sort_status);
+    cudaFree(c->bounds); cudaFree(c->order); cudaFree(c->ctl); cudaFree(c->fb_scratch); cudaFree(c->sort_ctl); cudaFree(c->sort_status);
     cudaFreeHost(c->ctl_host); cudaFreeHost(c->status_ring);
     for (int k = 0; k < 6; ++k) if (c->ev[k]) cudaEventDestroy(c->ev[k]);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -494,17 +496,17 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
     nvtxRangePop();
     if (timed) CK(cudaEventRecord(c->ev[1], s));
     nvtxRangePushA("splat: K2 tile offsets + scatter");
-    launch_tile_offsets(U, c->ctl, c->bounds, s);
+    launch_tile_offsets(U, c->ctl, c->bounds, c->order, s);
     if (c->n) launch_scatter_pairs(c->ctl, c->park_key, c->park_ts, c->chunk_fill, c->bounds, c->pairs, slot, c->frame_no, c->sm_count, s);
     else { slot->total_pairs = 0; slot->total_slots = 0; slot->overflow = 0; slot->max_tile_pairs = 0; slot->frame_no = c->frame_no; }
     nvtxRangePop();
     if (timed) CK(cudaEventRecord(c->ev[2], s));
     nvtxRangePushA("splat: K3 per-tile sort");
-    if (c->n) launch_tile_sort(U, c->ctl, c->bounds, c->pairs, c->arrival, s);
+    if (c->n) launch_tile_sort(U, c->ctl, c->bounds, c->order, c->pairs, c->arrival, s);
     nvtxRangePop();
     if (timed) { CK(cudaEventRecord(c->ev[3], s)); CK(cudaEventRecord(c->ev[4], s)); }
     nvtxRangePushA("splat: K5 blend");
-    launch_blend(U, c->rec, c->pairs, c->arrival, c->bounds, fb, c->ctl, (flags & SPLAT_FLAG_COUNT_WORK) != 0, s);
+    launch_blend(U, c->rec, c->pairs, c->arrival, c->bounds, c->order, fb, c->ctl, (flags & SPLAT_FLAG_COUNT_WORK) != 0, s);
     nvtxRangePop();
     if (timed) CK(cudaEventRecord(c->ev[5], s));
     CK(cudaGetLastError());

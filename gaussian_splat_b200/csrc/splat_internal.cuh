@@ -153,13 +153,14 @@ void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_reco
 // into bounds[T + 1]; scatter_pairs moves every parked pair to pairs[bounds[tile] + slot]; tile_sort sorts every tile's
 // list in shared memory on the whole 64-bit pair: a total order, so the result equals a stable sort of instance-ordered
 // pairs on tile | depth. LAYER50 also gets the list in instance order (arrival).
-void launch_tile_offsets(const FrameUniforms& U, FrameCtl* ctl, unsigned int* bounds, cudaStream_t s);
+// order[0 .. band tiles): the band's tile ids, longest lists first: the CTA -> tile mapping of the sort and the blend
+void launch_tile_offsets(const FrameUniforms& U, FrameCtl* ctl, unsigned int* bounds, unsigned int* order, cudaStream_t s);
 // status_slot: 32 bytes of mapped page-locked memory that receive D / slots used / overflow / longest list and, last, frame_no
 void launch_scatter_pairs(const FrameCtl* ctl, const unsigned long long* park_key, const unsigned long long* park_ts,
                           const unsigned int* chunk_fill, const unsigned int* bounds, unsigned long long* pairs,
                           void* status_slot, unsigned int frame_no, int sm_count, cudaStream_t s);
-void launch_tile_sort(const FrameUniforms& U, const FrameCtl* ctl, const unsigned int* bounds, unsigned long long* pairs,
-                      unsigned int* arrival, cudaStream_t s);
+void launch_tile_sort(const FrameUniforms& U, const FrameCtl* ctl, const unsigned int* bounds, const unsigned int* order,
+                      unsigned long long* pairs, unsigned int* arrival, cudaStream_t s);
 // Stand-alone sort (k_sort.cu). Per-pass digit histograms of keys[0..n) into ctl->hist.
 void launch_sort_histogram(const void* keys, int key_bytes, unsigned long long n, SortCtl* ctl, SortPlan plan,
                            int sm_count, cudaStream_t s);
@@ -176,4 +177,5 @@ cudaError_t launch_ply_decode_chunk(const float* rows_dev, unsigned int n_rows, 
 // pairs: the tile lists (u64 per pair, instance index in the low word), depth-ordered (TILE, LAYER50) or instance-ordered
 // (MLAB); arrival: LAYER50's instance-ordered list (u32 per pair). bounds[t] .. bounds[t + 1] = tile t's list.
 void launch_blend(const FrameUniforms& U, const splat_record_row* rec, const unsigned long long* pairs,
-                  const unsigned int* arrival, const unsigned int* bounds, void* fb_half4, FrameCtl* ctl, bool count_work, cudaStream_t s);
+                  const unsigned int* arrival, const unsigned int* bounds, const unsigned int* order, void* fb_half4, FrameCtl* ctl,
+                  bool count_work, cudaStream_t s);
