@@ -286,11 +286,18 @@ def c3_bands_leg(ctx, torch, dist, args, dev, rank, world, steps, sh_degree=0, e
             if it >= 3:
                 for k, v in ctx.stage_times().items():
                     acc[k] = acc.get(k, 0.0) + v / 5
+        # frames back to back through splat_render_batch, the same call the banded loop below makes (the library keeps two
+        # frames in flight on two frame sets)
+        fb1 = [fb] + [torch.zeros_like(fb) for _ in range(3)]
+        vs1, ps1 = np.stack([V] * steps), np.stack([P] * steps)
+        ptr1 = [fb1[i & 3].data_ptr() for i in range(steps)]
+        ctx.render_batch(stream, ptr1[:4], vs1[:4], ps1[:4], w, h, full); torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(steps):
-            ctx.render(stream, fb.data_ptr(), V, P, w, h, full)
+        ctx.render_batch(stream, ptr1, vs1, ps1, w, h, full)
         e1.record(); torch.cuda.synchronize()
+        assert torch.equal(fb1[1], fb_single) and torch.equal(fb1[2], fb_single)
+        del fb1
         one_gpu = {"frames_per_s": steps * 1e3 / e0.elapsed_time(e1), "ms_per_frame": e0.elapsed_time(e1) / steps,
                    "stage_us": {k: round(v * 1e3, 1) for k, v in acc.items()}, "pairs_D": int(st_full.n_pairs)}
     dist.barrier()
@@ -317,10 +324,63 @@ def c3_bands_leg(ctx, torch, dist, args, dev, rank, world, steps, sh_degree=0, e
             dist.all_gather(allt, tt)
             wts = multigpu.reweight_rows(wts, band_list, [float(x.item()) for x in allt])
             band_list = multigpu.band_rows(tiles_y, world, wts)
-    row0, row1 = band_list[rank]
-    rows_px = multigpu.bands_to_pixel_rows(band_list, h)
-    have_rows = row1 > row0
-    plain = capi.make_opts(mode=mode, sh_degree=sh_degree, tile_row_begin=row0, tile_row_end=row1)
+    GROUP = 8                                   # frames per splat_render_batch call; two groups of framebuffers alternate
+    fbs = [fb] + [torch.zeros_like(fb) for _ in range(2 * GROUP - 1)]
+    comm = torch.cuda.Stream(device=dev)
+    ev_r = [torch.cuda.Event() for _ in range(2)]; ev_g = [torch.cuda.Event() for _ in range(2)]
+    main_s = torch.cuda.current_stream()
+    vsg, psg = np.stack([V] * GROUP), np.stack([P] * GROUP)
+    st8 = {}                                    # the current partition: set by use_bands()
+
+    def use_bands(bl):
+        a, b = bl[rank]
+        st8.update(row0=a, row1=b, rows_px=multigpu.bands_to_pixel_rows(bl, h), have_rows=b > a,
+                   plain=capi.make_opts(mode=mode, sh_degree=sh_degree, tile_row_begin=a, tile_row_end=b))
+
+    peer = multigpu.PeerFrames(2 * GROUP, h, w, rank, world, dev, dst=0)      # rank 0's framebuffers, mapped by every rank
+
+    def group(g, ev_pair=None, exchange="peer"):
+        """GROUP frames of this rank's band (the library keeps two in flight), then the exchange on the side stream:
+        "peer"  the blend wrote the band straight into rank 0's framebuffer over NVLink; a 4-byte all-reduce signals completion
+        "nccl"  the bands are gathered on rank 0 by grouped ncclSend / ncclRecv (one NCCL group for the GROUP frames)
+        ev_pair: timing events recorded around the rendering alone (after the wait for the framebuffers)."""
+        b = g & 1
+        mine_fbs = fbs[b * GROUP:(b + 1) * GROUP]
+        if g >= 2:
+            main_s.wait_event(ev_g[b])          # the exchange that last touched these framebuffers
+        if ev_pair:
+            ev_pair[0].record(main_s)
+        if st8["have_rows"]:
+            ptrs = [peer.ptr(b * GROUP + k) for k in range(GROUP)] if exchange == "peer" else [f.data_ptr() for f in mine_fbs]
+            ctx.render_batch(stream, ptrs, vsg, psg, w, h, st8["plain"])
+        if ev_pair:
+            ev_pair[1].record(main_s)
+        ev_r[b].record(main_s)
+        with torch.cuda.stream(comm):
+            comm.wait_event(ev_r[b])
+            if exchange == "peer":
+                peer.signal()
+            elif exchange == "nccl":
+                multigpu.gather_bands_batch(mine_fbs, st8["rows_px"], rank, world, dst=0)
+            ev_g[b].record(comm)
+
+    use_bands(band_list)
+    if not even_bands:
+        # three more rounds on what each rank's rendering takes INSIDE the real loop: two frames in flight, and on rank 0
+        # the gather's receive kernels sharing the SMs (the serial stage times above see neither)
+        for _ in range(3):
+            evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(6)]
+            for g in range(6):
+                group(g, evs[g])
+            torch.cuda.synchronize(); dist.barrier()
+            mine_t = float(np.median([a_.elapsed_time(b_) for a_, b_ in evs[2:]])) / GROUP
+            tt = torch.tensor([mine_t], dtype=torch.float64, device=dev)
+            allt = [torch.zeros_like(tt) for _ in range(world)]
+            dist.all_gather(allt, tt)
+            wts = multigpu.reweight_rows(wts, band_list, [float(x.item()) for x in allt], damping=0.5)
+            band_list = multigpu.band_rows(tiles_y, world, wts)
+            use_bands(band_list)
+    row0, row1, rows_px, have_rows, plain = st8["row0"], st8["row1"], st8["rows_px"], st8["have_rows"], st8["plain"]
     timed = capi.make_opts(mode=mode, sh_degree=sh_degree, tile_row_begin=row0, tile_row_end=row1, flags=capi.FLAG_TIMING)
 
     # ---- parity of the real NCCL path: bands rendered by the ranks, gathered on rank 0, against rank 0's own whole frame
@@ -332,42 +392,39 @@ def c3_bands_leg(ctx, torch, dist, args, dev, rank, world, steps, sh_degree=0, e
     equal = bool(torch.equal(fb, fb_single)) if rank == 0 else True
     assert equal, "the NCCL-gathered band frame differs from the single-GPU frame"
 
-    # ---- timed: frame i's gather (side stream, framebuffer i & 1) overlaps frame i+1's kernels; one region of K frames,
-    # device-timed, the render stream finally waits for the last gather. No L2 flush: scene planes + records are several
-    # times the 126 MB L2.
-    fbs = [fb, torch.zeros_like(fb)]
-    comm = torch.cuda.Stream(device=dev)
-    ev_r = [torch.cuda.Event() for _ in range(2)]; ev_g = [torch.cuda.Event() for _ in range(2)]
-    main_s = torch.cuda.current_stream()
-
-    def frame(i):
-        b = i & 1
-        if i >= 2:
-            main_s.wait_event(ev_g[b])
-        if have_rows:
-            ctx.render(stream, fbs[b].data_ptr(), V, P, w, h, plain)
-        ev_r[b].record(main_s)
-        with torch.cuda.stream(comm):
-            comm.wait_event(ev_r[b])
-            multigpu.gather_bands(fbs[b], rows_px, rank, world, dst=0)
-            ev_g[b].record(comm)
-    for i in range(6):
-        frame(i)
-    torch.cuda.synchronize(); dist.barrier()
+    # ---- timed: groups of eight frames through splat_render_batch (two frames in flight inside the library); a group's
+    # gathers (side stream) overlap the next group's kernels; one region of K frames, device-timed, the render stream finally
+    # waits for the last gather. No L2 flush: scene planes + records are several times the 126 MB L2.
+    n_groups = max(1, steps // GROUP)
+    steps = n_groups * GROUP
     sampler = ClockSampler(dev.index)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sampler.start()
-    e0.record(main_s)
-    for i in range(steps):
-        frame(i)
-    main_s.wait_stream(comm)
-    e1.record(main_s)
-    torch.cuda.synchronize()
-    dist.barrier()
-    sampler.stop_flag = True; sampler.join()
-    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_per_frame = float(t.item()) / steps
+
+    def timed_loop(exchange, sample=False):
+        for g in range(4):
+            group(g, exchange=exchange)
+        torch.cuda.synchronize(); dist.barrier()
+        if rank == 0:       # every framebuffer of both groups holds a complete frame, equal to the one-GPU frame
+            frames_ = [peer.tensor(k) for k in range(2 * GROUP)] if exchange == "peer" else fbs
+            assert all(torch.equal(f, fb_single) for f in frames_), "a pipelined band frame (%s) differs from the single-GPU frame" % exchange
+        t0_, t1_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if sample:
+            sampler.start()
+        t0_.record(main_s)
+        for g in range(n_groups):
+            group(g, exchange=exchange)
+        main_s.wait_stream(comm)
+        t1_.record(main_s)
+        torch.cuda.synchronize()
+        dist.barrier()
+        if sample:
+            sampler.stop_flag = True; sampler.join()
+        t_ = torch.tensor([t0_.elapsed_time(t1_)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t_, op=dist.ReduceOp.MAX)
+        return float(t_.item()) / steps
+
+    ms_nccl = timed_loop("nccl")
+    ms_per_frame = timed_loop("peer", sample=True)
+    fbs = fbs[:2]
 
     # ---- per-stage times of every rank's band (a short separate, synchronising loop) and the gather on its own
     acc = {}
@@ -419,6 +476,7 @@ def c3_bands_leg(ctx, torch, dist, args, dev, rank, world, steps, sh_degree=0, e
         assert host_equal, "the shared host frame differs from the single-GPU frame"
     for fr in frames:
         fr.close()
+    peer.close()
     t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_fps = e2e_steps / float(t.item())
@@ -427,8 +485,12 @@ def c3_bands_leg(ctx, torch, dist, args, dev, rank, world, steps, sh_degree=0, e
     out = {
         "workload": name, "n_gaussians": n, "width": w, "height": h, "mode": "TILE", "parallelism": "bands%d+nccl_gather" % world,
         "frames_per_s": fps, "ms_per_frame": ms_per_frame, "steps": steps,
+        "exchange": "fused: every rank's blend kernel writes its band straight into rank 0's framebuffer over NVLink (CUDA IPC peer "
+                    "memory, splat_peer_alloc / splat_peer_open); one 4-byte NCCL all-reduce per group of %d frames is the completion signal" % GROUP,
+        "frames_per_s_nccl_gather": 1e3 / ms_nccl, "speedup_nccl_gather": None,
+        "nccl_gather_note": "the same loop with the bands gathered on rank 0 by grouped ncclSend / ncclRecv (splat_gather_bands_batch) instead",
         "frames_per_s_1gpu": None, "speedup": None, "one_gpu": None,
-        "bands": band_list, "band_balance": "even" if even_bands else "pairs per tile row, then 6 rounds of measured-time balancing",
+        "bands": band_list, "band_balance": "even" if even_bands else "pairs per tile row, 6 rounds on serial stage times, 3 rounds on each rank's render time inside the pipelined loop",
         "per_rank": everyone, "slowest_rank_stage_us": slow["stage_us"], "gather_us": max(d["gather_us"] for d in everyone),
         "gather_bytes_per_frame": w * h * 8,
         "e2e_frames_per_s": e2e_fps, "e2e_steps": e2e_steps, "e2e_d2h_bytes_per_step_per_rank": (rows_px[rank][1] - rows_px[rank][0]) * w * 8,
@@ -438,6 +500,7 @@ def c3_bands_leg(ctx, torch, dist, args, dev, rank, world, steps, sh_degree=0, e
     }
     if rank == 0:
         out["frames_per_s_1gpu"] = one_gpu["frames_per_s"]; out["speedup"] = fps / one_gpu["frames_per_s"]; out["one_gpu"] = one_gpu
+        out["speedup_nccl_gather"] = out["frames_per_s_nccl_gather"] / one_gpu["frames_per_s"]
     return out
 
 
@@ -640,7 +703,7 @@ def main():
         b0.record()
         ctx.render_batch(stream, dptrs, views, projs, w, h, eopts)
         b1.record(); torch.cuda.synchronize()
-        two = (not mode) and n <= 2_500_000 and w * h <= 2_400_000      # the library's own rule (splat_api.cu: two_frames_in_flight)
+        two = os.environ.get("SPLAT_TWO_FRAMES", "1") != "0"      # the library's own rule (splat_api.cu: two_frames_in_flight)
         inflight = {"frames_per_s": e2e_steps * 1e3 / b0.elapsed_time(b1), "frames": e2e_steps, "frames_in_flight": 2 if two else 1,
                     "note": "splat_render_batch, framebuffers stay on the device; no L2 flush (a frame touches ~2x the L2)"}
         del dfb

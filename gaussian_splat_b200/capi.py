@@ -31,7 +31,8 @@ EXPORTS = [
     "splat_create", "splat_destroy", "splat_upload", "splat_upload_sh", "splat_render",
     "splat_render_host", "splat_render_batch", "splat_render_batch_host", "splat_pack_bgra8", "splat_upload_ply_rows", "splat_frame_status", "splat_debug_fetch",
     "splat_stage_times", "splat_sort_pairs_u64_u32", "splat_sort_pairs_u32_u32", "splat_last_error_string", "splat_version",
-    "splat_band_rows", "splat_gather_bands", "splat_sort_pairs_u64_u32_static",
+    "splat_band_rows", "splat_gather_bands", "splat_gather_bands_batch", "splat_sort_pairs_u64_u32_static",
+    "splat_peer_alloc", "splat_peer_free", "splat_peer_open", "splat_peer_close",
 ]
 
 
@@ -81,6 +82,11 @@ def lib():
         L.splat_sort_pairs_u64_u32_static.argtypes = [vp, vp, vp, vp, vp, C.c_uint64, C.c_int, C.c_int, C.POINTER(C.c_int)]
         L.splat_band_rows.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int32)]
         L.splat_gather_bands.argtypes = [vp, vp, vp, C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+        L.splat_gather_bands_batch.argtypes = [vp, vp, vp, C.c_int, C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+        L.splat_peer_alloc.argtypes = [C.c_size_t, C.POINTER(vp), vp]
+        L.splat_peer_free.argtypes = [vp]
+        L.splat_peer_open.argtypes = [vp, C.POINTER(vp)]
+        L.splat_peer_close.argtypes = [vp]
         L.splat_last_error_string.restype = C.c_char_p
         L.splat_version.restype = C.c_int
         _LIB = L
@@ -228,3 +234,34 @@ def gather_bands(nccl_comm_ptr: int, stream_ptr: int, fb_dev_ptr: int, pixel_row
     _check(lib().splat_gather_bands(C.c_void_p(nccl_comm_ptr), C.c_void_p(stream_ptr), C.c_void_p(fb_dev_ptr),
                                     rows.ctypes.data_as(C.POINTER(C.c_int32)), w, bytes_per_pixel, rank, world, dst),
            "splat_gather_bands")
+
+
+def gather_bands_batch(nccl_comm_ptr: int, stream_ptr: int, fb_dev_ptrs, pixel_rows, w: int, bytes_per_pixel: int, rank: int,
+                       world: int, dst: int = 0):
+    """splat_gather_bands_batch: the gather of several framebuffers of one partition inside one NCCL group."""
+    rows = np.ascontiguousarray(np.asarray(pixel_rows, np.int32).reshape(-1))
+    arr = (C.c_void_p * len(fb_dev_ptrs))(*fb_dev_ptrs)
+    _check(lib().splat_gather_bands_batch(C.c_void_p(nccl_comm_ptr), C.c_void_p(stream_ptr), arr, len(fb_dev_ptrs),
+                                          rows.ctypes.data_as(C.POINTER(C.c_int32)), w, bytes_per_pixel, rank, world, dst),
+           "splat_gather_bands_batch")
+
+
+def peer_alloc(nbytes: int):
+    """splat_peer_alloc: (device pointer, 64-byte handle) of a buffer other processes can map with peer_open."""
+    p = C.c_void_p(); h = C.create_string_buffer(64)
+    _check(lib().splat_peer_alloc(nbytes, C.byref(p), h), "splat_peer_alloc")
+    return int(p.value), bytes(h.raw)
+
+
+def peer_open(handle: bytes) -> int:
+    p = C.c_void_p(); h = C.create_string_buffer(handle, 64)
+    _check(lib().splat_peer_open(h, C.byref(p)), "splat_peer_open")
+    return int(p.value)
+
+
+def peer_close(ptr: int):
+    _check(lib().splat_peer_close(C.c_void_p(ptr)), "splat_peer_close")
+
+
+def peer_free(ptr: int):
+    _check(lib().splat_peer_free(C.c_void_p(ptr)), "splat_peer_free")

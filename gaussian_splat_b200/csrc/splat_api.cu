@@ -531,12 +531,15 @@ int splat_render(splat_ctx* c, void* stream, void* fb, const float* view, const 
     return enqueue_frame(c, (cudaStream_t)stream, fb, U, o ? o->flags : 0);
 }
 
-// Two frames in flight only pay while one frame leaves SMs idle in its latency-bound stages. Measured on B200:
-// 1M / 1080p TILE +11% end to end; 2M LAYER50 -14% and 6M / 4K -48% (two sets of persistent sort CTAs and two
-// 16 MB+ working sets fight over shared memory and L2), so large frames and LAYER50 stay serial.
-static bool two_frames_in_flight(const splat_ctx* c, int w, int h, const splat_opts* o) {
-    if (o && o->mode == SPLAT_MODE_LAYER50) return false;
-    return c->n <= 2500000u && (long long)w * h <= 2400000ll;
+// Two frames in flight: the latency-bound stages of one frame (block culling, the one-CTA tile scan, the sort's tail) leave
+// SMs idle that the other frame's kernels fill. Measured on B200 with this round's pipeline (device-resident camera batch,
+// frames/s serial -> two in flight): 1M / 1080p TILE 3456 -> 3834, 2M LAYER50 1395 -> 1542, 6M / 4K 639 -> 689, one band of
+// eight of the 6M / 4K frame 238 -> 197 us per frame. Round 1's pipeline (persistent onesweep CTAs, 16 MB+ working sets
+// fighting over shared memory and L2) lost 14 .. 48% on the large cases and kept them serial; that no longer holds.
+// SPLAT_TWO_FRAMES=0 / 1 forces either way (tuning knob).
+static bool two_frames_in_flight(const splat_ctx*, int, int, const splat_opts*) {
+    static const int force = [] { const char* e = getenv("SPLAT_TWO_FRAMES"); return e ? (e[0] == '0' ? 0 : 1) : -1; }();
+    return force != 0;
 }
 
 // Camera batches keep two frames in flight: view v runs on frame set v & 1 (own scratch, own stream), so the
@@ -990,11 +993,13 @@ int splat_band_rows(int tiles_y, int world, const double* row_weights, int32_t* 
     return SPLAT_OK;
 }
 
-int splat_gather_bands(void* nccl_comm, void* stream, void* fb_dev, const int32_t* pixel_rows, int w, int bytes_per_pixel,
-                       int rank, int world, int dst) {
-    if (!nccl_comm || !fb_dev || !pixel_rows || w <= 0 || bytes_per_pixel <= 0 || world <= 0 || rank < 0 || rank >= world || dst < 0 || dst >= world)
+int splat_gather_bands_batch(void* nccl_comm, void* stream, void* const* fbs_dev, int n_fb, const int32_t* pixel_rows, int w,
+                             int bytes_per_pixel, int rank, int world, int dst) {
+    if (!nccl_comm || !pixel_rows || w <= 0 || bytes_per_pixel <= 0 || world <= 0 || rank < 0 || rank >= world || dst < 0 || dst >= world ||
+        n_fb < 0 || (n_fb && !fbs_dev))
         ARG_FAIL("splat_gather_bands: bad arguments");
-    if (world == 1) return SPLAT_OK;
+    for (int f = 0; f < n_fb; ++f) if (!fbs_dev[f]) ARG_FAIL("splat_gather_bands: NULL framebuffer");
+    if (world == 1 || n_fb == 0) return SPLAT_OK;
     typedef ncclResult_t (*group_fn)(void);
     typedef ncclResult_t (*p2p_send_fn)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
     typedef ncclResult_t (*p2p_recv_fn)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
@@ -1009,18 +1014,75 @@ int splat_gather_bands(void* nccl_comm, void* stream, void* fb_dev, const int32_
     }
     ncclComm_t comm = (ncclComm_t)nccl_comm; cudaStream_t s = (cudaStream_t)stream;
     const size_t row_bytes = (size_t)w * bytes_per_pixel;
+    // ONE group for every framebuffer: NCCL fuses the sends / receives of a peer into one kernel launch
     ncclResult_t rc = g_start();
-    if (rank == dst) {
-        for (int r = 0; r < world && rc == ncclSuccess; ++r) {
-            const int32_t a = pixel_rows[2 * r], b = pixel_rows[2 * r + 1];
-            if (r != dst && b > a) rc = g_recv((char*)fb_dev + (size_t)a * row_bytes, (size_t)(b - a) * row_bytes, ncclUint8, r, comm, s);
+    for (int f = 0; f < n_fb && rc == ncclSuccess; ++f) {
+        if (rank == dst) {
+            for (int r = 0; r < world && rc == ncclSuccess; ++r) {
+                const int32_t a = pixel_rows[2 * r], b = pixel_rows[2 * r + 1];
+                if (r != dst && b > a) rc = g_recv((char*)fbs_dev[f] + (size_t)a * row_bytes, (size_t)(b - a) * row_bytes, ncclUint8, r, comm, s);
+            }
+        } else {
+            const int32_t a = pixel_rows[2 * rank], b = pixel_rows[2 * rank + 1];
+            if (b > a) rc = g_send((const char*)fbs_dev[f] + (size_t)a * row_bytes, (size_t)(b - a) * row_bytes, ncclUint8, dst, comm, s);
         }
-    } else {
-        const int32_t a = pixel_rows[2 * rank], b = pixel_rows[2 * rank + 1];
-        if (b > a && rc == ncclSuccess) rc = g_send((const char*)fb_dev + (size_t)a * row_bytes, (size_t)(b - a) * row_bytes, ncclUint8, dst, comm, s);
     }
     const ncclResult_t rc2 = g_end();
     if (rc != ncclSuccess || rc2 != ncclSuccess) { g_err = "splat_gather_bands: NCCL send / recv failed"; return SPLAT_ERR_CUDA; }
+    return SPLAT_OK;
+}
+
+int splat_gather_bands(void* nccl_comm, void* stream, void* fb_dev, const int32_t* pixel_rows, int w, int bytes_per_pixel,
+                       int rank, int world, int dst) {
+    if (!fb_dev) ARG_FAIL("splat_gather_bands: bad arguments");
+    void* one[1] = {fb_dev};
+    return splat_gather_bands_batch(nccl_comm, stream, one, 1, pixel_rows, w, bytes_per_pixel, rank, world, dst);
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------ multi-GPU single frame, fused exchange: peer framebuffers
+// The gather as stores instead of a collective: the destination rank allocates its framebuffers here and exports them
+// (CUDA IPC); every other rank opens them and passes the mapped pointer to splat_render as ITS framebuffer, so its blend
+// kernel writes the band's pixels straight into the destination's memory over NVLink - no gather kernel, no SM time on the
+// destination, the transfer spread over the blend's run time. What remains to exchange is a completion signal (any
+// stream-ordered cross-GPU synchronisation after the render, e.g. a 4-byte NCCL all-reduce).
+extern "C" {
+
+int splat_peer_alloc(size_t bytes, void** ptr, void* handle64) {
+    if (!ptr || !handle64 || bytes == 0) ARG_FAIL("splat_peer_alloc: bad arguments");
+    *ptr = nullptr;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "the exported handle is 64 bytes");
+    void* p = nullptr;
+    CK(cudaMalloc(&p, bytes));
+    cudaIpcMemHandle_t h;
+    const cudaError_t e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) { cudaFree(p); g_err = std::string("splat_peer_alloc: cudaIpcGetMemHandle: ") + cudaGetErrorString(e); return SPLAT_ERR_CUDA; }
+    std::memcpy(handle64, &h, 64);
+    CK(cudaMemset(p, 0, bytes));
+    *ptr = p;
+    return SPLAT_OK;
+}
+
+int splat_peer_free(void* ptr) {
+    if (ptr) CK(cudaFree(ptr));
+    return SPLAT_OK;
+}
+
+int splat_peer_open(const void* handle64, void** ptr) {
+    if (!ptr || !handle64) ARG_FAIL("splat_peer_open: bad arguments");
+    *ptr = nullptr;
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle64, 64);
+    void* p = nullptr;
+    const cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { g_err = std::string("splat_peer_open: cudaIpcOpenMemHandle: ") + cudaGetErrorString(e); return SPLAT_ERR_CUDA; }
+    *ptr = p;
+    return SPLAT_OK;
+}
+
+int splat_peer_close(void* ptr) {
+    if (ptr) CK(cudaIpcCloseMemHandle(ptr));
     return SPLAT_OK;
 }
 

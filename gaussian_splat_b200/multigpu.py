@@ -104,6 +104,83 @@ def gather_bands(fb, pixel_rows: Sequence[Tuple[int, int]], rank: int, world: in
             w.wait()
 
 
+def gather_bands_batch(fbs, pixel_rows: Sequence[Tuple[int, int]], rank: int, world: int, dst: int = 0):
+    """gather_bands for several framebuffers of the same partition (consecutive frames of a pipelined loop): under nccl one
+    fused exchange (the C ABI's splat_gather_bands_batch), otherwise one gather_bands per framebuffer."""
+    import torch
+    import torch.distributed as dist
+    fbs = list(fbs)
+    if world == 1 or not fbs:
+        return
+    if fbs[0].is_cuda and dist.get_backend() == "nccl":
+        comm = _nccl_comm_ptr(fbs[0].device)
+        if comm:
+            from . import capi
+            capi.gather_bands_batch(comm, torch.cuda.current_stream(fbs[0].device).cuda_stream, [f.data_ptr() for f in fbs],
+                                    list(pixel_rows), fbs[0].shape[1], fbs[0].shape[2] * fbs[0].element_size(), rank, world, dst)
+            return
+    for f in fbs:
+        gather_bands(f, pixel_rows, rank, world, dst)
+
+
+class _DevView:
+    """A device buffer that is not torch's, presented through __cuda_array_interface__ (torch.as_tensor aliases it)."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+class PeerFrames:
+    """The banded frame's exchange as stores instead of a gather: `count` framebuffers [H, W, 4] half live on rank `dst`
+    (splat_peer_alloc) and are mapped by every other rank (CUDA IPC, splat_peer_open). A rank renders its band with
+    `ptr(i)` as the framebuffer, so its blend kernel writes the band straight into rank dst's memory over NVLink; nothing
+    is gathered afterwards. `signal()` enqueues the completion signal on the current stream (a 4-byte all-reduce: when it
+    has completed on rank dst, every rank's stream has passed its render). Call on every rank (collective)."""
+
+    def __init__(self, count: int, height: int, width: int, rank: int, world: int, device, dst: int = 0):
+        import torch
+        import torch.distributed as dist
+        from . import capi
+        self.rank, self.world, self.dst, self.h, self.w = rank, world, dst, height, width
+        self.nbytes = height * width * 8
+        self._own, self._mapped = [], []
+        handles = [None] * count
+        if rank == dst:
+            for k in range(count):
+                p, hd = capi.peer_alloc(self.nbytes)
+                self._own.append(p); handles[k] = hd
+        if world > 1:
+            dist.broadcast_object_list(handles, src=dst)
+        if rank == dst:
+            self._ptrs = list(self._own)
+        else:
+            self._mapped = [capi.peer_open(hd) for hd in handles]
+            self._ptrs = list(self._mapped)
+        self._flag = torch.zeros(1, dtype=torch.int32, device=device)
+
+    def ptr(self, i: int) -> int:
+        return self._ptrs[i]
+
+    def tensor(self, i: int):
+        """Rank dst only: framebuffer i as a torch tensor [H, W, 4] float16 aliasing the device memory."""
+        import torch
+        assert self.rank == self.dst
+        return torch.as_tensor(_DevView(self._own[i], (self.h, self.w, 4), "<f2"), device=self._flag.device)
+
+    def signal(self):
+        import torch.distributed as dist
+        if self.world > 1:
+            dist.all_reduce(self._flag)
+
+    def close(self):
+        from . import capi
+        for p in self._mapped:
+            capi.peer_close(p)
+        for p in self._own:
+            capi.peer_free(p)
+        self._mapped, self._own, self._ptrs = [], [], []
+
+
 class SharedHostFrame:
     """One host framebuffer shared by every rank of the node: a POSIX shared-memory file mapped by all processes
     and page-locked in each (cudaHostRegister), so a rank's device-to-host copy lands its band in the final frame

@@ -207,6 +207,23 @@ int splat_pack_bgra8(splat_ctx* ctx, void* stream, const void* fb_half4, void* b
 int splat_band_rows(int tiles_y, int world, const double* row_weights, int32_t* bands);
 int splat_gather_bands(void* nccl_comm, void* stream, void* fb_dev, const int32_t* pixel_rows, int w, int bytes_per_pixel,
                        int rank, int world, int dst);
+/* The same exchange for n_fb framebuffers of the same partition (consecutive frames of a pipelined loop) inside ONE NCCL group:
+ * one fused launch instead of n_fb. */
+int splat_gather_bands_batch(void* nccl_comm, void* stream, void* const* fbs_dev, int n_fb, const int32_t* pixel_rows, int w,
+                             int bytes_per_pixel, int rank, int world, int dst);
+
+/* Fused exchange for the banded frame: instead of gathering, every rank's blend kernel writes its band straight into the
+ * destination rank's framebuffer over NVLink. The destination allocates its framebuffers with splat_peer_alloc (device memory
+ * of the current device + a 64-byte handle to send to the other processes by any means); each other rank maps it with
+ * splat_peer_open (current device = its own GPU; peer access is enabled on first use) and passes the mapped pointer to
+ * splat_render / splat_render_batch as fb_half4_dev together with its tile_row_begin / tile_row_end. The pixels are in
+ * place when the writer's stream has passed the render AND the two GPUs have synchronised (an event the destination
+ * waits on, or any collective enqueued after the render on both sides). splat_peer_close unmaps, splat_peer_free frees.
+ * No counterpart in the reference (single Metal device). */
+int splat_peer_alloc(size_t bytes, void** ptr, void* handle64);
+int splat_peer_free(void* ptr);
+int splat_peer_open(const void* handle64, void** ptr);
+int splat_peer_close(void* ptr);
 
 const char* splat_last_error_string(void);
 int splat_version(void);

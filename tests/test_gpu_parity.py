@@ -424,3 +424,28 @@ def test_reference_shader_golden_images_vertex_stage_cases(gpu_ctx, case, name, 
     assert (got == ref).all(axis=2)[under].mean() > 0.9
     F = O.Frame(inst, V, P, w, h, mode=mode, order=1)
     assert np.array_equal(got, F.blend()[0])
+
+
+def test_render_into_a_peer_framebuffer(gpu_ctx, small_scene):
+    """splat_peer_alloc: the framebuffer other ranks map and write their bands into (the fused exchange of the banded frame).
+    On one GPU: a frame composed of two bands rendered straight into such a buffer equals the frame rendered into an ordinary
+    device buffer, and the exported handle is 64 bytes. (Mapping it from another process needs a second GPU process:
+    bench.py --workload c3 asserts that path against the one-GPU frame at N = 2, 4, 8.)"""
+    import torch
+    from gaussian_splat_b200 import capi, multigpu
+    from oracle import oracle as O
+    w, h = 640, 360
+    V, P = O.app_camera(w, h)
+    gpu_ctx.upload(small_scene)
+    want, _ = _render(gpu_ctx, small_scene, V, P, w, h, mode=0)
+    ptr, handle = capi.peer_alloc(w * h * 8)
+    try:
+        assert len(handle) == 64 and any(handle)
+        s = torch.cuda.current_stream().cuda_stream
+        for a, b in ((0, 9), (9, 23)):
+            gpu_ctx.render(s, ptr, V, P, w, h, capi.make_opts(tile_row_begin=a, tile_row_end=b))
+        torch.cuda.synchronize()
+        got = torch.as_tensor(multigpu._DevView(ptr, (h, w, 4), "<f2"), device="cuda:0").cpu().numpy().view(np.uint16)
+        assert np.array_equal(got, want)
+    finally:
+        capi.peer_free(ptr)
