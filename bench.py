@@ -504,6 +504,80 @@ def c3_bands_leg(ctx, torch, dist, args, dev, rank, world, steps, sh_degree=0, e
     return out
 
 
+def c4_leg(ctx, torch, dist, dev, rank, world, reps=3):
+    """Config 4: 3M gaussians, 64 orbit views at 1080p, views block-sharded over the ranks (8 per GPU at N = 8), no data-path
+    collective. Every rank renders its views through splat_render_batch into device framebuffers; frames/s = 64 / the slowest
+    rank's device time (median of `reps` passes)."""
+    from gaussian_splat_b200 import capi, multigpu, scene
+    n, w, h, mode, cfg, name = WORKLOADS["c4"]
+    inst, _ = scene.make_instances(n, scene.CONFIG_SEEDS[cfg])
+    n = inst.shape[0]
+    ctx.upload(inst)
+    del inst
+    n_views = 64
+    mine = multigpu.shard_views(n_views, rank, world)
+    cams = [orbit_camera(k, n_views, w, h) for k in mine]
+    views = np.stack([c[0] for c in cams]); projs = np.stack([c[1] for c in cams])
+    fbs = torch.zeros((min(8, len(mine)), h, w, 4), dtype=torch.float16, device=dev)
+    ptrs = [fbs[k % fbs.shape[0]].data_ptr() for k in range(len(mine))]
+    stream = torch.cuda.current_stream().cuda_stream
+    opts = capi.make_opts(mode=mode)
+    for _ in range(2):                      # warm-up; grows the pair buffers if a view overflowed
+        ctx.render_batch(stream, ptrs, views, projs, w, h, opts); torch.cuda.synchronize()
+        st = ctx.status()
+    assert not st.overflow
+    ts = []
+    for _ in range(reps):
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ctx.render_batch(stream, ptrs, views, projs, w, h, opts)
+        e1.record(); torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ts.append(float(t.item()))
+    ms = float(np.median(ts))
+    return {"workload": name, "n_gaussians": n, "width": w, "height": h, "mode": "TILE", "views": n_views, "views_per_gpu": len(mine),
+            "parallelism": "views%d" % world, "frames_per_s": n_views * 1e3 / ms, "mgaussians_per_s": n * n_views * 1e3 / ms / 1e6,
+            "ms_for_all_views": ms, "pairs_D_last_view": int(st.n_pairs),
+            "note": "splat_render_batch (two frames in flight), framebuffers stay on the device; max over ranks, median of %d passes" % reps}
+
+
+def c5_leg(ctx, torch, dev, steps=60):
+    """Config 5: 2M gaussians, the 50-layer variant (K = 50; the mode the reference app executes), 1080p, one GPU: single frames
+    with an L2 flush between them, as the headline loop."""
+    from gaussian_splat_b200 import camera, capi, scene
+    n, w, h, mode, cfg, name = WORKLOADS["c5"]
+    inst, _ = scene.make_instances(n, scene.CONFIG_SEEDS[cfg])
+    n = inst.shape[0]
+    ctx.upload(inst)
+    del inst
+    V, P = camera.app_camera(w, h)
+    fb = torch.zeros((h, w, 4), dtype=torch.float16, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    opts = capi.make_opts(mode=mode, flags=capi.FLAG_TIMING)
+    for _ in range(4):
+        ctx.render(stream, fb.data_ptr(), V, P, w, h, opts); torch.cuda.synchronize()
+        st = ctx.status()
+    assert not st.overflow
+    acc, total = {}, 0.0
+    for i in range(steps):
+        flush.fill_(i & 0xFF)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); ctx.render(stream, fb.data_ptr(), V, P, w, h, opts); e1.record(); e1.synchronize()
+        total += e0.elapsed_time(e1)
+        for k, v in ctx.stage_times().items():
+            acc[k] = acc.get(k, 0.0) + v / steps
+    ms = total / steps
+    return {"workload": name, "n_gaussians": n, "width": w, "height": h, "mode": "LAYER50", "K": 50, "order": "near_first",
+            "frames_per_s": 1e3 / ms, "mgaussians_per_s": n / ms / 1e3, "ms_per_frame": ms, "pairs_D": int(st.n_pairs),
+            "stage_us": {k: round(v * 1e3, 1) for k, v in acc.items()}, "steps": steps,
+            "l2": "flushed between timed frames (256 MiB write, untimed)"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -515,6 +589,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sort-bench", action="store_true")
     ap.add_argument("--no-c3-leg", action="store_true", help="N > 1: skip the config-3 band + gather leg reported in config.c3")
+    ap.add_argument("--no-extra-legs", action="store_true", help="skip the config-4 (and, at N = 1, config-5) legs reported in config.c4 / config.c5")
     ap.add_argument("--even-bands", action="store_true", help="c3: equal tile-row bands instead of balanced ones")
     args = ap.parse_args()
     if args.warmup < 3:
@@ -719,9 +794,17 @@ def main():
         cpu_leg["cpu_model"] = cpu_model()
         cpu_leg["note"] = "single thread = the named baseline; the --impl reference arm uses all cores (its binning stages stay single-threaded)"
     del inst
+    c4 = c5 = None
+    if wl == "c2" and not args.no_extra_legs:
+        del fb, flush
+        torch.cuda.empty_cache()
+        fb = flush = None
+        c4 = c4_leg(ctx, torch, dist, dev, rank, world)
+        if world == 1:
+            c5 = c5_leg(ctx, torch, dev)
     c3 = None
     if world > 1 and wl == "c2" and not args.no_c3_leg:
-        del fb, flush
+        fb = flush = None
         torch.cuda.empty_cache()
         c3 = c3_bands_leg(ctx, torch, dist, args, dev, rank, world, min(args.steps, 100), 0, args.even_bands)
 
@@ -768,6 +851,10 @@ def main():
         if sb is not None:
             config.update({"sort_bench_gb_per_s": sb["gb_per_s"], "sort_bench_frac_measured": sb["frac_of_hbm_peak"],
                            "sort_bench_frac_8TBs": sb["frac_of_8TBs_nominal"], "sort_bench_n_pairs": sb["n_pairs"], "sort_bench_ms": sb["ms"]})
+        if c4 is not None:
+            config["c4"] = c4
+        if c5 is not None:
+            config["c5"] = c5
         if c3 is not None:
             config["c3"] = c3
             config["band_frame_equals_single_gpu"] = c3["band_frame_equals_single_gpu"]

@@ -26,8 +26,21 @@ __global__ void __launch_bounds__(256) sort_histogram_kernel(const KeyT* __restr
     __shared__ unsigned int h[SPLAT_MAX_SORT_PASSES][256];
     for (int p = 0; p < SPLAT_MAX_SORT_PASSES; ++p) h[p][threadIdx.x] = 0;
     __syncthreads();
+    // four independent key loads in flight per thread (one at a time left the pass at 1.7 TB/s: 0.29 ms of a 4.05 ms sort of
+    // 64M pairs), then their 4 x n_pass shared-memory atomics, which bound it now (8 and 16 loads in flight: no faster)
     const unsigned long long stride = (unsigned long long)gridDim.x * 256ull;
-    for (unsigned long long i = (unsigned long long)blockIdx.x * 256ull + threadIdx.x; i < n; i += stride) {
+    unsigned long long i = (unsigned long long)blockIdx.x * 256ull + threadIdx.x;
+    for (; i + 3ull * stride < n; i += 4ull * stride) {
+        KeyT k[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) k[u] = __ldg(keys + i + (unsigned long long)u * stride);
+        for (int p = 0; p < plan.n_pass; ++p) {
+            const int sh = plan.shift[p]; const unsigned int m = plan.mask[p]; unsigned int* hp = h[plan.slot[p]];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) atomicAdd(hp + ((unsigned int)(k[u] >> sh) & m), 1u);
+        }
+    }
+    for (; i < n; i += stride) {
         const KeyT k = __ldg(keys + i);
         for (int p = 0; p < plan.n_pass; ++p) atomicAdd(&h[plan.slot[p]][(unsigned int)(k >> plan.shift[p]) & plan.mask[p]], 1u);
     }
@@ -138,11 +151,6 @@ __device__ __forceinline__ void onesweep_pass_body(
             const unsigned int li = wofs + i * 32;
             key[i] = li < tcount ? keys_in[tbase + li] : ~(KeyT)0;
         }
-#pragma unroll
-        for (int i = 0; i < ITEMS; ++i) {
-            const unsigned int li = wofs + i * 32;
-            val[i] = li < tcount ? vals_in[tbase + li] : 0u;
-        }
         if (tid == 0) {
             // next ticket, and its tile pulled into L2 by the TMA unit while this tile is processed: the
             // plain loads above otherwise wait ~10K cycles on DRAM with nothing else of this CTA to run
@@ -179,7 +187,12 @@ __device__ __forceinline__ void onesweep_pass_body(
         // 2.92 -> 3.19 TB/s, and the frame's four passes 77 -> 73 us.
         // RANK_SETS independent counter sets (items [c*ITEMS/SETS, (c+1)*ITEMS/SETS) use set c) share the two
         // warp barriers of a round.
-        unsigned int rank[ITEMS];
+        // ranks are below TILE_KEYS <= 8192: two per register (every index below is a compile-time constant)
+        unsigned int rankp[(ITEMS + 1) / 2];
+#pragma unroll
+        for (int i = 0; i < (ITEMS + 1) / 2; ++i) rankp[i] = 0u;
+#define RANK_GET(i) ((rankp[(i) >> 1] >> (((i) & 1) * 16)) & 0xFFFFu)
+#define RANK_SET(i, v) (rankp[(i) >> 1] = (rankp[(i) >> 1] & ~(0xFFFFu << (((i) & 1) * 16))) | ((v) << (((i) & 1) * 16)))
         constexpr int PER_SET = ITEMS / RANK_SETS;
 #pragma unroll
         for (int i = 0; i < PER_SET; ++i) {
@@ -192,7 +205,7 @@ __device__ __forceinline__ void onesweep_pass_body(
 #pragma unroll
                 for (int b = 0; b < 8; ++b) p = ballot_match_step(p, dd[c], 1u << b);
                 peers[c] = p;
-                rank[c * PER_SET + i] = before[c] + __popc(p & lt_mask);
+                RANK_SET(c * PER_SET + i, before[c] + __popc(p & lt_mask));
             }
             __syncwarp();
 #pragma unroll
@@ -228,13 +241,26 @@ __device__ __forceinline__ void onesweep_pass_body(
         PROF(3);
         // ---- pairs: registers -> shared at their tile-local rank (frees the registers before the
         // lookback; global offsets are not needed yet)
+        // keys first: once they sit in shared memory their registers are free, and the values - only needed now - are loaded
+        // into them (from L2: the tile was prefetched there one tile ahead). Values held through the ranking cost a register
+        // per pair; without them, and with the ranks packed two per register, a 64-bit tile grows from 16 to 24 pairs per
+        // thread at the same two CTAs per SM, which amortises the per-tile chain (counter clearing, digit scans, on average
+        // 3.6 serial L2 round trips of lookback): 64M pairs 3.31 -> 3.92 TB/s. Measured around it: 20 / 22 / 26 / 28 pairs per
+        // thread 3.63 / 3.88 / 3.81 / 3.58 (spills from 26 on); lookback depth 3 / 6 / 8 at 24 pairs 3.91 / 3.88 / 3.79.
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) {
             const unsigned int d = (unsigned int)(key[i] >> shift) & mask;
-            const unsigned int r = rank[i] + (unsigned int)s_wh[i / PER_SET][warp][d];
+            const unsigned int r = RANK_GET(i) + (unsigned int)s_wh[i / PER_SET][warp][d];
+            RANK_SET(i, r);
             s_keys[r] = key[i];
-            s_vals[r] = val[i];
         }
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+            const unsigned int li = wofs + i * 32;
+            val[i] = li < tcount ? vals_in[tbase + li] : 0u;
+        }
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) s_vals[RANK_GET(i)] = val[i];
         PROF(4);
         // Decoupled lookback, LB_DEPTH predecessors in flight per step: with every tile of a small
         // sort resident at once, a one-at-a-time walk is a serial chain of L2 round trips.
@@ -283,7 +309,7 @@ __device__ __forceinline__ void onesweep_pass_body(
 // body (more spills), so the callers below pass SETS == SETS_LONG and choose on the host's estimate of n.
 #define SORT_LONG 8000000u
 #ifndef K_ITEMS_WIDE
-#define K_ITEMS_WIDE SORT_ITEMS
+#define K_ITEMS_WIDE 24           // 64-bit keys: 6144 pairs per tile (see the staging comment in the pass body)
 #endif
 #ifndef K_CTAS_WIDE
 #define K_CTAS_WIDE 2
