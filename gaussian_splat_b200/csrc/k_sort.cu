@@ -149,7 +149,7 @@ __device__ __forceinline__ void onesweep_pass_body(
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) {
             const unsigned int li = wofs + i * 32;
-            key[i] = li < tcount ? keys_in[tbase + li] : ~(KeyT)0;
+            key[i] = li < tcount ? __ldcg(keys_in + tbase + li) : ~(KeyT)0;      // L2 only: the buffer was written by the previous pass (PDL-linked)
         }
         if (tid == 0) {
             // next ticket, and its tile pulled into L2 by the TMA unit while this tile is processed: the
@@ -257,7 +257,7 @@ __device__ __forceinline__ void onesweep_pass_body(
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) {
             const unsigned int li = wofs + i * 32;
-            val[i] = li < tcount ? vals_in[tbase + li] : 0u;
+            val[i] = li < tcount ? __ldcg(vals_in + tbase + li) : 0u;
         }
 #pragma unroll
         for (int i = 0; i < ITEMS; ++i) s_vals[RANK_GET(i)] = val[i];

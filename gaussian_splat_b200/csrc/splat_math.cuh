@@ -68,6 +68,9 @@ __device__ __forceinline__ unsigned int preprocess_one(
     mat4_point(U.V, px, py, pz, vp);
     const float zFront = -vp[2];
     if (!(zFront >= 1e-4f)) return 0;
+    // the fragment stage discards in.depth < 0.001 (gaussian_splat_tile.metal:187, gaussian_splat_50layer.metal:154,
+    // gaussian_splat.metal:209) and depth = zFront is constant over the quad: such a splat draws nothing in any mode
+    if (zFront < 0.001f) return 0;
 
     // :40-49 quaternionToMatrix (normalize = v / sqrt(dot))
     const float qlen = sqrtf(((qw * qw + qx * qx) + qy * qy) + qz * qz);

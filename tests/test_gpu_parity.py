@@ -449,3 +449,29 @@ def test_render_into_a_peer_framebuffer(gpu_ctx, small_scene):
         assert np.array_equal(got, want)
     finally:
         capi.peer_free(ptr)
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_fragment_near_discard_with_a_tiny_near_plane(gpu_ctx, mode):
+    """The shaders' fragment stage discards depth < 0.001 (gaussian_splat_tile.metal:187, gaussian_splat_50layer.metal:154,
+    gaussian_splat.metal:209). The app's near plane (zNDC = 0 at zFront = 0.19998) hides that rule; a caller's projection with
+    a near plane of 1e-5 does not: splats with 1e-4 <= zFront < 1e-3 pass the vertex stage's cull and the clip volume, and
+    must still draw nothing. Stages and image bit-exact against Oracle-B, which carries the same rule."""
+    from oracle import oracle as O
+    w, h = 256, 192
+    V = O.look_at((0.0, 0.0, 0.0), (0.0, 0.0, -1.0), (0.0, -1.0, 0.0))
+    P = O.perspective(45.0, w, h, 1e-5, 10.0)
+    rng = np.random.default_rng(7)
+    n = 400
+    inst = np.zeros((n, 14), np.float32)
+    inst[:, 0] = 1.0                                               # identity rotation
+    z = np.concatenate([rng.uniform(2e-4, 9e-4, n // 2), rng.uniform(1.2e-3, 6e-3, n - n // 2)]).astype(np.float32)
+    inst[:, 9] = -z                                                # straight ahead, zFront = z
+    inst[:, 7:9] = (rng.uniform(-0.2, 0.2, (n, 2)) * z[:, None]).astype(np.float32)
+    inst[:, 4:7] = (z[:, None] * rng.uniform(0.004, 0.02, (n, 3))).astype(np.float32)     # a few pixels on screen at any depth
+    inst[:, 10:13] = rng.uniform(0.1, 1.0, (n, 3)).astype(np.float32)
+    inst[:, 13] = rng.uniform(0.2, 0.9, n).astype(np.float32)
+    F = _check_all(gpu_ctx, inst, V, P, w, h, mode, 0)
+    touched = F.tiles_touched
+    assert not touched[: n // 2].any()                             # zFront in [2e-4, 9e-4]: discarded although inside the clip volume
+    assert (touched[n // 2:] > 0).sum() > n // 4                   # zFront > 1.2e-3: drawn
