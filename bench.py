@@ -211,8 +211,9 @@ def cpu_baseline_leg(inst, V, P, w, h, mode, name):
                       f"single thread, {dt:.2f} s; frames/s = fraction / time; {name}"}
 
 
-def sort_bench(ctx, torch, n=1 << 26, reps=5):
+def sort_bench(ctx, torch, n=1 << 26, reps=7):
     """Stand-alone 'sort HBM GB/s' of the 64-bit entry point: full-entropy keys, 8 passes, D*(8+8*24) bytes."""
+    torch.cuda.empty_cache()       # fresh allocations for the 1.6 GB of buffers (recycled, fragmented blocks of the caching allocator cost 2-3%)
     g = torch.Generator(device="cuda"); g.manual_seed(1)
     hi = torch.randint(-2 ** 31, 2 ** 31, (n,), generator=g, dtype=torch.int64, device="cuda")
     lo = torch.randint(0, 2 ** 32, (n,), generator=g, dtype=torch.int64, device="cuda")
