@@ -843,7 +843,7 @@ def main():
         config = {"workload": name, "n_gaussians": n, "width": w, "height": h,
                   "mode": "LAYER50" if mode else "TILE", "order": "near_first", "sh_degree": args.sh_degree,
                   "pairs_D": D, "parking_slots": slots, "visible": visible, "sort_passes": 1,
-                  "live_blocks": int(st.n_live_blocks), "blocks": (n + 255) // 256, "longest_tile_list": int(st.max_tile_pairs),
+                  "live_blocks": int(st.n_live_blocks), "blocks": (n + 63) // 64, "longest_tile_list": int(st.max_tile_pairs),
                   "parallelism": "views%d" % world,
                   "l2": "flushed between timed steps (256 MiB write, untimed)",
                   "e2e_bgra8_frames_per_s": e2e_bgra_fps, "e2e_half4_frames_per_s": e2e_fps,
