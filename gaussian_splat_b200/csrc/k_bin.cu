@@ -122,7 +122,7 @@ void launch_tile_offsets(const FrameUniforms& U, FrameCtl* ctl, unsigned int* bo
 // A CTA takes eight parking chunks at a time, one slot per thread and chunk: the (key; tile, slot) loads, the bounds lookups
 // and the stores are eight independent chains, no atomics (K1 drew the slots). Thread 0 of CTA 0 also leaves the frame's
 // status in page-locked host memory (the frame number last), where the next entry-point call finds it without a copy.
-struct FrameStatusSlotDev { unsigned long long total_pairs, total_slots; unsigned int overflow, max_tile_pairs, frame_no, pad; };
+struct FrameStatusSlotDev { unsigned long long total_pairs, total_slots; unsigned int overflow, max_tile_pairs, frame_no, live_blocks; };
 __global__ void __launch_bounds__(PARK_CHUNK) scatter_pairs_kernel(const FrameCtl* ctl, const unsigned long long* park_key,
                                                                    const unsigned long long* park_ts, const unsigned int* chunk_fill,
                                                                    const unsigned int* bounds, unsigned long long* __restrict__ pairs,
@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(PARK_CHUNK) scatter_pairs_kernel(const FrameCt
     const unsigned int over = __ldcg(&ctl->overflow), n_chunks = __ldcg(&ctl->n_chunks);
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         slot->total_pairs = __ldcg(&ctl->total_pairs); slot->total_slots = (unsigned long long)n_chunks * PARK_CHUNK;
-        slot->overflow = over; slot->max_tile_pairs = __ldcg(&ctl->max_tile_pairs);
+        slot->overflow = over; slot->max_tile_pairs = __ldcg(&ctl->max_tile_pairs); slot->live_blocks = __ldcg(&ctl->n_live_blocks);
         __threadfence_system();
         slot->frame_no = frame_no;
     }

@@ -261,23 +261,29 @@ __global__ void __launch_bounds__(256) block_cull_kernel(ScenePlanes sp, const _
 #ifndef K1_MIN_CTAS
 #define K1_MIN_CTAS 1
 #endif
+// TAIL = false: the CTA takes unit blockIdx.x (one unit = 1024 splats = K1_BLOCKS live blocks) and leaves: the main launch, whose
+// grid is sized from the live-block count of an EARLIER frame of the same shape (the host's hint; all units when it has none) -
+// a band's frame otherwise launched five CTAs for every one that found a live block. TAIL = true: a small second launch whose
+// CTAs stride over the units beyond the main grid; it finds none unless the hint was stale, so a stale hint costs time, never a
+// result. Two instantiations because the looping form needs 113 registers (two resident CTAs) where the single-unit form needs 64.
+template <bool TAIL>
 __global__ void __launch_bounds__(256, K1_MIN_CTAS) preprocess_kernel(ScenePlanes sp, const __grid_constant__ FrameUniforms U,
                                                          splat_record_row* __restrict__ rec, FrameCtl* ctl,
                                                          const unsigned int* live, unsigned long long* __restrict__ park_key,
                                                          unsigned long long* __restrict__ park_ts, unsigned int* __restrict__ chunk_fill,
-                                                         unsigned long long capacity)
+                                                         unsigned long long capacity, unsigned int first_unit)
 {
     constexpr int K1_CTA_SPLATS = 256 * K1_ITEMS;
     __shared__ unsigned short s_list[K1_CTA_SPLATS];
     constexpr int K1_BLOCKS = K1_CTA_SPLATS / (int)SCENE_BLOCK;      // live blocks a CTA takes
     __shared__ unsigned int s_count, s_blk[K1_BLOCKS];
     __shared__ float4 s_p[K1_CTA_SPLATS], s_t[K1_CTA_SPLATS];
-    const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     pdl_prologue();
     const unsigned int n_live = __ldcg(&ctl->n_live_blocks);
-    if (blockIdx.x * K1_BLOCKS >= n_live) return;
+    const unsigned int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (unsigned int unit = first_unit + blockIdx.x; unit * K1_BLOCKS < n_live; unit += gridDim.x) {
     if (tid == 0) s_count = 0;
-    if (tid < K1_BLOCKS) s_blk[tid] = blockIdx.x * K1_BLOCKS + tid < n_live ? __ldcg(live + blockIdx.x * K1_BLOCKS + tid) : 0xFFFFFFFFu;
+    if (tid < K1_BLOCKS) s_blk[tid] = unit * K1_BLOCKS + tid < n_live ? __ldcg(live + unit * K1_BLOCKS + tid) : 0xFFFFFFFFu;
     __syncthreads();
     float4 p[K1_ITEMS], t[K1_ITEMS];
     unsigned int idx[K1_ITEMS];
@@ -424,15 +430,28 @@ __global__ void __launch_bounds__(256, K1_MIN_CTAS) preprocess_kernel(ScenePlane
     }
     if (pend_g != 0xFFFFFFFFu) park_ts[pend_g] = ((unsigned long long)pend_tile << 32) | pend_slot;
     if (chunk != 0xFFFFFFFFu && (unsigned long long)(chunk + 1u) * PARK_CHUNK <= capacity && lane == 0) chunk_fill[chunk] = used;
+    if (!TAIL) return;          // the main launch: one unit per CTA
+    __syncthreads();            // the shared arrays are reused by the next unit
+    }
 }
 
 void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record_row* rec, FrameCtl* ctl, unsigned int* live,
                        unsigned long long* park_key, unsigned long long* park_ts, unsigned int* chunk_fill, unsigned long long capacity,
-                       cudaStream_t s)
+                       unsigned int live_blocks_hint, cudaStream_t s)
 {
     if (U.n == 0) return;
     launch_pdl(block_cull_kernel, dim3((sp.n_blocks + 255u) / 256u), dim3(256), 0, s, sp, U, ctl, live);
-    const unsigned int per_cta = 256u * K1_ITEMS / SCENE_BLOCK;
-    launch_pdl(preprocess_kernel, dim3((sp.n_blocks + per_cta - 1) / per_cta), dim3(256), 0, s, sp, U, rec, ctl,
-               (const unsigned int*)live, park_key, park_ts, chunk_fill, capacity);
+    const unsigned int per_cta = 256u * K1_ITEMS / SCENE_BLOCK, all_units = (sp.n_blocks + per_cta - 1) / per_cta;
+    unsigned int grid = all_units;
+    if (live_blocks_hint) {     // 1/8 + 16 units of slack over the hint; never fewer CTAs than fill the machine once
+        const unsigned int want = (live_blocks_hint + per_cta - 1) / per_cta;
+        grid = want + want / 8u + 16u;
+        if (grid < 592u) grid = 592u;
+        if (grid > all_units) grid = all_units;
+    }
+    launch_pdl(preprocess_kernel<false>, dim3(grid), dim3(256), 0, s, sp, U, rec, ctl,
+               (const unsigned int*)live, park_key, park_ts, chunk_fill, capacity, 0u);
+    if (grid < all_units)
+        launch_pdl(preprocess_kernel<true>, dim3(148), dim3(256), 0, s, sp, U, rec, ctl,
+                   (const unsigned int*)live, park_key, park_ts, chunk_fill, capacity, grid);
 }

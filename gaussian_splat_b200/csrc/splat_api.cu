@@ -48,7 +48,7 @@ struct FrameSet {
 
 // Status of frame `frame_no`, written by its tile_offsets_kernel straight into page-locked host memory (no copy is
 // enqueued): the next entry-point call sees an overflow without synchronising.
-struct FrameStatusSlot { unsigned long long total_pairs, total_slots; unsigned int overflow, max_tile_pairs, frame_no, pad; };
+struct FrameStatusSlot { unsigned long long total_pairs, total_slots; unsigned int overflow, max_tile_pairs, frame_no, live_blocks; };
 #define STATUS_RING 64
 
 #define FB_RING 4
@@ -62,6 +62,9 @@ struct splat_ctx : FrameSet {
     FrameCtl* ctl_host = nullptr;
     FrameStatusSlot* status_ring = nullptr;      // page-locked, mapped
     uint32_t frame_no = 0, checked_frame = 0;    // frames enqueued / frames whose status has been looked at
+    // live blocks of the latest landed frame with the same band and viewport (sizes K1's grid; 0 = no hint)
+    uint32_t hint_live = 0; int hint_w = 0, hint_h = 0, hint_r0 = 0, hint_r1 = 0;
+    struct { int w, h, r0, r1; } frame_sig[STATUS_RING] = {};
     // stand-alone sort
     SortCtl* sort_ctl = nullptr; unsigned long long* sort_status = nullptr; size_t sort_status_tiles = 0; uint32_t sort_epoch = 0;
     FrameUniforms lastU{}; bool have_frame = false;
@@ -454,6 +457,10 @@ static int check_overflow(splat_ctx* c, bool wait, unsigned long long* worst_out
         const volatile FrameStatusSlot* sl = c->status_ring + (f % STATUS_RING);
         if (sl->frame_no != f) { if (!wait) break; c->checked_frame = f; continue; }    // not landed (or a frame without kernels)
         if (sl->overflow && sl->total_slots > worst) worst = sl->total_slots;
+        if (!sl->overflow) {           // a landed frame: its live-block count sizes K1's grid for the next frame of the same shape
+            const auto& sg = c->frame_sig[f % STATUS_RING];
+            c->hint_live = sl->live_blocks; c->hint_w = sg.w; c->hint_h = sg.h; c->hint_r0 = sg.r0; c->hint_r1 = sg.r1;
+        }
         c->checked_frame = f;
     }
     if (worst_out) *worst_out = worst;
@@ -485,13 +492,15 @@ static int enqueue_frame(splat_ctx* c, cudaStream_t s, void* fb, const FrameUnif
     c->frame_no = c->frame_no + 1;
     if (c->frame_no == 0) { c->frame_no = 1; c->checked_frame = 0; }
     FrameStatusSlot* slot = c->status_ring + (c->frame_no % STATUS_RING);
+    c->frame_sig[c->frame_no % STATUS_RING] = {U.w, U.h, U.row_begin, U.row_end};
+    const uint32_t live_hint = (c->hint_w == U.w && c->hint_h == U.h && c->hint_r0 == U.row_begin && c->hint_r1 == U.row_end) ? c->hint_live : 0u;
     if (timed) CK(cudaEventRecord(c->ev[0], s));
     CK(cudaMemsetAsync(c->ctl, 0, sizeof(FrameCtl) + ((size_t)T + 1) * 4, s));       // control block + tile counters
     // stage labels for Nsight (the reference labels its encoders: src/instanced_splat_renderer.mm:487,504)
     nvtxRangePushA("splat: K1 block cull + preprocess + candidates");
     if (c->n) {
         ScenePlanes sp{c->rot, c->pos_sx, c->syz, c->bq, c->base_rgb, c->orig, c->blk_lo, c->blk_hi, c->n_blocks, c->sh, c->n_pad};
-        launch_preprocess(sp, U, c->rec, c->ctl, c->live, c->park_key, c->park_ts, c->chunk_fill, c->capacity, s);
+        launch_preprocess(sp, U, c->rec, c->ctl, c->live, c->park_key, c->park_ts, c->chunk_fill, c->capacity, live_hint, s);
     }
     nvtxRangePop();
     if (timed) CK(cudaEventRecord(c->ev[1], s));

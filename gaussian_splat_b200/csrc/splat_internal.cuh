@@ -147,7 +147,7 @@ void launch_upload_sh(const float* sh_rest45_dev, const unsigned int* perm, unsi
 // K1 (k_preprocess.cu): block culling, then per live block the records (rec[original index]) and the parked candidates.
 void launch_preprocess(const ScenePlanes& sp, const FrameUniforms& U, splat_record_row* rec, FrameCtl* ctl, unsigned int* live,
                        unsigned long long* park_key, unsigned long long* park_ts, unsigned int* chunk_fill, unsigned long long capacity,
-                       cudaStream_t s);
+                       unsigned int live_blocks_hint, cudaStream_t s);      // hint: live blocks of an earlier, similar frame (0 = none): sizes K1's grid
 // K2 binning (k_bin.cu). K1 parked every (splat, tile) pair that passed the D9' tile test as (key = depth field << 32 |
 // instance index; tile << 32 | slot in the tile's list) and counted the pairs per tile. tile_offsets scans the counters
 // into bounds[T + 1]; scatter_pairs moves every parked pair to pairs[bounds[tile] + slot]; tile_sort sorts every tile's
