@@ -639,7 +639,7 @@ def main():
                         "d2h_bytes_per_step": leg["e2e_d2h_bytes_per_step_per_rank"], "steps": leg["e2e_steps"],
                         "note": "per frame: matrices from host, band rendered, band copied device -> shared page-locked host frame by "
                                 "every rank in parallel (no collective; copies overlap the next frame); d2h bytes are rank 0's band"},
-                "gpu_launches": args.steps * 6, "clocks": leg["clocks"], "numa": numa,
+                "gpu_launches": args.steps * 7, "clocks": leg["clocks"], "numa": numa,
             }
             emit(line)
         ctx.close()
@@ -872,7 +872,7 @@ def main():
                     "bgra8": {"value": e2e_bgra_fps, "d2h_bytes_per_step": w * h * 4 + 24,
                               "note": "same call with SPLAT_FLAG_HOST_BGRA8: frames delivered as the reference drawable's BGRA8Unorm"}},
             "camera_batch_device": inflight,
-            "gpu_launches": args.steps * 6,      # block cull, preprocess, tile offsets, scatter, tile sort, blend (+1 memset node, not counted)
+            "gpu_launches": args.steps * 7,      # block cull, preprocess, its tail launch (present when the hinted grid is smaller than the scene), tile offsets, scatter, tile sort, blend (+1 memset node, not counted)
             "clocks": clocks, "wall_s": t_wall, "numa": numa,
         }
         if sb is not None:
