@@ -7,9 +7,11 @@
 //   tile_offsets_kernel  exclusive scan of the T tile counters -> bounds[T + 1], D,
 //                        the longest list
 //   scatter_pairs_kernel pairs[bounds[tile] + slot] = key
-//   tile_sort_kernel     one CTA per tile sorts its list on the whole 64-bit pair. Instance indices are unique within a
-//                        list, so the key is total and the result is what a stable sort of instance-ordered pairs on
-//                        tile | depth gives, whatever order the atomics handed the slots out in.
+//   tile_sort_kernel     one CTA per tile (longest lists first) sorts its list in the order of the whole 64-bit pair: a
+//                        bitonic network on 32-bit keys (half depth << 16 | slot), then runs of equal half depth put in
+//                        instance-index order. Instance indices are unique within a list, so that order is total and is
+//                        what a stable sort of instance-ordered pairs on tile | depth gives, whatever order
+//                        the atomics handed the slots out in.
 // Round 1 sorted the frame's (tile << 16 | depth) keys with four onesweep passes over all D pairs and searched the tile
 // boundaries afterwards: at frame sizes (1.6M pairs = less than one wave of sort tiles) that was four latency-bound
 // chains of load / rank / lookback / scatter, 66 + 10 us of a 346 us frame at 23% of HBM. Here every pair is written

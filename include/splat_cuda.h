@@ -37,7 +37,7 @@ enum {
 };
 enum {
     SPLAT_FLAG_TIMING = 1,        /* record per-stage CUDA events (adds event overhead)          */
-    SPLAT_FLAG_KEEP_UNSORTED = 2, /* keep a copy of the unsorted pairs for splat_debug_fetch      */
+    SPLAT_FLAG_KEEP_UNSORTED = 2, /* accepted for compatibility, no effect: the unsorted pairs stay fetchable from every frame */
     SPLAT_FLAG_COUNT_WORK = 8,    /* the blend counts the (warp, splat) candidates it executes (splat_status.blend_warp_candidates):
                                      the work count of the blend's roofline; a slower instantiation, not for timed frames */
     SPLAT_FLAG_HOST_BGRA8 = 4     /* splat_render_host / splat_render_batch_host deliver the frame as the
@@ -136,19 +136,20 @@ enum {
     SPLAT_FETCH_RECORDS = 0,     /* splat_record[n]  (culled entries zeroed)  */
     SPLAT_FETCH_TILES_TOUCHED,   /* uint32[n]                                 */
     SPLAT_FETCH_OFFSETS,         /* uint32[n] exclusive scan                  */
-    SPLAT_FETCH_KEYS_UNSORTED,   /* uint64[D]  (frame must use SPLAT_FLAG_KEEP_UNSORTED) */
+    SPLAT_FETCH_KEYS_UNSORTED,   /* uint64[D]  tile << 32 | depth field, in emission order (instance order, a splat's tiles row-major) */
     SPLAT_FETCH_VALS_UNSORTED,   /* uint32[D]                                 */
     SPLAT_FETCH_KEYS_SORTED,     /* uint64[D]                                 */
     SPLAT_FETCH_VALS_SORTED,     /* uint32[D]                                 */
     SPLAT_FETCH_TILE_RANGES,     /* uint32[T][2]                              */
-    SPLAT_FETCH_DIGIT_HISTOGRAMS,/* uint32[8][256]: per-pass digit counts of the last frame or stand-alone sort */
+    SPLAT_FETCH_DIGIT_HISTOGRAMS,/* uint32[8][256]: per-pass digit counts of the last stand-alone sort (frames sort per tile)  */
     SPLAT_FETCH_INSTANCES,       /* SplatInstancePOD[n]: the uploaded scene rebuilt from the device planes (no frame needed) */
     SPLAT_FETCH_SH_REST          /* float[n][45]: uploaded f_rest rows rebuilt from the SH planes (no frame needed)        */
 };
 int splat_debug_fetch(splat_ctx* ctx, int what, void* host_dst, size_t* bytes);
 
 /* ms of the last frame rendered with SPLAT_FLAG_TIMING:
- * [0] preprocess [1] scan+duplicate [2] sort [3] ranges [4] blend [5] total. Synchronises. */
+ * [0] block cull + preprocess + candidate binning [1] tile offsets + scatter [2] per-tile sort [3] unused (was: tile ranges)
+ * [4] blend [5] total. Synchronises. */
 int splat_stage_times(splat_ctx* ctx, float ms[8]);
 
 /* Stand-alone stable LSD radix sort of (uint64 key, uint32 value) pairs on device
@@ -158,8 +159,7 @@ int splat_stage_times(splat_ctx* ctx, float ms[8]);
 int splat_sort_pairs_u64_u32(splat_ctx* ctx, void* stream, uint64_t* keys, uint32_t* vals,
                              uint64_t* keys_alt, uint32_t* vals_alt, uint64_t n,
                              int begin_bit, int end_bit, int* result_in_alt);
-/* The same sort on 32-bit keys, the width the frame pipeline itself sorts (tile << 16 | half depth):
- * 16 B per pair and pass instead of 24. end_bit <= 32. */
+/* The same sort on 32-bit keys: 16 B per pair and pass instead of 24. end_bit <= 32. */
 int splat_sort_pairs_u32_u32(splat_ctx* ctx, void* stream, uint32_t* keys, uint32_t* vals,
                              uint32_t* keys_alt, uint32_t* vals_alt, uint64_t n,
                              int begin_bit, int end_bit, int* result_in_alt);
