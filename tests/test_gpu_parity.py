@@ -475,3 +475,77 @@ def test_fragment_near_discard_with_a_tiny_near_plane(gpu_ctx, mode):
     touched = F.tiles_touched
     assert not touched[: n // 2].any()                             # zFront in [2e-4, 9e-4]: discarded although inside the clip volume
     assert (touched[n // 2:] > 0).sum() > n // 4                   # zFront > 1.2e-3: drawn
+
+
+def _wall_scene(n, seed, spread=1.2, scale=0.25):
+    """n splats on the plane z = 0 seen head-on from (0, 0, 5): every zFront is exactly 5, so every pair of a tile has the
+    same half depth - the sorted order is decided by the instance index alone."""
+    rng = np.random.default_rng(seed)
+    inst = np.zeros((n, 14), np.float32)
+    inst[:, 0] = 1.0
+    inst[:, 4:7] = scale
+    inst[:, 7:9] = rng.uniform(-spread, spread, (n, 2)).astype(np.float32)
+    inst[:, 10:13] = rng.uniform(0.05, 1.0, (n, 3)).astype(np.float32)
+    inst[:, 13] = rng.uniform(0.02, 0.2, n).astype(np.float32)
+    return inst
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_tile_sort_long_runs_of_equal_depth(gpu_ctx, mode):
+    """The per-tile sort runs its network on 32-bit keys (half depth << 16 | slot) and then orders runs of equal half depth by
+    instance index; a run longer than 48 sends the list through the 64-bit network instead. A wall of splats at one depth makes
+    every list ONE run of several hundred pairs. Stages and image bit-exact against Oracle-B."""
+    from oracle import oracle as O
+    w, h = 160, 128
+    V, P = O.app_camera(w, h, eye=(0.0, 0.0, 5.0))
+    inst = _wall_scene(700, 3)
+    F = _check_all(gpu_ctx, inst, V, P, w, h, mode, 0)
+    r = F.tile_ranges.astype(np.int64)
+    assert (r[:, 1] - r[:, 0]).max() > 300                       # long lists ...
+    assert len(np.unique(F.records["bd"][F.tiles_touched > 0] >> 16)) == 1      # ... of one half depth
+    _check_all(gpu_ctx, inst, V, P, w, h, mode, 1)               # the shader's literal (descending) order too
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_tile_sort_lists_beyond_the_register_network(gpu_ctx, mode):
+    """Tile lists of more than 2048 pairs take the network run in global / shared memory by the tile's CTA (exact, slow, rare:
+    the benchmark scenes' longest list is 1586). 2600 large splats over a 96 x 64 viewport put about 2600 pairs into every
+    tile; random depths in one mode pass, one depth for all (ties broken by instance index over the whole list) in another."""
+    from gaussian_splat_b200 import scene
+    from oracle import oracle as O
+    w, h = 96, 64
+    V, P = O.app_camera(w, h, eye=(0.0, 0.0, 5.0))
+    inst, _ = scene.make_instances(2600, 0x5EED0C11)
+    inst[:, 7:10] *= 0.15
+    inst[:, 4:7] = 0.6
+    inst[:, 13] *= 0.05
+    F = _check_all(gpu_ctx, inst, V, P, w, h, mode, 0)
+    r = F.tile_ranges.astype(np.int64)
+    assert (r[:, 1] - r[:, 0]).max() > 2048
+    wall = _wall_scene(2600, 5, spread=0.5, scale=0.8)
+    F = _check_all(gpu_ctx, wall, V, P, w, h, mode, 0)
+    assert (F.tile_ranges[:, 1].astype(np.int64) - F.tile_ranges[:, 0]).max() > 2048
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_non_finite_splats_among_ordinary_ones(gpu_ctx, small_scene, mode):
+    """The scene is stored in Morton order and culled per 64-splat block: non-finite positions sort last and are ignored by the
+    block bounds, a block holding a non-finite or huge scale is never culled by its bound. Splats with NaN / infinite position,
+    scale or rotation scattered among ordinary ones: every stage and the image bit-exact against Oracle-B (which culls
+    them through its comparisons), in the whole frame and in a band."""
+    from oracle import oracle as O
+    w, h = 480, 270
+    V, P = O.app_camera(w, h)
+    inst = small_scene[:6000].copy()
+    rng = np.random.default_rng(13)
+    bad = rng.choice(len(inst), 300, replace=False)
+    inst[bad[:60], 7] = np.nan                      # position x
+    inst[bad[60:100], 8] = np.inf
+    inst[bad[100:140], 9] = -np.inf
+    inst[bad[140:180], 4] = np.inf                  # scale
+    inst[bad[180:220], 5] = np.nan
+    inst[bad[220:250], 0:4] = 0.0                   # zero quaternion: normalisation divides by zero
+    inst[bad[275:300], 6] = 1e30                    # a finite but absurd scale
+    with np.errstate(all="ignore"):
+        _check_all(gpu_ctx, inst, V, P, w, h, mode, 0)
+        _check_all(gpu_ctx, inst, V, P, w, h, mode, 0, rows=(4, 9))
