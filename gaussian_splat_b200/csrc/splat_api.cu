@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -49,7 +50,7 @@ struct FrameSet {
 // Status of frame `frame_no`, written by its tile_offsets_kernel straight into page-locked host memory (no copy is
 // enqueued): the next entry-point call sees an overflow without synchronising.
 struct FrameStatusSlot { unsigned long long total_pairs, total_slots; unsigned int overflow, max_tile_pairs, frame_no, live_blocks; };
-#define STATUS_RING 64
+#define STATUS_RING 256
 
 #define FB_RING 4
 struct splat_ctx : FrameSet {
@@ -75,7 +76,7 @@ struct splat_ctx : FrameSet {
     cudaStream_t copy_stream = nullptr; void* fb_ring[FB_RING] = {}; size_t fb_ring_bytes = 0;
     void* bgra_scratch[FB_RING] = {}; size_t bgra_bytes = 0;      // SPLAT_FLAG_HOST_BGRA8 staging
     cudaEvent_t ev_rendered[FB_RING] = {}, ev_copied[FB_RING] = {}, ev_fork = nullptr;
-    unsigned int* batch_flags = nullptr; int batch_flags_cap = 0;   // pinned: overflow word + D of every view
+    unsigned int* batch_flags = nullptr; int batch_flags_cap = 0;   // splat_render_batch_host: the frame number of every view
 };
 
 static void swap_sets(splat_ctx* c) {
@@ -240,7 +241,7 @@ int splat_destroy(splat_ctx* c) {
     for (int k = 0; k < FB_RING; ++k) { if (c->ev_rendered[k]) cudaEventDestroy(c->ev_rendered[k]); if (c->ev_copied[k]) cudaEventDestroy(c->ev_copied[k]); }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     for (int k = 0; k < FB_RING; ++k) { cudaFree(c->fb_ring[k]); cudaFree(c->bgra_scratch[k]); }
-    cudaFreeHost(c->batch_flags);
+    std::free(c->batch_flags);
     delete c;
     return SPLAT_OK;
 }
@@ -639,7 +640,7 @@ int splat_render_host(splat_ctx* c, void* fb_host, const float* view, const floa
     for (int attempt = 0; attempt < 4; ++attempt) {
         rc = enqueue_frame(c, c->own_stream, c->fb_scratch, U, o ? o->flags : 0);
         if (rc) return rc;
-        CK(cudaMemcpyAsync(c->ctl_host, c->ctl, 64, cudaMemcpyDeviceToHost, c->own_stream));
+        const uint32_t this_frame = c->frame_no;      // its status arrives in the mapped ring (written by the scatter kernel): no copy
         if (row1 > row0 && bgra) {
             launch_pack_bgra8((char*)c->fb_scratch + row0 * w * 8, (char*)c->bgra_scratch[0] + row0 * w * 4, (row1 - row0) * w, c->own_stream);
             CK(cudaMemcpyAsync((char*)fb_host + row0 * w * 4, (char*)c->bgra_scratch[0] + row0 * w * 4, (row1 - row0) * w * 4,
@@ -649,8 +650,10 @@ int splat_render_host(splat_ctx* c, void* fb_host, const float* view, const floa
                                cudaMemcpyDeviceToHost, c->own_stream));
         CK(cudaStreamSynchronize(c->own_stream));
         c->checked_frame = c->frame_no;          // this frame's status is handled right here
-        if (!c->ctl_host->overflow) return SPLAT_OK;
-        const unsigned long long D = (unsigned long long)c->ctl_host->n_chunks * PARK_CHUNK;
+        const volatile FrameStatusSlot* sl = c->status_ring + (this_frame % STATUS_RING);
+        if (sl->frame_no != this_frame) { g_err = "splat_render_host: the frame's status did not arrive"; return SPLAT_ERR_STATE; }
+        if (!sl->overflow) return SPLAT_OK;
+        const unsigned long long D = sl->total_slots;
         rc = ensure_pairs_all(c, D + D / 4 + 4096);
         if (rc) return rc;
     }
@@ -671,9 +674,18 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
         for (int k = 0; k < FB_RING; ++k) { cudaFree(c->fb_ring[k]); c->fb_ring[k] = nullptr; CK(cudaMalloc(&c->fb_ring[k], bytes)); }
         c->fb_ring_bytes = bytes;
     }
-    if (n_views > c->batch_flags_cap) {
-        cudaFreeHost(c->batch_flags); c->batch_flags = nullptr;
-        CK(cudaMallocHost(&c->batch_flags, (size_t)n_views * 24));
+    if (n_views > STATUS_RING) {        // every view's status must still be in the ring when the batch has drained: take it in pieces
+        for (int v0 = 0; v0 < n_views; v0 += STATUS_RING) {
+            const int nv = n_views - v0 < STATUS_RING ? n_views - v0 : STATUS_RING;
+            const int rc = splat_render_batch_host(c, fb_host + v0, views + 16 * v0, projs + 16 * v0, nv, w, h, o);
+            if (rc) return rc;
+        }
+        return SPLAT_OK;
+    }
+    if (n_views > c->batch_flags_cap) {  // the views' frame numbers (plain host memory)
+        std::free(c->batch_flags); c->batch_flags = nullptr;
+        c->batch_flags = (unsigned int*)std::malloc((size_t)n_views * 4);
+        if (!c->batch_flags) { c->batch_flags_cap = 0; g_err = "splat_render_batch_host: out of host memory"; return SPLAT_ERR_STATE; }
         c->batch_flags_cap = n_views;
     }
     use_set(c, 0);
@@ -700,7 +712,8 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
             if (v >= FB_RING) CK(cudaStreamWaitEvent(c->own_stream, c->ev_copied[b], 0));     // slot b is free again
             rc = enqueue_frame(c, c->own_stream, buf[b], U, flags);
             if (rc) return rc;
-            CK(cudaMemcpyAsync(c->batch_flags + 6 * v, c->ctl, 24, cudaMemcpyDeviceToHost, c->own_stream));   // D, overflow, chunks
+            c->batch_flags[v] = c->frame_no;         // the view's status arrives in the mapped ring; a 24-byte copy here shared the
+                                                     // copy engine with the previous frame's delivery and stalled this stream behind it
             const size_t row0 = (size_t)U.row_begin * SPLAT_TILE;
             const size_t row1 = (size_t)U.row_end * SPLAT_TILE < (size_t)h ? (size_t)U.row_end * SPLAT_TILE : (size_t)h;
             if (bgra && row1 > row0)
@@ -719,8 +732,9 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
         c->checked_frame = c->frame_no;          // the views' status is handled right here
         unsigned long long worst = 0; bool over = false;
         for (int v = 0; v < n_views; ++v) {
-            const unsigned long long D = (unsigned long long)c->batch_flags[6 * v + 3] * PARK_CHUNK;      // FrameCtl::n_chunks
-            if (c->batch_flags[6 * v + 2]) { over = true; if (D > worst) worst = D; }
+            const volatile FrameStatusSlot* sl = c->status_ring + (c->batch_flags[v] % STATUS_RING);
+            if (sl->frame_no != c->batch_flags[v]) { g_err = "splat_render_batch_host: a view's status did not arrive"; return SPLAT_ERR_STATE; }
+            if (sl->overflow) { over = true; if (sl->total_slots > worst) worst = sl->total_slots; }
         }
         if (!over) return SPLAT_OK;
         const int rc = ensure_pairs_all(c, worst + worst / 4 + 4096);
