@@ -710,7 +710,7 @@ int splat_render_batch_host(splat_ctx* c, void* const* fb_host, const float* vie
             int rc = build_frame(c, views + 16 * v, projs + 16 * v, w, h, o, U);
             if (rc) return rc;
             if (v >= FB_RING) CK(cudaStreamWaitEvent(c->own_stream, c->ev_copied[b], 0));     // slot b is free again
-            rc = enqueue_frame(c, c->own_stream, buf[b], U, flags);
+            rc = enqueue_frame(c, c->own_stream, buf[b], U, flags | (two ? FRAME_NO_PDL : 0));      // as splat_render_batch: two frames in flight fill each other's gaps
             if (rc) return rc;
             c->batch_flags[v] = c->frame_no;         // the view's status arrives in the mapped ring; a 24-byte copy here shared the
                                                      // copy engine with the previous frame's delivery and stalled this stream behind it
